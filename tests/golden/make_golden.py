@@ -1,0 +1,78 @@
+"""Generate tests/golden/*.npz from the UNMODIFIED vendored reference code.
+
+Run once in the dev container (where /root/reference exists):
+    python tests/golden/make_golden.py
+The GPU box has no /root/reference; tests only read the committed .npz files.
+
+Source of truth:  third_party/rtdetr/rtdetrv2_pytorch/src/zoo/rtdetr/hybrid_encoder.py
+  * TransformerEncoderLayer (:116-161): the dense FFN at :157 is the op the MoE replaces
+    (E identical experts + renormalised gates must reproduce it), and the post-norm
+    residual wrapper at :154-160 is the step either side of the path.
+The package __init__ chain needs faster_coco_eval (absent), so the three files are loaded
+through empty stub packages.
+"""
+import importlib.util
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+REF = "/root/reference/third_party/rtdetr/rtdetrv2_pytorch/src"
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def load_vendored():
+    for name in ("_rtv2", "_rtv2.core", "_rtv2.zoo", "_rtv2.zoo.rtdetr"):
+        m = types.ModuleType(name)
+        m.__path__ = []
+        sys.modules[name] = m
+
+    def load(modname, path):
+        spec = importlib.util.spec_from_file_location(modname, path)
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[modname] = mod
+        spec.loader.exec_module(mod)
+        return mod
+
+    ws = load("_rtv2.core.workspace", f"{REF}/core/workspace.py")
+    sys.modules["_rtv2.core"].register = ws.register
+    load("_rtv2.zoo.rtdetr.utils", f"{REF}/zoo/rtdetr/utils.py")
+    return load("_rtv2.zoo.rtdetr.hybrid_encoder", f"{REF}/zoo/rtdetr/hybrid_encoder.py")
+
+
+def main():
+    he = load_vendored()
+    torch.manual_seed(20260220)
+    d, F, B, HW = 64, 128, 2, 25
+    layer = he.TransformerEncoderLayer(d, 8, F, 0.0, "gelu")
+    layer.eval()
+    x = torch.randn(B, HW, d, requires_grad=True)
+    go = torch.randn(B, HW, d)
+
+    # the dense FFN exactly as hybrid_encoder.py:157 spells it
+    y = layer.linear2(layer.dropout(layer.activation(layer.linear1(x))))
+    (y * go).sum().backward()
+    out = {
+        "x": x.detach().numpy(), "go": go.numpy(), "y": y.detach().numpy(), "dx": x.grad.numpy(),
+        "w1": layer.linear1.weight.detach().numpy(), "b1": layer.linear1.bias.detach().numpy(),
+        "w2": layer.linear2.weight.detach().numpy(), "b2": layer.linear2.bias.detach().numpy(),
+        "dw1": layer.linear1.weight.grad.numpy(), "db1": layer.linear1.bias.grad.numpy(),
+        "dw2": layer.linear2.weight.grad.numpy(), "db2": layer.linear2.bias.grad.numpy(),
+    }
+    np.savez_compressed(os.path.join(HERE, "dense_ffn_d64_f128.npz"), **out)
+
+    # the post-norm wrapper (:154-160): norm2(residual + ffn(src)) on the same src
+    with torch.no_grad():
+        src = torch.randn(B, HW, d)
+        wrapped = layer.norm2(src + layer.linear2(layer.activation(layer.linear1(src))))
+        full = layer(src)
+    np.savez_compressed(os.path.join(HERE, "postnorm_ffn_d64_f128.npz"), src=src.numpy(), out=wrapped.numpy(),
+                        full_layer_out=full.numpy(),
+                        **{k: v.numpy() for k, v in layer.state_dict().items()})
+    print("wrote", os.listdir(HERE))
+
+
+if __name__ == "__main__":
+    main()
