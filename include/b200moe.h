@@ -1,0 +1,153 @@
+/* libb200moe — C ABI of the B200-native context-gated MoE FFN layer (sm_100a only).
+ *
+ * The reference repository (scaleoutsystems/multimodal-MoE) has no FFI for this path: the op this library
+ * replaces is the dense encoder FFN `linear2(dropout(gelu(linear1(src))))` at
+ *   third_party/rtdetr/rtdetrv2_pytorch/src/zoo/rtdetr/hybrid_encoder.py:129-131 (parameters), :157 (forward)
+ * and the layer semantics are SURVEY.md Appendix A (A.1..A.12).  Each entry point below names the step of
+ * that path it implements.  A maintainer binds these with ctypes; the Python host class
+ * `b200moe.ContextMoE` is the drop-in for hybrid_encoder.py:157.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller (PyTorch caching allocator); the library allocates
+ *     nothing and keeps no state between calls;
+ *   - every call enqueues work on `stream` (a cudaStream_t passed as void*) and never synchronises;
+ *   - return value: 0 = ok, negative = B200MOE_E* code; b200moe_last_error() gives the message (thread-local);
+ *   - bf16 tensors are passed as `const void*` / `void*` (row-major, 16-byte aligned rows);
+ *   - T tokens, d model width, F expert hidden width, E experts, k = top_k, R = rows of the permuted buffer.
+ *   - there is NO CPU fallback: on a device that is not compute capability 10.x every compute call fails.
+ */
+#ifndef B200MOE_H_
+#define B200MOE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200MOE_OK 0
+#define B200MOE_EINVAL (-1)   /* bad shape / alignment / argument */
+#define B200MOE_EARCH (-2)    /* not an sm_100 device */
+#define B200MOE_ECUDA (-3)    /* CUDA runtime / driver error */
+
+#define B200MOE_ROW_PAD 128          /* expert segments of the permuted buffer are padded to this many rows */
+#define B200MOE_ROUTER_BLOCK 128     /* tokens per router block (granularity of the priority scan) */
+#define B200MOE_META_INTS 8          /* meta[0]=R (padded rows in use) meta[1]=R/128 meta[2]=dropped meta[3]=kept */
+
+int b200moe_version(void);
+const char* b200moe_last_error(void);
+/* 0 when the current device is compute capability 10.x, else B200MOE_EARCH. */
+int b200moe_check_device(void);
+
+/* Upper bound (multiple of 128) on rows of the permuted buffer: min(T*k, E*capacity) + E*127, rounded up. */
+int b200moe_rows_upper_bound(int T, int k, int E, int capacity);
+/* ceil(T / B200MOE_ROUTER_BLOCK): first dimension of block_counts / block_stats. */
+int b200moe_num_router_blocks(int T);
+
+/* fp32 master weights -> bf16 operands (autocast step that torch does before hybrid_encoder.py:157). */
+int b200moe_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
+
+/* A.2-A.4 + statistics for A.8/A.9.  Gate GEMV over the token plus the per-image context bias, fp32 softmax,
+ * top-k with (p desc, index asc) order, optional renormalisation.
+ *   x [T,d] bf16; ctx_bias [B,E] fp32 or NULL (tok2img = t / tokens_per_image); wg [E,d] fp32
+ *   logits [T,E] fp32; topk_idx [T,k] int32; topk_gate [T,k] fp32
+ *   block_counts [nblk,k,E] int32 (pre-drop assignments per router block, slot, expert)
+ *   block_stats  [nblk,E+1] fp32 (sum_t p[t,e] per block; last column sum_t lse^2)                         */
+int b200moe_router_fwd(const void* x, const float* ctx_bias, int tokens_per_image, const float* wg,
+                       int T, int d, int E, int k, int normalize_topk,
+                       float* logits, int32_t* topk_idx, float* topk_gate,
+                       int32_t* block_counts, float* block_stats, void* stream);
+
+/* A.5 + A.8-A.10.  Slot-major / token-major priority scan, capacity clamp, padded expert offsets, row maps, losses.
+ *   global_offset [k,E] int32 or NULL: earlier-priority assignments owned by other ranks (expert parallelism)
+ *   expert_order  [E] int32 or NULL : position of expert e in the row layout (NULL = identity)
+ *   row_pad: 128 on one GPU (GEMM tiles), 1 for an all-to-all send buffer
+ *   out: expert_offsets [E+1] (in layout order: offsets[i] is the first row of the expert at position i)
+ *        meta [B200MOE_META_INTS]; tile_expert [rows_cap/128] (expert of each 128-row tile, -1 beyond R)
+ *        tokens_per_expert [E] (pre-drop); kept_per_expert [E]
+ *        losses [3] = {aux_loss_weight*lb + z_loss_weight*z, lb, z}
+ *        row_of_assignment [T,k] (-1 = dropped); token_of_row [rows_cap] (-1 = pad); gate_of_row [rows_cap]
+ *   block_counts is overwritten with the first row of every (block, slot, expert); slot_limit [k,E] is scratch. */
+int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int32_t* block_counts,
+                 const float* block_stats, int T, int k, int E, int capacity,
+                 const int32_t* global_offset, const int32_t* expert_order, int row_pad, int rows_cap,
+                 float aux_loss_weight, float z_loss_weight,
+                 int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert,
+                 int32_t* tokens_per_expert, int32_t* kept_per_expert, float* losses, int32_t* slot_limit,
+                 int32_t* row_of_assignment, int32_t* token_of_row, float* gate_of_row, void* stream);
+
+/* Dispatch: xp[r,:] = x[token_of_row[r],:] (zero rows for pads), r < meta[0]. 128-bit loads/stores. */
+int b200moe_permute(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
+                    void* xp, void* stream);
+
+/* A.7 combine: y[t,:] = sum_s gate[t,s] * yo[row_of_assignment[t,s],:] in slot order, fp32 accumulate. */
+int b200moe_combine(const void* yo, const int32_t* row_of_assignment, const float* topk_gate,
+                    int T, int k, int d, void* y, void* stream);
+
+/* Backward of combine: dyp[r,:] = gate_of_row[r] * dy[token_of_row[r],:] (0 for pads);
+ * dgate_row[r] = <dy[token,:], yo[r,:]>. */
+int b200moe_combine_bwd(const void* dy, const void* yo, const int32_t* token_of_row, const float* gate_of_row,
+                        const int32_t* meta, int rows_cap, int d, void* dyp, float* dgate_row, void* stream);
+
+/* Expert FFN, forward (A.6).  Grouped bf16 GEMMs on tcgen05/TMEM fed by TMA.
+ *   up  : pre = xp @ w1[e]^T + b1[e];  h = gelu_erf(pre)      w1 [E,F,d] bf16, b1 [E,F] fp32
+ *   down: yo  = h  @ w2[e]^T + b2[e]                          w2 [E,d,F] bf16, b2 [E,d] fp32
+ *   pre may be NULL (inference: nothing saved for backward).                                         */
+int b200moe_ffn_up(const void* xp, const void* w1, const float* b1, const int32_t* meta,
+                   const int32_t* tile_expert, int rows_cap, int d, int F, int E,
+                   void* pre, void* h, void* stream);
+int b200moe_ffn_down(const void* h, const void* w2, const float* b2, const int32_t* meta,
+                     const int32_t* tile_expert, int rows_cap, int d, int F, int E,
+                     void* yo, void* stream);
+
+/* Expert FFN, backward.
+ *   dgrad_down: dhpre = (dyp @ w2[e]) * gelu_erf'(pre)        [R,F]
+ *   dgrad_up  : dxp   = dhpre @ w1[e]                         [R,d]
+ *   wgrad     : dw[e] = a[rows of e]^T @ b[rows of e]         a [R,M] bf16, b [R,N] bf16 -> dw [E,M,N] fp32
+ *               (dw2 = dyp^T h, dw1 = dhpre^T xp); accumulate != 0 adds into dw
+ *   colsum    : db[e,:] = sum over rows of e of a[r,:]        (db2 from dyp, db1 from dhpre)            */
+int b200moe_ffn_dgrad_down(const void* dyp, const void* w2, const void* pre, const int32_t* meta,
+                           const int32_t* tile_expert, int rows_cap, int d, int F, int E,
+                           void* dhpre, void* stream);
+int b200moe_ffn_dgrad_up(const void* dhpre, const void* w1, const int32_t* meta,
+                         const int32_t* tile_expert, int rows_cap, int d, int F, int E,
+                         void* dxp, void* stream);
+int b200moe_ffn_wgrad(const void* a, const void* b, const int32_t* expert_offsets, int rows_cap,
+                      int M, int N, int E, float* dw, int accumulate, void* stream);
+int b200moe_colsum(const void* a, const int32_t* expert_offsets, int rows_cap, int ncols, int E,
+                   float* db, int accumulate, void* stream);
+
+/* A.12 router gradient.  dlogits from the gate gradient (softmax + renormalisation Jacobian on the selected k),
+ * the load-balance term through P_e and the z-loss through lse.  d_aux is the upstream gradient of the weighted
+ * auxiliary loss (device scalar, may be NULL = 0).  dgate_row may be NULL (no gradient through the gates).    */
+int b200moe_router_bwd_dlogits(const float* logits, const int32_t* topk_idx, const int32_t* row_of_assignment,
+                               const float* dgate_row, const int32_t* tokens_per_expert, const float* d_aux,
+                               int T, int E, int k, int normalize_topk, float aux_loss_weight,
+                               float z_loss_weight, float* dlogits, void* stream);
+/* dwg [E,d] = dlogits^T x (fp32, deterministic two-stage reduction; scratch >= b200moe_dwg_scratch_floats). */
+int64_t b200moe_dwg_scratch_floats(int T, int d, int E);
+int b200moe_router_bwd_dwg(const float* dlogits, const void* x, int T, int d, int E, float* scratch,
+                           float* dwg, void* stream);
+/* dctx_bias [B,E] = segment sums of dlogits over the tokens of each image. */
+int b200moe_router_bwd_dctx(const float* dlogits, int T, int E, int tokens_per_image, float* dctx_bias,
+                            void* stream);
+/* Backward of permute fused with the router's dx: dx[t,:] = sum_s dxp[row_of_assignment[t,s],:] + dlogits[t,:] @ wg.
+ * dxp / dlogits may each be NULL. */
+int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assignment, const float* dlogits,
+                          const float* wg, int T, int k, int d, int E, void* dx, void* stream);
+
+/* Expert-parallel receive side: rows arrive grouped by (local expert, source rank); build the padded layout.
+ *   recv_counts [n_seg] int32 rows per segment, seg_expert [n_seg] local expert of each segment (non-decreasing)
+ *   out: expert_offsets [E_local+1] (padded to 128), meta, tile_expert, src_of_row [rows_cap] (-1 = pad)      */
+int b200moe_ep_recv_plan(const int32_t* recv_counts, const int32_t* seg_expert, int n_seg, int E_local,
+                         int rows_cap, int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert,
+                         int32_t* src_of_row, void* stream);
+/* Inverse row gather used on the EP return path: out[src_of_row[r],:] = in[r,:] for r < meta[0], src >= 0. */
+int b200moe_scatter_rows(const void* in, const int32_t* src_of_row, const int32_t* meta, int rows_cap, int d,
+                         void* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200MOE_H_ */

@@ -1,0 +1,82 @@
+"""ctypes binding of libb200moe.so (include/b200moe.h).  No CPU fallback: a missing library is a hard error."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200moe.so")
+
+_P, _I, _F, _L = C.c_void_p, C.c_int, C.c_float, C.c_int64
+
+# name -> argtypes (return type is int unless listed in _RESTYPE); mirrors include/b200moe.h one to one
+SIGNATURES = {
+    "b200moe_version": [],
+    "b200moe_last_error": [],
+    "b200moe_check_device": [],
+    "b200moe_rows_upper_bound": [_I, _I, _I, _I],
+    "b200moe_num_router_blocks": [_I],
+    "b200moe_cast_f32_bf16": [_P, _P, _L, _P],
+    "b200moe_router_fwd": [_P, _P, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],
+    "b200moe_plan": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "b200moe_permute": [_P, _P, _P, _I, _I, _P, _P],
+    "b200moe_combine": [_P, _P, _P, _I, _I, _I, _P, _P],
+    "b200moe_combine_bwd": [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P],
+    "b200moe_ffn_up": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _P],
+    "b200moe_ffn_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
+    "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
+    "b200moe_ffn_dgrad_up": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
+    "b200moe_ffn_wgrad": [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
+    "b200moe_colsum": [_P, _P, _I, _I, _I, _P, _I, _P],
+    "b200moe_router_bwd_dlogits": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _P, _P],
+    "b200moe_dwg_scratch_floats": [_I, _I, _I],
+    "b200moe_router_bwd_dwg": [_P, _P, _I, _I, _I, _P, _P, _P],
+    "b200moe_router_bwd_dctx": [_P, _I, _I, _I, _P, _P],
+    "b200moe_unpermute_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
+    "b200moe_ep_recv_plan": [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P],
+    "b200moe_scatter_rows": [_P, _P, _P, _I, _I, _P, _P],
+}
+_RESTYPE = {"b200moe_last_error": C.c_char_p, "b200moe_dwg_scratch_floats": C.c_int64}
+
+_lib: Optional[C.CDLL] = None
+
+
+def load() -> C.CDLL:
+    """Load the shared library once.  Raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python multimodal-moe_b200/build.py` "
+            "(b200moe has no CPU or PyTorch fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here == header and library out of sync
+        fn.argtypes = argtypes
+        fn.restype = _RESTYPE.get(name, C.c_int)
+    _lib = lib
+    return lib
+
+
+def ptr(t: Optional[torch.Tensor]):
+    """Device pointer of a contiguous tensor (None -> NULL)."""
+    if t is None:
+        return None
+    assert t.is_contiguous(), "b200moe: tensors passed to the C ABI must be contiguous"
+    return t.data_ptr()
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def call(name: str, *args) -> None:
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        msg = lib.b200moe_last_error()
+        raise RuntimeError(f"{name} failed ({rc}): {msg.decode() if msg else ''}")

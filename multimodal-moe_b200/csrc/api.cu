@@ -1,0 +1,65 @@
+// libb200moe: error plumbing and the small host-only entry points of include/b200moe.h.
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "common.cuh"
+
+namespace b200moe {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return B200MOE_ECUDA;
+  }
+  return B200MOE_OK;
+}
+
+}  // namespace b200moe
+
+extern "C" {
+
+int b200moe_version(void) { return 100; }
+
+const char* b200moe_last_error(void) { return b200moe::g_err; }
+
+int b200moe_check_device(void) {
+  int dev = 0, major = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess ||
+      cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) {
+    cudaGetLastError();
+    b200moe::set_error("no CUDA device available (libb200moe has no CPU fallback)");
+    return B200MOE_EARCH;
+  }
+  if (major != 10) {
+    b200moe::set_error("device compute capability %d.x is not sm_100 (libb200moe is B200-only)", major);
+    return B200MOE_EARCH;
+  }
+  return B200MOE_OK;
+}
+
+int b200moe_rows_upper_bound(int T, int k, int E, int capacity) {
+  if (T < 0 || k <= 0 || E <= 0) return B200MOE_EINVAL;
+  long long kept = 1LL * T * k;
+  if (capacity >= 0 && 1LL * E * capacity < kept) kept = 1LL * E * capacity;
+  long long rows = kept + 1LL * E * (B200MOE_ROW_PAD - 1);
+  rows = (rows + B200MOE_ROW_PAD - 1) / B200MOE_ROW_PAD * B200MOE_ROW_PAD;
+  if (rows < B200MOE_ROW_PAD) rows = B200MOE_ROW_PAD;
+  if (rows > 0x7fffff00LL) return B200MOE_EINVAL;
+  return static_cast<int>(rows);
+}
+
+int b200moe_num_router_blocks(int T) {
+  return T <= 0 ? 0 : (T + B200MOE_ROUTER_BLOCK - 1) / B200MOE_ROUTER_BLOCK;
+}
+
+}  // extern "C"

@@ -1,0 +1,271 @@
+// Grouped expert GEMMs on tcgen05 / TMEM fed by TMA (sm_100a).  SURVEY.md Appendix A.6 and §8(d).
+//
+// One persistent warp-specialised kernel template covers the six contractions of the expert FFN:
+//   row mode  (M = rows of the permuted buffer, 128-row tiles never straddle experts; tile_expert[] picks the
+//              weight slab): up-proj, down-proj (A and B K-major), dgrad-down, dgrad-up (B = weights read MN-major,
+//              i.e. W[e] is used as [K,N] without a transposed copy);
+//   wgrad mode (M,N = weight dims, K = rows of one expert): A and B are both activations read MN-major.
+// Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
+// warps 2..5 = epilogue (warp w owns TMEM lanes 32*(w%4)..+31 = output rows).  A kStages-deep smem ring
+// (full/empty mbarriers) decouples TMA from MMA; two TMEM accumulator stages (tmem_full/tmem_empty) let the
+// epilogue of tile i overlap the main loop of tile i+1.
+//
+// Shared-memory operand tiles are 128-byte-swizzled exactly as TMA writes them:
+//   K-major  tile [rows][64 bf16]      : 8-row groups 1024 B apart (SBO); one k-step (16 bf16) = +32 B
+//   MN-major tile [64 k-rows][64 bf16] per 64-wide chunk of M/N, chunks 8192 B apart (LBO), 8-k-row groups
+//            1024 B apart (SBO); one k-step (16 k-rows) = +2048 B
+#include "common.cuh"
+
+namespace b200moe {
+
+enum : int { EPI_UP = 0, EPI_DOWN = 1, EPI_DGRAD_DOWN = 2, EPI_DGRAD_UP = 3, EPI_WGRAD = 4 };
+
+constexpr int BM = 128;
+constexpr int BK = 64;
+constexpr int kGemmThreads = 192;
+constexpr int kEpiThreads = 128;
+
+struct GemmArgs {
+  const int32_t* meta;            // row mode: meta[1] = number of 128-row tiles in use
+  const int32_t* tile_expert;     // row mode
+  const int32_t* expert_offsets;  // wgrad mode
+  int K;        // row mode: reduction length (d or F)
+  int N;        // output columns per expert
+  int M;        // wgrad mode: output rows per expert
+  int E;
+  const float* bias;              // [E,N] fp32 or null
+  const __nv_bfloat16* aux;       // EPI_DGRAD_DOWN: pre [R,N]
+  __nv_bfloat16* out0;            // bf16 output [R,N]
+  __nv_bfloat16* out1;            // EPI_UP: second output (pre) or null
+  float* outf;                    // EPI_WGRAD: [E,M,N]
+  int accumulate;
+};
+
+template <int BN>
+struct SmemCfg {
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kTotal = kStages * kStageBytes + kBarBytes + 1024;  // + alignment slack
+};
+
+template <int BN, bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmArgs args) {
+  using Cfg = SmemCfg<BN>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr bool kWgrad = (EPI == EPI_WGRAD);
+  constexpr uint32_t kTmemCols = 2 * BN;  // 256 or 512: power of two
+  constexpr uint32_t kIdesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tfull_bar = empty_bar + kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], kEpiThreads); }
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // ---- tile schedule (identical in every role) -------------------------------------------------------------
+  const int tiles_n = args.N / BN;
+  const int tiles_m = kWgrad ? args.M / BM : 0;
+  const int total_tiles = kWgrad ? args.E * tiles_m * tiles_n : args.meta[1] * tiles_n;
+
+  auto decode = [&](int tile, int& e, int& m_tile, int& n_tile, int& krow0, int& kblocks) {
+    if (kWgrad) {
+      const int per_e = tiles_m * tiles_n;
+      e = tile / per_e;
+      const int r = tile - e * per_e;
+      m_tile = r / tiles_n;
+      n_tile = r - m_tile * tiles_n;
+      const int r0 = args.expert_offsets[e], r1 = args.expert_offsets[e + 1];
+      krow0 = r0;
+      kblocks = (r1 - r0) / BK;
+    } else {
+      m_tile = tile / tiles_n;
+      n_tile = tile - m_tile * tiles_n;
+      e = args.tile_expert[m_tile];
+      krow0 = 0;
+      kblocks = args.K / BK;
+    }
+  };
+
+  if (warp == 0) {
+    // ======================= TMA producer =======================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int e, m_tile, n_tile, krow0, kblocks;
+        decode(tile, e, m_tile, n_tile, krow0, kblocks);
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          unsigned char* sa = smem + stage * Cfg::kStageBytes;
+          unsigned char* sb = sa + Cfg::kABytes;
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          if (A_MN) {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(sa + j * 8192, &tmA, &full_bar[stage], m_tile * BM + j * 64, krow0 + kb * BK);
+          } else {
+            tma_load_2d(sa, &tmA, &full_bar[stage], kb * BK, m_tile * BM);
+          }
+          if (B_MN) {
+            const int krow = kWgrad ? krow0 + kb * BK : e * args.K + kb * BK;
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sb + j * 8192, &tmB, &full_bar[stage], n_tile * BN + j * 64, krow);
+          } else {
+            tma_load_2d(sb, &tmB, &full_bar[stage], kb * BK, e * args.N + n_tile * BN);
+          }
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================= MMA issuer =======================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int e, m_tile, n_tile, krow0, kblocks;
+        decode(tile, e, m_tile, n_tile, krow0, kblocks);
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * BN;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sb = sa + Cfg::kABytes;
+          const uint64_t da = A_MN ? make_smem_desc(sa, 8192, 1024) : make_smem_desc(sa, 16, 1024);
+          const uint64_t db = B_MN ? make_smem_desc(sb, 8192, 1024) : make_smem_desc(sb, 16, 1024);
+#pragma unroll
+          for (int ks = 0; ks < BK / 16; ++ks) {
+            const uint64_t a_k = da + static_cast<uint64_t>(ks * (A_MN ? 128 : 2));
+            const uint64_t b_k = db + static_cast<uint64_t>(ks * (B_MN ? 128 : 2));
+            umma_bf16_ss(tmem_d, a_k, b_k, kIdesc, (kb | ks) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);   // frees the smem slot once these MMAs have read it
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        if (kblocks > 0) umma_commit(&tfull_bar[acc]);   // accumulator complete
+        else mbar_arrive(&tfull_bar[acc]);               // empty expert: nothing to wait for
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ======================= epilogue (warps 2..5) =======================
+    const int quarter = warp & 3;              // TMEM lane quarter this warp may read
+    const int row_in_tile = quarter * 32 + lane;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      int e, m_tile, n_tile, krow0, kblocks;
+      decode(tile, e, m_tile, n_tile, krow0, kblocks);
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
+      const size_t grow = static_cast<size_t>(m_tile) * BM + row_in_tile;   // row of the output
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c * 32, v);
+        tmem_ld_wait();
+        const int col0 = n_tile * BN + c * 32;
+        if (EPI == EPI_WGRAD) {
+          float* o = args.outf + (static_cast<size_t>(e) * args.M + grow) * args.N + col0;
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float4 r = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                   __uint_as_float(v[j + 3]));
+            if (kblocks == 0) r = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (args.accumulate) {
+              const float4 p = *reinterpret_cast<const float4*>(o + j);
+              r.x += p.x; r.y += p.y; r.z += p.z; r.w += p.w;
+            }
+            *reinterpret_cast<float4*>(o + j) = r;
+          }
+        } else {
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          if (EPI == EPI_UP || EPI == EPI_DOWN) {
+            const float* b = args.bias + static_cast<size_t>(e) * args.N + col0;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 bv = __ldg(reinterpret_cast<const float4*>(b + j));
+              f[j] += bv.x; f[j + 1] += bv.y; f[j + 2] += bv.z; f[j + 3] += bv.w;
+            }
+          }
+          const size_t off = grow * args.N + col0;
+          if (EPI == EPI_UP && args.out1) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 pk;
+              pk.x = float2_to_bf16x2(f[j], f[j + 1]); pk.y = float2_to_bf16x2(f[j + 2], f[j + 3]);
+              pk.z = float2_to_bf16x2(f[j + 4], f[j + 5]); pk.w = float2_to_bf16x2(f[j + 6], f[j + 7]);
+              *reinterpret_cast<uint4*>(args.out1 + off + j) = pk;
+            }
+          }
+          if (EPI == EPI_UP) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+          }
+          if (EPI == EPI_DGRAD_DOWN) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              const uint4 pr = *reinterpret_cast<const uint4*>(args.aux + off + j);
+              float2 t;
+              t = bf16x2_to_float2(pr.x); f[j] *= gelu_erf_grad(t.x); f[j + 1] *= gelu_erf_grad(t.y);
+              t = bf16x2_to_float2(pr.y); f[j + 2] *= gelu_erf_grad(t.x); f[j + 3] *= gelu_erf_grad(t.y);
+              t = bf16x2_to_float2(pr.z); f[j + 4] *= gelu_erf_grad(t.x); f[j + 5] *= gelu_erf_grad(t.y);
+              t = bf16x2_to_float2(pr.w); f[j + 6] *= gelu_erf_grad(t.x); f[j + 7] *= gelu_erf_grad(t.y);
+            }
+          }
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 pk;
+            pk.x = float2_to_bf16x2(f[j], f[j + 1]); pk.y = float2_to_bf16x2(f[j + 2], f[j + 3]);
+            pk.z = float2_to_bf16x2(f[j + 4], f[j + 5]); pk.w = float2_to_bf16x2(f[j + 6], f[j + 7]);
+            *reinterpret_cast<uint4*>(args.out0 + off + j) = pk;
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<kTmemCols>(tmem_base);
+  }
+}
+
+}  // namespace b200moe
+
+#include "gemm_host.inc"

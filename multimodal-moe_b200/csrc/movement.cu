@@ -1,0 +1,281 @@
+// HBM-bound row movement: dispatch (permute), combine, their backward passes, casts, column sums.
+// One warp moves one row with 128-bit loads/stores (a row of d bf16 is d/8 16-byte chunks, lanes stride them),
+// so every request is a run of full 32-byte sectors and consecutive lanes touch consecutive addresses.
+#include "common.cuh"
+
+namespace b200moe {
+
+constexpr int kMoveWarps = 8;
+constexpr int kMoveThreads = kMoveWarps * 32;
+
+__device__ __forceinline__ void unpack8(const uint4& r, float (&v)[8]) {
+  float2 f;
+  f = bf16x2_to_float2(r.x); v[0] = f.x; v[1] = f.y;
+  f = bf16x2_to_float2(r.y); v[2] = f.x; v[3] = f.y;
+  f = bf16x2_to_float2(r.z); v[4] = f.x; v[5] = f.y;
+  f = bf16x2_to_float2(r.w); v[6] = f.x; v[7] = f.y;
+}
+__device__ __forceinline__ uint4 pack8(const float (&v)[8]) {
+  uint4 r;
+  r.x = float2_to_bf16x2(v[0], v[1]); r.y = float2_to_bf16x2(v[2], v[3]);
+  r.z = float2_to_bf16x2(v[4], v[5]); r.w = float2_to_bf16x2(v[6], v[7]);
+  return r;
+}
+
+// xp[r] = x[token_of_row[r]] or 0
+__global__ void __launch_bounds__(kMoveThreads)
+permute_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ token_of_row,
+               const int32_t* __restrict__ meta, int d, __nv_bfloat16* __restrict__ xp) {
+  const int R = meta[0];
+  const int nchunk = d >> 3;
+  const int lane = threadIdx.x & 31;
+  for (int r = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); r < R; r += gridDim.x * kMoveWarps) {
+    const int t = token_of_row[r];
+    __nv_bfloat16* dst = xp + static_cast<size_t>(r) * d;
+    if (t >= 0) {
+      const __nv_bfloat16* src = x + static_cast<size_t>(t) * d;
+      for (int c = lane; c < nchunk; c += 32) stg128(dst + c * 8, ldg128(src + c * 8));
+    } else {
+      for (int c = lane; c < nchunk; c += 32) stg128(dst + c * 8, make_uint4(0, 0, 0, 0));
+    }
+  }
+}
+
+// out[src_of_row[r]] = in[r]   (EP return path)
+__global__ void __launch_bounds__(kMoveThreads)
+scatter_rows_kernel(const __nv_bfloat16* __restrict__ in, const int32_t* __restrict__ src_of_row,
+                    const int32_t* __restrict__ meta, int d, __nv_bfloat16* __restrict__ out) {
+  const int R = meta[0];
+  const int nchunk = d >> 3;
+  const int lane = threadIdx.x & 31;
+  for (int r = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); r < R; r += gridDim.x * kMoveWarps) {
+    const int t = src_of_row[r];
+    if (t < 0) continue;
+    const __nv_bfloat16* src = in + static_cast<size_t>(r) * d;
+    __nv_bfloat16* dst = out + static_cast<size_t>(t) * d;
+    for (int c = lane; c < nchunk; c += 32) stg128(dst + c * 8, ldg128(src + c * 8));
+  }
+}
+
+// y[t] = sum_s gate[t,s] * yo[row[t,s]]   (slot order, fp32)
+__global__ void __launch_bounds__(kMoveThreads)
+combine_kernel(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ row_of_assignment,
+               const float* __restrict__ topk_gate, int T, int k, int d, __nv_bfloat16* __restrict__ y) {
+  const int nchunk = d >> 3;
+  const int lane = threadIdx.x & 31;
+  for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps) {
+    for (int c = lane; c < nchunk; c += 32) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int s = 0; s < k; ++s) {
+        const int r = row_of_assignment[static_cast<size_t>(t) * k + s];
+        if (r < 0) continue;
+        const float g = topk_gate[static_cast<size_t>(t) * k + s];
+        float v[8];
+        unpack8(ldg128(yo + static_cast<size_t>(r) * d + c * 8), v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = fmaf(g, v[j], acc[j]);
+      }
+      stg128(y + static_cast<size_t>(t) * d + c * 8, pack8(acc));
+    }
+  }
+}
+
+// dyp[r] = gate_of_row[r] * dy[token_of_row[r]];  dgate_row[r] = <dy[token], yo[r]>
+__global__ void __launch_bounds__(kMoveThreads)
+combine_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ yo,
+                   const int32_t* __restrict__ token_of_row, const float* __restrict__ gate_of_row,
+                   const int32_t* __restrict__ meta, int d, __nv_bfloat16* __restrict__ dyp,
+                   float* __restrict__ dgate_row) {
+  const int R = meta[0];
+  const int nchunk = d >> 3;
+  const int lane = threadIdx.x & 31;
+  for (int r = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); r < R; r += gridDim.x * kMoveWarps) {
+    const int t = token_of_row[r];
+    __nv_bfloat16* dst = dyp + static_cast<size_t>(r) * d;
+    if (t < 0) {
+      for (int c = lane; c < nchunk; c += 32) stg128(dst + c * 8, make_uint4(0, 0, 0, 0));
+      if (lane == 0 && dgate_row) dgate_row[r] = 0.f;
+      continue;
+    }
+    const float g = gate_of_row[r];
+    float dot = 0.f;
+    for (int c = lane; c < nchunk; c += 32) {
+      float a[8], b[8], o[8];
+      unpack8(ldg128(dy + static_cast<size_t>(t) * d + c * 8), a);
+      if (yo) unpack8(ldg128(yo + static_cast<size_t>(r) * d + c * 8), b);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        o[j] = g * a[j];
+        if (yo) dot = fmaf(a[j], b[j], dot);
+      }
+      stg128(dst + c * 8, pack8(o));
+    }
+    if (dgate_row) {
+      dot = warp_sum(dot);
+      if (lane == 0) dgate_row[r] = dot;
+    }
+  }
+}
+
+// dx[t] = sum_s dxp[row[t,s]] + dlogits[t] @ wg
+__global__ void __launch_bounds__(kMoveThreads)
+unpermute_bwd_kernel(const __nv_bfloat16* __restrict__ dxp, const int32_t* __restrict__ row_of_assignment,
+                     const float* __restrict__ dlogits, const float* __restrict__ wg, int T, int k, int d, int E,
+                     __nv_bfloat16* __restrict__ dx) {
+  const int nchunk = d >> 3;
+  const int lane = threadIdx.x & 31;
+  for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps) {
+    for (int c = lane; c < nchunk; c += 32) {
+      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (dxp) {
+        for (int s = 0; s < k; ++s) {
+          const int r = row_of_assignment[static_cast<size_t>(t) * k + s];
+          if (r < 0) continue;
+          float v[8];
+          unpack8(ldg128(dxp + static_cast<size_t>(r) * d + c * 8), v);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[j] += v[j];
+        }
+      }
+      if (dlogits) {
+        for (int e = 0; e < E; ++e) {
+          const float g = __ldg(dlogits + static_cast<size_t>(t) * E + e);
+          const float4 wa = __ldg(reinterpret_cast<const float4*>(wg + static_cast<size_t>(e) * d + c * 8));
+          const float4 wb = __ldg(reinterpret_cast<const float4*>(wg + static_cast<size_t>(e) * d + c * 8 + 4));
+          acc[0] = fmaf(g, wa.x, acc[0]); acc[1] = fmaf(g, wa.y, acc[1]);
+          acc[2] = fmaf(g, wa.z, acc[2]); acc[3] = fmaf(g, wa.w, acc[3]);
+          acc[4] = fmaf(g, wb.x, acc[4]); acc[5] = fmaf(g, wb.y, acc[5]);
+          acc[6] = fmaf(g, wb.z, acc[6]); acc[7] = fmaf(g, wb.w, acc[7]);
+        }
+      }
+      stg128(dx + static_cast<size_t>(t) * d + c * 8, pack8(acc));
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int64_t n8, int64_t n) {
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(src) + 2 * i);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(src) + 2 * i + 1);
+    const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    stg128(dst + 8 * i, pack8(v));
+  }
+  if (blockIdx.x == 0)
+    for (int64_t i = n8 * 8 + threadIdx.x; i < n; i += blockDim.x) dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+// db[e, c] = sum over rows of expert e of a[r, c].  Block = (column slab of 256, expert, row split); fixed order.
+__global__ void __launch_bounds__(256)
+colsum_kernel(const __nv_bfloat16* __restrict__ a, const int32_t* __restrict__ expert_offsets, int ncols,
+              float* __restrict__ db, int accumulate) {
+  __shared__ float part[8][256];
+  const int e = blockIdx.y;
+  const int r0 = expert_offsets[e], r1 = expert_offsets[e + 1];
+  // thread = (row phase 0..7, 8-column chunk 0..31): a warp reads 512 contiguous bytes of one row
+  const int chunk = threadIdx.x & 31, phase = threadIdx.x >> 5;
+  const int col0 = blockIdx.x * 256 + chunk * 8;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (col0 < ncols) {
+    for (int r = r0 + phase; r < r1; r += 8) {
+      float v[8];
+      unpack8(ldg128(a + static_cast<size_t>(r) * ncols + col0), v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) part[phase][chunk * 8 + j] = acc[j];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < ncols) {
+    float s = 0.f;
+#pragma unroll
+    for (int p = 0; p < 8; ++p) s += part[p][threadIdx.x];
+    float* o = db + static_cast<size_t>(e) * ncols + c;
+    *o = accumulate ? *o + s : s;
+  }
+}
+
+static inline int move_grid(long long rows) {
+  long long b = (rows + kMoveWarps - 1) / kMoveWarps;
+  const long long cap = static_cast<long long>(kNumSMs) * 8;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+}  // namespace b200moe
+
+using namespace b200moe;
+#define BF(p) static_cast<const __nv_bfloat16*>(p)
+#define BFW(p) static_cast<__nv_bfloat16*>(p)
+#define ST(s) static_cast<cudaStream_t>(s)
+
+extern "C" int b200moe_permute(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
+                               void* xp, void* stream) {
+  B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "permute: d=%d must be a multiple of 8", d);
+  if (int rc = b200moe_check_device()) return rc;
+  permute_kernel<<<move_grid(rows_cap), kMoveThreads, 0, ST(stream)>>>(BF(x), token_of_row, meta, d, BFW(xp));
+  return check_launch("permute");
+}
+
+extern "C" int b200moe_scatter_rows(const void* in, const int32_t* src_of_row, const int32_t* meta, int rows_cap,
+                                    int d, void* out, void* stream) {
+  B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "scatter_rows: d=%d must be a multiple of 8", d);
+  if (int rc = b200moe_check_device()) return rc;
+  scatter_rows_kernel<<<move_grid(rows_cap), kMoveThreads, 0, ST(stream)>>>(BF(in), src_of_row, meta, d, BFW(out));
+  return check_launch("scatter_rows");
+}
+
+extern "C" int b200moe_combine(const void* yo, const int32_t* row_of_assignment, const float* topk_gate, int T,
+                               int k, int d, void* y, void* stream) {
+  B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "combine: d=%d must be a multiple of 8", d);
+  if (T == 0) return B200MOE_OK;
+  if (int rc = b200moe_check_device()) return rc;
+  combine_kernel<<<move_grid(T), kMoveThreads, 0, ST(stream)>>>(BF(yo), row_of_assignment, topk_gate, T, k, d, BFW(y));
+  return check_launch("combine");
+}
+
+extern "C" int b200moe_combine_bwd(const void* dy, const void* yo, const int32_t* token_of_row,
+                                   const float* gate_of_row, const int32_t* meta, int rows_cap, int d, void* dyp,
+                                   float* dgate_row, void* stream) {
+  B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "combine_bwd: d=%d must be a multiple of 8", d);
+  if (int rc = b200moe_check_device()) return rc;
+  combine_bwd_kernel<<<move_grid(rows_cap), kMoveThreads, 0, ST(stream)>>>(BF(dy), BF(yo), token_of_row, gate_of_row,
+                                                                           meta, d, BFW(dyp), dgate_row);
+  return check_launch("combine_bwd");
+}
+
+extern "C" int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assignment, const float* dlogits,
+                                     const float* wg, int T, int k, int d, int E, void* dx, void* stream) {
+  B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "unpermute_bwd: d=%d must be a multiple of 8", d);
+  if (T == 0) return B200MOE_OK;
+  if (int rc = b200moe_check_device()) return rc;
+  unpermute_bwd_kernel<<<move_grid(T), kMoveThreads, 0, ST(stream)>>>(BF(dxp), row_of_assignment, dlogits, wg, T, k,
+                                                                      d, E, BFW(dx));
+  return check_launch("unpermute_bwd");
+}
+
+extern "C" int b200moe_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {
+  B200MOE_REQUIRE(n >= 0, B200MOE_EINVAL, "cast: negative length");
+  if (n == 0) return B200MOE_OK;
+  if (int rc = b200moe_check_device()) return rc;
+  const int64_t n8 = n / 8;
+  int64_t blocks = (n8 + 255) / 256;
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks < 1) blocks = 1;
+  cast_f32_bf16_kernel<<<static_cast<int>(blocks), 256, 0, ST(stream)>>>(src, BFW(dst), n8, n);
+  return check_launch("cast_f32_bf16");
+}
+
+extern "C" int b200moe_colsum(const void* a, const int32_t* expert_offsets, int rows_cap, int ncols, int E,
+                              float* db, int accumulate, void* stream) {
+  (void)rows_cap;
+  B200MOE_REQUIRE(ncols > 0 && ncols % 8 == 0, B200MOE_EINVAL, "colsum: ncols=%d must be a multiple of 8", ncols);
+  if (int rc = b200moe_check_device()) return rc;
+  dim3 grid((ncols + 255) / 256, E);
+  colsum_kernel<<<grid, 256, 0, ST(stream)>>>(BF(a), expert_offsets, ncols, db, accumulate);
+  return check_launch("colsum");
+}

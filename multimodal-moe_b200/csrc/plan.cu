@@ -1,0 +1,201 @@
+// Capacity plan: priority scan -> per-expert offsets -> row maps.
+//
+// Priority of an assignment is (slot, token index): all first choices in token order, then all second choices.
+// The router already counted assignments per (router block, slot, expert); plan_scan_kernel turns those counts into
+// exclusive bases with warp scans (one warp per (slot, expert) sequence over the blocks, fixed order), clamps them
+// to the capacity, lays the experts out back to back with each segment padded to `row_pad` rows, and reduces the
+// loss statistics in a fixed order.  plan_assign_kernel then gives every assignment its row: base of its block +
+// its rank among the same-expert assignments of the block (match_any + popc), which is exactly the slot-major /
+// token-major order, so rows inside an expert are sorted by priority and "kept" == "row below the slot limit".
+#include "common.cuh"
+
+namespace b200moe {
+
+constexpr int kScanThreads = 1024;
+
+__global__ void __launch_bounds__(kScanThreads)
+plan_scan_kernel(int32_t* __restrict__ block_counts, const float* __restrict__ block_stats, int nblk, int T, int k,
+                 int E, int capacity, const int32_t* __restrict__ global_offset,
+                 const int32_t* __restrict__ expert_order, int row_pad, int rows_cap, float aux_w, float z_w,
+                 int32_t* __restrict__ expert_offsets, int32_t* __restrict__ meta, int32_t* __restrict__ tile_expert,
+                 int32_t* __restrict__ tokens_per_expert, int32_t* __restrict__ kept_per_expert,
+                 float* __restrict__ losses, int32_t* __restrict__ slot_limit) {
+  __shared__ int total_s[8 * 64];      // [k][E] assignments per (slot, expert) on this rank
+  __shared__ int rowbase_s[8 * 64];    // [k][E] first row (relative to the expert segment) of slot s
+  __shared__ int keptslot_s[8 * 64];
+  __shared__ int kept_s[64], count_s[64], off_s[65], expert_at_s[64];
+  __shared__ float P_s[65];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = kScanThreads / 32;
+  const int kE = k * E;
+
+  // phase 1: exclusive scan over the router blocks for every (slot, expert) sequence
+  for (int q = warp; q < kE; q += nwarps) {
+    int run = 0;
+    for (int b0 = 0; b0 < nblk; b0 += 32) {
+      const int b = b0 + lane;
+      const int v = (b < nblk) ? block_counts[static_cast<size_t>(b) * kE + q] : 0;
+      int inc = v;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += n;
+      }
+      if (b < nblk) block_counts[static_cast<size_t>(b) * kE + q] = run + inc - v;
+      run += __shfl_sync(0xffffffffu, inc, 31);
+    }
+    if (lane == 0) total_s[q] = run;
+  }
+  // loss statistics: one warp per column of block_stats, lanes stride the blocks, fixed shuffle tree
+  for (int e = warp; e <= E; e += nwarps) {
+    float s = 0.f;
+    for (int b = lane; b < nblk; b += 32) s += block_stats[static_cast<size_t>(b) * (E + 1) + e];
+    s = warp_sum(s);
+    if (lane == 0) P_s[e] = s;
+  }
+  __syncthreads();
+
+  // phase 2: per expert, slot bases against the capacity
+  if (threadIdx.x < E) {
+    const int e = threadIdx.x;
+    int lower = 0, kept = 0, count = 0;
+    for (int s = 0; s < k; ++s) {
+      const int n = total_s[s * E + e];
+      const int base = global_offset ? global_offset[s * E + e] : lower;  // earlier-priority assignments
+      int room = capacity - base;
+      room = room < 0 ? 0 : room;
+      const int ks = n < room ? n : room;
+      keptslot_s[s * E + e] = ks;
+      rowbase_s[s * E + e] = kept;
+      kept += ks;
+      lower += n;
+      count += n;
+    }
+    kept_s[e] = kept;
+    count_s[e] = count;
+    tokens_per_expert[e] = count;
+    kept_per_expert[e] = kept;
+    expert_at_s[expert_order ? expert_order[e] : e] = e;
+  }
+  __syncthreads();
+
+  // phase 3: segment offsets in layout order, losses
+  if (threadIdx.x == 0) {
+    int off = 0, kept_total = 0, count_total = 0;
+    for (int i = 0; i < E; ++i) {
+      off_s[i] = off;
+      const int e = expert_at_s[i];
+      off += (kept_s[e] + row_pad - 1) / row_pad * row_pad;
+      kept_total += kept_s[e];
+      count_total += count_s[e];
+    }
+    off_s[E] = off;
+    meta[0] = off;
+    meta[1] = (off + kRowPad - 1) / kRowPad;
+    meta[2] = count_total - kept_total;
+    meta[3] = kept_total;
+    meta[4] = capacity;
+    meta[5] = meta[6] = meta[7] = 0;
+    float lb = 0.f;
+    const float invT = T > 0 ? 1.0f / static_cast<float>(T) : 0.f;
+    for (int e = 0; e < E; ++e)
+      lb += (static_cast<float>(count_s[e]) / static_cast<float>(static_cast<long long>(T) * k)) * (P_s[e] * invT);
+    lb *= static_cast<float>(E);
+    const float z = P_s[E] * invT;
+    losses[0] = aux_w * lb + z_w * z;
+    losses[1] = lb;
+    losses[2] = z;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i <= E; i += blockDim.x) expert_offsets[i] = off_s[i];
+
+  // phase 4: absolute bases for the assign kernel
+  for (int q = threadIdx.x; q < kE; q += blockDim.x) {
+    const int e = q % E;
+    const int pos = expert_order ? expert_order[e] : e;
+    const int first = off_s[pos] + rowbase_s[q];
+    rowbase_s[q] = first;
+    slot_limit[q] = first + keptslot_s[q];
+  }
+  __syncthreads();
+  for (int q = warp; q < kE; q += nwarps) {
+    const int first = rowbase_s[q];
+    for (int b = lane; b < nblk; b += 32) block_counts[static_cast<size_t>(b) * kE + q] += first;
+  }
+  if (tile_expert) {
+    const int ntiles_cap = rows_cap / kRowPad;
+    const int ntiles = off_s[E] / kRowPad;
+    for (int tIdx = threadIdx.x; tIdx < ntiles_cap; tIdx += blockDim.x) {
+      int e = -1;
+      if (tIdx < ntiles) {
+        const int row = tIdx * kRowPad;
+        int pos = 0;
+        while (pos + 1 < E && off_s[pos + 1] <= row) ++pos;
+        e = expert_at_s[pos];
+      }
+      tile_expert[tIdx] = e;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kRouterTokPerBlock)
+plan_assign_kernel(const int32_t* __restrict__ topk_idx, const float* __restrict__ topk_gate,
+                   const int32_t* __restrict__ block_base, const int32_t* __restrict__ slot_limit, int T, int k,
+                   int E, int32_t* __restrict__ row_of_assignment, int32_t* __restrict__ token_of_row,
+                   float* __restrict__ gate_of_row) {
+  __shared__ int wc[kRouterTokPerBlock / 32][64];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t = blockIdx.x * kRouterTokPerBlock + threadIdx.x;
+  const bool live = t < T;
+  for (int s = 0; s < k; ++s) {
+    for (int i = threadIdx.x; i < (kRouterTokPerBlock / 32) * 64; i += blockDim.x) (&wc[0][0])[i] = 0;
+    __syncthreads();
+    const int e = live ? topk_idx[static_cast<size_t>(t) * k + s] : (0x40000000 + lane);
+    const unsigned same = __match_any_sync(0xffffffffu, e);
+    const int rank_in_warp = __popc(same & ((1u << lane) - 1u));
+    if (live && rank_in_warp == 0) wc[warp][e] = __popc(same);
+    __syncthreads();
+    if (live) {
+      int rank = rank_in_warp;
+      for (int w = 0; w < warp; ++w) rank += wc[w][e];
+      const int q = s * E + e;
+      const int row = block_base[static_cast<size_t>(blockIdx.x) * k * E + q] + rank;
+      const bool keep = row < slot_limit[q];
+      row_of_assignment[static_cast<size_t>(t) * k + s] = keep ? row : -1;
+      if (keep) {
+        token_of_row[row] = t;
+        gate_of_row[row] = topk_gate[static_cast<size_t>(t) * k + s];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace b200moe
+
+extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int32_t* block_counts,
+                            const float* block_stats, int T, int k, int E, int capacity,
+                            const int32_t* global_offset, const int32_t* expert_order, int row_pad, int rows_cap,
+                            float aux_loss_weight, float z_loss_weight, int32_t* expert_offsets, int32_t* meta,
+                            int32_t* tile_expert, int32_t* tokens_per_expert, int32_t* kept_per_expert,
+                            float* losses, int32_t* slot_limit, int32_t* row_of_assignment, int32_t* token_of_row,
+                            float* gate_of_row, void* stream) {
+  using namespace b200moe;
+  B200MOE_REQUIRE(T > 0, B200MOE_EINVAL, "plan: T=%d must be positive", T);
+  B200MOE_REQUIRE(E >= 1 && E <= 64 && k >= 1 && k <= 8 && k <= E, B200MOE_EINVAL, "plan: bad E=%d / k=%d", E, k);
+  B200MOE_REQUIRE(row_pad == 1 || row_pad == kRowPad, B200MOE_EINVAL, "plan: row_pad must be 1 or 128");
+  B200MOE_REQUIRE(capacity >= 0, B200MOE_EINVAL, "plan: negative capacity");
+  B200MOE_REQUIRE(rows_cap > 0 && rows_cap % kRowPad == 0, B200MOE_EINVAL, "plan: rows_cap must be a multiple of 128");
+  if (int rc = b200moe_check_device()) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nblk = (T + kRouterTokPerBlock - 1) / kRouterTokPerBlock;
+  cudaMemsetAsync(token_of_row, 0xFF, sizeof(int32_t) * static_cast<size_t>(rows_cap), st);
+  cudaMemsetAsync(gate_of_row, 0, sizeof(float) * static_cast<size_t>(rows_cap), st);
+  plan_scan_kernel<<<1, kScanThreads, 0, st>>>(block_counts, block_stats, nblk, T, k, E, capacity, global_offset,
+                                               expert_order, row_pad, rows_cap, aux_loss_weight, z_loss_weight,
+                                               expert_offsets, meta, tile_expert, tokens_per_expert,
+                                               kept_per_expert, losses, slot_limit);
+  if (int rc = check_launch("plan_scan")) return rc;
+  plan_assign_kernel<<<nblk, kRouterTokPerBlock, 0, st>>>(topk_idx, topk_gate, block_counts, slot_limit, T, k, E,
+                                                          row_of_assignment, token_of_row, gate_of_row);
+  return check_launch("plan_assign");
+}

@@ -55,12 +55,15 @@ def capacity_of(capacity_factor: Optional[float], T: int, k: int, E: int) -> int
 def route(logits: torch.Tensor, top_k: int, normalize_topk: bool = True):
     """A.3/A.4: fp32 softmax, top-k by (p desc, expert index asc), optional renormalisation.
 
+    The ranking is taken on the logits: softmax is monotone, so (logit desc, index asc) IS the (p desc, index asc)
+    order of A.4, minus the spurious ties that fp32 rounding of p can fabricate between two distinct logits
+    (which would make "bit-exact routing on identical fp32 logits" depend on the exp implementation).
     Returns (p [T,E], idx [T,k] int64, gates [T,k]).
     """
     logits = logits.float()
     p = torch.softmax(logits, dim=-1)
     # stable descending sort == lowest index wins ties; torch.topk does not guarantee that
-    idx = torch.sort(p, dim=-1, descending=True, stable=True).indices[:, :top_k]
+    idx = torch.sort(logits, dim=-1, descending=True, stable=True).indices[:, :top_k]
     g = torch.gather(p, 1, idx)
     if normalize_topk:
         g = g / (g.sum(dim=-1, keepdim=True) + 1e-9)

@@ -63,6 +63,24 @@ def main():
     }
     np.savez_compressed(os.path.join(HERE, "dense_ffn_d64_f128.npz"), **out)
 
+    # same op at the smallest shape the tcgen05 tiles accept (d, F multiples of 128): the GPU known-answer test
+    torch.manual_seed(20260221)
+    d2, F2, B2, HW2 = 128, 256, 2, 50
+    layer2 = he.TransformerEncoderLayer(d2, 8, F2, 0.0, "gelu")
+    layer2.eval()
+    x2 = torch.randn(B2, HW2, d2, requires_grad=True)
+    go2 = torch.randn(B2, HW2, d2)
+    y2 = layer2.linear2(layer2.dropout(layer2.activation(layer2.linear1(x2))))
+    (y2 * go2).sum().backward()
+    out2 = {
+        "x": x2.detach().numpy(), "go": go2.numpy(), "y": y2.detach().numpy(), "dx": x2.grad.numpy(),
+        "w1": layer2.linear1.weight.detach().numpy(), "b1": layer2.linear1.bias.detach().numpy(),
+        "w2": layer2.linear2.weight.detach().numpy(), "b2": layer2.linear2.bias.detach().numpy(),
+        "dw1": layer2.linear1.weight.grad.numpy(), "db1": layer2.linear1.bias.grad.numpy(),
+        "dw2": layer2.linear2.weight.grad.numpy(), "db2": layer2.linear2.bias.grad.numpy(),
+    }
+    np.savez_compressed(os.path.join(HERE, "dense_ffn_d128_f256.npz"), **out2)
+
     # the post-norm wrapper (:154-160): norm2(residual + ffn(src)) on the same src
     with torch.no_grad():
         src = torch.randn(B, HW, d)
