@@ -74,9 +74,46 @@ def stream_ptr() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+# kernels launched by each entry point (memset nodes not counted); used for bench.py's gpu_launches
+KERNELS_PER_CALL = {
+    "b200moe_cast_f32_bf16": 1, "b200moe_router_fwd": 1, "b200moe_plan": 2, "b200moe_permute": 1,
+    "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
+    "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
+    "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,
+    "b200moe_unpermute_bwd": 1, "b200moe_ep_recv_plan": 1, "b200moe_scatter_rows": 1,
+}
+
+
+class Counters:
+    """Launch counter and optional per-call CUDA-event timing (bench.py's instrumented pass)."""
+    launches = 0
+    timing = False
+    events: list = []   # (name, start_event, end_event)
+
+    @classmethod
+    def reset(cls, timing: bool = False):
+        cls.launches, cls.timing, cls.events = 0, timing, []
+
+    @classmethod
+    def durations_ms(cls) -> dict:
+        """name -> list of per-call durations (call after torch.cuda.synchronize())."""
+        out: dict = {}
+        for name, a, b in cls.events:
+            out.setdefault(name, []).append(a.elapsed_time(b))
+        return out
+
+
 def call(name: str, *args) -> None:
     lib = load()
-    rc = getattr(lib, name)(*args)
+    if Counters.timing:
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        rc = getattr(lib, name)(*args)
+        b.record()
+        Counters.events.append((name, a, b))
+    else:
+        rc = getattr(lib, name)(*args)
+    Counters.launches += KERNELS_PER_CALL.get(name, 0)
     if rc != 0:
         msg = lib.b200moe_last_error()
         raise RuntimeError(f"{name} failed ({rc}): {msg.decode() if msg else ''}")

@@ -27,8 +27,7 @@ class _MoEFunction(torch.autograd.Function):
     def forward(ctx, x2, ctx_bias, wg, w1, b1, w2, b2, mod, tokens_per_image):
         T, d = x2.shape
         E, k = mod.num_experts, mod.top_k
-        need_grad = torch.is_grad_enabled() and any(
-            t is not None and t.requires_grad for t in (x2, ctx_bias, wg, w1, b1, w2, b2))
+        need_grad = any(ctx.needs_input_grad)   # forward runs under no_grad: ask autograd, not the grad mode
         w1b, w2b = mod._bf16_weight("w1", w1), mod._bf16_weight("w2", w2)
         b1f, b2f = b1.float().contiguous(), b2.float().contiguous()
         wgf = wg.float().contiguous()

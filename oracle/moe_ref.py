@@ -199,7 +199,7 @@ class ContextMoERef(nn.Module):
         return F.linear(h, self.w2[e].float(), self.b2[e].float())
 
     def forward(self, x: torch.Tensor, context: Optional[torch.Tensor] = None,
-                logits_override: Optional[torch.Tensor] = None,
+                logits_override: Optional[torch.Tensor] = None, logits_value: Optional[torch.Tensor] = None,
                 global_offset: Optional[torch.Tensor] = None, capacity_override: Optional[int] = None):
         shape = x.shape
         d, E, k = self.d_model, self.num_experts, self.top_k
@@ -208,6 +208,9 @@ class ContextMoERef(nn.Module):
         B = shape[0] if x.dim() == 3 else 1
         hw = T // B
         lg = self.logits(x2, self.context_bias(context), hw) if logits_override is None else logits_override.float()
+        if logits_value is not None:
+            # parity "on identical fp32 logits" (A.11): take the VALUES from the kernel, keep this graph for autograd
+            lg = lg + (logits_value.float() - lg).detach()
         p, idx, g = route(lg, k, self.normalize_topk)
         cap = capacity_override if capacity_override is not None else capacity_of(self.capacity_factor, T, k, E)
         pos, keep = assign_slots(idx, E, cap, global_offset)

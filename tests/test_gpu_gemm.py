@@ -1,0 +1,140 @@
+"""GPU parity: each tcgen05 grouped GEMM stage against a plain fp32 torch contraction of the same bf16 inputs.
+
+Tolerances: outputs are bf16 (rel 2^-8 per element) of fp32-accumulated sums, so rel-L2 <= 5e-3 against the fp32
+reference and max-abs <= a few bf16 ulps of the output scale; wgrad outputs are fp32 (rel-L2 <= 1e-4... bf16 inputs
+are exact, only the accumulation order differs).
+"""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import b200moe
+    b200moe.load_library()
+    return b200moe.ops
+
+
+def _layout(E, rows_per_expert, seed=0):
+    """Hand-built plan: expert e owns rows_per_expert[e] rows, segments padded to 128."""
+    offs = [0]
+    for n in rows_per_expert:
+        offs.append(offs[-1] + (n + 127) // 128 * 128)
+    R = offs[-1]
+    rows_cap = R + 256                                       # spare tiles beyond R must be skipped
+    meta = torch.zeros(8, dtype=torch.int32)
+    meta[0], meta[1] = R, R // 128
+    tile_expert = torch.full((rows_cap // 128,), -1, dtype=torch.int32)
+    valid = torch.zeros(rows_cap, dtype=torch.bool)
+    row_expert = torch.zeros(rows_cap, dtype=torch.long)
+    for e, n in enumerate(rows_per_expert):
+        tile_expert[offs[e] // 128: offs[e + 1] // 128] = e
+        valid[offs[e]: offs[e] + n] = True
+        row_expert[offs[e]: offs[e + 1]] = e
+    return torch.tensor(offs, dtype=torch.int32), meta, tile_expert, valid, row_expert, R, rows_cap
+
+
+def _rel(a, b):
+    return float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))
+
+
+CASES = [
+    (8, 256, 1024, [800, 790, 1, 0, 128, 129, 300, 555]),     # config A shape, ragged incl. an empty expert
+    (4, 128, 256, [5, 200, 0, 130]),                          # smallest tile-able shape
+    (16, 512, 2048, [400] * 16),                              # config C shape
+    (2, 1024, 4096, [3000, 2500]),                            # config D shape, BN=256 path
+]
+
+
+@pytest.mark.parametrize("E,d,F,rows", CASES)
+def test_ffn_forward_stages(ops, E, d, F, rows):
+    g = torch.Generator().manual_seed(E * 1000 + d)
+    offs, meta, te, valid, rexp, R, rows_cap = _layout(E, rows)
+    xp = torch.randn(rows_cap, d, generator=g).to(torch.bfloat16)
+    xp[~valid] = 0
+    w1 = (torch.randn(E, F, d, generator=g) * d ** -0.5).to(torch.bfloat16)
+    b1 = torch.randn(E, F, generator=g) * 0.1
+    w2 = (torch.randn(E, d, F, generator=g) * F ** -0.5).to(torch.bfloat16)
+    b2 = torch.randn(E, d, generator=g) * 0.1
+    dev = "cuda"
+    pre, h = ops.ffn_up(xp.to(dev), w1.to(dev), b1.to(dev), meta.to(dev), te.to(dev))
+    yo = ops.ffn_down(h, w2.to(dev), b2.to(dev), meta.to(dev), te.to(dev))
+    torch.cuda.synchronize()
+    pre, h, yo = pre.cpu()[:R], h.cpu()[:R], yo.cpu()[:R]
+    for e in range(E):
+        sl = slice(int(offs[e]), int(offs[e + 1]))
+        if sl.stop == sl.start:
+            continue
+        pre_ref = xp[sl].float() @ w1[e].float().t() + b1[e]
+        assert _rel(pre[sl], pre_ref) < 5e-3, f"pre expert {e}"
+        h_ref = torch.nn.functional.gelu(pre_ref)
+        assert _rel(h[sl], h_ref) < 6e-3, f"h expert {e}"
+        yo_ref = h[sl].float() @ w2[e].float().t() + b2[e]          # from the kernel's own bf16 h
+        assert _rel(yo[sl], yo_ref) < 5e-3, f"yo expert {e}"
+        assert float((yo[sl].float() - yo_ref).abs().max()) < 0.05 * float(yo_ref.abs().max())
+
+
+@pytest.mark.parametrize("E,d,F,rows", CASES)
+def test_ffn_backward_stages(ops, E, d, F, rows):
+    g = torch.Generator().manual_seed(E * 1000 + d + 1)
+    offs, meta, te, valid, rexp, R, rows_cap = _layout(E, rows)
+    dev = "cuda"
+    dyp = torch.randn(rows_cap, d, generator=g).to(torch.bfloat16)
+    dyp[~valid] = 0
+    pre = torch.randn(rows_cap, F, generator=g).to(torch.bfloat16)
+    h = torch.randn(rows_cap, F, generator=g).to(torch.bfloat16)
+    xp = torch.randn(rows_cap, d, generator=g).to(torch.bfloat16)
+    xp[~valid] = 0
+    w1 = (torch.randn(E, F, d, generator=g) * d ** -0.5).to(torch.bfloat16)
+    w2 = (torch.randn(E, d, F, generator=g) * F ** -0.5).to(torch.bfloat16)
+    md, ted, od = meta.to(dev), te.to(dev), offs.to(dev)
+
+    dhpre = ops.ffn_dgrad_down(dyp.to(dev), w2.to(dev), pre.to(dev), md, ted)
+    dxp = ops.ffn_dgrad_up(dhpre, w1.to(dev), md, ted)
+    dw2 = ops.ffn_wgrad(dyp.to(dev), h.to(dev), od, E)
+    dw1 = ops.ffn_wgrad(dhpre, xp.to(dev), od, E)
+    db2 = ops.colsum(dyp.to(dev), od, E)
+    db1 = ops.colsum(dhpre, od, E)
+    torch.cuda.synchronize()
+    dhpre_c, dxp_c = dhpre.cpu(), dxp.cpu()
+    for e in range(E):
+        sl = slice(int(offs[e]), int(offs[e + 1]))
+        if sl.stop == sl.start:
+            assert float(dw2[e].abs().max()) == 0.0 and float(dw1[e].abs().max()) == 0.0
+            assert float(db2[e].abs().max()) == 0.0
+            continue
+        pf = pre[sl].float().requires_grad_(True)
+        torch.nn.functional.gelu(pf).backward(dyp[sl].float() @ w2[e].float())
+        assert _rel(dhpre_c[sl], pf.grad) < 6e-3, f"dhpre expert {e}"
+        dxp_ref = dhpre_c[sl].float() @ w1[e].float()
+        assert _rel(dxp_c[sl], dxp_ref) < 5e-3, f"dxp expert {e}"
+        dw2_ref = dyp[sl].float().t() @ h[sl].float()
+        assert _rel(dw2[e].cpu(), dw2_ref) < 1e-4, f"dw2 expert {e}"
+        dw1_ref = dhpre_c[sl].float().t() @ xp[sl].float()
+        assert _rel(dw1[e].cpu(), dw1_ref) < 1e-4, f"dw1 expert {e}"
+        assert torch.allclose(db2[e].cpu(), dyp[sl].float().sum(0), atol=1e-2, rtol=1e-3)
+        assert torch.allclose(db1[e].cpu(), dhpre_c[sl].float().sum(0), atol=1e-2, rtol=1e-3)
+
+
+def test_wgrad_accumulate(ops):
+    E, M, N = 2, 128, 256
+    offs, meta, te, valid, rexp, R, rows_cap = _layout(E, [100, 260])
+    g = torch.Generator().manual_seed(9)
+    a = torch.randn(rows_cap, M, generator=g).to(torch.bfloat16)
+    b = torch.randn(rows_cap, N, generator=g).to(torch.bfloat16)
+    a[~valid] = 0
+    od = offs.cuda()
+    out = ops.ffn_wgrad(a.cuda(), b.cuda(), od, E)
+    out2 = ops.ffn_wgrad(a.cuda(), b.cuda(), od, E, out=out.clone(), accumulate=True)
+    assert torch.allclose(out2, 2 * out, rtol=1e-6, atol=1e-6)
+
+
+def test_bad_shapes_fail_loudly(ops):
+    offs, meta, te, valid, rexp, R, rows_cap = _layout(2, [10, 10])
+    xp = torch.zeros(rows_cap, 96, dtype=torch.bfloat16, device="cuda")
+    w1 = torch.zeros(2, 256, 96, dtype=torch.bfloat16, device="cuda")
+    b1 = torch.zeros(2, 256, device="cuda")
+    with pytest.raises(RuntimeError, match="multiple of 128"):
+        ops.ffn_up(xp, w1, b1, meta.cuda(), te.cuda())
