@@ -128,3 +128,264 @@ def run_reference(args, w):
         t0 = time.perf_counter(); step(); ts.append(time.perf_counter() - t0)
     ms = 1e3 * sum(ts) / len(ts)
     return T / (ms * 1e-3), ms, torch.get_num_threads(), f"{sample_B}x{w['HW']} tokens of the workload, fp32, fwd+bwd"
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------------
+GEMM_CALLS = ("b200moe_ffn_up", "b200moe_ffn_down", "b200moe_ffn_dgrad_down", "b200moe_ffn_dgrad_up",
+              "b200moe_ffn_wgrad")
+
+
+def build_layer(w, device, ep_group=None):
+    import b200moe
+    torch.manual_seed(0)
+    m = b200moe.ContextMoE(w["d"], w["F"], w["E"], w["k"], w["cf"], context_vocab_sizes=CONTEXT_VOCAB,
+                           ep_group=ep_group)
+    return m.to(device)
+
+
+class L2Flusher:
+    """Writes a buffer larger than the 126 MB L2 between timed steps (outside the timed region)."""
+
+    def __init__(self, device, mb=256):
+        self.buf = torch.empty(mb * 1024 * 1024 // 4, dtype=torch.float32, device=device)
+
+    def __call__(self):
+        self.buf.fill_(1.0)
+
+
+def time_steps(step_fn, steps, warmup, flush, dist_on):
+    """K individually event-bracketed steps (L2 flushed in between); returns per-step ms list (this rank)."""
+    import torch.distributed as dist
+    for _ in range(warmup):
+        flush(); step_fn()
+    if dist_on:
+        dist.barrier()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(steps):
+        flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); step_fn(); b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    if dist_on:
+        dist.barrier()
+    return [a.elapsed_time(b) for a, b in evs]
+
+
+def measure_layer(w, steps, warmup, device, ep_group=None, dist_on=False, want_e2e=True, want_roofline=True,
+                  use_graph=True):
+    from b200moe import _lib
+    m = build_layer(w, device, ep_group)
+    x_h, go_h, ctx_h = make_inputs(w, seed=1234 + (torch.distributed.get_rank() if dist_on else 0))
+    x, go, ctx = x_h.to(device), go_h.to(device), ctx_h.to(device)
+    T = w["B"] * w["HW"]
+    flush = L2Flusher(device)
+    xg = x.clone().requires_grad_(True)
+
+    def step():
+        m._wcache.clear()                     # weights change every training step: re-cast fp32 -> bf16 each step
+        m.zero_grad(set_to_none=True)
+        xg.grad = None
+        y = m(xg, ctx)
+        torch.autograd.backward([y, m.aux_loss], [go, torch.ones_like(m.aux_loss)])
+
+    # (1) eager: every kernel launched from Python through the C ABI (host launch latency included)
+    _lib.Counters.reset()
+    ms_eager = time_steps(step, steps, warmup, flush, dist_on)
+    launches = _lib.Counters.launches // (steps + warmup)
+    res = {"ms_eager": ms_eager, "T": T, "launches_per_step": launches,
+           "kept": int(m.last_aux["meta"][3]), "dropped": int(m.last_aux["meta"][2])}
+
+    # (2) the same step captured once into a CUDA graph and replayed (no host sync anywhere in the layer)
+    res["ms"] = ms_eager
+    res["graph"] = False
+    if not dist_on and use_graph:
+        try:
+            graph = torch.cuda.CUDAGraph()
+            m.zero_grad(set_to_none=True)
+            xg.grad = None
+            m.aux_loss, m.last_aux = None, {}        # drop the eager autograd graph (its AccumulateGrad nodes
+            side = torch.cuda.Stream()               # belong to the default stream) and warm up on a side stream
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    step()
+                m.zero_grad(set_to_none=True)
+                xg.grad = None
+                m.aux_loss, m.last_aux = None, {}
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            with torch.cuda.graph(graph):
+                step()
+            torch.cuda.synchronize()
+            res["ms"] = time_steps(graph.replay, steps, warmup, flush, dist_on)
+            res["graph"] = True
+            del graph
+        except Exception as ex:  # noqa: BLE001
+            res["graph_error"] = repr(ex)
+
+    if want_roofline:
+        # (3) instrumented eager pass: every C-ABI call bracketed by CUDA events on the launching stream; a ~3 ms
+        # device-side sleep ahead of each step lets the host queue the whole step first, so durations are GPU time
+        torch.cuda.synchronize()
+        _lib.Counters.reset(timing=True)
+        for _ in range(steps):
+            torch.cuda._sleep(6_000_000)
+            flush(); step()
+        torch.cuda.synchronize()
+        dur = _lib.Counters.durations_ms()
+        _lib.Counters.reset()
+        per_step = {k_: sum(v) / steps for k_, v in dur.items()}
+        res["per_call_ms"] = {k_.replace("b200moe_", ""): round(v, 5) for k_, v in sorted(per_step.items())}
+        res["gemm_ms"] = sum(per_step.get(n, 0.0) for n in GEMM_CALLS)
+        res["gemm_launches"] = sum(len(dur.get(n, [])) for n in GEMM_CALLS) // steps
+
+    if want_e2e:
+        xp_h, ctxp_h = x_h.pin_memory(), ctx_h.pin_memory()
+
+        def e2e_step():
+            m.zero_grad(set_to_none=True)
+            xd = xp_h.to(device, non_blocking=True).requires_grad_(True)
+            cd = ctxp_h.to(device, non_blocking=True)
+            y = m(xd, cd)
+            loss = (y.float() * go).sum() + m.aux_loss
+            loss.backward()
+            return float(loss.item())                       # device -> host read of the step's result
+
+        for _ in range(warmup):
+            e2e_step()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            e2e_step()
+        b.record()
+        torch.cuda.synchronize()
+        res["e2e_ms"] = a.elapsed_time(b) / steps
+        res["h2d"] = x_h.numel() * 2 + ctx_h.numel() * 8
+        res["d2h"] = 4
+    return res
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, choices=[None, "A", "C", "D"])
+    ap.add_argument("--no-sweep", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    wl_name = args.workload or ("A" if world == 1 else "D")
+    w = WORKLOADS[wl_name]
+    pk = peaks()
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        steps, warmup = min(args.steps, 20), min(args.warmup, 5)
+        args.steps, args.warmup = max(steps, 1), warmup
+        v, ms, cores, sample = run_reference(args, w)
+        line = {"impl": "reference", "metric": "moe_layer_fwd_bwd_tokens_per_s", "value": v, "unit": "tokens/s",
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": {"workload": w["name"]},
+                "cpu_baseline": {"value": v, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample},
+                "e2e": {"value": v, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a B200; there is no CPU fallback (use --impl reference)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    dist_on = world > 1
+    ep_group = None
+    if dist_on:
+        dist.init_process_group("nccl", device_id=device)
+        ep_group = dist.group.WORLD
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    res = measure_layer(w, args.steps, args.warmup, device, ep_group, dist_on)
+    clocks = sampler.stop() if sampler else None
+
+    # max over ranks of the per-step device times
+    ms_t = torch.tensor(res["ms"], device=device)
+    e2e_t = torch.tensor([res.get("e2e_ms", 0.0)], device=device)
+    if dist_on:
+        dist.all_reduce(ms_t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    total_ms = float(ms_t.sum())
+    ms_per_step = total_ms / args.steps
+    T_all = res["T"] * world
+    value = T_all / (ms_per_step * 1e-3)
+
+    line = {"metric": "moe_layer_fwd_bwd_tokens_per_s", "value": value, "unit": "tokens/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": w["name"], "tokens_per_step": T_all, "l2": "flushed between steps (256 MB write)",
+                       "parallelism": "single GPU" if world == 1 else f"expert-parallel ep{world}",
+                       "kept_assignments": res["kept"], "dropped_assignments": res["dropped"]},
+            "gpu_launches": res["launches_per_step"] * args.steps,
+            "gpu_launches_per_step": res["launches_per_step"], "clocks": clocks,
+            "cuda_graph": res["graph"],
+            "eager_ms_per_step": sum(res["ms_eager"]) / len(res["ms_eager"])}
+    if "graph_error" in res:
+        line["graph_error"] = res["graph_error"]
+    if "e2e_ms" in res:
+        line["e2e"] = {"value": T_all / (float(e2e_t[0]) * 1e-3), "unit": "tokens/s",
+                       "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"]}
+    if "gemm_ms" in res and res["gemm_ms"] > 0:
+        fl = flops_per_step(w, res["kept"]) if world == 1 else None
+        if fl is not None:
+            ach = fl / (res["gemm_ms"] * 1e-3) / 1e12
+            peak = pk["tf_burst"] if ms_per_step < 1.0 else pk["tf_sust"]
+            line["roofline"] = {"bound": "tensor", "kernel": "grouped_gemm_kernel (6 launches: up, down, 2 dgrad, 2 wgrad)",
+                                "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                                "peak_source": pk["src"] + (" burst" if ms_per_step < 1.0 else " sustained"),
+                                "flops_per_step": fl, "gemm_ms_per_step": res["gemm_ms"], "traffic": None}
+        line["per_call_ms"] = res["per_call_ms"]
+
+    if rank == 0 and world == 1:
+        # CPU baseline: the oracle on this box's host cores, bounded sample
+        ra = argparse.Namespace(steps=5, warmup=2)
+        v, ms, cores, sample = run_reference(ra, w)
+        line["cpu_baseline"] = {"value": v, "unit": "tokens/s", "cores": cores, "kind": "port", "sample": sample,
+                                "ms_per_step": ms}
+        if not args.no_sweep:
+            sweep = []
+            for name, B, HW in (("A", 8, 400), ("A", 164, 400), ("C", 16, 920), ("C", 71, 923), ("D", 16, 1024)):
+                ww = dict(WORKLOADS[name], B=B, HW=HW)
+                try:
+                    r = measure_layer(ww, min(args.steps, 10), 3, device, want_e2e=False)
+                    mean_ms = sum(r["ms"]) / len(r["ms"])
+                    fl = flops_per_step(ww, r["kept"])
+                    pkk = pk["tf_burst"] if mean_ms < 1.0 else pk["tf_sust"]
+                    sweep.append({"workload": name, "tokens": B * HW, "ms_per_step": mean_ms, "cuda_graph": r["graph"],
+                                  "tokens_per_s": B * HW / (mean_ms * 1e-3), "gemm_ms": r["gemm_ms"],
+                                  "gemm_tflops": fl / (r["gemm_ms"] * 1e-3) / 1e12,
+                                  "gemm_frac_of_peak": fl / (r["gemm_ms"] * 1e-3) / 1e12 / pkk,
+                                  "per_call_ms": r["per_call_ms"]})
+                except Exception as ex:  # noqa: BLE001
+                    sweep.append({"workload": name, "tokens": B * HW, "error": repr(ex)})
+                torch.cuda.empty_cache()
+            line["sweep"] = sweep
+    if rank == 0:
+        print(json.dumps(line))
+    if dist_on:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

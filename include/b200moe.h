@@ -32,7 +32,7 @@ extern "C" {
 #define B200MOE_ECUDA (-3)    /* CUDA runtime / driver error */
 
 #define B200MOE_ROW_PAD 128          /* expert segments of the permuted buffer are padded to this many rows */
-#define B200MOE_ROUTER_BLOCK 128     /* tokens per router block (granularity of the priority scan) */
+#define B200MOE_ROUTER_BLOCK 128     /* max tokens per router block (granularity of the priority scan) */
 #define B200MOE_META_INTS 8          /* meta[0]=R (padded rows in use) meta[1]=R/128 meta[2]=dropped meta[3]=kept */
 
 int b200moe_version(void);
@@ -42,7 +42,9 @@ int b200moe_check_device(void);
 
 /* Upper bound (multiple of 128) on rows of the permuted buffer: min(T*k, E*capacity) + E*127, rounded up. */
 int b200moe_rows_upper_bound(int T, int k, int E, int capacity);
-/* ceil(T / B200MOE_ROUTER_BLOCK): first dimension of block_counts / block_stats. */
+/* Tokens per router block for a batch of T tokens (32, 64 or 128) and the resulting block count
+ * ceil(T / block): first dimension of block_counts / block_stats. */
+int b200moe_router_block(int T);
 int b200moe_num_router_blocks(int T);
 
 /* fp32 master weights -> bf16 operands (autocast step that torch does before hybrid_encoder.py:157). */
@@ -116,7 +118,7 @@ int b200moe_ffn_dgrad_up(const void* dhpre, const void* w1, const int32_t* meta,
 int b200moe_ffn_wgrad(const void* a, const void* b, const int32_t* expert_offsets, int rows_cap,
                       int M, int N, int E, float* dw, int accumulate, void* stream);
 int b200moe_colsum(const void* a, const int32_t* expert_offsets, int rows_cap, int ncols, int E,
-                   float* db, int accumulate, void* stream);
+                   float* scratch /* rows_cap/128 * ncols floats */, float* db, int accumulate, void* stream);
 
 /* A.12 router gradient.  dlogits from the gate gradient (softmax + renormalisation Jacobian on the selected k),
  * the load-balance term through P_e and the z-loss through lse.  d_aux is the upstream gradient of the weighted

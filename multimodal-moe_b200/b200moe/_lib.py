@@ -18,6 +18,7 @@ SIGNATURES = {
     "b200moe_last_error": [],
     "b200moe_check_device": [],
     "b200moe_rows_upper_bound": [_I, _I, _I, _I],
+    "b200moe_router_block": [_I],
     "b200moe_num_router_blocks": [_I],
     "b200moe_cast_f32_bf16": [_P, _P, _L, _P],
     "b200moe_router_fwd": [_P, _P, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],
@@ -30,7 +31,7 @@ SIGNATURES = {
     "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
     "b200moe_ffn_dgrad_up": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
     "b200moe_ffn_wgrad": [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
-    "b200moe_colsum": [_P, _P, _I, _I, _I, _P, _I, _P],
+    "b200moe_colsum": [_P, _P, _I, _I, _I, _P, _P, _I, _P],
     "b200moe_router_bwd_dlogits": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _P, _P],
     "b200moe_dwg_scratch_floats": [_I, _I, _I],
     "b200moe_router_bwd_dwg": [_P, _P, _I, _I, _I, _P, _P, _P],
@@ -78,7 +79,7 @@ def stream_ptr() -> int:
 KERNELS_PER_CALL = {
     "b200moe_cast_f32_bf16": 1, "b200moe_router_fwd": 1, "b200moe_plan": 2, "b200moe_permute": 1,
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
-    "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
+    "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 2,
     "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,
     "b200moe_unpermute_bwd": 1, "b200moe_ep_recv_plan": 1, "b200moe_scatter_rows": 1,
 }

@@ -56,7 +56,7 @@ def router_fwd(x: torch.Tensor, wg: torch.Tensor, ctx_bias: Optional[torch.Tenso
     T, d = x.shape
     E = wg.shape[0]
     dev = x.device
-    nblk = (T + ROUTER_BLOCK - 1) // ROUTER_BLOCK
+    nblk = _lib.load().b200moe_num_router_blocks(T)
     r = Routing(_empty((T, E), torch.float32, dev), _empty((T, k), torch.int32, dev),
                 _empty((T, k), torch.float32, dev), _empty((nblk, k, E), torch.int32, dev),
                 _empty((nblk, E + 1), torch.float32, dev))
@@ -184,7 +184,9 @@ def colsum(a, expert_offsets, E: int, out: Optional[torch.Tensor] = None, accumu
     if out is None:
         out = _empty((E, n), torch.float32, a.device)
         accumulate = False
-    call("b200moe_colsum", ptr(a), ptr(expert_offsets), rows_cap, n, E, ptr(out), int(accumulate), stream_ptr())
+    scratch = _empty((rows_cap // ROW_PAD, n), torch.float32, a.device)
+    call("b200moe_colsum", ptr(a), ptr(expert_offsets), rows_cap, n, E, ptr(scratch), ptr(out), int(accumulate),
+         stream_ptr())
     return out
 
 

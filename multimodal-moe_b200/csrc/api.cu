@@ -58,8 +58,11 @@ int b200moe_rows_upper_bound(int T, int k, int E, int capacity) {
   return static_cast<int>(rows);
 }
 
+int b200moe_router_block(int T) { return b200moe::router_block_tokens(T); }
+
 int b200moe_num_router_blocks(int T) {
-  return T <= 0 ? 0 : (T + B200MOE_ROUTER_BLOCK - 1) / B200MOE_ROUTER_BLOCK;
+  const int tb = b200moe::router_block_tokens(T);
+  return T <= 0 ? 0 : (T + tb - 1) / tb;
 }
 
 }  // extern "C"

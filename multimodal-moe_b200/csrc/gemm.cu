@@ -5,8 +5,8 @@
 //              weight slab): up-proj, down-proj (A and B K-major), dgrad-down, dgrad-up (B = weights read MN-major,
 //              i.e. W[e] is used as [K,N] without a transposed copy);
 //   wgrad mode (M,N = weight dims, K = rows of one expert): A and B are both activations read MN-major.
-// Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
-// warps 2..5 = epilogue (warp w owns TMEM lanes 32*(w%4)..+31 = output rows).  A kStages-deep smem ring
+// Roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
+// warps 2..9 = epilogue (warp w owns TMEM lanes 32*(w%4)..+31 = output rows and one half of the tile's columns).  A kStages-deep smem ring
 // (full/empty mbarriers) decouples TMA from MMA; two TMEM accumulator stages (tmem_full/tmem_empty) let the
 // epilogue of tile i overlap the main loop of tile i+1.
 //
@@ -22,8 +22,9 @@ enum : int { EPI_UP = 0, EPI_DOWN = 1, EPI_DGRAD_DOWN = 2, EPI_DGRAD_UP = 3, EPI
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kGemmThreads = 192;
-constexpr int kEpiThreads = 128;
+constexpr int kEpiWarps = 8;                         // two warps per TMEM lane quarter, each takes half the columns
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kGemmThreads = 64 + kEpiThreads;
 
 struct GemmArgs {
   const int32_t* meta;            // row mode: meta[1] = number of 128-row tiles in use
@@ -175,8 +176,9 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
   } else {
-    // ======================= epilogue (warps 2..5) =======================
+    // ======================= epilogue (warps 2..9) =======================
     const int quarter = warp & 3;              // TMEM lane quarter this warp may read
+    const int chalf = (warp - 2) >> 2;         // which half of the tile's columns
     const int row_in_tile = quarter * 32 + lane;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -188,7 +190,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
       const size_t grow = static_cast<size_t>(m_tile) * BM + row_in_tile;   // row of the output
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
         uint32_t v[32];
         tmem_ld32(taddr + c * 32, v);
         tmem_ld_wait();

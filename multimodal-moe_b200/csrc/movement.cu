@@ -166,23 +166,33 @@ cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ 
     for (int64_t i = n8 * 8 + threadIdx.x; i < n; i += blockDim.x) dst[i] = __float2bfloat16_rn(src[i]);
 }
 
-// db[e, c] = sum over rows of expert e of a[r, c].  Block = (column slab of 256, expert, row split); fixed order.
+// db[e, c] = sum over rows of expert e of a[r, c], in two fixed-order stages (deterministic, no atomics):
+//   stage 1: block = (256-column slab, 128-row tile) -> partial[tile][c]; a warp reads 512 contiguous bytes of a row
+//   stage 2: block = (256-column slab, expert)       -> sum of the expert's tiles
 __global__ void __launch_bounds__(256)
-colsum_kernel(const __nv_bfloat16* __restrict__ a, const int32_t* __restrict__ expert_offsets, int ncols,
-              float* __restrict__ db, int accumulate) {
+colsum_partial_kernel(const __nv_bfloat16* __restrict__ a, const int32_t* __restrict__ expert_offsets, int E,
+                      int ncols, float* __restrict__ partial) {
   __shared__ float part[8][256];
-  const int e = blockIdx.y;
-  const int r0 = expert_offsets[e], r1 = expert_offsets[e + 1];
-  // thread = (row phase 0..7, 8-column chunk 0..31): a warp reads 512 contiguous bytes of one row
+  const int R = expert_offsets[E];
+  const int r0 = blockIdx.y * kRowPad;
+  if (r0 >= R) return;
   const int chunk = threadIdx.x & 31, phase = threadIdx.x >> 5;
   const int col0 = blockIdx.x * 256 + chunk * 8;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (col0 < ncols) {
-    for (int r = r0 + phase; r < r1; r += 8) {
-      float v[8];
-      unpack8(ldg128(a + static_cast<size_t>(r) * ncols + col0), v);
+    uint4 raw[4];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] += v[j];
+    for (int it = 0; it < 4; ++it) {     // 16 rows per thread, 4 loads in flight
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        raw[u] = ldg128(a + static_cast<size_t>(r0 + phase + 8 * (it * 4 + u)) * ncols + col0);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float v[8];
+        unpack8(raw[u], v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += v[j];
+      }
     }
   }
 #pragma unroll
@@ -193,9 +203,21 @@ colsum_kernel(const __nv_bfloat16* __restrict__ a, const int32_t* __restrict__ e
     float s = 0.f;
 #pragma unroll
     for (int p = 0; p < 8; ++p) s += part[p][threadIdx.x];
-    float* o = db + static_cast<size_t>(e) * ncols + c;
-    *o = accumulate ? *o + s : s;
+    partial[static_cast<size_t>(blockIdx.y) * ncols + c] = s;
   }
+}
+
+__global__ void __launch_bounds__(256)
+colsum_reduce_kernel(const float* __restrict__ partial, const int32_t* __restrict__ expert_offsets, int ncols,
+                     float* __restrict__ db, int accumulate) {
+  const int e = blockIdx.y;
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= ncols) return;
+  const int t0 = expert_offsets[e] / kRowPad, t1 = expert_offsets[e + 1] / kRowPad;
+  float s = 0.f;
+  for (int t = t0; t < t1; ++t) s += partial[static_cast<size_t>(t) * ncols + c];
+  float* o = db + static_cast<size_t>(e) * ncols + c;
+  *o = accumulate ? *o + s : s;
 }
 
 static inline int move_grid(long long rows) {
@@ -271,11 +293,15 @@ extern "C" int b200moe_cast_f32_bf16(const float* src, void* dst, int64_t n, voi
 }
 
 extern "C" int b200moe_colsum(const void* a, const int32_t* expert_offsets, int rows_cap, int ncols, int E,
-                              float* db, int accumulate, void* stream) {
-  (void)rows_cap;
+                              float* scratch, float* db, int accumulate, void* stream) {
   B200MOE_REQUIRE(ncols > 0 && ncols % 8 == 0, B200MOE_EINVAL, "colsum: ncols=%d must be a multiple of 8", ncols);
+  B200MOE_REQUIRE(rows_cap > 0 && rows_cap % kRowPad == 0, B200MOE_EINVAL, "colsum: rows_cap must be a multiple of 128");
+  B200MOE_REQUIRE(scratch != nullptr, B200MOE_EINVAL, "colsum: scratch of rows_cap/128*ncols floats required");
   if (int rc = b200moe_check_device()) return rc;
-  dim3 grid((ncols + 255) / 256, E);
-  colsum_kernel<<<grid, 256, 0, ST(stream)>>>(BF(a), expert_offsets, ncols, db, accumulate);
-  return check_launch("colsum");
+  dim3 g1((ncols + 255) / 256, rows_cap / kRowPad);
+  colsum_partial_kernel<<<g1, 256, 0, ST(stream)>>>(BF(a), expert_offsets, E, ncols, scratch);
+  if (int rc = check_launch("colsum_partial")) return rc;
+  dim3 g2((ncols + 255) / 256, E);
+  colsum_reduce_kernel<<<g2, 256, 0, ST(stream)>>>(scratch, expert_offsets, ncols, db, accumulate);
+  return check_launch("colsum_reduce");
 }

@@ -19,7 +19,8 @@ plan_scan_kernel(int32_t* __restrict__ block_counts, const float* __restrict__ b
                  const int32_t* __restrict__ expert_order, int row_pad, int rows_cap, float aux_w, float z_w,
                  int32_t* __restrict__ expert_offsets, int32_t* __restrict__ meta, int32_t* __restrict__ tile_expert,
                  int32_t* __restrict__ tokens_per_expert, int32_t* __restrict__ kept_per_expert,
-                 float* __restrict__ losses, int32_t* __restrict__ slot_limit) {
+                 float* __restrict__ losses, int32_t* __restrict__ slot_limit, int32_t* __restrict__ token_of_row,
+                 float* __restrict__ gate_of_row, int init_rows) {
   __shared__ int total_s[8 * 64];      // [k][E] assignments per (slot, expert) on this rank
   __shared__ int rowbase_s[8 * 64];    // [k][E] first row (relative to the expert segment) of slot s
   __shared__ int keptslot_s[8 * 64];
@@ -27,6 +28,9 @@ plan_scan_kernel(int32_t* __restrict__ block_counts, const float* __restrict__ b
   __shared__ float P_s[65];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = kScanThreads / 32;
   const int kE = k * E;
+
+  // row maps start as "pad" (small buffers only; the host issues memsets for large ones)
+  for (int i = threadIdx.x; i < init_rows; i += blockDim.x) { token_of_row[i] = -1; gate_of_row[i] = 0.f; }
 
   // phase 1: exclusive scan over the router blocks for every (slot, expert) sequence
   for (int q = warp; q < kE; q += nwarps) {
@@ -144,7 +148,7 @@ plan_assign_kernel(const int32_t* __restrict__ topk_idx, const float* __restrict
                    float* __restrict__ gate_of_row) {
   __shared__ int wc[kRouterTokPerBlock / 32][64];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int t = blockIdx.x * kRouterTokPerBlock + threadIdx.x;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = t < T;
   for (int s = 0; s < k; ++s) {
     for (int i = threadIdx.x; i < (kRouterTokPerBlock / 32) * 64; i += blockDim.x) (&wc[0][0])[i] = 0;
@@ -187,15 +191,20 @@ extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int
   B200MOE_REQUIRE(rows_cap > 0 && rows_cap % kRowPad == 0, B200MOE_EINVAL, "plan: rows_cap must be a multiple of 128");
   if (int rc = b200moe_check_device()) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int nblk = (T + kRouterTokPerBlock - 1) / kRouterTokPerBlock;
-  cudaMemsetAsync(token_of_row, 0xFF, sizeof(int32_t) * static_cast<size_t>(rows_cap), st);
-  cudaMemsetAsync(gate_of_row, 0, sizeof(float) * static_cast<size_t>(rows_cap), st);
+  const int tb = router_block_tokens(T);
+  const int nblk = (T + tb - 1) / tb;
+  const bool init_in_kernel = rows_cap <= 16 * 1024;
+  if (!init_in_kernel) {
+    cudaMemsetAsync(token_of_row, 0xFF, sizeof(int32_t) * static_cast<size_t>(rows_cap), st);
+    cudaMemsetAsync(gate_of_row, 0, sizeof(float) * static_cast<size_t>(rows_cap), st);
+  }
   plan_scan_kernel<<<1, kScanThreads, 0, st>>>(block_counts, block_stats, nblk, T, k, E, capacity, global_offset,
                                                expert_order, row_pad, rows_cap, aux_loss_weight, z_loss_weight,
                                                expert_offsets, meta, tile_expert, tokens_per_expert,
-                                               kept_per_expert, losses, slot_limit);
+                                               kept_per_expert, losses, slot_limit, token_of_row, gate_of_row,
+                                               init_in_kernel ? rows_cap : 0);
   if (int rc = check_launch("plan_scan")) return rc;
-  plan_assign_kernel<<<nblk, kRouterTokPerBlock, 0, st>>>(topk_idx, topk_gate, block_counts, slot_limit, T, k, E,
+  plan_assign_kernel<<<nblk, tb, 0, st>>>(topk_idx, topk_gate, block_counts, slot_limit, T, k, E,
                                                           row_of_assignment, token_of_row, gate_of_row);
   return check_launch("plan_assign");
 }

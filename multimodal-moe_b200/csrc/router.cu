@@ -19,7 +19,7 @@ constexpr int kRouterThreads = kRouterWarps * 32;
 template <int EP, bool W_IN_SMEM>
 __global__ void __launch_bounds__(kRouterThreads)
 router_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ ctx_bias, int tokens_per_image,
-                  const float* __restrict__ wg, int T, int d, int E, int k, int normalize,
+                  const float* __restrict__ wg, int T, int d, int E, int k, int normalize, int tb,
                   float* __restrict__ logits_out, int32_t* __restrict__ topk_idx, float* __restrict__ topk_gate,
                   int32_t* __restrict__ block_counts, float* __restrict__ block_stats) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -37,11 +37,11 @@ router_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__
   __syncthreads();
   const float* wsrc = W_IN_SMEM ? w_s : wg;
 
-  const int t0 = blockIdx.x * kRouterTokPerBlock;
+  const int t0 = blockIdx.x * tb;
   const int nchunk = d >> 3;  // 16-byte chunks per row
   float psum0 = 0.f, psum1 = 0.f, zsum = 0.f;  // lane e owns sum_t p[t,e] (and e+32)
 
-  for (int i = warp; i < kRouterTokPerBlock; i += kRouterWarps) {
+  for (int i = warp; i < tb; i += kRouterWarps) {
     const int t = t0 + i;
     if (t >= T) break;
     float acc[EP];
@@ -152,7 +152,8 @@ template <int EP>
 static int launch_router(const void* x, const float* ctx_bias, int tpi, const float* wg, int T, int d, int E, int k,
                          int normalize, float* logits, int32_t* idx, float* gate, int32_t* bc, float* bs,
                          cudaStream_t st) {
-  const int nblk = (T + kRouterTokPerBlock - 1) / kRouterTokPerBlock;
+  const int tb = router_block_tokens(T);
+  const int nblk = (T + tb - 1) / tb;
   const size_t tail = sizeof(float) * kRouterWarps * (EP + 1) + sizeof(int) * k * E;
   const size_t wbytes = sizeof(float) * static_cast<size_t>(E) * d;
   const bool in_smem = wbytes + tail <= 160 * 1024;
@@ -161,9 +162,9 @@ static int launch_router(const void* x, const float* ctx_bias, int tpi, const fl
   if (in_smem) {
     auto kern = router_fwd_kernel<EP, true>;
     if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-    kern<<<nblk, kRouterThreads, smem, st>>>(xb, ctx_bias, tpi, wg, T, d, E, k, normalize, logits, idx, gate, bc, bs);
+    kern<<<nblk, kRouterThreads, smem, st>>>(xb, ctx_bias, tpi, wg, T, d, E, k, normalize, tb, logits, idx, gate, bc, bs);
   } else {
-    router_fwd_kernel<EP, false><<<nblk, kRouterThreads, smem, st>>>(xb, ctx_bias, tpi, wg, T, d, E, k, normalize,
+    router_fwd_kernel<EP, false><<<nblk, kRouterThreads, smem, st>>>(xb, ctx_bias, tpi, wg, T, d, E, k, normalize, tb,
                                                                      logits, idx, gate, bc, bs);
   }
   return check_launch("router_fwd");

@@ -83,7 +83,7 @@ router_dlogits_kernel(const float* __restrict__ logits, const int32_t* __restric
 }
 
 // stage 1: block (token chunk c, column slab j) -> scratch[c][e][col] ; thread owns one column and E accumulators
-constexpr int kDwgTok = 256;  // tokens per chunk
+constexpr int kDwgTok = 64;   // minimum tokens per chunk
 template <int EP>
 __global__ void __launch_bounds__(256)
 router_dwg_partial_kernel(const float* __restrict__ dlogits, const __nv_bfloat16* __restrict__ x, int T, int d, int E,
@@ -140,7 +140,7 @@ router_dctx_kernel(const float* __restrict__ dlogits, int T, int E, int tpi, flo
 
 static int dwg_chunks(int T) {
   int chunks = (T + kDwgTok - 1) / kDwgTok;
-  const int cap = kNumSMs * 2;
+  const int cap = kNumSMs * 4;
   if (chunks > cap) chunks = cap;
   return chunks < 1 ? 1 : chunks;
 }

@@ -42,10 +42,13 @@ def test_router_matches_oracle(ops, T, d, E, k):
     assert torch.equal(r.topk_idx.cpu().long(), idx)       # bit-exact expert choice and slot order
     assert torch.allclose(r.topk_gate.cpu(), g, atol=1e-6, rtol=1e-5)
     # per-block counts and statistics
-    nblk = (T + 127) // 128
+    import b200moe
+    tb = b200moe.load_library().b200moe_router_block(T)
+    nblk = (T + tb - 1) // tb
     bc = r.block_counts.cpu()
+    assert bc.shape[0] == nblk
     for b in (0, nblk - 1):
-        sl = idx[b * 128:(b + 1) * 128]
+        sl = idx[b * tb:(b + 1) * tb]
         for s in range(k):
             assert torch.equal(bc[b, s].long(), torch.bincount(sl[:, s], minlength=E))
     ps = r.block_stats.cpu()
@@ -67,7 +70,8 @@ def test_router_all_ties_pick_lowest_index(ops):
 
 
 @pytest.mark.parametrize("T,E,k,cf", [(3200, 8, 2, None), (3200, 8, 2, 1.25), (1000, 16, 2, 0.5), (777, 64, 2, 1.0),
-                                      (130, 4, 1, 0.25), (5000, 8, 3, 1.25), (128, 8, 2, 1.25), (1, 8, 2, None)])
+                                      (130, 4, 1, 0.25), (5000, 8, 3, 1.25), (128, 8, 2, 1.25), (1, 8, 2, None),
+                                      (40000, 8, 2, 1.25), (20000, 16, 2, 1.0)])
 def test_plan_matches_oracle(ops, T, E, k, cf):
     d = 256
     x, wg = _mk(T, d, E, seed=7 + T)
