@@ -6,7 +6,9 @@
 //              i.e. W[e] is used as [K,N] without a transposed copy);
 //   wgrad mode (M,N = weight dims, K = rows of one expert): A and B are both activations read MN-major.
 // Roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (one elected lane),
-// warps 2..9 = epilogue (warp w owns TMEM lanes 32*(w%4)..+31 = output rows and one half of the tile's columns).  A kStages-deep smem ring
+// warps 2..9 = epilogue (warp w owns TMEM lanes 32*(w%4)..+31 = output rows and one half of the tile's columns;
+// results leave through swizzled smem boxes and TMA stores, fp32 weight gradients optionally as TMA reduce-add).
+// A kStages-deep smem ring
 // (full/empty mbarriers) decouples TMA from MMA; two TMEM accumulator stages (tmem_full/tmem_empty) let the
 // epilogue of tile i overlap the main loop of tile i+1.
 //
@@ -48,13 +50,15 @@ struct SmemCfg {
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kOutBytes = kEpiWarps * 4096;                       // epilogue staging for the TMA stores
   static constexpr int kBarBytes = 256;
-  static constexpr int kTotal = kStages * kStageBytes + kBarBytes + 1024;  // + alignment slack
+  static constexpr int kTotal = kStages * kStageBytes + kOutBytes + kBarBytes + 1024;  // + alignment slack
 };
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC0, const __grid_constant__ CUtensorMap tmC1,
                     const GemmArgs args) {
   using Cfg = SmemCfg<BN>;
   constexpr int kStages = Cfg::kStages;
@@ -64,7 +68,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  unsigned char* stage_out = smem + kStages * Cfg::kStageBytes;            // 8 warps x 4 KB epilogue staging
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + Cfg::kOutBytes);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tfull_bar = empty_bar + kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -75,6 +80,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC0);
+    if (EPI == EPI_UP) tma_prefetch_desc(&tmC1);
     for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], kEpiThreads); }
     fence_mbar_init();
@@ -177,57 +184,85 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else {
     // ======================= epilogue (warps 2..9) =======================
+    // TMEM -> registers -> (bias / GELU / GELU') -> swizzled smem box -> TMA store.  Each warp owns 32 output rows
+    // and a private 4 KB staging area, so no cross-warp synchronisation is needed: lane 0 issues the bulk stores
+    // and is the one that waits for them to have read the staging area before it is overwritten.
     const int quarter = warp & 3;              // TMEM lane quarter this warp may read
     const int chalf = (warp - 2) >> 2;         // which half of the tile's columns
-    const int row_in_tile = quarter * 32 + lane;
+    unsigned char* stg = stage_out + (warp - 2) * 4096;
     int acc = 0;
     uint32_t acc_phase = 0;
+    uint32_t nstore = 0;                       // boxes issued by this warp (alternates the two 2 KB halves)
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       int e, m_tile, n_tile, krow0, kblocks;
       decode(tile, e, m_tile, n_tile, krow0, kblocks);
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
-      const size_t grow = static_cast<size_t>(m_tile) * BM + row_in_tile;   // row of the output
+      const int row0 = m_tile * BM + quarter * 32;                 // first of this warp's 32 output rows
+      const size_t grow = static_cast<size_t>(row0) + lane;        // this thread's output row
 #pragma unroll 1
       for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
+        const int col0 = n_tile * BN + c * 32;
         uint32_t v[32];
         tmem_ld32(taddr + c * 32, v);
-        tmem_ld_wait();
-        const int col0 = n_tile * BN + c * 32;
-        if (EPI == EPI_WGRAD) {
-          float* o = args.outf + (static_cast<size_t>(e) * args.M + grow) * args.N + col0;
+        uint4 pr[4];
+        if (EPI == EPI_DGRAD_DOWN) {           // pre-activation row chunk (64 contiguous bytes), overlaps the TMEM load
+          const __nv_bfloat16* ap = args.aux + grow * args.N + col0;
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            float4 r = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
-                                   __uint_as_float(v[j + 3]));
-            if (kblocks == 0) r = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (args.accumulate) {
-              const float4 p = *reinterpret_cast<const float4*>(o + j);
-              r.x += p.x; r.y += p.y; r.z += p.z; r.w += p.w;
-            }
-            *reinterpret_cast<float4*>(o + j) = r;
+          for (int j = 0; j < 4; ++j) pr[j] = __ldg(reinterpret_cast<const uint4*>(ap) + j);   // L1-allocating: the
+          // other half of the 128-byte line is this thread's next chunk
+        }
+        tmem_ld_wait();
+        if (EPI == EPI_WGRAD) {
+          // fp32 box [32 rows][32 cols] = 4 KB, 128-byte swizzle: 16-byte chunk j of row r sits at j ^ (r & 7)
+          if (lane == 0) tma_store_wait_read0();
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint4 q = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            if (kblocks == 0) q = make_uint4(0, 0, 0, 0);
+            *reinterpret_cast<uint4*>(stg + lane * 128 + ((j ^ (lane & 7)) << 4)) = q;
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            const int grow0 = e * args.M + row0;
+            if (args.accumulate) tma_reduce_add_2d(&tmC0, stg, col0, grow0);
+            else tma_store_2d(&tmC0, stg, col0, grow0);
+            tma_store_commit();
           }
         } else {
           float f[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
           if (EPI == EPI_UP || EPI == EPI_DOWN) {
-            const float* b = args.bias + static_cast<size_t>(e) * args.N + col0;
+            const float* bp = args.bias + static_cast<size_t>(e) * args.N + col0;
 #pragma unroll
             for (int j = 0; j < 32; j += 4) {
-              const float4 bv = __ldg(reinterpret_cast<const float4*>(b + j));
+              const float4 bv = __ldg(reinterpret_cast<const float4*>(bp + j));
               f[j] += bv.x; f[j + 1] += bv.y; f[j + 2] += bv.z; f[j + 3] += bv.w;
             }
           }
-          const size_t off = grow * args.N + col0;
+          // bf16 box [32 rows][32 cols] = 2 KB, 64-byte swizzle: 16-byte chunk j of row r sits at j ^ ((r >> 1) & 3)
+          const uint32_t swz = (lane >> 1) & 3;
+          unsigned char* box0;
+          unsigned char* box1 = nullptr;
+          if (EPI == EPI_UP) {                 // two outputs per chunk: both halves, wait for everything before reuse
+            if (lane == 0) tma_store_wait_read0();
+            box0 = stg; box1 = stg + 2048;
+          } else {                             // one output: alternate halves, one store may still be reading
+            if (lane == 0) tma_store_wait_read1();
+            box0 = stg + (nstore & 1) * 2048;
+          }
+          __syncwarp();
           if (EPI == EPI_UP && args.out1) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
+            for (int j = 0; j < 4; ++j) {
               uint4 pk;
-              pk.x = float2_to_bf16x2(f[j], f[j + 1]); pk.y = float2_to_bf16x2(f[j + 2], f[j + 3]);
-              pk.z = float2_to_bf16x2(f[j + 4], f[j + 5]); pk.w = float2_to_bf16x2(f[j + 6], f[j + 7]);
-              *reinterpret_cast<uint4*>(args.out1 + off + j) = pk;
+              pk.x = float2_to_bf16x2(f[8 * j], f[8 * j + 1]); pk.y = float2_to_bf16x2(f[8 * j + 2], f[8 * j + 3]);
+              pk.z = float2_to_bf16x2(f[8 * j + 4], f[8 * j + 5]); pk.w = float2_to_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+              *reinterpret_cast<uint4*>(box1 + lane * 64 + ((j ^ swz) << 4)) = pk;
             }
           }
           if (EPI == EPI_UP) {
@@ -236,28 +271,36 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           if (EPI == EPI_DGRAD_DOWN) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              const uint4 pr = *reinterpret_cast<const uint4*>(args.aux + off + j);
+            for (int j = 0; j < 4; ++j) {
               float2 t;
-              t = bf16x2_to_float2(pr.x); f[j] *= gelu_erf_grad(t.x); f[j + 1] *= gelu_erf_grad(t.y);
-              t = bf16x2_to_float2(pr.y); f[j + 2] *= gelu_erf_grad(t.x); f[j + 3] *= gelu_erf_grad(t.y);
-              t = bf16x2_to_float2(pr.z); f[j + 4] *= gelu_erf_grad(t.x); f[j + 5] *= gelu_erf_grad(t.y);
-              t = bf16x2_to_float2(pr.w); f[j + 6] *= gelu_erf_grad(t.x); f[j + 7] *= gelu_erf_grad(t.y);
+              t = bf16x2_to_float2(pr[j].x); f[8 * j] *= gelu_erf_grad(t.x); f[8 * j + 1] *= gelu_erf_grad(t.y);
+              t = bf16x2_to_float2(pr[j].y); f[8 * j + 2] *= gelu_erf_grad(t.x); f[8 * j + 3] *= gelu_erf_grad(t.y);
+              t = bf16x2_to_float2(pr[j].z); f[8 * j + 4] *= gelu_erf_grad(t.x); f[8 * j + 5] *= gelu_erf_grad(t.y);
+              t = bf16x2_to_float2(pr[j].w); f[8 * j + 6] *= gelu_erf_grad(t.x); f[8 * j + 7] *= gelu_erf_grad(t.y);
             }
           }
 #pragma unroll
-          for (int j = 0; j < 32; j += 8) {
+          for (int j = 0; j < 4; ++j) {
             uint4 pk;
-            pk.x = float2_to_bf16x2(f[j], f[j + 1]); pk.y = float2_to_bf16x2(f[j + 2], f[j + 3]);
-            pk.z = float2_to_bf16x2(f[j + 4], f[j + 5]); pk.w = float2_to_bf16x2(f[j + 6], f[j + 7]);
-            *reinterpret_cast<uint4*>(args.out0 + off + j) = pk;
+            pk.x = float2_to_bf16x2(f[8 * j], f[8 * j + 1]); pk.y = float2_to_bf16x2(f[8 * j + 2], f[8 * j + 3]);
+            pk.z = float2_to_bf16x2(f[8 * j + 4], f[8 * j + 5]); pk.w = float2_to_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+            *reinterpret_cast<uint4*>(box0 + lane * 64 + ((j ^ swz) << 4)) = pk;
           }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmC0, box0, col0, row0);
+            if (EPI == EPI_UP && args.out1) tma_store_2d(&tmC1, box1, col0, row0);
+            tma_store_commit();
+          }
+          ++nstore;
         }
       }
       tc_fence_before();
       mbar_arrive(&tempty_bar[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (lane == 0) tma_store_wait_all0();      // staging smem must outlive the bulk stores that read it
   }
 
   tc_fence_before();
