@@ -139,8 +139,9 @@ int b200moe_router_bwd_dctx(const float* dlogits, int T, int E, int tokens_per_i
 int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assignment, const float* dlogits,
                           const float* wg, int T, int k, int d, int E, void* dx, void* stream);
 
-/* Expert-parallel receive side: rows arrive grouped by (local expert, source rank); build the padded layout.
- *   recv_counts [n_seg] int32 rows per segment, seg_expert [n_seg] local expert of each segment (non-decreasing)
+/* Expert-parallel receive side: rows arrive as n_seg <= 1024 back-to-back segments (source rank major, local
+ * expert minor); build the 128-row-padded expert-major layout.
+ *   recv_counts [n_seg] int32 rows per segment, seg_expert [n_seg] local expert of each segment
  *   out: expert_offsets [E_local+1] (padded to 128), meta, tile_expert, src_of_row [rows_cap] (-1 = pad)      */
 int b200moe_ep_recv_plan(const int32_t* recv_counts, const int32_t* seg_expert, int n_seg, int E_local,
                          int rows_cap, int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert,

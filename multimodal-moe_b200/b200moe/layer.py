@@ -92,7 +92,8 @@ class _MoEFunction(torch.autograd.Function):
 
 class ContextMoE(nn.Module):
     """Context-gated top-k MoE FFN; parameters: gate.weight [E,d], ctx_embed.{i}.weight,
-    ctx_proj.weight [E, n_fields*context_dim], w1 [E,F,d], b1 [E,F], w2 [E,d,F], b2 [E,d]."""
+    ctx_proj.weight [E, n_fields*context_dim], w1 [E,F,d], b1 [E,F], w2 [E,d,F], b2 [E,d] (under expert parallelism
+    the four expert tensors hold this rank's E / world_size experts)."""
 
     def __init__(self, d_model: int, dim_feedforward: int, num_experts: int, top_k: int = 2,
                  capacity_factor: Optional[float] = 1.25, context_vocab_sizes: Sequence[int] = (),
@@ -115,12 +116,19 @@ class ContextMoE(nn.Module):
         self.context_vocab_sizes = tuple(context_vocab_sizes)
         self.context_dim = context_dim
         self.ep_group = ep_group
+        self.ep_size, self.ep_rank = 1, 0
+        if ep_group is not None:
+            import torch.distributed as dist
+            self.ep_size, self.ep_rank = dist.get_world_size(ep_group), dist.get_rank(ep_group)
+        if num_experts % self.ep_size:
+            raise ValueError("num_experts must be divisible by the expert-parallel world size")
+        self.num_local_experts = num_experts // self.ep_size   # experts [ep_rank*EL, (ep_rank+1)*EL) live here
 
-        E, Fh, d = num_experts, dim_feedforward, d_model
-        self.gate = nn.Linear(d, E, bias=False)
+        E, Fh, d = self.num_local_experts, dim_feedforward, d_model
+        self.gate = nn.Linear(d, num_experts, bias=False)
         self.ctx_embed = nn.ModuleList([nn.Embedding(v, context_dim) for v in self.context_vocab_sizes])
         nctx = len(self.context_vocab_sizes) * context_dim
-        self.ctx_proj = nn.Linear(nctx, E, bias=False) if nctx else None
+        self.ctx_proj = nn.Linear(nctx, num_experts, bias=False) if nctx else None
         self.w1 = nn.Parameter(torch.empty(E, Fh, d))
         self.b1 = nn.Parameter(torch.empty(E, Fh))
         self.w2 = nn.Parameter(torch.empty(E, d, Fh))
@@ -153,14 +161,20 @@ class ContextMoE(nn.Module):
 
     def reset_parameters(self):
         """A.6: every expert initialised like nn.Linear; gate N(0, d^-1/2); ctx_proj N(0, 0.02)."""
+        lo = self.ep_rank * self.num_local_experts
         with torch.no_grad():
+            # every rank draws all E experts in the same order and keeps its own slice, so a seed gives the same
+            # global model whatever the expert-parallel world size
             for e in range(self.num_experts):
-                nn.init.kaiming_uniform_(self.w1[e], a=math.sqrt(5))
-                nn.init.kaiming_uniform_(self.w2[e], a=math.sqrt(5))
-                b = 1.0 / math.sqrt(self.d_model)
-                self.b1[e].uniform_(-b, b)
-                b = 1.0 / math.sqrt(self.dim_feedforward)
-                self.b2[e].uniform_(-b, b)
+                w1 = nn.init.kaiming_uniform_(torch.empty(self.dim_feedforward, self.d_model), a=math.sqrt(5))
+                w2 = nn.init.kaiming_uniform_(torch.empty(self.d_model, self.dim_feedforward), a=math.sqrt(5))
+                b1 = torch.empty(self.dim_feedforward).uniform_(-1.0 / math.sqrt(self.d_model),
+                                                                1.0 / math.sqrt(self.d_model))
+                b2 = torch.empty(self.d_model).uniform_(-1.0 / math.sqrt(self.dim_feedforward),
+                                                        1.0 / math.sqrt(self.dim_feedforward))
+                if lo <= e < lo + self.num_local_experts:
+                    self.w1[e - lo].copy_(w1); self.w2[e - lo].copy_(w2)
+                    self.b1[e - lo].copy_(b1); self.b2[e - lo].copy_(b2)
             nn.init.normal_(self.gate.weight, std=self.d_model ** -0.5)
             if self.ctx_proj is not None:
                 nn.init.normal_(self.ctx_proj.weight, std=0.02)
@@ -205,7 +219,7 @@ class ContextMoE(nn.Module):
         tpi = T // B
         xb = x2.to(torch.bfloat16).contiguous()
         cb = self.context_bias(context)
-        if self.ep_group is not None and torch.distributed.get_world_size(self.ep_group) > 1:
+        if self.ep_size > 1:
             from .ep import ep_forward
             y, aux, stats = ep_forward(self, xb, cb, tpi)
         else:
