@@ -10,6 +10,11 @@ Data flow per forward (rank r, E_local = E / W experts [r*E_local, (r+1)*E_local
   -> permute into the send buffer -> all_to_all_single (uneven splits) -> ep_recv_plan + permute = 128-row-padded
   expert-major layout -> grouped GEMMs on the local experts -> scatter back to arrival order -> all_to_all_single
   -> combine on the token's home rank.  Backward mirrors it.
+
+Overlap: the local experts are cut into `ep_chunks` groups; the send buffer is laid out (group, destination rank,
+expert) so that every group has its own contiguous all-to-all.  The all-to-alls run on a side stream, the grouped
+GEMMs of group c wait only for group c's rows (CUDA events), so the transfer of group c+1 and the return of group
+c-1 overlap the GEMMs of group c.
 """
 from __future__ import annotations
 
@@ -41,22 +46,57 @@ def route_tables(hist_all: torch.Tensor, tokens_all: torch.Tensor, rank: int, ca
     return base[rank].to(torch.int32).contiguous(), capacity, kept
 
 
-def split_sizes(kept: torch.Tensor, rank: int, W: int) -> Tuple[List[int], List[int], torch.Tensor, torch.Tensor]:
-    """kept [W,E] (host).  Returns (send_splits[W], recv_splits[W], recv_counts [W*E_local], seg_expert)."""
+def chunk_layout(E: int, W: int, chunks: int):
+    """Expert order of the send buffer for `chunks` groups of local experts: position of global expert
+    e = w*EL + c*ELc + j is c*(W*ELc) + w*ELc + j.  Returns (C, ELc, order[E] int32)."""
+    EL = E // W
+    C = max(1, min(chunks, EL))
+    while EL % C:
+        C -= 1
+    ELc = EL // C
+    e = torch.arange(E)
+    w, c, j = e // EL, (e % EL) // ELc, e % ELc
+    return C, ELc, (c * (W * ELc) + w * ELc + j).to(torch.int32)
+
+
+def split_sizes(kept: torch.Tensor, rank: int, W: int, C: int = 1):
+    """kept [W,E] (host).  Per chunk c of local experts: rows sent to / received from every rank, and the receive
+    segments (source rank major, expert minor).  Returns lists over chunks:
+    (send_splits[c][W], recv_splits[c][W], recv_counts[c] int32 [W*ELc], seg_expert int32 [W*ELc])."""
     E = kept.shape[1]
     EL = E // W
-    send = kept[rank].view(W, EL).sum(1).tolist()           # rows this rank sends to each destination rank
-    mine = kept[:, rank * EL:(rank + 1) * EL]               # [W, EL] rows arriving from each source, per local expert
-    recv = mine.sum(1).tolist()
-    recv_counts = mine.reshape(-1).to(torch.int32)          # arrival order: source rank major, local expert minor
-    seg_expert = torch.arange(EL, dtype=torch.int32).repeat(W)
+    ELc = EL // C
+    out_view = kept[rank].view(W, C, ELc)                   # this rank -> (dest rank, chunk, expert)
+    in_view = kept[:, rank * EL:(rank + 1) * EL].reshape(W, C, ELc)   # (source rank, chunk, expert) -> this rank
+    send = [out_view[:, c].sum(-1).tolist() for c in range(C)]
+    recv = [in_view[:, c].sum(-1).tolist() for c in range(C)]
+    recv_counts = [in_view[:, c].reshape(-1).to(torch.int32).contiguous() for c in range(C)]
+    seg_expert = torch.arange(ELc, dtype=torch.int32).repeat(W)
     return send, recv, recv_counts, seg_expert
 
 
-def _a2a(buf: torch.Tensor, out_rows: int, in_splits: List[int], out_splits: List[int], group) -> torch.Tensor:
-    out = torch.empty((out_rows, buf.shape[1]), dtype=buf.dtype, device=buf.device)
+def _a2a_into(out: torch.Tensor, buf: torch.Tensor, in_splits: List[int], out_splits: List[int], group):
     dist.all_to_all_single(out, buf, output_split_sizes=out_splits, input_split_sizes=in_splits, group=group)
+
+
+def _comm_stream(mod, dev) -> torch.cuda.Stream:
+    s = mod.__dict__.get("_ep_comm_stream")
+    if s is None or s.device != dev:
+        s = torch.cuda.Stream(device=dev)
+        mod.__dict__["_ep_comm_stream"] = s
+    return s
+
+
+def _cumsum0(xs: List[int]) -> List[int]:
+    out = [0]
+    for v in xs:
+        out.append(out[-1] + v)
     return out
+
+
+class _Chunk:
+    """Receive-side state of one group of local experts."""
+    __slots__ = ("n_recv", "cap", "offs", "meta", "tile_e", "src", "xp", "pre", "h", "lo", "hi")
 
 
 class _EPFunction(torch.autograd.Function):
@@ -72,6 +112,7 @@ class _EPFunction(torch.autograd.Function):
         wgf = wg.float().contiguous()
         cb = ctx_bias.float().contiguous() if ctx_bias is not None else None
         dev = x2.device
+        comp, comm = torch.cuda.current_stream(), _comm_stream(mod, dev)
 
         r = ops.router_fwd(x2, wgf, cb, tokens_per_image, k, mod.normalize_topk)
         # histograms of every rank (+ token counts) in one small all-gather
@@ -82,32 +123,63 @@ class _EPFunction(torch.autograd.Function):
         hist_all, tokens_all = allh[:, :-1].reshape(W, k, E), allh[:, -1]
         goff, cap, kept = route_tables(hist_all, tokens_all, rank, mod.capacity_factor, k)
         kept_h = kept.cpu()                                  # the one host sync of the pass: all-to-all split sizes
-        send_splits, recv_splits, recv_counts, seg_expert = split_sizes(kept_h, rank, W)
-        n_send, n_recv = sum(send_splits), sum(recv_splits)
+        C, ELc, order = chunk_layout(E, W, getattr(mod, "ep_chunks", 2))
+        send_splits, recv_splits, recv_counts, seg_expert = split_sizes(kept_h, rank, W, C)
+        send_off = _cumsum0([sum(s_) for s_ in send_splits])
+        n_send = send_off[-1]
 
         send_cap = ops.rows_upper_bound(T, k, E, -1)
         p = ops.plan(r, T, k, E, cap, mod.aux_loss_weight, mod.z_loss_weight, global_offset=goff.to(dev),
-                     row_pad=1, rows_cap=send_cap)
+                     expert_order=order.to(dev), row_pad=1, rows_cap=send_cap)
         xs = ops.permute(x2, p.token_of_row, p.meta, send_cap)
-        xr = _a2a(xs[:n_send], n_recv, send_splits, recv_splits, group)
+        seg_dev = seg_expert.to(dev)
 
-        recv_cap = max(128, (n_recv + EL * 127 + 127) // 128 * 128)
-        offs, meta_r, tile_e, src_of_row = ops.ep_recv_plan(recv_counts.to(dev), seg_expert.to(dev), EL, recv_cap)
-        if n_recv == 0:
-            xr = torch.zeros((1, d), dtype=torch.bfloat16, device=dev)
-        xp = ops.permute(xr, src_of_row, meta_r, recv_cap)
-        pre, h = ops.ffn_up(xp, w1b, b1f, meta_r, tile_e, save_pre=need_grad)
-        yo = ops.ffn_down(h, w2b, b2f, meta_r, tile_e)
-        yr = ops.scatter_rows(yo, src_of_row, meta_r, max(n_recv, 1))
-        ys = _a2a(yr[:n_recv], n_send, recv_splits, send_splits, group)
-        yo_home = ys                                         # rows come back in this rank's send layout
-        y = ops.combine(yo_home, p.row_of_assignment, r.topk_gate)
+        # dispatch all groups on the communication stream
+        ready = torch.cuda.Event()
+        ready.record(comp)
+        comm.wait_event(ready)
+        chunks, arrived = [], []
+        with torch.cuda.stream(comm):
+            for c in range(C):
+                ch = _Chunk()
+                ch.n_recv = sum(recv_splits[c])
+                ch.lo, ch.hi = c * ELc, (c + 1) * ELc
+                xr = torch.empty((max(ch.n_recv, 1), d), dtype=torch.bfloat16, device=dev)
+                _a2a_into(xr[:ch.n_recv], xs[send_off[c]:send_off[c + 1]], send_splits[c], recv_splits[c], group)
+                ch.xp = xr                                    # replaced by the padded layout below
+                ev = torch.cuda.Event()
+                ev.record(comm)
+                chunks.append(ch)
+                arrived.append(ev)
+        # grouped GEMMs per group as its rows arrive; results go home on the communication stream
+        ys = torch.empty((max(n_send, 1), d), dtype=torch.bfloat16, device=dev)
+        for c, ch in enumerate(chunks):
+            comp.wait_event(arrived[c])
+            xr = ch.xp
+            xr.record_stream(comp)
+            ch.cap = max(128, (ch.n_recv + ELc * 127 + 127) // 128 * 128)
+            ch.offs, ch.meta, ch.tile_e, ch.src = ops.ep_recv_plan(recv_counts[c].to(dev), seg_dev, ELc, ch.cap)
+            ch.xp = ops.permute(xr, ch.src, ch.meta, ch.cap)
+            ch.pre, ch.h = ops.ffn_up(ch.xp, w1b[ch.lo:ch.hi], b1f[ch.lo:ch.hi], ch.meta, ch.tile_e,
+                                      save_pre=need_grad)
+            yo = ops.ffn_down(ch.h, w2b[ch.lo:ch.hi], b2f[ch.lo:ch.hi], ch.meta, ch.tile_e)
+            yr = ops.scatter_rows(yo, ch.src, ch.meta, max(ch.n_recv, 1))
+            done = torch.cuda.Event()
+            done.record(comp)
+            with torch.cuda.stream(comm):
+                comm.wait_event(done)
+                yr.record_stream(comm)
+                _a2a_into(ys[send_off[c]:send_off[c + 1]], yr[:ch.n_recv], recv_splits[c], send_splits[c], group)
+        home = torch.cuda.Event()
+        home.record(comm)
+        comp.wait_event(home)
+        y = ops.combine(ys, p.row_of_assignment, r.topk_gate)
 
         ctx.mod, ctx.tpi, ctx.plan, ctx.routing = mod, tokens_per_image, p, r
         ctx.has_ctx = ctx_bias is not None
         ctx.dtypes = (w1.dtype, b1.dtype, w2.dtype, b2.dtype, wg.dtype)
-        ctx.ep = (send_splits, recv_splits, n_send, n_recv, send_cap, recv_cap, offs, meta_r, tile_e, src_of_row)
-        ctx.save_for_backward(x2, wgf, w1b, w2b, xp, pre, h, yo_home)
+        ctx.ep = (send_splits, recv_splits, send_off, send_cap, chunks)
+        ctx.save_for_backward(x2, wgf, w1b, w2b, ys)
         aux = p.losses[0]
         stats = p.losses.detach()
         ctx.mark_non_differentiable(stats)
@@ -116,39 +188,76 @@ class _EPFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy, d_aux, _d_stats):
-        x2, wgf, w1b, w2b, xp, pre, h, yo_home = ctx.saved_tensors
+        x2, wgf, w1b, w2b, ys = ctx.saved_tensors
         mod, p, r = ctx.mod, ctx.plan, ctx.routing
         group = mod.ep_group
-        send_splits, recv_splits, n_send, n_recv, send_cap, recv_cap, offs, meta_r, tile_e, src_of_row = ctx.ep
+        send_splits, recv_splits, send_off, send_cap, chunks = ctx.ep
+        n_send = send_off[-1]
         T, d = x2.shape
-        k, EL = mod.top_k, mod.num_local_experts
+        k, EL, F = mod.top_k, mod.num_local_experts, mod.dim_feedforward
         need = ctx.needs_input_grad
         dev = x2.device
+        comp, comm = torch.cuda.current_stream(), _comm_stream(mod, dev)
         if dy is None:
             dy = torch.zeros_like(x2)
         dy = dy.contiguous().to(torch.bfloat16)
         d_aux_t = d_aux.float().contiguous() if d_aux is not None else None
 
-        dys, dgate_row = ops.combine_bwd(dy, yo_home, p.token_of_row, p.gate_of_row, p.meta, send_cap)
-        dyr = _a2a(dys[:n_send], n_recv, send_splits, recv_splits, group)
-        if n_recv == 0:
-            dyr = torch.zeros((1, d), dtype=torch.bfloat16, device=dev)
-        dyp = ops.permute(dyr, src_of_row, meta_r, recv_cap)
-        dhpre = ops.ffn_dgrad_down(dyp, w2b, pre, meta_r, tile_e)
-        dw2 = ops.ffn_wgrad(dyp, h, offs, EL) if need[5] else None
-        db2 = ops.colsum(dyp, offs, EL) if need[6] else None
-        dw1 = ops.ffn_wgrad(dhpre, xp, offs, EL) if need[3] else None
-        db1 = ops.colsum(dhpre, offs, EL) if need[4] else None
+        dys, dgate_row = ops.combine_bwd(dy, ys, p.token_of_row, p.gate_of_row, p.meta, send_cap)
+        ready = torch.cuda.Event()
+        ready.record(comp)
+        comm.wait_event(ready)
+        arrived, dyrs = [], []
+        with torch.cuda.stream(comm):
+            for c, ch in enumerate(chunks):
+                dyr = torch.empty((max(ch.n_recv, 1), d), dtype=torch.bfloat16, device=dev)
+                _a2a_into(dyr[:ch.n_recv], dys[send_off[c]:send_off[c + 1]], send_splits[c], recv_splits[c], group)
+                ev = torch.cuda.Event()
+                ev.record(comm)
+                arrived.append(ev)
+                dyrs.append(dyr)
+        # router gradient does not depend on the experts: it fills the bubble while the first rows travel
         dlogits = ops.router_bwd_dlogits(r.logits, r.topk_idx, p.row_of_assignment, dgate_row, p.tokens_per_expert,
                                          d_aux_t, mod.normalize_topk, mod.aux_loss_weight, mod.z_loss_weight)
-        dx = None
-        if need[0]:
-            dxp = ops.ffn_dgrad_up(dhpre, w1b, meta_r, tile_e)
-            dxr = ops.scatter_rows(dxp, src_of_row, meta_r, max(n_recv, 1))
-            dxs = _a2a(dxr[:n_recv], n_send, recv_splits, send_splits, group)
-            dx = ops.unpermute_bwd(dxs, p.row_of_assignment, dlogits, wgf, T, k, d)
         dwg = ops.router_bwd_dwg(dlogits, x2) if need[2] else None
         dctx = ops.router_bwd_dctx(dlogits, ctx.tpi) if (ctx.has_ctx and need[1]) else None
+
+        f32 = torch.float32
+        dw1 = torch.empty((EL, F, d), dtype=f32, device=dev) if need[3] else None
+        db1 = torch.empty((EL, F), dtype=f32, device=dev) if need[4] else None
+        dw2 = torch.empty((EL, d, F), dtype=f32, device=dev) if need[5] else None
+        db2 = torch.empty((EL, d), dtype=f32, device=dev) if need[6] else None
+        dxs = torch.empty((max(n_send, 1), d), dtype=torch.bfloat16, device=dev) if need[0] else None
+        for c, ch in enumerate(chunks):
+            comp.wait_event(arrived[c])
+            dyrs[c].record_stream(comp)
+            n = ch.hi - ch.lo
+            dyp = ops.permute(dyrs[c], ch.src, ch.meta, ch.cap)
+            dhpre = ops.ffn_dgrad_down(dyp, w2b[ch.lo:ch.hi], ch.pre, ch.meta, ch.tile_e)
+            if need[0]:
+                dxp = ops.ffn_dgrad_up(dhpre, w1b[ch.lo:ch.hi], ch.meta, ch.tile_e)
+                dxr = ops.scatter_rows(dxp, ch.src, ch.meta, max(ch.n_recv, 1))
+                done = torch.cuda.Event()
+                done.record(comp)
+                with torch.cuda.stream(comm):
+                    comm.wait_event(done)
+                    dxr.record_stream(comm)
+                    _a2a_into(dxs[send_off[c]:send_off[c + 1]], dxr[:ch.n_recv], recv_splits[c], send_splits[c],
+                              group)
+            if need[5]:
+                ops.ffn_wgrad(dyp, ch.h, ch.offs, n, out=dw2[ch.lo:ch.hi])
+            if need[6]:
+                ops.colsum(dyp, ch.offs, n, out=db2[ch.lo:ch.hi])
+            if need[3]:
+                ops.ffn_wgrad(dhpre, ch.xp, ch.offs, n, out=dw1[ch.lo:ch.hi])
+            if need[4]:
+                ops.colsum(dhpre, ch.offs, n, out=db1[ch.lo:ch.hi])
+        dx = None
+        if need[0]:
+            home = torch.cuda.Event()
+            home.record(comm)
+            comp.wait_event(home)
+            dx = ops.unpermute_bwd(dxs, p.row_of_assignment, dlogits, wgf, T, k, d)
         t_w1, t_b1, t_w2, t_b2, t_wg = ctx.dtypes
 
         def cast(g, dt):

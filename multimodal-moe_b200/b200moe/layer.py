@@ -116,6 +116,7 @@ class ContextMoE(nn.Module):
         self.context_vocab_sizes = tuple(context_vocab_sizes)
         self.context_dim = context_dim
         self.ep_group = ep_group
+        self.ep_chunks = 2            # groups of local experts whose all-to-all overlaps the other groups' GEMMs
         self.ep_size, self.ep_rank = 1, 0
         if ep_group is not None:
             import torch.distributed as dist
@@ -144,6 +145,8 @@ class ContextMoE(nn.Module):
         new = self.__class__.__new__(self.__class__)
         memo[id(self)] = new
         for k_, v in self.__dict__.items():
+            if k_ == "_ep_comm_stream":
+                continue
             if k_ in ("_wcache", "last_aux"):
                 new.__dict__[k_] = {}
             elif k_ == "aux_loss":
@@ -157,6 +160,7 @@ class ContextMoE(nn.Module):
     def __getstate__(self):
         s = dict(self.__dict__)
         s["_wcache"], s["last_aux"], s["aux_loss"], s["ep_group"] = {}, {}, torch.zeros(()), None
+        s.pop("_ep_comm_stream", None)
         return s
 
     def reset_parameters(self):

@@ -23,7 +23,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, T, E, k, cf, out):
+def _worker(rank, world, port, T, E, k, cf, chunks, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -39,25 +39,36 @@ def _worker(rank, world, port, T, E, k, cf, out):
         allh = torch.stack(allh)
         hist_all, tokens_all = allh[:, :-1].reshape(world, k, E), allh[:, -1]
         goff, cap, kept = ep.route_tables(hist_all, tokens_all, rank, cf, k)
-        send, recv, recv_counts, seg_expert = ep.split_sizes(kept, rank, world)
+        C, ELc, order = ep.chunk_layout(E, world, chunks)
+        send, recv, recv_counts, seg_expert = ep.split_sizes(kept, rank, world, C)
 
         # local view of the global plan, through the oracle with this rank's global offsets
         pos, keep = R.assign_slots(idx, E, cap, global_offset=goff.long())
         offs, kept_l, soa, tor = R.permutation(idx, keep, E, pad_to=1)
         assert kept_l.tolist() == kept[rank].tolist()
-        assert sum(send) == int(kept_l.sum())
+        assert sum(sum(s_) for s_ in send) == int(kept_l.sum())
 
-        # move rows: payload = (global token id, expert) so the receiver can check what it got
-        payload = torch.zeros(int(offs[-1]), 2, dtype=torch.int64)
-        rows_e = torch.repeat_interleave(torch.arange(E), kept_l)
-        payload[:, 0] = tor + rank * T
-        payload[:, 1] = rows_e
-        got = torch.empty(sum(recv), 2, dtype=torch.int64)
-        dist.all_to_all_single(got, payload, output_split_sizes=recv, input_split_sizes=send)
+        # send buffer in the chunked layout (group, destination rank, expert); payload = (global token id, expert)
+        by_pos = sorted(range(E), key=lambda e: int(order[e]))
+        rows = []
+        for e in by_pos:
+            seg = tor[int(offs[e]):int(offs[e + 1])]
+            rows.append(torch.stack([seg + rank * T, torch.full_like(seg, e)], 1))
+        payload = torch.cat(rows) if rows else torch.zeros(0, 2, dtype=torch.int64)
         EL = E // world
-        assert ((got[:, 1] >= rank * EL) & (got[:, 1] < (rank + 1) * EL)).all()      # only my experts arrive
-        seg_rows = torch.repeat_interleave(seg_expert.long() + rank * EL, recv_counts.long())
-        assert torch.equal(seg_rows, got[:, 1])                                       # in the announced segment order
+        got_all, start = [], 0
+        for c in range(C):
+            n_out = sum(send[c])
+            got = torch.empty(sum(recv[c]), 2, dtype=torch.int64)
+            dist.all_to_all_single(got, payload[start:start + n_out].contiguous(), output_split_sizes=recv[c],
+                                   input_split_sizes=send[c])
+            start += n_out
+            lo = rank * EL + c * ELc
+            assert ((got[:, 1] >= lo) & (got[:, 1] < lo + ELc)).all()                # only this group's experts arrive
+            seg_rows = torch.repeat_interleave(seg_expert.long() + lo, recv_counts[c].long())
+            assert torch.equal(seg_rows, got[:, 1])                                  # in the announced segment order
+            got_all.append(got)
+        got = torch.cat(got_all)
         gathered = [None] * world
         dist.all_gather_object(gathered, (idx, keep, got))
         if rank == 0:
@@ -76,12 +87,12 @@ def _worker(rank, world, port, T, E, k, cf, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("T,E,k,cf", [(257, 8, 2, 1.0), (64, 4, 1, 0.5), (300, 16, 2, None)])
-def test_ep_tables_world2(T, E, k, cf):
+@pytest.mark.parametrize("T,E,k,cf,chunks", [(257, 8, 2, 1.0, 2), (64, 4, 1, 0.5, 1), (300, 16, 2, None, 4)])
+def test_ep_tables_world2(T, E, k, cf, chunks):
     ctx = mp.get_context("spawn")
     out = ctx.SimpleQueue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, T, E, k, cf, out)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, T, E, k, cf, chunks, out)) for r in range(2)]
     for p in procs:
         p.start()
     for p in procs:
