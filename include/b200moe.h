@@ -42,7 +42,7 @@ int b200moe_check_device(void);
 
 /* Upper bound (multiple of 128) on rows of the permuted buffer: min(T*k, E*capacity) + E*127, rounded up. */
 int b200moe_rows_upper_bound(int T, int k, int E, int capacity);
-/* Tokens per router block for a batch of T tokens (32, 64 or 128) and the resulting block count
+/* Tokens per router block (128 = one tcgen05 M tile of the router) and the resulting block count
  * ceil(T / block): first dimension of block_counts / block_stats. */
 int b200moe_router_block(int T);
 int b200moe_num_router_blocks(int T);
@@ -52,12 +52,15 @@ int b200moe_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
 
 /* A.2-A.4 + statistics for A.8/A.9.  Gate GEMV over the token plus the per-image context bias, fp32 softmax,
  * top-k with (p desc, index asc) order, optional renormalisation.
- *   x [T,d] bf16; ctx_bias [B,E] fp32 or NULL (tok2img = t / tokens_per_image); wg [E,d] fp32
+ *   x [T,d] bf16 (d % 64 == 0); ctx_bias [B,E] fp32 or NULL (tok2img = t / tokens_per_image); wg [E,d] fp32
+ *   wg_split: scratch of b200moe_router_scratch_bytes(d,E) bytes (the gate product runs on tcgen05 with wg split
+ *   into bf16 hi + lo, fp32 accumulate)
  *   logits [T,E] fp32; topk_idx [T,k] int32; topk_gate [T,k] fp32
  *   block_counts [nblk,k,E] int32 (pre-drop assignments per router block, slot, expert)
  *   block_stats  [nblk,E+1] fp32 (sum_t p[t,e] per block; last column sum_t lse^2)                         */
+int64_t b200moe_router_scratch_bytes(int d, int E);   /* size of wg_split: bf16 hi/lo split of wg, [2*EP, d] */
 int b200moe_router_fwd(const void* x, const float* ctx_bias, int tokens_per_image, const float* wg,
-                       int T, int d, int E, int k, int normalize_topk,
+                       void* wg_split, int T, int d, int E, int k, int normalize_topk,
                        float* logits, int32_t* topk_idx, float* topk_gate,
                        int32_t* block_counts, float* block_stats, void* stream);
 

@@ -21,7 +21,8 @@ SIGNATURES = {
     "b200moe_router_block": [_I],
     "b200moe_num_router_blocks": [_I],
     "b200moe_cast_f32_bf16": [_P, _P, _L, _P],
-    "b200moe_router_fwd": [_P, _P, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],
+    "b200moe_router_scratch_bytes": [_I, _I],
+    "b200moe_router_fwd": [_P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],
     "b200moe_plan": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b200moe_permute": [_P, _P, _P, _I, _I, _P, _P],
     "b200moe_combine": [_P, _P, _P, _I, _I, _I, _P, _P],
@@ -40,7 +41,8 @@ SIGNATURES = {
     "b200moe_ep_recv_plan": [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P],
     "b200moe_scatter_rows": [_P, _P, _P, _I, _I, _P, _P],
 }
-_RESTYPE = {"b200moe_last_error": C.c_char_p, "b200moe_dwg_scratch_floats": C.c_int64}
+_RESTYPE = {"b200moe_last_error": C.c_char_p, "b200moe_dwg_scratch_floats": C.c_int64,
+            "b200moe_router_scratch_bytes": C.c_int64}
 
 _lib: Optional[C.CDLL] = None
 
@@ -77,7 +79,7 @@ def stream_ptr() -> int:
 
 # kernels launched by each entry point (memset nodes not counted); used for bench.py's gpu_launches
 KERNELS_PER_CALL = {
-    "b200moe_cast_f32_bf16": 1, "b200moe_router_fwd": 1, "b200moe_plan": 2, "b200moe_permute": 1,
+    "b200moe_cast_f32_bf16": 1, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
     "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 2,
     "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,

@@ -60,7 +60,12 @@ def router_fwd(x: torch.Tensor, wg: torch.Tensor, ctx_bias: Optional[torch.Tenso
     r = Routing(_empty((T, E), torch.float32, dev), _empty((T, k), torch.int32, dev),
                 _empty((T, k), torch.float32, dev), _empty((nblk, k, E), torch.int32, dev),
                 _empty((nblk, E + 1), torch.float32, dev))
-    call("b200moe_router_fwd", ptr(x), ptr(ctx_bias), tokens_per_image, ptr(wg), T, d, E, k, int(normalize),
+    nscratch = _lib.load().b200moe_router_scratch_bytes(d, E)
+    if nscratch < 0:
+        raise RuntimeError(f"router_fwd: num_experts={E} outside [1,64]")
+    wsplit = _empty((nscratch // 2,), torch.bfloat16, dev)
+    call("b200moe_router_fwd", ptr(x), ptr(ctx_bias), tokens_per_image, ptr(wg), ptr(wsplit), T, d, E, k,
+         int(normalize),
          ptr(r.logits), ptr(r.topk_idx), ptr(r.topk_gate), ptr(r.block_counts), ptr(r.block_stats), stream_ptr())
     return r
 

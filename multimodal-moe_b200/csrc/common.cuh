@@ -25,11 +25,8 @@ int check_launch(const char* what);
 constexpr int kNumSMs = 148;
 constexpr int kRowPad = 128;          // every expert segment of the permuted buffer starts at a multiple of this
 constexpr int kRouterTokPerBlock = 128;  // max tokens per router/plan block (granularity of the priority scan)
-// Tokens per router block for a batch of T tokens: smaller blocks for small batches so that the grid still covers
-// the 148 SMs (the detector-encoder batch is 3200 tokens).  Router, plan and the host wrappers all use this.
-__host__ __device__ inline int router_block_tokens(int T) {
-  return T >= 128 * 2 * 148 ? 128 : (T >= 64 * 2 * 148 ? 64 : 32);
-}
+// Tokens per router block: one 128-token tcgen05 M tile (router.cu).  Router, plan and the host wrappers all use this.
+__host__ __device__ inline int router_block_tokens(int /*T*/) { return kRouterTokPerBlock; }
 
 // ---- small device utilities -----------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {

@@ -1,195 +1,343 @@
-// Fused router, forward (SURVEY.md Appendix A.2-A.4 and the statistics of A.8/A.9).
+// Fused router, forward (SURVEY.md Appendix A.2-A.4 and the statistics of A.8/A.9) on tcgen05 / TMEM fed by TMA.
 //
-// One warp per token: the lanes split the d-long dot products with 128-bit loads of the bf16 token row, the gate
-// matrix sits in shared memory in fp32, partial sums are all-reduced with xor shuffles so that every lane holds
-// all E logits, then softmax / top-k / gate renormalisation run in registers in fp32.  Ranking is done on
-// (logit desc, expert index asc): softmax is monotone, so this is the order A.4 asks for, without the ties that
-// fp32 rounding of p could fabricate.  A block owns B200MOE_ROUTER_BLOCK consecutive tokens and emits the
-// per-(slot, expert) assignment counts and the sum_t p[t,e] / sum_t lse^2 partials that the plan kernel scans
-// in a fixed order (deterministic, no float atomics).
+// The gate product logits[T,E] = x[T,d] . Wg[E,d]^T is the one part of the router that CUDA cores cannot do at HBM
+// speed (2*T*d*E FMAs against T*d*2 bytes: for E >= 16 the FMA pipe, and the shared-memory reads of Wg that feed
+// it, take longer than streaming x).  So the product runs on the tensor pipe while x streams through a TMA ring
+// exactly once:
+//   * Wg stays fp32-accurate: a prep kernel splits it into bf16 hi + bf16 lo (w = hi + lo + O(2^-17 |w|)); the MMA
+//     issuer accumulates x.hi and x.lo into the same TMEM columns, x is bf16 already, products are exact in fp32.
+//   * one CTA = 128-token tiles (persistent over tiles): warp 0 TMA producer, warp 1 MMA issuer, warps 2..5 epilogue.
+//     The accumulator is [128 tokens][EP experts] fp32 in TMEM, double-buffered so the epilogue of tile i overlaps
+//     the loads of tile i+1.
+//   * epilogue: one thread per token reads its E logits from TMEM, adds the per-image context bias (A.2), softmax
+//     in fp32, top-k by (logit desc, expert index asc) -- softmax is monotone, so this is the order A.4 asks for
+//     without the ties fp32 rounding of p could fabricate -- gate renormalisation, and the per-tile statistics:
+//     assignment counts per (slot, expert) and sum_t p[t,e] / sum_t lse^2, reduced in a fixed order (warp shuffle
+//     tree, then the four warps in order): deterministic, no float atomics.  The plan kernel scans the tiles.
 #include <math.h>
 
 #include "common.cuh"
 
 namespace b200moe {
 
-constexpr int kRouterWarps = 8;
-constexpr int kRouterThreads = kRouterWarps * 32;
+constexpr int kRtThreads = 192;            // TMA warp, MMA warp, four epilogue warps
+constexpr int kRtTile = kRouterTokPerBlock;  // 128 tokens = one MMA M tile = one router block of the plan
+constexpr int kRtXBytes = kRtTile * 64 * 2;  // one k-block of the token tile: [128][64] bf16, 128-byte swizzle
 
-template <int EP, bool W_IN_SMEM>
-__global__ void __launch_bounds__(kRouterThreads)
-router_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ ctx_bias, int tokens_per_image,
-                  const float* __restrict__ wg, int T, int d, int E, int k, int normalize, int tb,
-                  float* __restrict__ logits_out, int32_t* __restrict__ topk_idx, float* __restrict__ topk_gate,
-                  int32_t* __restrict__ block_counts, float* __restrict__ block_stats) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  float* w_s = reinterpret_cast<float*>(smem_raw);                       // [E][d] when W_IN_SMEM
-  float* stat_s = w_s + (W_IN_SMEM ? static_cast<size_t>(E) * d : 0);    // [warps][EP+1]
-  int* cnt_s = reinterpret_cast<int*>(stat_s + kRouterWarps * (EP + 1));  // [k][E]
+template <int EP>
+struct RouterCfg {
+  static constexpr int kWBytes = 2 * EP * 64 * 2;           // hi rows then lo rows, [2*EP][64] bf16
+  static constexpr int kStageBytes = kRtXBytes + kWBytes;
+  static constexpr int kStages = (EP == 64) ? 6 : 8;
+  static constexpr int kTail = 2 * 4 * (EP + 1) * 4 /*stat_s*/ + 2 * 8 * 64 * 4 /*cnt_s*/ + 256 /*barriers*/;
+  static constexpr int kTotal = kStages * kStageBytes + kTail + 1024;
+  static constexpr uint32_t kTmemCols = 2 * EP < 32 ? 32 : 2 * EP;
+};
+
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+struct RouterArgs {
+  const float* ctx_bias;
+  int tokens_per_image;
+  int T, d, E, k, normalize;
+  float* logits;
+  int32_t* topk_idx;
+  float* topk_gate;
+  int32_t* block_counts;
+  float* block_stats;
+};
+
+template <int EP>
+__global__ void __launch_bounds__(kRtThreads, 1)
+router_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+                  const RouterArgs a) {
+  using Cfg = RouterCfg<EP>;
+  constexpr int kStages = Cfg::kStages;
+  constexpr uint32_t kIdesc = make_idesc_bf16(kRtTile, EP, false, false);
+
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  unsigned char* tail = smem + kStages * Cfg::kStageBytes;
+  float* stat_s = reinterpret_cast<float*>(tail);                            // [2][4 warps][EP+1]
+  int* cnt_s = reinterpret_cast<int*>(stat_s + 2 * 4 * (EP + 1));           // [2][k*E] (<= 8*64)
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(cnt_s + 2 * 8 * 64);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* tfull_bar = empty_bar + kStages;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (W_IN_SMEM) {
-    const int n4 = (E * d) >> 2;
-    for (int i = threadIdx.x; i < n4; i += blockDim.x)
-      reinterpret_cast<float4*>(w_s)[i] = reinterpret_cast<const float4*>(wg)[i];
+  const int E = a.E, k = a.k, T = a.T;
+  const int kE = k * E;
+  const int ntiles = (T + kRtTile - 1) / kRtTile;
+  const int kblocks = a.d / 64;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmW);
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull_bar[s], 1); mbar_init(&tempty_bar[s], 128); }
+    fence_mbar_init();
   }
-  for (int i = threadIdx.x; i < k * E; i += blockDim.x) cnt_s[i] = 0;
+  for (int i = threadIdx.x; i < 2 * 8 * 64; i += kRtThreads) cnt_s[i] = 0;
+  if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
+  tc_fence_before();
   __syncthreads();
-  const float* wsrc = W_IN_SMEM ? w_s : wg;
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
 
-  const int t0 = blockIdx.x * tb;
-  const int nchunk = d >> 3;  // 16-byte chunks per row
-  float psum0 = 0.f, psum1 = 0.f, zsum = 0.f;  // lane e owns sum_t p[t,e] (and e+32)
-
-  for (int i = warp; i < tb; i += kRouterWarps) {
-    const int t = t0 + i;
-    if (t >= T) break;
-    float acc[EP];
+  if (warp == 0) {
+    // ======================= TMA producer =======================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          unsigned char* sx = smem + stage * Cfg::kStageBytes;
+          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          tma_load_2d(sx, &tmX, &full_bar[stage], kb * 64, tile * kRtTile);   // rows past T arrive as zeros
+          tma_load_2d(sx + kRtXBytes, &tmW, &full_bar[stage], kb * 64, 0);    // hi rows 0..EP-1, lo rows EP..2EP-1
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ======================= MMA issuer =======================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + acc * EP;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sx = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint64_t dx = make_smem_desc(sx, 16, 1024);
+          const uint64_t dhi = make_smem_desc(sx + kRtXBytes, 16, 1024);
+          const uint64_t dlo = make_smem_desc(sx + kRtXBytes + EP * 128, 16, 1024);
 #pragma unroll
-    for (int e = 0; e < EP; ++e) acc[e] = 0.f;
-    const __nv_bfloat16* xr = x + static_cast<size_t>(t) * d;
-    for (int c = lane; c < nchunk; c += 32) {
-      const uint4 raw = ldg128(xr + c * 8);
-      float xv[8];
-      float2 f;
-      f = bf16x2_to_float2(raw.x); xv[0] = f.x; xv[1] = f.y;
-      f = bf16x2_to_float2(raw.y); xv[2] = f.x; xv[3] = f.y;
-      f = bf16x2_to_float2(raw.z); xv[4] = f.x; xv[5] = f.y;
-      f = bf16x2_to_float2(raw.w); xv[6] = f.x; xv[7] = f.y;
+          for (int ks = 0; ks < 4; ++ks) {
+            umma_bf16_ss(tmem_d, dx + 2 * ks, dhi + 2 * ks, kIdesc, (kb | ks) != 0 ? 1u : 0u);
+            umma_bf16_ss(tmem_d, dx + 2 * ks, dlo + 2 * ks, kIdesc, 1u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull_bar[acc]);
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ======================= epilogue: one thread per token =======================
+    const int quarter = warp & 3;                 // TMEM lane quarter this warp may read
+    const int et = threadIdx.x - 64;              // 0..127 among the epilogue threads
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    int buf = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      mbar_wait(&tfull_bar[acc], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * EP;
+      uint32_t raw[EP];
+      if (EP == 16) {
+        tmem_ld16(taddr, raw);
+      } else {
+#pragma unroll
+        for (int c = 0; c < EP / 32; ++c) tmem_ld32(taddr + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&raw[c * 32]));
+      }
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&tempty_bar[acc]);              // accumulator is in registers: the MMA warp may reuse it
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+
+      const int t = tile * kRtTile + quarter * 32 + lane;
+      const bool live = t < T;
+      const float* cb = (a.ctx_bias && live) ? a.ctx_bias + static_cast<size_t>(t / a.tokens_per_image) * E : nullptr;
+      float lg[EP];
+      float mx = -INFINITY;
+#pragma unroll
+      for (int e = 0; e < EP; ++e) {
+        float v = __uint_as_float(raw[e]);
+        if (e < E) {
+          if (cb) v += __ldg(cb + e);
+          mx = fmaxf(mx, v);
+        } else {
+          v = -INFINITY;
+        }
+        lg[e] = v;
+      }
+      float p[EP];
+      float ssum = 0.f;
+#pragma unroll
+      for (int e = 0; e < EP; ++e) {
+        p[e] = (e < E) ? expf(lg[e] - mx) : 0.f;
+        ssum += p[e];
+      }
+      const float inv = 1.0f / ssum;
+      const float lse = mx + logf(ssum);
+      // top-k by (logit desc, index asc)
+      unsigned long long taken = 0ull;
+      int sel[8];
+      float gate[8];
+      float gsum = 0.f;
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        if (s < k) {
+          float best = -INFINITY;
+          int bi = 0;
+          bool found = false;
+          float pb = 0.f;
+#pragma unroll
+          for (int e = 0; e < EP; ++e) {
+            const bool ok = (e < E) && !((taken >> e) & 1ull) && (!found || lg[e] > best);
+            if (ok) { best = lg[e]; bi = e; found = true; pb = p[e]; }
+          }
+          taken |= 1ull << bi;
+          sel[s] = bi;
+          gate[s] = pb * inv;
+          gsum += gate[s];
+        }
+      }
+      if (live) {
+#pragma unroll
+        for (int s = 0; s < 8; ++s) {
+          if (s < k) {
+            a.topk_idx[static_cast<size_t>(t) * k + s] = sel[s];
+            a.topk_gate[static_cast<size_t>(t) * k + s] = a.normalize ? gate[s] / (gsum + 1e-9f) : gate[s];
+            atomicAdd(&cnt_s[buf * 512 + s * E + sel[s]], 1);
+          }
+        }
+        float* lo = a.logits + static_cast<size_t>(t) * E;
+        if ((E & 3) == 0) {
+#pragma unroll
+          for (int e = 0; e < EP; e += 4)
+            if (e < E) *reinterpret_cast<float4*>(lo + e) = make_float4(lg[e], lg[e + 1], lg[e + 2], lg[e + 3]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < EP; ++e)
+            if (e < E) lo[e] = lg[e];
+        }
+      }
+      // tile statistics: shuffle tree per expert, then the four warps in a fixed order
+      float* st = stat_s + (buf * 4 + quarter) * (EP + 1);
 #pragma unroll
       for (int e = 0; e < EP; ++e) {
         if (e < E) {
-          const float4 wa = *reinterpret_cast<const float4*>(wsrc + static_cast<size_t>(e) * d + c * 8);
-          const float4 wb = *reinterpret_cast<const float4*>(wsrc + static_cast<size_t>(e) * d + c * 8 + 4);
-          float a = acc[e];
-          a = fmaf(xv[0], wa.x, a); a = fmaf(xv[1], wa.y, a); a = fmaf(xv[2], wa.z, a); a = fmaf(xv[3], wa.w, a);
-          a = fmaf(xv[4], wb.x, a); a = fmaf(xv[5], wb.y, a); a = fmaf(xv[6], wb.z, a); a = fmaf(xv[7], wb.w, a);
-          acc[e] = a;
+          const float s = warp_sum(live ? p[e] * inv : 0.f);
+          if (lane == (e & 31)) st[e] = s;
         }
       }
-    }
-    // all-reduce over the lanes, add the per-image context bias (A.2: additive on the logits)
-    const float* cb = ctx_bias ? ctx_bias + static_cast<size_t>(t / tokens_per_image) * E : nullptr;
-    float mx = -INFINITY;
-#pragma unroll
-    for (int e = 0; e < EP; ++e) {
-      float v = warp_sum(acc[e]);
-      if (e < E) {
-        if (cb) v += __ldg(cb + e);
-        mx = fmaxf(mx, v);
-      } else {
-        v = -INFINITY;
+      {
+        const float z = warp_sum(live ? lse * lse : 0.f);
+        if (lane == 0) st[EP] = z;
       }
-      acc[e] = v;
-    }
-    float ssum = 0.f;
-    float p[EP];
-#pragma unroll
-    for (int e = 0; e < EP; ++e) {
-      p[e] = (e < E) ? expf(acc[e] - mx) : 0.f;
-      ssum += p[e];
-    }
-    const float inv = 1.0f / ssum;
-    const float lse = mx + logf(ssum);
-    // top-k by (logit desc, index asc); every lane computes the same answer
-    unsigned long long taken = 0ull;
-    int my_idx = 0;       // lane s keeps slot s
-    float my_gate = 0.f;
-    float gsum = 0.f;
-    for (int s = 0; s < k; ++s) {
-      float best = -INFINITY;
-      int bi = 0;
-      bool found = false;
-#pragma unroll
-      for (int e = 0; e < EP; ++e) {
-        if (e < E && !((taken >> e) & 1ull)) {
-          if (!found || acc[e] > best) { best = acc[e]; bi = e; found = true; }
-        }
+      epi_bar_sync();
+      for (int e = et; e <= E; e += 128) {
+        const int col = (e == E) ? EP : e;
+        const float* sb = stat_s + buf * 4 * (EP + 1);
+        const float s = ((sb[col] + sb[(EP + 1) + col]) + sb[2 * (EP + 1) + col]) + sb[3 * (EP + 1) + col];
+        a.block_stats[static_cast<size_t>(tile) * (E + 1) + e] = s;
       }
-      taken |= 1ull << bi;
-      float pb = 0.f;
-#pragma unroll
-      for (int e = 0; e < EP; ++e) pb = (e == bi) ? p[e] * inv : pb;
-      gsum += pb;
-      if (lane == s) { my_idx = bi; my_gate = pb; }
+      for (int i = et; i < kE; i += 128) {
+        a.block_counts[static_cast<size_t>(tile) * kE + i] = cnt_s[buf * 512 + i];
+        cnt_s[buf * 512 + i] = 0;                 // this buffer is next used two tiles (two barriers) from now
+      }
+      buf ^= 1;
     }
-    if (normalize) my_gate = my_gate / (gsum + 1e-9f);
-    if (lane < k) {
-      topk_idx[static_cast<size_t>(t) * k + lane] = my_idx;
-      topk_gate[static_cast<size_t>(t) * k + lane] = my_gate;
-      atomicAdd(&cnt_s[lane * E + my_idx], 1);
-    }
-    // logits out + per-lane statistics
-    float lo = 0.f, hi = 0.f, plo = 0.f, phi = 0.f;
-#pragma unroll
-    for (int e = 0; e < EP; ++e) {
-      if (e < 32) { if (lane == e) { lo = acc[e]; plo = p[e] * inv; } }
-      else        { if (lane == e - 32) { hi = acc[e]; phi = p[e] * inv; } }
-    }
-    if (lane < E) logits_out[static_cast<size_t>(t) * E + lane] = lo;
-    if (EP > 32 && lane + 32 < E) logits_out[static_cast<size_t>(t) * E + lane + 32] = hi;
-    psum0 += plo;
-    psum1 += phi;
-    zsum += lse * lse;
   }
-  // block partials in a fixed warp order
-  if (lane < EP) stat_s[warp * (EP + 1) + lane] = psum0;
-  if (EP > 32 && lane + 32 < EP) stat_s[warp * (EP + 1) + lane + 32] = psum1;
-  if (lane == 0) stat_s[warp * (EP + 1) + EP] = zsum;
+
+  tc_fence_before();
   __syncthreads();
-  for (int e = threadIdx.x; e <= E; e += blockDim.x) {
-    const int col = (e == E) ? EP : e;
-    float s = 0.f;
-#pragma unroll
-    for (int w = 0; w < kRouterWarps; ++w) s += stat_s[w * (EP + 1) + col];
-    block_stats[static_cast<size_t>(blockIdx.x) * (E + 1) + e] = s;
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<Cfg::kTmemCols>(tmem_base);
   }
-  for (int i = threadIdx.x; i < k * E; i += blockDim.x)
-    block_counts[static_cast<size_t>(blockIdx.x) * k * E + i] = cnt_s[i];
 }
 
-template <int EP>
-static int launch_router(const void* x, const float* ctx_bias, int tpi, const float* wg, int T, int d, int E, int k,
-                         int normalize, float* logits, int32_t* idx, float* gate, int32_t* bc, float* bs,
-                         cudaStream_t st) {
-  const int tb = router_block_tokens(T);
-  const int nblk = (T + tb - 1) / tb;
-  const size_t tail = sizeof(float) * kRouterWarps * (EP + 1) + sizeof(int) * k * E;
-  const size_t wbytes = sizeof(float) * static_cast<size_t>(E) * d;
-  const bool in_smem = wbytes + tail <= 160 * 1024;
-  const size_t smem = (in_smem ? wbytes : 0) + tail;
-  auto xb = static_cast<const __nv_bfloat16*>(x);
-  if (in_smem) {
-    auto kern = router_fwd_kernel<EP, true>;
-    if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-    kern<<<nblk, kRouterThreads, smem, st>>>(xb, ctx_bias, tpi, wg, T, d, E, k, normalize, tb, logits, idx, gate, bc, bs);
-  } else {
-    router_fwd_kernel<EP, false><<<nblk, kRouterThreads, smem, st>>>(xb, ctx_bias, tpi, wg, T, d, E, k, normalize, tb,
-                                                                     logits, idx, gate, bc, bs);
+// Wg fp32 [E,d] -> bf16 [2*EP, d]: rows 0..E-1 = hi, rows EP..EP+E-1 = lo = bf16(w - hi); padding rows zero.
+__global__ void router_split_wg_kernel(const float* __restrict__ wg, __nv_bfloat16* __restrict__ out, int E, int EP,
+                                       int d) {
+  const int n = 2 * EP * d;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int row = i / d, col = i - row * d;
+    const int e = row < EP ? row : row - EP;
+    float v = 0.f;
+    if (e < E) {
+      const float w = wg[static_cast<size_t>(e) * d + col];
+      const __nv_bfloat16 hi = __float2bfloat16_rn(w);
+      v = row < EP ? w : w - __bfloat162float(hi);
+    }
+    out[i] = __float2bfloat16_rn(v);
   }
+}
+
+int make_tmap_bf16_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint32_t box_inner,
+                      uint32_t box_outer);   // gemm.cu
+
+template <int EP>
+static int launch_router(const void* x, const void* wsplit, const RouterArgs& a, cudaStream_t st) {
+  using Cfg = RouterCfg<EP>;
+  CUtensorMap tmX, tmW;
+  if (int rc = make_tmap_bf16_2d(&tmX, x, a.d, a.T, 64, kRtTile)) return rc;
+  if (int rc = make_tmap_bf16_2d(&tmW, wsplit, a.d, 2 * EP, 64, 2 * EP)) return rc;
+  auto kern = router_fwd_kernel<EP>;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kTotal);
+    B200MOE_REQUIRE(e == cudaSuccess, B200MOE_ECUDA, "router_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    configured = true;
+  }
+  const int ntiles = (a.T + kRtTile - 1) / kRtTile;
+  const int grid = ntiles < kNumSMs ? ntiles : kNumSMs;
+  kern<<<grid, kRtThreads, Cfg::kTotal, st>>>(tmX, tmW, a);
   return check_launch("router_fwd");
 }
 
+static int router_ep(int E) { return E <= 16 ? 16 : (E <= 32 ? 32 : 64); }
+
 }  // namespace b200moe
 
+extern "C" int64_t b200moe_router_scratch_bytes(int d, int E) {
+  if (d <= 0 || E < 1 || E > 64) return -1;
+  return static_cast<int64_t>(2) * b200moe::router_ep(E) * d * 2;
+}
+
 extern "C" int b200moe_router_fwd(const void* x, const float* ctx_bias, int tokens_per_image, const float* wg,
-                                  int T, int d, int E, int k, int normalize_topk, float* logits, int32_t* topk_idx,
-                                  float* topk_gate, int32_t* block_counts, float* block_stats, void* stream) {
+                                  void* wg_split, int T, int d, int E, int k, int normalize_topk, float* logits,
+                                  int32_t* topk_idx, float* topk_gate, int32_t* block_counts, float* block_stats,
+                                  void* stream) {
   using namespace b200moe;
-  B200MOE_REQUIRE(T >= 0 && d > 0 && d % 8 == 0, B200MOE_EINVAL, "router_fwd: d=%d must be a positive multiple of 8", d);
+  B200MOE_REQUIRE(T >= 0 && d > 0 && d % 64 == 0, B200MOE_EINVAL, "router_fwd: d=%d must be a positive multiple of 64", d);
   B200MOE_REQUIRE(E >= 1 && E <= 64, B200MOE_EINVAL, "router_fwd: num_experts=%d outside [1,64]", E);
   B200MOE_REQUIRE(k >= 1 && k <= E && k <= 8, B200MOE_EINVAL, "router_fwd: top_k=%d must be in [1,min(E,8)]", k);
   B200MOE_REQUIRE(ctx_bias == nullptr || tokens_per_image > 0, B200MOE_EINVAL, "router_fwd: tokens_per_image <= 0");
+  B200MOE_REQUIRE(wg_split != nullptr, B200MOE_EINVAL, "router_fwd: wg_split scratch is NULL (b200moe_router_scratch_bytes)");
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (tokens_per_image <= 0) tokens_per_image = T;
-#define B200MOE_ROUTER_CASE(EP)                                                                              \
-  return launch_router<EP>(x, ctx_bias, tokens_per_image, wg, T, d, E, k, normalize_topk, logits, topk_idx, \
-                           topk_gate, block_counts, block_stats, st)
-  if (E <= 8) B200MOE_ROUTER_CASE(8);
-  if (E <= 16) B200MOE_ROUTER_CASE(16);
-  if (E <= 32) B200MOE_ROUTER_CASE(32);
-  B200MOE_ROUTER_CASE(64);
-#undef B200MOE_ROUTER_CASE
+  const int EP = router_ep(E);
+  {
+    const int n = 2 * EP * d;
+    int blocks = (n + 255) / 256;
+    if (blocks > 4 * kNumSMs) blocks = 4 * kNumSMs;
+    router_split_wg_kernel<<<blocks, 256, 0, st>>>(wg, static_cast<__nv_bfloat16*>(wg_split), E, EP, d);
+    if (int rc = check_launch("router_split_wg")) return rc;
+  }
+  RouterArgs a{ctx_bias, tokens_per_image, T, d, E, k, normalize_topk, logits, topk_idx, topk_gate, block_counts, block_stats};
+  if (EP == 16) return launch_router<16>(x, wg_split, a, st);
+  if (EP == 32) return launch_router<32>(x, wg_split, a, st);
+  return launch_router<64>(x, wg_split, a, st);
 }

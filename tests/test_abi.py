@@ -45,8 +45,9 @@ def test_host_only_entry_points(lib):
     assert lib.b200moe_rows_upper_bound(3200, 2, 8, 1000) == 7424          # 6400 kept + 8*127, rounded to 128
     assert lib.b200moe_rows_upper_bound(3200, 2, 8, 100) == 1920           # capacity-bounded
     assert lib.b200moe_rows_upper_bound(10, 2, 4, -1) % 128 == 0
-    assert [lib.b200moe_router_block(t) for t in (1, 3200, 20000, 40000)] == [32, 32, 64, 128]
-    assert lib.b200moe_num_router_blocks(3200) == 100
+    assert [lib.b200moe_router_block(t) for t in (1, 3200, 20000, 40000)] == [128, 128, 128, 128]
+    assert lib.b200moe_num_router_blocks(3200) == 25
+    assert lib.b200moe_router_scratch_bytes(256, 8) == 2 * 16 * 256 * 2
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="only meaningful on a box without a GPU")

@@ -182,8 +182,8 @@ def test_permute_combine_bit_exact(ops):
 
 
 def test_errors_are_loud(ops):
-    x, wg = _mk(64, 100, 8)                                # d not a multiple of 8
-    with pytest.raises(RuntimeError, match="multiple of 8"):
+    x, wg = _mk(64, 100, 8)                                # d not a multiple of 64
+    with pytest.raises(RuntimeError, match="multiple of 64"):
         ops.router_fwd(x.cuda(), wg.cuda(), None, 64, 2, True)
     x, wg = _mk(64, 128, 4)
     with pytest.raises(RuntimeError, match="top_k"):
