@@ -133,8 +133,7 @@ def run_reference(args, w):
 # ---------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------
-GEMM_CALLS = ("b200moe_ffn_up", "b200moe_ffn_down", "b200moe_ffn_dgrad_down", "b200moe_ffn_dgrad_up",
-              "b200moe_ffn_wgrad")
+GEMM_CALLS = ("ffn_up", "ffn_down", "ffn_dgrad_down", "ffn_dgrad_up", "ffn_wgrad")
 
 
 def build_layer(w, device, ep_group=None):
@@ -232,14 +231,19 @@ def measure_layer(w, steps, warmup, device, ep_group=None, dist_on=False, want_e
         # device-side sleep ahead of each step lets the host queue the whole step first, so durations are GPU time
         torch.cuda.synchronize()
         _lib.Counters.reset(timing=True)
+        _lib.layer_profile(True)              # events around every kernel inside b200moe_layer_fwd / _bwd
         for _ in range(steps):
             torch.cuda._sleep(6_000_000)
             flush(); step()
         torch.cuda.synchronize()
-        dur = _lib.Counters.durations_ms()
+        dur = {k_.replace("b200moe_", ""): v for k_, v in _lib.Counters.durations_ms().items()
+               if k_ not in ("b200moe_layer_fwd", "b200moe_layer_bwd")}
+        for k_, v in _lib.layer_profile_durations().items():
+            dur.setdefault(k_, []).extend(v)
+        _lib.layer_profile(False)
         _lib.Counters.reset()
         per_step = {k_: sum(v) / steps for k_, v in dur.items()}
-        res["per_call_ms"] = {k_.replace("b200moe_", ""): round(v, 5) for k_, v in sorted(per_step.items())}
+        res["per_call_ms"] = {k_: round(v, 5) for k_, v in sorted(per_step.items())}
         res["gemm_ms"] = sum(per_step.get(n, 0.0) for n in GEMM_CALLS)
         res["gemm_launches"] = sum(len(dur.get(n, [])) for n in GEMM_CALLS) // steps
 

@@ -49,6 +49,11 @@ int b200moe_num_router_blocks(int T);
 
 /* fp32 master weights -> bf16 operands (autocast step that torch does before hybrid_encoder.py:157). */
 int b200moe_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream);
+/* Once per optimizer step, ONE launch: w1, w2 fp32 -> bf16 operands (n1, n2 elements, multiples of 8; either may be
+ * 0) and wg [E,d] fp32 -> wg_split (bf16 hi/lo rows for the tcgen05 router, b200moe_router_scratch_bytes; wg may be
+ * NULL).  b200moe_router_fwd called with wg == NULL then uses wg_split as it is. */
+int b200moe_prepare_weights(const float* w1, void* w1_bf16, int64_t n1, const float* w2, void* w2_bf16, int64_t n2,
+                            const float* wg, void* wg_split, int d, int E, void* stream);
 
 /* A.2-A.4 + statistics for A.8/A.9.  Gate GEMV over the token plus the per-image context bias, fp32 softmax,
  * top-k with (p desc, index asc) order, optional renormalisation.
@@ -111,7 +116,7 @@ int b200moe_ffn_down(const void* h, const void* w2, const float* b2, const int32
  *   dgrad_up  : dxp   = dhpre @ w1[e]                         [R,d]
  *   wgrad     : dw[e] = a[rows of e]^T @ b[rows of e]         a [R,M] bf16, b [R,N] bf16 -> dw [E,M,N] fp32
  *               (dw2 = dyp^T h, dw1 = dhpre^T xp); accumulate != 0 adds into dw
- *   colsum    : db[e,:] = sum over rows of e of a[r,:]        (db2 from dyp, db1 from dhpre)            */
+ *   colsum    : db[e,:] = sum over rows of e of a[r,:]        (db2 from dyp, db1 from dhpre)  */
 int b200moe_ffn_dgrad_down(const void* dyp, const void* w2, const void* pre, const int32_t* meta,
                            const int32_t* tile_expert, int rows_cap, int d, int F, int E,
                            void* dhpre, void* stream);
@@ -120,8 +125,10 @@ int b200moe_ffn_dgrad_up(const void* dhpre, const void* w1, const int32_t* meta,
                          void* dxp, void* stream);
 int b200moe_ffn_wgrad(const void* a, const void* b, const int32_t* expert_offsets, int rows_cap,
                       int M, int N, int E, float* dw, int accumulate, void* stream);
-int b200moe_colsum(const void* a, const int32_t* expert_offsets, int rows_cap, int ncols, int E,
-                   float* scratch /* rows_cap/128 * ncols floats */, float* db, int accumulate, void* stream);
+/* Bias gradients of both projections in ONE launch (a1 may be NULL): db0[e,:] = column sums of a0 over the rows of
+ * expert e, same for (a1, db1).  Fixed summation order, no scratch.  ncols multiples of 64. */
+int b200moe_colsum(const void* a0, int ncols0, float* db0, const void* a1, int ncols1, float* db1,
+                   const int32_t* expert_offsets, int E, int accumulate, void* stream);
 
 /* A.12 router gradient.  dlogits from the gate gradient (softmax + renormalisation Jacobian on the selected k),
  * the load-balance term through P_e and the z-loss through lse.  d_aux is the upstream gradient of the weighted
@@ -152,6 +159,61 @@ int b200moe_ep_recv_plan(const int32_t* recv_counts, const int32_t* seg_expert, 
 /* Inverse row gather used on the EP return path: out[src_of_row[r],:] = in[r,:] for r < meta[0], src >= 0. */
 int b200moe_scatter_rows(const void* in, const int32_t* src_of_row, const int32_t* meta, int rows_cap, int d,
                          void* out, void* stream);
+
+/* ---- Context bias (A.2): ctx_bias[b,e] = sum_i Embed_i[context[b,i],:] . Wc[e, i*cd:(i+1)*cd] ------------------
+ * context [B,n_fields] int64 (device); tables: HOST array of n_fields device pointers, table i is [vocab[i], cd]
+ * fp32; vocab: HOST array; wc [E, n_fields*cd] fp32.  Ids outside [0, vocab[i]) contribute nothing.
+ * Backward writes every element of dtables[i] and dwc (fixed summation order over the images).                 */
+#define B200MOE_MAX_CTX_FIELDS 8
+int b200moe_ctx_bias_fwd(const int64_t* context, const float* const* tables, const int32_t* vocab, int n_fields,
+                         int context_dim, const float* wc, int B, int E, float* ctx_bias, void* stream);
+int b200moe_ctx_bias_bwd(const int64_t* context, const float* dctx_bias, const float* const* tables,
+                         const int32_t* vocab, int n_fields, int context_dim, const float* wc, int B, int E,
+                         float* const* dtables, float* dwc, void* stream);
+
+/* ---- Whole layer in one call each way (what b200moe.ContextMoE uses) ---------------------------------------------
+ * The caller owns two workspaces whose layout b200moe_layer_ws_layout / b200moe_layer_bwd_ws_layout describe
+ * (byte offsets of every buffer, 256-byte aligned; return value = total bytes, < 0 on a bad descriptor).  The
+ * forward workspace doubles as "saved for backward" and as the telemetry source (logits, topk_idx, ...).      */
+typedef struct b200moe_layer_desc {
+  int32_t T, d, F, E, k;
+  int32_t tokens_per_image;   /* tok2img = t / tokens_per_image (ignored when ctx_bias is NULL) */
+  int32_t capacity;           /* A.5: ceil(capacity_factor * T * k / E), or T*k for "no limit" */
+  int32_t rows_cap;           /* b200moe_rows_upper_bound(T, k, E, capacity) */
+  int32_t normalize_topk;
+  float aux_loss_weight, z_loss_weight;
+} b200moe_layer_desc;
+
+enum {
+  B200MOE_WS_LOGITS = 0, B200MOE_WS_TOPK_IDX, B200MOE_WS_TOPK_GATE, B200MOE_WS_BLOCK_COUNTS, B200MOE_WS_BLOCK_STATS,
+  B200MOE_WS_EXPERT_OFFSETS, B200MOE_WS_META, B200MOE_WS_TILE_EXPERT, B200MOE_WS_TOKENS_PER_EXPERT,
+  B200MOE_WS_KEPT_PER_EXPERT, B200MOE_WS_LOSSES, B200MOE_WS_SLOT_LIMIT, B200MOE_WS_ROW_OF_ASSIGNMENT,
+  B200MOE_WS_TOKEN_OF_ROW, B200MOE_WS_GATE_OF_ROW, B200MOE_WS_XP, B200MOE_WS_PRE, B200MOE_WS_H, B200MOE_WS_YO,
+  B200MOE_WS_COUNT
+};
+enum {
+  B200MOE_BWS_DYP = 0, B200MOE_BWS_DGATE_ROW, B200MOE_BWS_DHPRE, B200MOE_BWS_DXP, B200MOE_BWS_DLOGITS,
+  B200MOE_BWS_DWG_SCRATCH, B200MOE_BWS_COUNT
+};
+int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* desc, int64_t* offsets /* [B200MOE_WS_COUNT] */);
+int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* desc, int64_t* offsets /* [B200MOE_BWS_COUNT] */);
+/* router -> plan -> permute -> up(+GELU) -> down -> combine.  x [T,d] bf16; ctx_bias [B,E] fp32 or NULL; wg_split
+ * from b200moe_prepare_weights; w1 [E,F,d], w2 [E,d,F] bf16; b1 [E,F], b2 [E,d] fp32; y [T,d] bf16.
+ * save_for_backward == 0 skips the pre-activation store. */
+int b200moe_layer_fwd(const b200moe_layer_desc* desc, const void* x, const float* ctx_bias, const void* wg_split,
+                      const void* w1, const float* b1, const void* w2, const float* b2, void* ws, void* y,
+                      int save_for_backward, void* stream);
+/* Mirror of the forward incl. the A.12 router gradient.  dy [T,d] bf16; d_aux: device scalar (gradient of the
+ * weighted auxiliary loss) or NULL.  Any of the gradient outputs may be NULL (not computed):
+ * dx [T,d] bf16, dctx_bias [B,E], dwg [E,d], dw1 [E,F,d], db1 [E,F], dw2 [E,d,F], db2 [E,d] (all fp32).      */
+int b200moe_layer_bwd(const b200moe_layer_desc* desc, const void* x, const float* wg, const void* w1,
+                      const void* w2, const void* ws, void* bws, const void* dy, const float* d_aux, void* dx,
+                      float* dctx_bias, float* dwg, float* dw1, float* db1, float* dw2, float* db2,
+                      int has_ctx_bias, void* stream);
+/* Per-step CUDA-event timing of the two calls above (measurement aid): enable, run, synchronize the stream, then read
+ * entries 0,1,... until the call returns B200MOE_EINVAL.  b200moe_layer_profile(x) also clears earlier entries. */
+int b200moe_layer_profile(int enable);
+int b200moe_layer_profile_read(int index, const char** name, float* ms);
 
 #ifdef __cplusplus
 }

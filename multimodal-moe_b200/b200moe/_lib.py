@@ -32,7 +32,16 @@ SIGNATURES = {
     "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
     "b200moe_ffn_dgrad_up": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
     "b200moe_ffn_wgrad": [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
-    "b200moe_colsum": [_P, _P, _I, _I, _I, _P, _P, _I, _P],
+    "b200moe_colsum": [_P, _I, _P, _P, _I, _P, _P, _I, _I, _P],
+    "b200moe_prepare_weights": [_P, _P, _L, _P, _P, _L, _P, _P, _I, _I, _P],
+    "b200moe_ctx_bias_fwd": [_P, _P, _P, _I, _I, _P, _I, _I, _P, _P],
+    "b200moe_ctx_bias_bwd": [_P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P, _P],
+    "b200moe_layer_profile": [_I],
+    "b200moe_layer_profile_read": [_I, _P, _P],
+    "b200moe_layer_ws_layout": [_P, _P],
+    "b200moe_layer_bwd_ws_layout": [_P, _P],
+    "b200moe_layer_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P],
+    "b200moe_layer_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P],
     "b200moe_router_bwd_dlogits": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _P, _P],
     "b200moe_dwg_scratch_floats": [_I, _I, _I],
     "b200moe_router_bwd_dwg": [_P, _P, _I, _I, _I, _P, _P, _P],
@@ -42,7 +51,21 @@ SIGNATURES = {
     "b200moe_scatter_rows": [_P, _P, _P, _I, _I, _P, _P],
 }
 _RESTYPE = {"b200moe_last_error": C.c_char_p, "b200moe_dwg_scratch_floats": C.c_int64,
-            "b200moe_router_scratch_bytes": C.c_int64}
+            "b200moe_router_scratch_bytes": C.c_int64, "b200moe_layer_ws_layout": C.c_int64,
+            "b200moe_layer_bwd_ws_layout": C.c_int64}
+
+
+class LayerDesc(C.Structure):
+    """b200moe_layer_desc of include/b200moe.h."""
+    _fields_ = [("T", C.c_int32), ("d", C.c_int32), ("F", C.c_int32), ("E", C.c_int32), ("k", C.c_int32),
+                ("tokens_per_image", C.c_int32), ("capacity", C.c_int32), ("rows_cap", C.c_int32),
+                ("normalize_topk", C.c_int32), ("aux_loss_weight", C.c_float), ("z_loss_weight", C.c_float)]
+
+
+WS_NAMES = ("logits", "topk_idx", "topk_gate", "block_counts", "block_stats", "expert_offsets", "meta", "tile_expert",
+            "tokens_per_expert", "kept_per_expert", "losses", "slot_limit", "row_of_assignment", "token_of_row",
+            "gate_of_row", "xp", "pre", "h", "yo")
+BWS_NAMES = ("dyp", "dgate_row", "dhpre", "dxp", "dlogits", "dwg_scratch")
 
 _lib: Optional[C.CDLL] = None
 
@@ -79,9 +102,10 @@ def stream_ptr() -> int:
 
 # kernels launched by each entry point (memset nodes not counted); used for bench.py's gpu_launches
 KERNELS_PER_CALL = {
-    "b200moe_cast_f32_bf16": 1, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
+    "b200moe_cast_f32_bf16": 1, "b200moe_prepare_weights": 1, "b200moe_ctx_bias_fwd": 1, "b200moe_ctx_bias_bwd": 1,
+    "b200moe_layer_fwd": 7, "b200moe_layer_bwd": 12, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
-    "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 2,
+    "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
     "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,
     "b200moe_unpermute_bwd": 1, "b200moe_ep_recv_plan": 1, "b200moe_scatter_rows": 1,
 }
@@ -104,6 +128,21 @@ class Counters:
         for name, a, b in cls.events:
             out.setdefault(name, []).append(a.elapsed_time(b))
         return out
+
+
+def layer_profile(enable: bool) -> None:
+    load().b200moe_layer_profile(int(enable))
+
+
+def layer_profile_durations() -> dict:
+    """step name -> list of durations (ms) recorded inside b200moe_layer_fwd / _bwd since layer_profile(True);
+    call after torch.cuda.synchronize()."""
+    lib, out, i = load(), {}, 0
+    name, ms = C.c_char_p(), C.c_float()
+    while lib.b200moe_layer_profile_read(i, C.byref(name), C.byref(ms)) == 0:
+        out.setdefault(name.value.decode(), []).append(ms.value)
+        i += 1
+    return out
 
 
 def call(name: str, *args) -> None:

@@ -11,83 +11,188 @@ PyTorch or CPU fallback: without the library, or on a non-sm_100 device, forward
 """
 from __future__ import annotations
 
+import ctypes as C
 import math
+from collections.abc import Mapping
 from typing import Optional, Sequence
 
 import torch
 import torch.nn as nn
 
-from . import ops
+from . import _lib, ops
+
+
+_WS_DTYPES = {"logits": torch.float32, "topk_idx": torch.int32, "topk_gate": torch.float32,
+              "block_counts": torch.int32, "block_stats": torch.float32, "expert_offsets": torch.int32,
+              "meta": torch.int32, "tile_expert": torch.int32, "tokens_per_expert": torch.int32,
+              "kept_per_expert": torch.int32, "losses": torch.float32, "slot_limit": torch.int32,
+              "row_of_assignment": torch.int32, "token_of_row": torch.int32, "gate_of_row": torch.float32,
+              "xp": torch.bfloat16, "pre": torch.bfloat16, "h": torch.bfloat16, "yo": torch.bfloat16}
+
+
+class _LayerPlan:
+    """Host-side description of one (T, tokens_per_image) problem: the C descriptor and both workspace layouts."""
+
+    def __init__(self, mod, T: int, tpi: int):
+        lib = _lib.load()
+        E, k, d, F = mod.num_experts, mod.top_k, mod.d_model, mod.dim_feedforward
+        cap = ops.capacity_of(mod.capacity_factor, T, k, E)
+        rows_cap = ops.rows_upper_bound(T, k, E, cap)
+        self.desc = _lib.LayerDesc(T, d, F, E, k, tpi, cap, rows_cap, int(mod.normalize_topk),
+                                   mod.aux_loss_weight, mod.z_loss_weight)
+        self.desc_ptr = C.addressof(self.desc)
+        off = (C.c_int64 * len(_lib.WS_NAMES))()
+        self.ws_bytes = lib.b200moe_layer_ws_layout(self.desc_ptr, C.addressof(off))
+        boff = (C.c_int64 * len(_lib.BWS_NAMES))()
+        self.bws_bytes = lib.b200moe_layer_bwd_ws_layout(self.desc_ptr, C.addressof(boff))
+        if self.ws_bytes < 0 or self.bws_bytes < 0:
+            raise RuntimeError("b200moe: " + lib.b200moe_last_error().decode())
+        self.off = dict(zip(_lib.WS_NAMES, list(off)))
+        nblk = lib.b200moe_num_router_blocks(T)
+        R = rows_cap
+        self.shape = {"logits": (T, E), "topk_idx": (T, k), "topk_gate": (T, k), "block_counts": (nblk, k, E),
+                      "block_stats": (nblk, E + 1), "expert_offsets": (E + 1,), "meta": (8,),
+                      "tile_expert": (R // 128,), "tokens_per_expert": (E,), "kept_per_expert": (E,), "losses": (3,),
+                      "slot_limit": (k * E,), "row_of_assignment": (T, k), "token_of_row": (R,),
+                      "gate_of_row": (R,), "xp": (R, d), "pre": (R, F), "h": (R, F), "yo": (R, d)}
+        self.capacity, self.rows_cap = cap, rows_cap
+
+    def view(self, ws: torch.Tensor, name: str) -> torch.Tensor:
+        dt, shp = _WS_DTYPES[name], self.shape[name]
+        n = dt.itemsize * math.prod(shp)
+        o = self.off[name]
+        return ws[o:o + n].view(dt).view(shp)
+
+
+class _Aux(Mapping):
+    """Telemetry of the last forward (SURVEY.md §8(b) `last_aux`): tensors are views into the forward workspace,
+    created on first access so that a training step pays nothing for what it does not read."""
+    _ALIAS = {"gates": "topk_gate"}
+    _KEYS = ("load_balance", "z_loss", "tokens_per_expert", "kept_per_expert", "dropped", "logits", "topk_idx",
+             "gates", "row_of_assignment", "token_of_row", "expert_offsets", "meta", "capacity")
+
+    def __init__(self, plan: _LayerPlan, ws: torch.Tensor):
+        self._plan, self._ws, self._cache = plan, ws, {}
+
+    def __getitem__(self, key):
+        if key in self._cache:
+            return self._cache[key]
+        if key not in self._KEYS:
+            raise KeyError(key)
+        pl, ws = self._plan, self._ws
+        if key == "capacity":
+            v = pl.capacity
+        elif key == "load_balance":
+            v = pl.view(ws, "losses")[1]
+        elif key == "z_loss":
+            v = pl.view(ws, "losses")[2]
+        elif key == "dropped":
+            v = pl.view(ws, "meta")[2]
+        else:
+            v = pl.view(ws, self._ALIAS.get(key, key))
+        self._cache[key] = v
+        return v
+
+    def __iter__(self):
+        return iter(self._KEYS)
+
+    def __len__(self):
+        return len(self._KEYS)
 
 
 class _MoEFunction(torch.autograd.Function):
-    """fwd: router -> plan -> permute -> up(+GELU) -> down -> combine;  bwd mirrors it (A.12 router gradient)."""
+    """One C call each way: b200moe_layer_fwd (router -> plan -> permute -> up(+GELU) -> down -> combine) and
+    b200moe_layer_bwd (mirror, incl. the A.12 router gradient); the context bias of A.2 and its gradient are one
+    more small kernel each."""
 
     @staticmethod
-    def forward(ctx, x2, ctx_bias, wg, w1, b1, w2, b2, mod, tokens_per_image):
+    def forward(ctx, x2, context, wg, wc, w1, b1, w2, b2, mod, tpi, *tables):
         T, d = x2.shape
-        E, k = mod.num_experts, mod.top_k
+        dev = x2.device
+        E = mod.num_experts
         need_grad = any(ctx.needs_input_grad)   # forward runs under no_grad: ask autograd, not the grad mode
-        w1b, w2b = mod._bf16_weight("w1", w1), mod._bf16_weight("w2", w2)
+        pl = mod._layer_plan(T, tpi)
+        w1b, w2b, wsplit, wgf = mod._prepared(w1, w2, wg)
         b1f, b2f = b1.float().contiguous(), b2.float().contiguous()
-        wgf = wg.float().contiguous()
-        cb = ctx_bias.float().contiguous() if ctx_bias is not None else None
-
-        r = ops.router_fwd(x2, wgf, cb, tokens_per_image, k, mod.normalize_topk)
-        cap = ops.capacity_of(mod.capacity_factor, T, k, E)
-        p = ops.plan(r, T, k, E, cap, mod.aux_loss_weight, mod.z_loss_weight)
-        xp = ops.permute(x2, p.token_of_row, p.meta, p.rows_cap)
-        pre, h = ops.ffn_up(xp, w1b, b1f, p.meta, p.tile_expert, save_pre=need_grad)
-        yo = ops.ffn_down(h, w2b, b2f, p.meta, p.tile_expert)
-        y = ops.combine(yo, p.row_of_assignment, r.topk_gate)
-
-        ctx.mod, ctx.tpi, ctx.plan, ctx.routing = mod, tokens_per_image, p, r
-        ctx.has_ctx = ctx_bias is not None
-        ctx.dtypes = (w1.dtype, b1.dtype, w2.dtype, b2.dtype, wg.dtype)
-        ctx.save_for_backward(x2, wgf, w1b, w2b, xp, pre, h, yo)
-        aux = p.losses[0]
-        stats = p.losses.detach()
+        st = _lib.stream_ptr()
+        cb = None
+        if context is not None and wc is not None:
+            B = context.shape[0]
+            cb = torch.empty((B, E), dtype=torch.float32, device=dev)
+            tabs = [t.float().contiguous() for t in tables]
+            wcf = wc.float().contiguous()
+            tp, vp = mod._ctx_arrays(tabs)
+            _lib.call("b200moe_ctx_bias_fwd", context.data_ptr(), tp, vp, len(tabs), mod.context_dim, wcf.data_ptr(),
+                      B, E, cb.data_ptr(), st)
+            ctx.ctx_saved = (context, tabs, wcf)
+        ws = torch.empty((pl.ws_bytes,), dtype=torch.uint8, device=dev)
+        y = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
+        _lib.call("b200moe_layer_fwd", pl.desc_ptr, x2.data_ptr(), cb.data_ptr() if cb is not None else None,
+                  wsplit.data_ptr(), w1b.data_ptr(), b1f.data_ptr(), w2b.data_ptr(), b2f.data_ptr(), ws.data_ptr(),
+                  y.data_ptr(), int(need_grad), st)
+        ctx.mod, ctx.pl, ctx.has_ctx = mod, pl, cb is not None
+        ctx.dtypes = (wg.dtype, w1.dtype, b1.dtype, w2.dtype, b2.dtype)
+        ctx.save_for_backward(x2, wgf, w1b, w2b, ws)
+        losses = pl.view(ws, "losses")
+        aux = losses[0]
+        stats = losses.detach()
         ctx.mark_non_differentiable(stats)
-        mod._stash(r, p)
+        mod._last_ws = (pl, ws)
         return y, aux, stats
 
     @staticmethod
     def backward(ctx, dy, d_aux, _d_stats):
-        x2, wgf, w1b, w2b, xp, pre, h, yo = ctx.saved_tensors
-        mod, p, r = ctx.mod, ctx.plan, ctx.routing
+        x2, wgf, w1b, w2b, ws = ctx.saved_tensors
+        mod, pl = ctx.mod, ctx.pl
         T, d = x2.shape
-        E, k = mod.num_experts, mod.top_k
-        need = ctx.needs_input_grad
+        E, F = mod.num_experts, mod.dim_feedforward
+        dev = x2.device
+        need = ctx.needs_input_grad      # x2, context, wg, wc, w1, b1, w2, b2, mod, tpi, *tables
         if dy is None:
             dy = torch.zeros_like(x2)
         dy = dy.contiguous().to(torch.bfloat16)
         d_aux_t = d_aux.float().contiguous() if d_aux is not None else None
-
-        dyp, dgate_row = ops.combine_bwd(dy, yo, p.token_of_row, p.gate_of_row, p.meta, p.rows_cap)
-        dhpre = ops.ffn_dgrad_down(dyp, w2b, pre, p.meta, p.tile_expert)
-        dw2 = db2 = dw1 = db1 = None
-        if need[5]:
-            dw2 = ops.ffn_wgrad(dyp, h, p.expert_offsets, E)
-        if need[6]:
-            db2 = ops.colsum(dyp, p.expert_offsets, E)
-        if need[3]:
-            dw1 = ops.ffn_wgrad(dhpre, xp, p.expert_offsets, E)
-        if need[4]:
-            db1 = ops.colsum(dhpre, p.expert_offsets, E)
-        dlogits = ops.router_bwd_dlogits(r.logits, r.topk_idx, p.row_of_assignment, dgate_row, p.tokens_per_expert,
-                                         d_aux_t, mod.normalize_topk, mod.aux_loss_weight, mod.z_loss_weight)
-        dx = None
-        if need[0]:
-            dxp = ops.ffn_dgrad_up(dhpre, w1b, p.meta, p.tile_expert)
-            dx = ops.unpermute_bwd(dxp, p.row_of_assignment, dlogits, wgf, T, k, d)
-        dwg = ops.router_bwd_dwg(dlogits, x2) if need[2] else None
-        dctx = ops.router_bwd_dctx(dlogits, ctx.tpi) if (ctx.has_ctx and need[1]) else None
-        t_w1, t_b1, t_w2, t_b2, t_wg = ctx.dtypes
+        f32 = torch.float32
+        dx = torch.empty((T, d), dtype=torch.bfloat16, device=dev) if need[0] else None
+        dwg = torch.empty((E, d), dtype=f32, device=dev) if need[2] else None
+        dw1 = torch.empty((E, F, d), dtype=f32, device=dev) if need[4] else None
+        db1 = torch.empty((E, F), dtype=f32, device=dev) if need[5] else None
+        dw2 = torch.empty((E, d, F), dtype=f32, device=dev) if need[6] else None
+        db2 = torch.empty((E, d), dtype=f32, device=dev) if need[7] else None
+        want_ctx = ctx.has_ctx and (need[3] or any(need[10:]))
+        dcb = None
+        if want_ctx:
+            B = ctx.ctx_saved[0].shape[0]
+            dcb = torch.empty((B, E), dtype=f32, device=dev)
+        bws = torch.empty((pl.bws_bytes,), dtype=torch.uint8, device=dev)
+        p = lambda t: t.data_ptr() if t is not None else None  # noqa: E731
+        st = _lib.stream_ptr()
+        _lib.call("b200moe_layer_bwd", pl.desc_ptr, x2.data_ptr(), wgf.data_ptr(), w1b.data_ptr(), w2b.data_ptr(),
+                  ws.data_ptr(), bws.data_ptr(), dy.data_ptr(), p(d_aux_t), p(dx), p(dcb), p(dwg), p(dw1), p(db1),
+                  p(dw2), p(db2), int(ctx.has_ctx), st)
+        dwc, dtabs = None, ()
+        if want_ctx:
+            context, tabs, wcf = ctx.ctx_saved
+            dwc = torch.empty_like(wcf)
+            flat = torch.empty((sum(t.numel() for t in tabs),), dtype=f32, device=dev)
+            dtabs, o = [], 0
+            for t in tabs:
+                dtabs.append(flat[o:o + t.numel()].view(t.shape))
+                o += t.numel()
+            tp, vp = mod._ctx_arrays(tabs)
+            dp = (C.c_void_p * len(tabs))(*[t.data_ptr() for t in dtabs])
+            _lib.call("b200moe_ctx_bias_bwd", context.data_ptr(), dcb.data_ptr(), tp, vp, len(tabs), mod.context_dim,
+                      wcf.data_ptr(), context.shape[0], E, C.addressof(dp), dwc.data_ptr(), st)
+            dtabs = tuple(dtabs)
+        t_wg, t_w1, t_b1, t_w2, t_b2 = ctx.dtypes
 
         def cast(g, dt):
             return g if g is None or g.dtype == dt else g.to(dt)
-        return (dx, dctx, cast(dwg, t_wg), cast(dw1, t_w1), cast(db1, t_b1), cast(dw2, t_w2), cast(db2, t_b2),
-                None, None)
+        n_tab = len(need) - 10
+        if not dtabs:
+            dtabs = (None,) * n_tab
+        return (dx, None, cast(dwg, t_wg), dwc, cast(dw1, t_w1), cast(db1, t_b1), cast(dw2, t_w2), cast(db2, t_b2),
+                None, None, *dtabs)
 
 
 class ContextMoE(nn.Module):
@@ -136,8 +241,9 @@ class ContextMoE(nn.Module):
         self.b2 = nn.Parameter(torch.empty(E, d))
         self.reset_parameters()
         self.aux_loss = torch.zeros(())
-        self.last_aux: dict = {}
-        self._wcache: dict = {}
+        self.last_aux = {}
+        self._wcache: dict = {}      # bf16 operand copies of the weights, keyed by parameter version
+        self._plans: dict = {}       # (T, tokens_per_image) -> _LayerPlan
 
     # module invariants (§8(b)): deepcopy-safe, plain state_dict -> caches and process groups are not copied
     def __deepcopy__(self, memo):
@@ -145,9 +251,9 @@ class ContextMoE(nn.Module):
         new = self.__class__.__new__(self.__class__)
         memo[id(self)] = new
         for k_, v in self.__dict__.items():
-            if k_ == "_ep_comm_stream":
+            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep"):
                 continue
-            if k_ in ("_wcache", "last_aux"):
+            if k_ in ("_wcache", "last_aux", "_plans"):
                 new.__dict__[k_] = {}
             elif k_ == "aux_loss":
                 new.__dict__[k_] = torch.zeros(())
@@ -159,8 +265,9 @@ class ContextMoE(nn.Module):
 
     def __getstate__(self):
         s = dict(self.__dict__)
-        s["_wcache"], s["last_aux"], s["aux_loss"], s["ep_group"] = {}, {}, torch.zeros(()), None
-        s.pop("_ep_comm_stream", None)
+        s["_wcache"], s["last_aux"], s["aux_loss"], s["ep_group"], s["_plans"] = {}, {}, torch.zeros(()), None, {}
+        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep"):
+            s.pop(k_, None)
         return s
 
     def reset_parameters(self):
@@ -198,6 +305,45 @@ class ContextMoE(nn.Module):
     def _stash(self, r, p):
         self._last = (r, p)
 
+    def _layer_plan(self, T: int, tpi: int) -> _LayerPlan:
+        pl = self._plans.get((T, tpi))
+        if pl is None:
+            if len(self._plans) > 64:       # multiscale training varies T per step (dataloader.yml:22)
+                self._plans.clear()
+            pl = self._plans[(T, tpi)] = _LayerPlan(self, T, tpi)
+        return pl
+
+    def _prepared(self, w1, w2, wg):
+        """bf16 operand copies of w1 / w2 and the bf16 hi/lo split of the gate (one launch), redone only when a
+        parameter changed (version counters).  Returns (w1_bf16, w2_bf16, wg_split, wg_fp32)."""
+        key = (w1.data_ptr(), w1._version, w2.data_ptr(), w2._version, wg.data_ptr(), wg._version, str(w1.device))
+        hit = self._wcache.get("prep")
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        dev, bf = w1.device, torch.bfloat16
+        w1d, w2d = w1.detach().contiguous(), w2.detach().contiguous()
+        wgf = wg.detach().float().contiguous()
+        w1b = w1d if w1d.dtype == bf else torch.empty(w1d.shape, dtype=bf, device=dev)
+        w2b = w2d if w2d.dtype == bf else torch.empty(w2d.shape, dtype=bf, device=dev)
+        nsplit = _lib.load().b200moe_router_scratch_bytes(self.d_model, self.num_experts) // 2
+        wsplit = torch.empty((nsplit,), dtype=bf, device=dev)
+        w1f = w1d.float() if w1d.dtype not in (bf, torch.float32) else w1d
+        w2f = w2d.float() if w2d.dtype not in (bf, torch.float32) else w2d
+        _lib.call("b200moe_prepare_weights",
+                  w1f.data_ptr() if w1b is not w1d else None, w1b.data_ptr(), w1f.numel() if w1b is not w1d else 0,
+                  w2f.data_ptr() if w2b is not w2d else None, w2b.data_ptr(), w2f.numel() if w2b is not w2d else 0,
+                  wgf.data_ptr(), wsplit.data_ptr(), self.d_model, self.num_experts, _lib.stream_ptr())
+        out = (w1b, w2b, wsplit, wgf)
+        self._wcache["prep"] = (key, out)
+        return out
+
+    def _ctx_arrays(self, tabs):
+        """HOST arrays (device pointers of the embedding tables, their vocabulary sizes) for the ctx_bias calls."""
+        arr = (C.c_void_p * len(tabs))(*[t.data_ptr() for t in tabs])
+        voc = (C.c_int32 * len(tabs))(*[t.shape[0] for t in tabs])
+        self._ctx_keep = (arr, voc)
+        return C.addressof(arr), C.addressof(voc)
+
     def context_bias(self, context: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
         """A.2: ctx_bias[B,E] = concat_i Embed_i(context[:, i]) @ Wc^T (fp32 regardless of autocast)."""
         if context is None or self.ctx_proj is None:
@@ -222,17 +368,23 @@ class ContextMoE(nn.Module):
             raise ValueError("context must have one row per image")
         tpi = T // B
         xb = x2.to(torch.bfloat16).contiguous()
-        cb = self.context_bias(context)
         if self.ep_size > 1:
             from .ep import ep_forward
-            y, aux, stats = ep_forward(self, xb, cb, tpi)
-        else:
-            y, aux, stats = _MoEFunction.apply(xb, cb, self.gate.weight, self.w1, self.b1, self.w2, self.b2, self, tpi)
+            y, aux, stats = ep_forward(self, xb, self.context_bias(context), tpi)
+            self.aux_loss = aux
+            r, p = self._last
+            self.last_aux = {"load_balance": stats[1], "z_loss": stats[2], "tokens_per_expert": p.tokens_per_expert,
+                             "kept_per_expert": p.kept_per_expert, "dropped": p.meta[2], "logits": r.logits,
+                             "topk_idx": r.topk_idx, "gates": r.topk_gate, "row_of_assignment": p.row_of_assignment,
+                             "token_of_row": p.token_of_row, "expert_offsets": p.expert_offsets, "meta": p.meta,
+                             "capacity": p.capacity}
+            return y.to(x.dtype).reshape(shape)
+        use_ctx = context is not None and self.ctx_proj is not None
+        ctx_ids = context.long().contiguous() if use_ctx else None
+        tables = [m.weight for m in self.ctx_embed] if use_ctx else []
+        y, aux, _stats = _MoEFunction.apply(xb, ctx_ids, self.gate.weight,
+                                            self.ctx_proj.weight if use_ctx else None, self.w1, self.b1, self.w2,
+                                            self.b2, self, tpi, *tables)
         self.aux_loss = aux
-        r, p = self._last
-        self.last_aux = {"load_balance": stats[1], "z_loss": stats[2], "tokens_per_expert": p.tokens_per_expert,
-                         "kept_per_expert": p.kept_per_expert, "dropped": p.meta[2], "logits": r.logits,
-                         "topk_idx": r.topk_idx, "gates": r.topk_gate, "row_of_assignment": p.row_of_assignment,
-                         "token_of_row": p.token_of_row, "expert_offsets": p.expert_offsets, "meta": p.meta,
-                         "capacity": p.capacity}
+        self.last_aux = _Aux(*self._last_ws)
         return y.to(x.dtype).reshape(shape)

@@ -184,15 +184,21 @@ def ffn_wgrad(a, b, expert_offsets, E: int, out: Optional[torch.Tensor] = None, 
     return out
 
 
-def colsum(a, expert_offsets, E: int, out: Optional[torch.Tensor] = None, accumulate: bool = False):
-    rows_cap, n = a.shape
+def colsum(a, expert_offsets, E: int, out: Optional[torch.Tensor] = None, accumulate: bool = False,
+           a1: Optional[torch.Tensor] = None, out1: Optional[torch.Tensor] = None):
+    """db[e,:] = column sums of a over the rows of expert e (and the same for a1 in the same launch)."""
+    n = a.shape[1]
     if out is None:
         out = _empty((E, n), torch.float32, a.device)
         accumulate = False
-    scratch = _empty((rows_cap // ROW_PAD, n), torch.float32, a.device)
-    call("b200moe_colsum", ptr(a), ptr(expert_offsets), rows_cap, n, E, ptr(scratch), ptr(out), int(accumulate),
+    n1 = 0
+    if a1 is not None:
+        n1 = a1.shape[1]
+        if out1 is None:
+            out1 = _empty((E, n1), torch.float32, a.device)
+    call("b200moe_colsum", ptr(a), n, ptr(out), ptr(a1), n1, ptr(out1), ptr(expert_offsets), E, int(accumulate),
          stream_ptr())
-    return out
+    return out if a1 is None else (out, out1)
 
 
 def router_bwd_dlogits(logits, topk_idx, row_of_assignment, dgate_row, tokens_per_expert, d_aux, normalize: bool,

@@ -1,0 +1,314 @@
+// Whole-layer entry points (include/b200moe.h): one C call runs every kernel of the forward (or backward) pass of
+// the context-gated MoE layer on the caller's stream, out of two caller-owned workspaces, so the host language pays
+// one FFI crossing per pass instead of one per kernel.  Also the context-bias kernels.
+#include "common.cuh"
+
+namespace b200moe {
+
+static inline int64_t align256(int64_t v) { return (v + 255) & ~static_cast<int64_t>(255); }
+
+// Optional per-kernel CUDA-event timing of the whole-layer calls (bench.py's roofline pass): events are recorded on
+// the launching stream around every step and read back with b200moe_layer_profile_read after a synchronize.
+constexpr int kMaxProf = 4096;
+struct ProfEntry { const char* name; cudaEvent_t a, b; };
+static bool g_prof_on = false;
+static ProfEntry g_prof[kMaxProf];
+static int g_prof_n = 0;
+
+struct ProfScope {
+  cudaStream_t st;
+  bool live;
+  ProfScope(const char* name, void* stream) : st(static_cast<cudaStream_t>(stream)), live(g_prof_on && g_prof_n < kMaxProf) {
+    if (!live) return;
+    ProfEntry& e = g_prof[g_prof_n];
+    e.name = name;
+    cudaEventCreate(&e.a);
+    cudaEventCreate(&e.b);
+    cudaEventRecord(e.a, st);
+  }
+  ~ProfScope() {
+    if (!live) return;
+    cudaEventRecord(g_prof[g_prof_n].b, st);
+    ++g_prof_n;
+  }
+};
+#define STEP(name, call)            \
+  do {                              \
+    ProfScope ps_(name, stream);    \
+    rc = (call);                    \
+  } while (0);                      \
+  if (rc) return rc
+
+static int check_desc(const b200moe_layer_desc* q, const char* what) {
+  B200MOE_REQUIRE(q != nullptr, B200MOE_EINVAL, "%s: NULL descriptor", what);
+  B200MOE_REQUIRE(q->T > 0, B200MOE_EINVAL, "%s: T=%d must be positive", what, q->T);
+  B200MOE_REQUIRE(q->d >= 128 && q->d % 128 == 0 && q->F >= 128 && q->F % 128 == 0, B200MOE_EINVAL,
+                  "%s: d_model=%d and dim_feedforward=%d must be multiples of 128", what, q->d, q->F);
+  B200MOE_REQUIRE(q->E >= 1 && q->E <= 64 && q->k >= 1 && q->k <= 8 && q->k <= q->E, B200MOE_EINVAL,
+                  "%s: bad num_experts=%d / top_k=%d", what, q->E, q->k);
+  B200MOE_REQUIRE(q->capacity >= 0, B200MOE_EINVAL, "%s: negative capacity", what);
+  B200MOE_REQUIRE(q->rows_cap > 0 && q->rows_cap % kRowPad == 0 &&
+                      q->rows_cap >= b200moe_rows_upper_bound(q->T, q->k, q->E, q->capacity),
+                  B200MOE_EINVAL, "%s: rows_cap=%d is not b200moe_rows_upper_bound(T,k,E,capacity)", what, q->rows_cap);
+  return B200MOE_OK;
+}
+
+// ---- context bias ---------------------------------------------------------------------------------------------
+struct CtxTables {
+  const float* table[B200MOE_MAX_CTX_FIELDS];
+  float* dtable[B200MOE_MAX_CTX_FIELDS];
+  int vocab[B200MOE_MAX_CTX_FIELDS];
+};
+
+// one block per image, thread per expert-strided output; the n*cd-long embedding row sits in shared memory
+__global__ void __launch_bounds__(128)
+ctx_bias_fwd_kernel(const int64_t* __restrict__ context, const CtxTables tb, int n, int cd,
+                    const float* __restrict__ wc, int E, float* __restrict__ out) {
+  extern __shared__ float emb_s[];   // [n*cd]
+  const int b = blockIdx.x;
+  for (int i = threadIdx.x; i < n * cd; i += blockDim.x) {
+    const int f = i / cd, j = i - f * cd;
+    const long long id = context[static_cast<size_t>(b) * n + f];
+    emb_s[i] = (id >= 0 && id < tb.vocab[f]) ? tb.table[f][static_cast<size_t>(id) * cd + j] : 0.f;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int e = warp; e < E; e += 4) {
+    float s = 0.f;
+    for (int i = lane; i < n * cd; i += 32) s = fmaf(emb_s[i], wc[static_cast<size_t>(e) * n * cd + i], s);
+    s = warp_sum(s);
+    if (lane == 0) out[static_cast<size_t>(b) * E + e] = s;
+  }
+}
+
+// dwc[e, i] = sum_b dctx[b,e] * emb_b[i];  dtable_f[v, j] = sum_{b: ctx[b,f]=v} sum_e dctx[b,e] * wc[e, f*cd+j]
+// One thread per output element, images in increasing order (deterministic).
+__global__ void __launch_bounds__(256)
+ctx_bias_bwd_kernel(const int64_t* __restrict__ context, const float* __restrict__ dctx, const CtxTables tb, int n,
+                    int cd, const float* __restrict__ wc, int B, int E, float* __restrict__ dwc, int n_dwc,
+                    int n_tab) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n_dwc) {
+    const int e = i / (n * cd), c = i - e * (n * cd);
+    const int f = c / cd, j = c - f * cd;
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) {
+      const long long id = context[static_cast<size_t>(b) * n + f];
+      if (id >= 0 && id < tb.vocab[f]) s = fmaf(dctx[static_cast<size_t>(b) * E + e], tb.table[f][static_cast<size_t>(id) * cd + j], s);
+    }
+    dwc[i] = s;
+  } else if (i < n_dwc + n_tab) {
+    int r = i - n_dwc;
+    int f = 0;
+    while (r >= tb.vocab[f] * cd) { r -= tb.vocab[f] * cd; ++f; }
+    const int v = r / cd, j = r - v * cd;
+    float s = 0.f;
+    for (int b = 0; b < B; ++b) {
+      if (context[static_cast<size_t>(b) * n + f] != v) continue;
+      float g = 0.f;
+      for (int e = 0; e < E; ++e) g = fmaf(dctx[static_cast<size_t>(b) * E + e], wc[static_cast<size_t>(e) * n * cd + f * cd + j], g);
+      s += g;
+    }
+    tb.dtable[f][r] = s;
+  }
+}
+
+static int fill_tables(CtxTables* tb, const float* const* tables, float* const* dtables, const int32_t* vocab, int n,
+                       const char* what) {
+  B200MOE_REQUIRE(n >= 1 && n <= B200MOE_MAX_CTX_FIELDS, B200MOE_EINVAL, "%s: n_fields=%d outside [1,%d]", what, n,
+                  B200MOE_MAX_CTX_FIELDS);
+  for (int i = 0; i < B200MOE_MAX_CTX_FIELDS; ++i) {
+    tb->table[i] = i < n ? tables[i] : nullptr;
+    tb->dtable[i] = (i < n && dtables) ? dtables[i] : nullptr;
+    tb->vocab[i] = i < n ? vocab[i] : 0;
+    if (i < n) B200MOE_REQUIRE(tables[i] != nullptr && vocab[i] > 0, B200MOE_EINVAL, "%s: bad table %d", what, i);
+  }
+  return B200MOE_OK;
+}
+
+}  // namespace b200moe
+
+using namespace b200moe;
+
+extern "C" int b200moe_ctx_bias_fwd(const int64_t* context, const float* const* tables, const int32_t* vocab,
+                                    int n_fields, int context_dim, const float* wc, int B, int E, float* ctx_bias,
+                                    void* stream) {
+  CtxTables tb;
+  if (int rc = fill_tables(&tb, tables, nullptr, vocab, n_fields, "ctx_bias_fwd")) return rc;
+  B200MOE_REQUIRE(context_dim > 0 && n_fields * context_dim <= 8192 && B > 0 && E >= 1 && E <= 64, B200MOE_EINVAL,
+                  "ctx_bias_fwd: bad shape (context_dim=%d, B=%d, E=%d)", context_dim, B, E);
+  if (int rc = b200moe_check_device()) return rc;
+  ctx_bias_fwd_kernel<<<B, 128, sizeof(float) * n_fields * context_dim, static_cast<cudaStream_t>(stream)>>>(
+      context, tb, n_fields, context_dim, wc, E, ctx_bias);
+  return check_launch("ctx_bias_fwd");
+}
+
+extern "C" int b200moe_ctx_bias_bwd(const int64_t* context, const float* dctx_bias, const float* const* tables,
+                                    const int32_t* vocab, int n_fields, int context_dim, const float* wc, int B,
+                                    int E, float* const* dtables, float* dwc, void* stream) {
+  CtxTables tb;
+  if (int rc = fill_tables(&tb, tables, dtables, vocab, n_fields, "ctx_bias_bwd")) return rc;
+  B200MOE_REQUIRE(dtables != nullptr && dwc != nullptr && dctx_bias != nullptr, B200MOE_EINVAL, "ctx_bias_bwd: NULL output");
+  for (int i = 0; i < n_fields; ++i)
+    B200MOE_REQUIRE(dtables[i] != nullptr, B200MOE_EINVAL, "ctx_bias_bwd: dtables[%d] is NULL", i);
+  if (int rc = b200moe_check_device()) return rc;
+  int n_tab = 0;
+  for (int i = 0; i < n_fields; ++i) n_tab += vocab[i] * context_dim;
+  const int n_dwc = E * n_fields * context_dim;
+  const int total = n_dwc + n_tab;
+  ctx_bias_bwd_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      context, dctx_bias, tb, n_fields, context_dim, wc, B, E, dwc, n_dwc, n_tab);
+  return check_launch("ctx_bias_bwd");
+}
+
+extern "C" int b200moe_layer_profile(int enable) {
+  for (int i = 0; i < g_prof_n; ++i) { cudaEventDestroy(g_prof[i].a); cudaEventDestroy(g_prof[i].b); }
+  g_prof_n = 0;
+  g_prof_on = enable != 0;
+  return B200MOE_OK;
+}
+
+extern "C" int b200moe_layer_profile_read(int index, const char** name, float* ms) {
+  if (index < 0 || index >= g_prof_n || !name || !ms) return B200MOE_EINVAL;
+  *name = g_prof[index].name;
+  cudaError_t e = cudaEventElapsedTime(ms, g_prof[index].a, g_prof[index].b);
+  if (e != cudaSuccess) { set_error("layer_profile_read: %s", cudaGetErrorString(e)); cudaGetLastError(); return B200MOE_ECUDA; }
+  return B200MOE_OK;
+}
+
+extern "C" int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* q, int64_t* off) {
+  if (check_desc(q, "layer_ws_layout") != B200MOE_OK || off == nullptr) return -1;
+  const int64_t T = q->T, d = q->d, F = q->F, E = q->E, k = q->k, R = q->rows_cap;
+  const int64_t nblk = b200moe_num_router_blocks(q->T);
+  int64_t bytes[B200MOE_WS_COUNT];
+  bytes[B200MOE_WS_LOGITS] = T * E * 4;
+  bytes[B200MOE_WS_TOPK_IDX] = T * k * 4;
+  bytes[B200MOE_WS_TOPK_GATE] = T * k * 4;
+  bytes[B200MOE_WS_BLOCK_COUNTS] = nblk * k * E * 4;
+  bytes[B200MOE_WS_BLOCK_STATS] = nblk * (E + 1) * 4;
+  bytes[B200MOE_WS_EXPERT_OFFSETS] = (E + 1) * 4;
+  bytes[B200MOE_WS_META] = B200MOE_META_INTS * 4;
+  bytes[B200MOE_WS_TILE_EXPERT] = (R / kRowPad) * 4;
+  bytes[B200MOE_WS_TOKENS_PER_EXPERT] = E * 4;
+  bytes[B200MOE_WS_KEPT_PER_EXPERT] = E * 4;
+  bytes[B200MOE_WS_LOSSES] = 3 * 4;
+  bytes[B200MOE_WS_SLOT_LIMIT] = k * E * 4;
+  bytes[B200MOE_WS_ROW_OF_ASSIGNMENT] = T * k * 4;
+  bytes[B200MOE_WS_TOKEN_OF_ROW] = R * 4;
+  bytes[B200MOE_WS_GATE_OF_ROW] = R * 4;
+  bytes[B200MOE_WS_XP] = R * d * 2;
+  bytes[B200MOE_WS_PRE] = R * F * 2;
+  bytes[B200MOE_WS_H] = R * F * 2;
+  bytes[B200MOE_WS_YO] = R * d * 2;
+  int64_t at = 0;
+  for (int i = 0; i < B200MOE_WS_COUNT; ++i) { off[i] = at; at += align256(bytes[i]); }
+  return at;
+}
+
+extern "C" int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* q, int64_t* off) {
+  if (check_desc(q, "layer_bwd_ws_layout") != B200MOE_OK || off == nullptr) return -1;
+  const int64_t T = q->T, d = q->d, F = q->F, E = q->E, R = q->rows_cap;
+  int64_t bytes[B200MOE_BWS_COUNT];
+  bytes[B200MOE_BWS_DYP] = R * d * 2;
+  bytes[B200MOE_BWS_DGATE_ROW] = R * 4;
+  bytes[B200MOE_BWS_DHPRE] = R * F * 2;
+  bytes[B200MOE_BWS_DXP] = R * d * 2;
+  bytes[B200MOE_BWS_DLOGITS] = T * E * 4;
+  bytes[B200MOE_BWS_DWG_SCRATCH] = b200moe_dwg_scratch_floats(q->T, q->d, q->E) * 4;
+  int64_t at = 0;
+  for (int i = 0; i < B200MOE_BWS_COUNT; ++i) { off[i] = at; at += align256(bytes[i]); }
+  return at;
+}
+
+#define WS(T_, i) reinterpret_cast<T_*>(base + off[i])
+
+extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, const float* ctx_bias,
+                                 const void* wg_split, const void* w1, const float* b1, const void* w2,
+                                 const float* b2, void* ws, void* y, int save_for_backward, void* stream) {
+  if (int rc = check_desc(q, "layer_fwd")) return rc;
+  B200MOE_REQUIRE(x && wg_split && w1 && b1 && w2 && b2 && ws && y, B200MOE_EINVAL, "layer_fwd: NULL argument");
+  int64_t off[B200MOE_WS_COUNT];
+  b200moe_layer_ws_layout(q, off);
+  unsigned char* base = static_cast<unsigned char*>(ws);
+  const int T = q->T, d = q->d, F = q->F, E = q->E, k = q->k, R = q->rows_cap;
+  const int32_t* meta = WS(int32_t, B200MOE_WS_META);
+  const int32_t* tile_expert = WS(int32_t, B200MOE_WS_TILE_EXPERT);
+  int rc;
+  STEP("router_fwd",
+       b200moe_router_fwd(x, ctx_bias, q->tokens_per_image, nullptr, const_cast<void*>(wg_split), T, d, E, k,
+                          q->normalize_topk, WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX),
+                          WS(float, B200MOE_WS_TOPK_GATE), WS(int32_t, B200MOE_WS_BLOCK_COUNTS),
+                          WS(float, B200MOE_WS_BLOCK_STATS), stream));
+  STEP("plan",
+       b200moe_plan(WS(int32_t, B200MOE_WS_TOPK_IDX), WS(float, B200MOE_WS_TOPK_GATE),
+                    WS(int32_t, B200MOE_WS_BLOCK_COUNTS), WS(float, B200MOE_WS_BLOCK_STATS), T, k, E, q->capacity,
+                    nullptr, nullptr, kRowPad, R, q->aux_loss_weight, q->z_loss_weight,
+                    WS(int32_t, B200MOE_WS_EXPERT_OFFSETS), WS(int32_t, B200MOE_WS_META),
+                    WS(int32_t, B200MOE_WS_TILE_EXPERT), WS(int32_t, B200MOE_WS_TOKENS_PER_EXPERT),
+                    WS(int32_t, B200MOE_WS_KEPT_PER_EXPERT), WS(float, B200MOE_WS_LOSSES),
+                    WS(int32_t, B200MOE_WS_SLOT_LIMIT), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
+                    WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW), stream));
+  STEP("permute", b200moe_permute(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP), stream));
+  STEP("ffn_up", b200moe_ffn_up(WS(void, B200MOE_WS_XP), w1, b1, meta, tile_expert, R, d, F, E,
+                                save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H), stream));
+  STEP("ffn_down", b200moe_ffn_down(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert, R, d, F, E,
+                                    WS(void, B200MOE_WS_YO), stream));
+  STEP("combine", b200moe_combine(WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
+                                  WS(float, B200MOE_WS_TOPK_GATE), T, k, d, y, stream));
+  return B200MOE_OK;
+}
+
+extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, const float* wg, const void* w1,
+                                 const void* w2, const void* ws, void* bws, const void* dy, const float* d_aux,
+                                 void* dx, float* dctx_bias, float* dwg, float* dw1, float* db1, float* dw2,
+                                 float* db2, int has_ctx_bias, void* stream) {
+  if (int rc = check_desc(q, "layer_bwd")) return rc;
+  B200MOE_REQUIRE(x && wg && w1 && w2 && ws && bws && dy, B200MOE_EINVAL, "layer_bwd: NULL argument");
+  int64_t off[B200MOE_WS_COUNT], boff[B200MOE_BWS_COUNT];
+  b200moe_layer_ws_layout(q, off);
+  b200moe_layer_bwd_ws_layout(q, boff);
+  unsigned char* base = static_cast<unsigned char*>(const_cast<void*>(ws));
+  unsigned char* bbase = static_cast<unsigned char*>(bws);
+#define BWS(T_, i) reinterpret_cast<T_*>(bbase + boff[i])
+  const int T = q->T, d = q->d, F = q->F, E = q->E, k = q->k, R = q->rows_cap;
+  const int32_t* meta = WS(int32_t, B200MOE_WS_META);
+  const int32_t* tile_expert = WS(int32_t, B200MOE_WS_TILE_EXPERT);
+  const int32_t* offs = WS(int32_t, B200MOE_WS_EXPERT_OFFSETS);
+  const int32_t* roa = WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT);
+  void* dyp = BWS(void, B200MOE_BWS_DYP);
+  void* dhpre = BWS(void, B200MOE_BWS_DHPRE);
+  float* dlogits = BWS(float, B200MOE_BWS_DLOGITS);
+  int rc;
+  STEP("combine_bwd",
+       b200moe_combine_bwd(dy, WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_TOKEN_OF_ROW),
+                           WS(float, B200MOE_WS_GATE_OF_ROW), meta, R, d, dyp, BWS(float, B200MOE_BWS_DGATE_ROW), stream));
+  STEP("ffn_dgrad_down",
+       b200moe_ffn_dgrad_down(dyp, w2, WS(void, B200MOE_WS_PRE), meta, tile_expert, R, d, F, E, dhpre, stream));
+  if (dw2) { STEP("ffn_wgrad", b200moe_ffn_wgrad(dyp, WS(void, B200MOE_WS_H), offs, R, d, F, E, dw2, 0, stream)); }
+  if (dw1) { STEP("ffn_wgrad", b200moe_ffn_wgrad(dhpre, WS(void, B200MOE_WS_XP), offs, R, F, d, E, dw1, 0, stream)); }
+  if (db2 && db1) {
+    STEP("colsum", b200moe_colsum(dyp, d, db2, dhpre, F, db1, offs, E, 0, stream));
+  } else if (db2) {
+    STEP("colsum", b200moe_colsum(dyp, d, db2, nullptr, 0, nullptr, offs, E, 0, stream));
+  } else if (db1) {
+    STEP("colsum", b200moe_colsum(dhpre, F, db1, nullptr, 0, nullptr, offs, E, 0, stream));
+  }
+  STEP("router_bwd_dlogits",
+       b200moe_router_bwd_dlogits(WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX), roa,
+                                  BWS(float, B200MOE_BWS_DGATE_ROW), WS(int32_t, B200MOE_WS_TOKENS_PER_EXPERT), d_aux,
+                                  T, E, k, q->normalize_topk, q->aux_loss_weight, q->z_loss_weight, dlogits, stream));
+  if (dx) {
+    void* dxp = BWS(void, B200MOE_BWS_DXP);
+    STEP("ffn_dgrad_up", b200moe_ffn_dgrad_up(dhpre, w1, meta, tile_expert, R, d, F, E, dxp, stream));
+    STEP("unpermute_bwd", b200moe_unpermute_bwd(dxp, roa, dlogits, wg, T, k, d, E, dx, stream));
+  }
+  if (dwg) {
+    STEP("router_bwd_dwg",
+         b200moe_router_bwd_dwg(dlogits, x, T, d, E, BWS(float, B200MOE_BWS_DWG_SCRATCH), dwg, stream));
+  }
+  if (dctx_bias && has_ctx_bias) {
+    STEP("router_bwd_dctx", b200moe_router_bwd_dctx(dlogits, T, E, q->tokens_per_image, dctx_bias, stream));
+  }
+  return B200MOE_OK;
+#undef BWS
+}

@@ -166,58 +166,102 @@ cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ 
     for (int64_t i = n8 * 8 + threadIdx.x; i < n; i += blockDim.x) dst[i] = __float2bfloat16_rn(src[i]);
 }
 
-// db[e, c] = sum over rows of expert e of a[r, c], in two fixed-order stages (deterministic, no atomics):
-//   stage 1: block = (256-column slab, 128-row tile) -> partial[tile][c]; a warp reads 512 contiguous bytes of a row
-//   stage 2: block = (256-column slab, expert)       -> sum of the expert's tiles
-__global__ void __launch_bounds__(256)
-colsum_partial_kernel(const __nv_bfloat16* __restrict__ a, const int32_t* __restrict__ expert_offsets, int E,
-                      int ncols, float* __restrict__ partial) {
-  __shared__ float part[8][256];
-  const int R = expert_offsets[E];
-  const int r0 = blockIdx.y * kRowPad;
-  if (r0 >= R) return;
-  const int chunk = threadIdx.x & 31, phase = threadIdx.x >> 5;
-  const int col0 = blockIdx.x * 256 + chunk * 8;
+// db[e, c] = sum over the rows of expert e of a[r, c] for up to two activation tensors in ONE launch, fixed order
+// (deterministic, no atomics, no scratch).  Block = (64-column slab of one of the tensors, expert), 1024 threads:
+// thread (chunk, phase) owns 8 columns and every 128th row of the expert's segment, four 16-byte loads in flight
+// (64 KB per block), then the 128 phases are summed in a fixed two-level order through shared memory.
+struct ColsumJob {
+  const __nv_bfloat16* a;
+  float* db;
+  int ncols;
+};
+constexpr int kColsumPhases = 128;
+
+__global__ void __launch_bounds__(8 * kColsumPhases)
+colsum_kernel(const ColsumJob j0, const ColsumJob j1, const int32_t* __restrict__ expert_offsets, int accumulate) {
+  __shared__ float part[kColsumPhases][65];
+  __shared__ float part2[8][64];
+  const int slabs0 = j0.ncols >> 6;
+  const bool second = static_cast<int>(blockIdx.x) >= slabs0;
+  const ColsumJob j = second ? j1 : j0;
+  const int slab = second ? blockIdx.x - slabs0 : blockIdx.x;
+  const int e = blockIdx.y;
+  const int r0 = expert_offsets[e], r1 = expert_offsets[e + 1];
+  const int chunk = threadIdx.x & 7, phase = threadIdx.x >> 3;
+  const int col0 = slab * 64 + chunk * 8;
+  const __nv_bfloat16* base = j.a + col0;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  if (col0 < ncols) {
+  for (int r = r0 + phase; r < r1; r += 4 * kColsumPhases) {
     uint4 raw[4];
 #pragma unroll
-    for (int it = 0; it < 4; ++it) {     // 16 rows per thread, 4 loads in flight
+    for (int u = 0; u < 4; ++u) {
+      const int rr = r + kColsumPhases * u;
+      raw[u] = rr < r1 ? ldg128(base + static_cast<size_t>(rr) * j.ncols) : make_uint4(0, 0, 0, 0);
+    }
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
-        raw[u] = ldg128(a + static_cast<size_t>(r0 + phase + 8 * (it * 4 + u)) * ncols + col0);
+    for (int u = 0; u < 4; ++u) {
+      float v[8];
+      unpack8(raw[u], v);
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        float v[8];
-        unpack8(raw[u], v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += v[j];
-      }
+      for (int q = 0; q < 8; ++q) acc[q] += v[q];
     }
   }
 #pragma unroll
-  for (int j = 0; j < 8; ++j) part[phase][chunk * 8 + j] = acc[j];
+  for (int q = 0; q < 8; ++q) part[phase][chunk * 8 + q] = acc[q];
   __syncthreads();
-  const int c = blockIdx.x * 256 + threadIdx.x;
-  if (c < ncols) {
-    float s = 0.f;
+  if (threadIdx.x < 512) {
+    const int g = threadIdx.x >> 6, c = threadIdx.x & 63;
+    float sum = 0.f;
 #pragma unroll
-    for (int p = 0; p < 8; ++p) s += part[p][threadIdx.x];
-    partial[static_cast<size_t>(blockIdx.y) * ncols + c] = s;
+    for (int p = 0; p < 16; ++p) sum += part[g * 16 + p][c];
+    part2[g][c] = sum;
+  }
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float sum = 0.f;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) sum += part2[g][threadIdx.x];
+    float* o = j.db + static_cast<size_t>(e) * j.ncols + slab * 64 + threadIdx.x;
+    *o = accumulate ? *o + sum : sum;
   }
 }
 
+// Once per optimizer step, ONE launch: fp32 master weights of the experts -> bf16 operands, and the gate matrix
+// -> its bf16 hi/lo split for the tcgen05 router (rows 0..E-1 hi, rows EP..EP+E-1 lo = bf16(w - hi), rest zero).
 __global__ void __launch_bounds__(256)
-colsum_reduce_kernel(const float* __restrict__ partial, const int32_t* __restrict__ expert_offsets, int ncols,
-                     float* __restrict__ db, int accumulate) {
-  const int e = blockIdx.y;
-  const int c = blockIdx.x * 256 + threadIdx.x;
-  if (c >= ncols) return;
-  const int t0 = expert_offsets[e] / kRowPad, t1 = expert_offsets[e + 1] / kRowPad;
-  float s = 0.f;
-  for (int t = t0; t < t1; ++t) s += partial[static_cast<size_t>(t) * ncols + c];
-  float* o = db + static_cast<size_t>(e) * ncols + c;
-  *o = accumulate ? *o + s : s;
+prepare_weights_kernel(const float* __restrict__ w1, __nv_bfloat16* __restrict__ w1b, int64_t n1_8,
+                       const float* __restrict__ w2, __nv_bfloat16* __restrict__ w2b, int64_t n2_8,
+                       const float* __restrict__ wg, __nv_bfloat16* __restrict__ wsplit, int E, int EP, int d) {
+  const int64_t ns_8 = wg ? (static_cast<int64_t>(2) * EP * d) >> 3 : 0;
+  const int64_t total = n1_8 + n2_8 + ns_8;
+  const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    if (i < n1_8 + n2_8) {
+      const bool first = i < n1_8;
+      const float* src = first ? w1 : w2;
+      __nv_bfloat16* dst = first ? w1b : w2b;
+      const int64_t c = first ? i : i - n1_8;
+      const float4 a = __ldg(reinterpret_cast<const float4*>(src) + 2 * c);
+      const float4 b = __ldg(reinterpret_cast<const float4*>(src) + 2 * c + 1);
+      const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+      stg128(dst + 8 * c, pack8(v));
+    } else {
+      const int64_t c = i - n1_8 - n2_8;
+      const int64_t el = c * 8;
+      const int row = static_cast<int>(el / d), col = static_cast<int>(el - static_cast<int64_t>(row) * d);
+      const int e = row < EP ? row : row - EP;
+      float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (e < E) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(wg + static_cast<size_t>(e) * d + col));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(wg + static_cast<size_t>(e) * d + col) + 1);
+        const float w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          v[q] = row < EP ? w[q] : w[q] - __bfloat162float(__float2bfloat16_rn(w[q]));
+      }
+      stg128(wsplit + el, pack8(v));
+    }
+  }
 }
 
 static inline int move_grid(long long rows) {
@@ -292,16 +336,34 @@ extern "C" int b200moe_cast_f32_bf16(const float* src, void* dst, int64_t n, voi
   return check_launch("cast_f32_bf16");
 }
 
-extern "C" int b200moe_colsum(const void* a, const int32_t* expert_offsets, int rows_cap, int ncols, int E,
-                              float* scratch, float* db, int accumulate, void* stream) {
-  B200MOE_REQUIRE(ncols > 0 && ncols % 8 == 0, B200MOE_EINVAL, "colsum: ncols=%d must be a multiple of 8", ncols);
-  B200MOE_REQUIRE(rows_cap > 0 && rows_cap % kRowPad == 0, B200MOE_EINVAL, "colsum: rows_cap must be a multiple of 128");
-  B200MOE_REQUIRE(scratch != nullptr, B200MOE_EINVAL, "colsum: scratch of rows_cap/128*ncols floats required");
+extern "C" int b200moe_colsum(const void* a0, int ncols0, float* db0, const void* a1, int ncols1, float* db1,
+                              const int32_t* expert_offsets, int E, int accumulate, void* stream) {
+  B200MOE_REQUIRE(a0 != nullptr && db0 != nullptr && ncols0 > 0 && ncols0 % 64 == 0, B200MOE_EINVAL,
+                  "colsum: ncols=%d must be a positive multiple of 64", ncols0);
+  B200MOE_REQUIRE(a1 == nullptr || (db1 != nullptr && ncols1 > 0 && ncols1 % 64 == 0), B200MOE_EINVAL,
+                  "colsum: second tensor: ncols=%d must be a positive multiple of 64", ncols1);
+  B200MOE_REQUIRE(E >= 1 && E <= 64, B200MOE_EINVAL, "colsum: num_experts=%d outside [1,64]", E);
   if (int rc = b200moe_check_device()) return rc;
-  dim3 g1((ncols + 255) / 256, rows_cap / kRowPad);
-  colsum_partial_kernel<<<g1, 256, 0, ST(stream)>>>(BF(a), expert_offsets, E, ncols, scratch);
-  if (int rc = check_launch("colsum_partial")) return rc;
-  dim3 g2((ncols + 255) / 256, E);
-  colsum_reduce_kernel<<<g2, 256, 0, ST(stream)>>>(scratch, expert_offsets, ncols, db, accumulate);
-  return check_launch("colsum_reduce");
+  ColsumJob j0{BF(a0), db0, ncols0};
+  ColsumJob j1{BF(a1), db1, a1 ? ncols1 : 0};
+  dim3 grid((ncols0 >> 6) + (a1 ? (ncols1 >> 6) : 0), E);
+  colsum_kernel<<<grid, 8 * kColsumPhases, 0, ST(stream)>>>(j0, j1, expert_offsets, accumulate);
+  return check_launch("colsum");
+}
+
+extern "C" int b200moe_prepare_weights(const float* w1, void* w1_bf16, int64_t n1, const float* w2, void* w2_bf16,
+                                       int64_t n2, const float* wg, void* wg_split, int d, int E, void* stream) {
+  B200MOE_REQUIRE(n1 >= 0 && n2 >= 0 && n1 % 8 == 0 && n2 % 8 == 0, B200MOE_EINVAL,
+                  "prepare_weights: element counts must be multiples of 8");
+  B200MOE_REQUIRE(wg == nullptr || (wg_split != nullptr && d > 0 && d % 8 == 0 && E >= 1 && E <= 64), B200MOE_EINVAL,
+                  "prepare_weights: bad gate shape d=%d E=%d", d, E);
+  if (int rc = b200moe_check_device()) return rc;
+  const int EP = E <= 16 ? 16 : (E <= 32 ? 32 : 64);
+  const int64_t total = n1 / 8 + n2 / 8 + (wg ? (static_cast<int64_t>(2) * EP * d) / 8 : 0);
+  if (total == 0) return B200MOE_OK;
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  prepare_weights_kernel<<<static_cast<int>(blocks), 256, 0, ST(stream)>>>(
+      w1, BFW(w1_bf16), n1 / 8, w2, BFW(w2_bf16), n2 / 8, wg, BFW(wg_split), E, EP, d);
+  return check_launch("prepare_weights");
 }

@@ -329,7 +329,7 @@ extern "C" int b200moe_router_fwd(const void* x, const float* ctx_bias, int toke
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (tokens_per_image <= 0) tokens_per_image = T;
   const int EP = router_ep(E);
-  {
+  if (wg != nullptr) {   // NULL: wg_split was already filled by b200moe_prepare_weights
     const int n = 2 * EP * d;
     int blocks = (n + 255) / 256;
     if (blocks > 4 * kNumSMs) blocks = 4 * kNumSMs;
