@@ -97,7 +97,8 @@ def ptr(t: Optional[torch.Tensor]):
 
 
 def stream_ptr() -> int:
-    return torch.cuda.current_stream().cuda_stream
+    """Raw cudaStream_t of torch's current stream on the current device."""
+    return torch._C._cuda_getCurrentRawStream(torch.cuda.current_device())
 
 
 # kernels launched by each entry point (memset nodes not counted); used for bench.py's gpu_launches

@@ -30,6 +30,14 @@ _WS_DTYPES = {"logits": torch.float32, "topk_idx": torch.int32, "topk_gate": tor
               "xp": torch.bfloat16, "pre": torch.bfloat16, "h": torch.bfloat16, "yo": torch.bfloat16}
 
 
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    """fp32 contiguous view of a parameter (the usual case: returned as it is, detached)."""
+    t = t.detach()
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t if t.is_contiguous() else t.contiguous()
+
+
 class _LayerPlan:
     """Host-side description of one (T, tokens_per_image) problem: the C descriptor and both workspace layouts."""
 
@@ -113,14 +121,14 @@ class _MoEFunction(torch.autograd.Function):
         need_grad = any(ctx.needs_input_grad)   # forward runs under no_grad: ask autograd, not the grad mode
         pl = mod._layer_plan(T, tpi)
         w1b, w2b, wsplit, wgf = mod._prepared(w1, w2, wg)
-        b1f, b2f = b1.float().contiguous(), b2.float().contiguous()
+        b1f, b2f = _f32c(b1), _f32c(b2)
         st = _lib.stream_ptr()
         cb = None
         if context is not None and wc is not None:
             B = context.shape[0]
             cb = torch.empty((B, E), dtype=torch.float32, device=dev)
-            tabs = [t.float().contiguous() for t in tables]
-            wcf = wc.float().contiguous()
+            tabs = [_f32c(t) for t in tables]
+            wcf = _f32c(wc)
             tp, vp = mod._ctx_arrays(tabs)
             _lib.call("b200moe_ctx_bias_fwd", context.data_ptr(), tp, vp, len(tabs), mod.context_dim, wcf.data_ptr(),
                       B, E, cb.data_ptr(), st)
@@ -137,7 +145,7 @@ class _MoEFunction(torch.autograd.Function):
         aux = losses[0]
         stats = losses.detach()
         ctx.mark_non_differentiable(stats)
-        mod._last_ws = (pl, ws)
+        mod.__dict__["_last_ws"] = (pl, ws)
         return y, aux, stats
 
     @staticmethod
@@ -151,7 +159,7 @@ class _MoEFunction(torch.autograd.Function):
         if dy is None:
             dy = torch.zeros_like(x2)
         dy = dy.contiguous().to(torch.bfloat16)
-        d_aux_t = d_aux.float().contiguous() if d_aux is not None else None
+        d_aux_t = _f32c(d_aux) if d_aux is not None else None
         f32 = torch.float32
         dx = torch.empty((T, d), dtype=torch.bfloat16, device=dev) if need[0] else None
         dwg = torch.empty((E, d), dtype=f32, device=dev) if need[2] else None
@@ -339,10 +347,13 @@ class ContextMoE(nn.Module):
 
     def _ctx_arrays(self, tabs):
         """HOST arrays (device pointers of the embedding tables, their vocabulary sizes) for the ctx_bias calls."""
-        arr = (C.c_void_p * len(tabs))(*[t.data_ptr() for t in tabs])
-        voc = (C.c_int32 * len(tabs))(*[t.shape[0] for t in tabs])
-        self._ctx_keep = (arr, voc)
-        return C.addressof(arr), C.addressof(voc)
+        key = tuple(t.data_ptr() for t in tabs)
+        keep = self.__dict__.get("_ctx_keep")
+        if keep is None or keep[0] != key:
+            arr = (C.c_void_p * len(tabs))(*key)
+            voc = (C.c_int32 * len(tabs))(*[t.shape[0] for t in tabs])
+            keep = self.__dict__["_ctx_keep"] = (key, arr, voc, C.addressof(arr), C.addressof(voc))
+        return keep[3], keep[4]
 
     def context_bias(self, context: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
         """A.2: ctx_bias[B,E] = concat_i Embed_i(context[:, i]) @ Wc^T (fp32 regardless of autocast)."""
@@ -367,7 +378,9 @@ class ContextMoE(nn.Module):
         if context is not None and context.shape[0] != B:
             raise ValueError("context must have one row per image")
         tpi = T // B
-        xb = x2.to(torch.bfloat16).contiguous()
+        xb = x2 if x2.dtype == torch.bfloat16 else x2.to(torch.bfloat16)
+        if not xb.is_contiguous():
+            xb = xb.contiguous()
         if self.ep_size > 1:
             from .ep import ep_forward
             y, aux, stats = ep_forward(self, xb, self.context_bias(context), tpi)
@@ -385,6 +398,7 @@ class ContextMoE(nn.Module):
         y, aux, _stats = _MoEFunction.apply(xb, ctx_ids, self.gate.weight,
                                             self.ctx_proj.weight if use_ctx else None, self.w1, self.b1, self.w2,
                                             self.b2, self, tpi, *tables)
-        self.aux_loss = aux
-        self.last_aux = _Aux(*self._last_ws)
-        return y.to(x.dtype).reshape(shape)
+        # plain attributes: bypass nn.Module.__setattr__ (several microseconds per assignment)
+        self.__dict__["aux_loss"] = aux
+        self.__dict__["last_aux"] = _Aux(*self._last_ws)
+        return (y if y.dtype == x.dtype else y.to(x.dtype)).reshape(shape)
