@@ -103,6 +103,29 @@ def flops_per_step(w, kept_rows):
     return 12.0 * kept_rows * w["d"] * w["F"]      # fwd 4AdF + bwd 8AdF
 
 
+def hbm_kernels(w, T, kept, per_call_ms, peak_gbs):
+    """Algorithmic HBM bytes (A = kept assignments, bf16 = 2 B) of the bandwidth-bound kernels and
+    what the per-call CUDA-event durations make of them."""
+    d, F, E, k = w["d"], w["F"], w["E"], w["k"]
+    A = kept
+    algo = {
+        "router_fwd": T * d * 2 + T * E * 4 + T * k * 8,            # read x; write logits, top-k indices and gates
+        "permute": 4 * A * d,                                       # gather read + write
+        "combine": 2 * A * d + 2 * T * d,                           # read kept rows, write y
+        "combine_bwd": 6 * A * d,                                   # read dy (gathered) and yo, write dyp
+        "unpermute_bwd": 2 * A * d + 2 * T * d,                     # read dxp, write dx
+        "colsum": 2 * A * (d + F),                                  # read dyp and dhpre
+        "prepare_weights": 6 * 2 * E * d * F,                       # fp32 read + bf16 write of w1, w2
+    }
+    out = {}
+    for name, nbytes in algo.items():
+        ms = per_call_ms.get(name)
+        if ms:
+            gbs = nbytes / (ms * 1e-3) / 1e9
+            out[name] = {"bytes": nbytes, "ms": round(ms, 5), "gbs": round(gbs, 1), "frac": round(gbs / peak_gbs, 3)}
+    return out
+
+
 def run_reference(args, w):
     """CPU arm: the fp32 oracle (port; the reference repo has no MoE implementation) on all host threads."""
     from oracle import moe_ref as R
@@ -360,6 +383,8 @@ def main():
                                 "peak_source": pk["src"] + (" burst" if ms_per_step < 1.0 else " sustained"),
                                 "flops_per_step": fl, "gemm_ms_per_step": res["gemm_ms"], "traffic": None}
         line["per_call_ms"] = res["per_call_ms"]
+        if world == 1:
+            line["hbm_kernels"] = hbm_kernels(w, res["T"], res["kept"], res["per_call_ms"], pk["hbm"])
 
     if rank == 0 and world == 1:
         # CPU baseline: the oracle on this box's host cores, bounded sample
@@ -380,7 +405,8 @@ def main():
                                   "tokens_per_s": B * HW / (mean_ms * 1e-3), "gemm_ms": r["gemm_ms"],
                                   "gemm_tflops": fl / (r["gemm_ms"] * 1e-3) / 1e12,
                                   "gemm_frac_of_peak": fl / (r["gemm_ms"] * 1e-3) / 1e12 / pkk,
-                                  "per_call_ms": r["per_call_ms"]})
+                                  "per_call_ms": r["per_call_ms"],
+                                  "hbm_kernels": hbm_kernels(ww, B * HW, r["kept"], r["per_call_ms"], pk["hbm"])})
                 except Exception as ex:  # noqa: BLE001
                     sweep.append({"workload": name, "tokens": B * HW, "error": repr(ex)})
                 torch.cuda.empty_cache()

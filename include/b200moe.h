@@ -78,7 +78,7 @@ int b200moe_router_fwd(const void* x, const float* ctx_bias, int tokens_per_imag
  *        tokens_per_expert [E] (pre-drop); kept_per_expert [E]
  *        losses [3] = {aux_loss_weight*lb + z_loss_weight*z, lb, z}
  *        row_of_assignment [T,k] (-1 = dropped); token_of_row [rows_cap] (-1 = pad); gate_of_row [rows_cap]
- *   block_counts is overwritten with the first row of every (block, slot, expert); slot_limit [k,E] is scratch. */
+ *   block_counts is overwritten with its exclusive scan over the blocks; slot_limit [2,k,E] is scratch. */
 int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int32_t* block_counts,
                  const float* block_stats, int T, int k, int E, int capacity,
                  const int32_t* global_offset, const int32_t* expert_order, int row_pad, int rows_cap,
@@ -141,6 +141,10 @@ int b200moe_router_bwd_dlogits(const float* logits, const int32_t* topk_idx, con
 int64_t b200moe_dwg_scratch_floats(int T, int d, int E);
 int b200moe_router_bwd_dwg(const float* dlogits, const void* x, int T, int d, int E, float* scratch,
                            float* dwg, void* stream);
+/* Both parameter gradients of the router in two launches (either output may be NULL): dwg as above and
+ * dctx_bias [B,E] = segment sums of dlogits over the tokens of each image, reduced inside the second launch. */
+int b200moe_router_bwd_params(const float* dlogits, const void* x, int T, int d, int E, int tokens_per_image,
+                              float* scratch, float* dwg, float* dctx_bias, void* stream);
 /* dctx_bias [B,E] = segment sums of dlogits over the tokens of each image. */
 int b200moe_router_bwd_dctx(const float* dlogits, int T, int E, int tokens_per_image, float* dctx_bias,
                             void* stream);

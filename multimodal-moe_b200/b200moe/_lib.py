@@ -46,6 +46,7 @@ SIGNATURES = {
     "b200moe_dwg_scratch_floats": [_I, _I, _I],
     "b200moe_router_bwd_dwg": [_P, _P, _I, _I, _I, _P, _P, _P],
     "b200moe_router_bwd_dctx": [_P, _I, _I, _I, _P, _P],
+    "b200moe_router_bwd_params": [_P, _P, _I, _I, _I, _I, _P, _P, _P, _P],
     "b200moe_unpermute_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
     "b200moe_ep_recv_plan": [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P],
     "b200moe_scatter_rows": [_P, _P, _P, _I, _I, _P, _P],
@@ -104,7 +105,7 @@ def stream_ptr() -> int:
 # kernels launched by each entry point (memset nodes not counted); used for bench.py's gpu_launches
 KERNELS_PER_CALL = {
     "b200moe_cast_f32_bf16": 1, "b200moe_prepare_weights": 1, "b200moe_ctx_bias_fwd": 1, "b200moe_ctx_bias_bwd": 1,
-    "b200moe_layer_fwd": 7, "b200moe_layer_bwd": 12, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
+    "b200moe_layer_fwd": 7, "b200moe_layer_bwd": 11, "b200moe_router_bwd_params": 2, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
     "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
     "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,

@@ -61,7 +61,7 @@ class _LayerPlan:
         self.shape = {"logits": (T, E), "topk_idx": (T, k), "topk_gate": (T, k), "block_counts": (nblk, k, E),
                       "block_stats": (nblk, E + 1), "expert_offsets": (E + 1,), "meta": (8,),
                       "tile_expert": (R // 128,), "tokens_per_expert": (E,), "kept_per_expert": (E,), "losses": (3,),
-                      "slot_limit": (k * E,), "row_of_assignment": (T, k), "token_of_row": (R,),
+                      "slot_limit": (2 * k * E,), "row_of_assignment": (T, k), "token_of_row": (R,),
                       "gate_of_row": (R,), "xp": (R, d), "pre": (R, F), "h": (R, F), "yo": (R, d)}
         self.capacity, self.rows_cap = cap, rows_cap
 

@@ -96,7 +96,7 @@ def plan(r: Routing, T: int, k: int, E: int, capacity: int, aux_w: float, z_w: f
              _empty((rows_cap // ROW_PAD,), i32, dev), _empty((E,), i32, dev), _empty((E,), i32, dev),
              _empty((3,), torch.float32, dev), _empty((T, k), i32, dev), _empty((rows_cap,), i32, dev),
              _empty((rows_cap,), torch.float32, dev))
-    slot_limit = _empty((k * E,), i32, dev)
+    slot_limit = _empty((2 * k * E,), i32, dev)
     call("b200moe_plan", ptr(r.topk_idx), ptr(r.topk_gate), ptr(r.block_counts), ptr(r.block_stats), T, k, E,
          capacity, ptr(global_offset), ptr(expert_order), row_pad, rows_cap, aux_w, z_w, ptr(p.expert_offsets),
          ptr(p.meta), ptr(p.tile_expert), ptr(p.tokens_per_expert), ptr(p.kept_per_expert), ptr(p.losses),

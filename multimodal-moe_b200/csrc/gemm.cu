@@ -24,9 +24,12 @@ enum : int { EPI_UP = 0, EPI_DOWN = 1, EPI_DGRAD_DOWN = 2, EPI_DGRAD_UP = 3, EPI
 
 constexpr int BM = 128;
 constexpr int BK = 64;
-constexpr int kEpiWarps = 8;                         // two warps per TMEM lane quarter, each takes half the columns
-constexpr int kEpiThreads = kEpiWarps * 32;
-constexpr int kGemmThreads = 64 + kEpiThreads;
+// Epilogue warps: the bf16 epilogues (bias / GELU / GELU' / pack / TMA store) are latency chains (TMEM load, proxy
+// fence, bulk-store read-back), so they run 16 warps = four per scheduler, four per TMEM lane quarter, each taking a
+// quarter of the tile's columns through a private 2 KB staging box.  The fp32 weight-gradient epilogue is a plain
+// copy: 8 warps with 4 KB boxes.
+__host__ __device__ constexpr int epi_warps(int epi) { return epi == 4 /*EPI_WGRAD*/ ? 8 : 16; }
+__host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
 
 struct GemmArgs {
   const int32_t* meta;            // row mode: meta[1] = number of 128-row tiles in use
@@ -50,25 +53,28 @@ struct SmemCfg {
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (BN == 256) ? 4 : 6;
-  static constexpr int kOutBytes = kEpiWarps * 4096;                       // epilogue staging for the TMA stores
+  static constexpr int kOutBytes = 8 * 4096;                               // epilogue staging: 8 x 4 KB or 16 x 2 KB
   static constexpr int kBarBytes = 256;
   static constexpr int kTotal = kStages * kStageBytes + kOutBytes + kBarBytes + 1024;  // + alignment slack
 };
 
 template <int BN, bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(gemm_threads(EPI), 1)
 grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC0, const __grid_constant__ CUtensorMap tmC1,
                     const GemmArgs args) {
   using Cfg = SmemCfg<BN>;
   constexpr int kStages = Cfg::kStages;
   constexpr bool kWgrad = (EPI == EPI_WGRAD);
+  constexpr int kEpiWarps = epi_warps(EPI);
+  constexpr int kEpiThreads = kEpiWarps * 32;
+  constexpr int kStgBytes = Cfg::kOutBytes / kEpiWarps;                    // 4 KB (wgrad) or 2 KB
   constexpr uint32_t kTmemCols = 2 * BN;  // 256 or 512: power of two
   constexpr uint32_t kIdesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
 
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  unsigned char* stage_out = smem + kStages * Cfg::kStageBytes;            // 8 warps x 4 KB epilogue staging
+  unsigned char* stage_out = smem + kStages * Cfg::kStageBytes;            // per-warp epilogue staging boxes
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + Cfg::kOutBytes);
   uint64_t* empty_bar = full_bar + kStages;
   uint64_t* tfull_bar = empty_bar + kStages;
@@ -183,16 +189,16 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
   } else {
-    // ======================= epilogue (warps 2..9) =======================
+    // ======================= epilogue (warps 2 ..) =======================
     // TMEM -> registers -> (bias / GELU / GELU') -> swizzled smem box -> TMA store.  Each warp owns 32 output rows
-    // and a private 4 KB staging area, so no cross-warp synchronisation is needed: lane 0 issues the bulk stores
-    // and is the one that waits for them to have read the staging area before it is overwritten.
+    // and a private staging box, so no cross-warp synchronisation is needed: lane 0 issues the bulk stores
+    // and is the one that waits for them to have read the staging box before it is overwritten.
     const int quarter = warp & 3;              // TMEM lane quarter this warp may read
-    const int chalf = (warp - 2) >> 2;         // which half of the tile's columns
-    unsigned char* stg = stage_out + (warp - 2) * 4096;
+    const int cgroup = (warp - 2) >> 2;        // which share of the tile's columns
+    constexpr int kChunksPerWarp = (BN / 32) / (kEpiWarps / 4);
+    unsigned char* stg = stage_out + (warp - 2) * kStgBytes;
     int acc = 0;
     uint32_t acc_phase = 0;
-    uint32_t nstore = 0;                       // boxes issued by this warp (alternates the two 2 KB halves)
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       int e, m_tile, n_tile, krow0, kblocks;
       decode(tile, e, m_tile, n_tile, krow0, kblocks);
@@ -202,7 +208,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int row0 = m_tile * BM + quarter * 32;                 // first of this warp's 32 output rows
       const size_t grow = static_cast<size_t>(row0) + lane;        // this thread's output row
 #pragma unroll 1
-      for (int c = chalf * (BN / 64); c < (chalf + 1) * (BN / 64); ++c) {
+      for (int c = cgroup * kChunksPerWarp; c < (cgroup + 1) * kChunksPerWarp; ++c) {
         const int col0 = n_tile * BN + c * 32;
         uint32_t v[32];
         tmem_ld32(taddr + c * 32, v);
@@ -212,6 +218,12 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 4; ++j) pr[j] = __ldg(reinterpret_cast<const uint4*>(ap) + j);   // L1-allocating: the
           // other half of the 128-byte line is this thread's next chunk
+        }
+        float4 bv[8];
+        if (EPI == EPI_UP || EPI == EPI_DOWN) {
+          const float* bp = args.bias + static_cast<size_t>(e) * args.N + col0;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bv[j] = __ldg(reinterpret_cast<const float4*>(bp) + j);
         }
         tmem_ld_wait();
         if (EPI == EPI_WGRAD) {
@@ -237,32 +249,28 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
           if (EPI == EPI_UP || EPI == EPI_DOWN) {
-            const float* bp = args.bias + static_cast<size_t>(e) * args.N + col0;
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              const float4 bv = __ldg(reinterpret_cast<const float4*>(bp + j));
-              f[j] += bv.x; f[j + 1] += bv.y; f[j + 2] += bv.z; f[j + 3] += bv.w;
+            for (int j = 0; j < 8; ++j) {
+              f[4 * j] += bv[j].x; f[4 * j + 1] += bv[j].y; f[4 * j + 2] += bv[j].z; f[4 * j + 3] += bv[j].w;
             }
           }
           // bf16 box [32 rows][32 cols] = 2 KB, 64-byte swizzle: 16-byte chunk j of row r sits at j ^ ((r >> 1) & 3)
           const uint32_t swz = (lane >> 1) & 3;
-          unsigned char* box0;
-          unsigned char* box1 = nullptr;
-          if (EPI == EPI_UP) {                 // two outputs per chunk: both halves, wait for everything before reuse
+          if (EPI == EPI_UP && args.out1) {    // pre-activation leaves first; its bulk store reads the box during the GELU math
             if (lane == 0) tma_store_wait_read0();
-            box0 = stg; box1 = stg + 2048;
-          } else {                             // one output: alternate halves, one store may still be reading
-            if (lane == 0) tma_store_wait_read1();
-            box0 = stg + (nstore & 1) * 2048;
-          }
-          __syncwarp();
-          if (EPI == EPI_UP && args.out1) {
+            __syncwarp();
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
               uint4 pk;
               pk.x = float2_to_bf16x2(f[8 * j], f[8 * j + 1]); pk.y = float2_to_bf16x2(f[8 * j + 2], f[8 * j + 3]);
               pk.z = float2_to_bf16x2(f[8 * j + 4], f[8 * j + 5]); pk.w = float2_to_bf16x2(f[8 * j + 6], f[8 * j + 7]);
-              *reinterpret_cast<uint4*>(box1 + lane * 64 + ((j ^ swz) << 4)) = pk;
+              *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ swz) << 4)) = pk;
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmC1, stg, col0, row0);
+              tma_store_commit();
             }
           }
           if (EPI == EPI_UP) {
@@ -279,21 +287,21 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               t = bf16x2_to_float2(pr[j].w); f[8 * j + 6] *= gelu_erf_grad(t.x); f[8 * j + 7] *= gelu_erf_grad(t.y);
             }
           }
+          if (lane == 0) tma_store_wait_read0();
+          __syncwarp();
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             uint4 pk;
             pk.x = float2_to_bf16x2(f[8 * j], f[8 * j + 1]); pk.y = float2_to_bf16x2(f[8 * j + 2], f[8 * j + 3]);
             pk.z = float2_to_bf16x2(f[8 * j + 4], f[8 * j + 5]); pk.w = float2_to_bf16x2(f[8 * j + 6], f[8 * j + 7]);
-            *reinterpret_cast<uint4*>(box0 + lane * 64 + ((j ^ swz) << 4)) = pk;
+            *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ swz) << 4)) = pk;
           }
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            tma_store_2d(&tmC0, box0, col0, row0);
-            if (EPI == EPI_UP && args.out1) tma_store_2d(&tmC1, box1, col0, row0);
+            tma_store_2d(&tmC0, stg, col0, row0);
             tma_store_commit();
           }
-          ++nstore;
         }
       }
       tc_fence_before();

@@ -192,7 +192,7 @@ extern "C" int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* q, int64_t*
   bytes[B200MOE_WS_TOKENS_PER_EXPERT] = E * 4;
   bytes[B200MOE_WS_KEPT_PER_EXPERT] = E * 4;
   bytes[B200MOE_WS_LOSSES] = 3 * 4;
-  bytes[B200MOE_WS_SLOT_LIMIT] = k * E * 4;
+  bytes[B200MOE_WS_SLOT_LIMIT] = 2 * k * E * 4;
   bytes[B200MOE_WS_ROW_OF_ASSIGNMENT] = T * k * 4;
   bytes[B200MOE_WS_TOKEN_OF_ROW] = R * 4;
   bytes[B200MOE_WS_GATE_OF_ROW] = R * 4;
@@ -302,12 +302,12 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
     STEP("ffn_dgrad_up", b200moe_ffn_dgrad_up(dhpre, w1, meta, tile_expert, R, d, F, E, dxp, stream));
     STEP("unpermute_bwd", b200moe_unpermute_bwd(dxp, roa, dlogits, wg, T, k, d, E, dx, stream));
   }
-  if (dwg) {
-    STEP("router_bwd_dwg",
-         b200moe_router_bwd_dwg(dlogits, x, T, d, E, BWS(float, B200MOE_BWS_DWG_SCRATCH), dwg, stream));
-  }
-  if (dctx_bias && has_ctx_bias) {
-    STEP("router_bwd_dctx", b200moe_router_bwd_dctx(dlogits, T, E, q->tokens_per_image, dctx_bias, stream));
+  {
+    float* dctx = (dctx_bias && has_ctx_bias) ? dctx_bias : nullptr;
+    if (dwg || dctx) {
+      STEP("router_bwd_params", b200moe_router_bwd_params(dlogits, x, T, d, E, q->tokens_per_image,
+                                                          BWS(float, B200MOE_BWS_DWG_SCRATCH), dwg, dctx, stream));
+    }
   }
   return B200MOE_OK;
 #undef BWS

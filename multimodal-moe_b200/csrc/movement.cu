@@ -117,38 +117,92 @@ combine_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
   }
 }
 
-// dx[t] = sum_s dxp[row[t,s]] + dlogits[t] @ wg
-__global__ void __launch_bounds__(kMoveThreads)
+// dx[t] = sum_s dxp[row[t,s]] + dlogits[t] @ wg      (backward of permute fused with the router's input gradient)
+// Block = 64 tokens x one 256-column slab.  The slab of wg [E][256] fp32 and the block's dlogits [64][E] sit in
+// shared memory; a warp owns 8 tokens, a lane two 4-column pieces (c, c+128: conflict-free 16-byte smem reads,
+// 256 contiguous bytes per warp access in global memory), so every wg value read from shared memory feeds 8 FMAs
+// per token x 8 tokens.  The k gathered rows of dxp are added in slot order in fp32.
+// TT = tokens per warp (8 for large batches; 2 for small ones so that the grid still covers the SMs).
+template <int TT>
+__global__ void __launch_bounds__(256)
 unpermute_bwd_kernel(const __nv_bfloat16* __restrict__ dxp, const int32_t* __restrict__ row_of_assignment,
                      const float* __restrict__ dlogits, const float* __restrict__ wg, int T, int k, int d, int E,
                      __nv_bfloat16* __restrict__ dx) {
-  const int nchunk = d >> 3;
-  const int lane = threadIdx.x & 31;
-  for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps) {
-    for (int c = lane; c < nchunk; c += 32) {
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (dxp) {
-        for (int s = 0; s < k; ++s) {
-          const int r = row_of_assignment[static_cast<size_t>(t) * k + s];
-          if (r < 0) continue;
-          float v[8];
-          unpack8(ldg128(dxp + static_cast<size_t>(r) * d + c * 8), v);
+  constexpr int kTok = 8 * TT;         // tokens per block
+  extern __shared__ __align__(16) float unp_s[];
+  float* wg_s = unp_s;                 // [E][256]
+  float* dl_s = unp_s + E * 256;       // [kTok][E]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t0 = blockIdx.x * kTok;
+  const int slab0 = blockIdx.y * 256;
+  const int c0 = slab0 + lane * 4, c1 = c0 + 128;
+  const bool has1 = c1 < d;            // d is a multiple of 128: the second piece is missing only when d == 128
+  float acc[TT][8];
 #pragma unroll
-          for (int j = 0; j < 8; ++j) acc[j] += v[j];
+  for (int tt = 0; tt < TT; ++tt)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[tt][j] = 0.f;
+  // gathers first (independent of the router part): all loads of up to 4 tokens in flight at once
+  if (dxp) {
+#pragma unroll
+    for (int h = 0; h < TT; h += 4) {
+      constexpr int kG = TT < 4 ? TT : 4;
+      for (int s = 0; s < k; ++s) {
+        uint2 va[kG], vb[kG];
+#pragma unroll
+        for (int q = 0; q < kG; ++q) {
+          const int t = t0 + warp * TT + h + q;
+          const int r = t < T ? row_of_assignment[static_cast<size_t>(t) * k + s] : -1;
+          const __nv_bfloat16* src = dxp + static_cast<size_t>(r < 0 ? 0 : r) * d;
+          va[q] = r >= 0 ? __ldg(reinterpret_cast<const uint2*>(src + c0)) : make_uint2(0, 0);
+          vb[q] = (r >= 0 && has1) ? __ldg(reinterpret_cast<const uint2*>(src + c1)) : make_uint2(0, 0);
+        }
+#pragma unroll
+        for (int q = 0; q < kG; ++q) {
+          float2 f;
+          f = bf16x2_to_float2(va[q].x); acc[h + q][0] += f.x; acc[h + q][1] += f.y;
+          f = bf16x2_to_float2(va[q].y); acc[h + q][2] += f.x; acc[h + q][3] += f.y;
+          f = bf16x2_to_float2(vb[q].x); acc[h + q][4] += f.x; acc[h + q][5] += f.y;
+          f = bf16x2_to_float2(vb[q].y); acc[h + q][6] += f.x; acc[h + q][7] += f.y;
         }
       }
-      if (dlogits) {
-        for (int e = 0; e < E; ++e) {
-          const float g = __ldg(dlogits + static_cast<size_t>(t) * E + e);
-          const float4 wa = __ldg(reinterpret_cast<const float4*>(wg + static_cast<size_t>(e) * d + c * 8));
-          const float4 wb = __ldg(reinterpret_cast<const float4*>(wg + static_cast<size_t>(e) * d + c * 8 + 4));
-          acc[0] = fmaf(g, wa.x, acc[0]); acc[1] = fmaf(g, wa.y, acc[1]);
-          acc[2] = fmaf(g, wa.z, acc[2]); acc[3] = fmaf(g, wa.w, acc[3]);
-          acc[4] = fmaf(g, wb.x, acc[4]); acc[5] = fmaf(g, wb.y, acc[5]);
-          acc[6] = fmaf(g, wb.z, acc[6]); acc[7] = fmaf(g, wb.w, acc[7]);
-        }
+    }
+  }
+  if (dlogits) {
+    for (int i = threadIdx.x; i < E * 64; i += 256) {
+      const int e = i >> 6, c4 = (i & 63) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (slab0 + c4 < d) v = __ldg(reinterpret_cast<const float4*>(wg + static_cast<size_t>(e) * d + slab0 + c4));
+      *reinterpret_cast<float4*>(wg_s + e * 256 + c4) = v;
+    }
+    const long long lim = static_cast<long long>(T) * E, base = static_cast<long long>(t0) * E;
+    for (int i = threadIdx.x; i < kTok * E; i += 256) dl_s[i] = (base + i < lim) ? dlogits[base + i] : 0.f;
+    __syncthreads();
+    const float* dlw = dl_s + warp * TT * E;
+#pragma unroll 2
+    for (int e = 0; e < E; ++e) {
+      const float4 wa = *reinterpret_cast<const float4*>(wg_s + e * 256 + lane * 4);
+      const float4 wb = *reinterpret_cast<const float4*>(wg_s + e * 256 + 128 + lane * 4);
+#pragma unroll
+      for (int tt = 0; tt < TT; ++tt) {
+        const float g = dlw[tt * E + e];
+        acc[tt][0] = fmaf(g, wa.x, acc[tt][0]); acc[tt][1] = fmaf(g, wa.y, acc[tt][1]);
+        acc[tt][2] = fmaf(g, wa.z, acc[tt][2]); acc[tt][3] = fmaf(g, wa.w, acc[tt][3]);
+        acc[tt][4] = fmaf(g, wb.x, acc[tt][4]); acc[tt][5] = fmaf(g, wb.y, acc[tt][5]);
+        acc[tt][6] = fmaf(g, wb.z, acc[tt][6]); acc[tt][7] = fmaf(g, wb.w, acc[tt][7]);
       }
-      stg128(dx + static_cast<size_t>(t) * d + c * 8, pack8(acc));
+    }
+  }
+#pragma unroll
+  for (int tt = 0; tt < TT; ++tt) {
+    const int t = t0 + warp * TT + tt;
+    if (t < T) {
+      __nv_bfloat16* dst = dx + static_cast<size_t>(t) * d;
+      *reinterpret_cast<uint2*>(dst + c0) =
+          make_uint2(float2_to_bf16x2(acc[tt][0], acc[tt][1]), float2_to_bf16x2(acc[tt][2], acc[tt][3]));
+      if (has1)
+        *reinterpret_cast<uint2*>(dst + c1) =
+            make_uint2(float2_to_bf16x2(acc[tt][4], acc[tt][5]), float2_to_bf16x2(acc[tt][6], acc[tt][7]));
     }
   }
 }
@@ -316,11 +370,27 @@ extern "C" int b200moe_combine_bwd(const void* dy, const void* yo, const int32_t
 
 extern "C" int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assignment, const float* dlogits,
                                      const float* wg, int T, int k, int d, int E, void* dx, void* stream) {
-  B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "unpermute_bwd: d=%d must be a multiple of 8", d);
+  B200MOE_REQUIRE(d > 0 && d % 128 == 0, B200MOE_EINVAL, "unpermute_bwd: d=%d must be a multiple of 128", d);
+  B200MOE_REQUIRE(E >= 1 && E <= 64, B200MOE_EINVAL, "unpermute_bwd: num_experts=%d outside [1,64]", E);
+  B200MOE_REQUIRE(dlogits == nullptr || wg != nullptr, B200MOE_EINVAL, "unpermute_bwd: dlogits without wg");
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
-  unpermute_bwd_kernel<<<move_grid(T), kMoveThreads, 0, ST(stream)>>>(BF(dxp), row_of_assignment, dlogits, wg, T, k,
-                                                                      d, E, BFW(dx));
+  const bool big = T >= 64 * 2 * kNumSMs;
+  const int tok = big ? 64 : 16;
+  const size_t smem = dlogits ? sizeof(float) * (static_cast<size_t>(E) * 256 + tok * E) : 0;
+  static bool configured = false;
+  if (!configured) {
+    const int mx = static_cast<int>(sizeof(float) * (64 * 256 + 64 * 64));
+    cudaError_t e1 = cudaFuncSetAttribute(unpermute_bwd_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    cudaError_t e2 = cudaFuncSetAttribute(unpermute_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    B200MOE_REQUIRE(e1 == cudaSuccess && e2 == cudaSuccess, B200MOE_ECUDA, "unpermute_bwd: cudaFuncSetAttribute failed");
+    configured = true;
+  }
+  dim3 grid((T + tok - 1) / tok, (d + 255) / 256);
+  if (big)
+    unpermute_bwd_kernel<8><<<grid, 256, smem, ST(stream)>>>(BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx));
+  else
+    unpermute_bwd_kernel<2><<<grid, 256, smem, ST(stream)>>>(BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx));
   return check_launch("unpermute_bwd");
 }
 

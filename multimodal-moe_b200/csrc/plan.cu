@@ -32,27 +32,45 @@ plan_scan_kernel(int32_t* __restrict__ block_counts, const float* __restrict__ b
   // row maps start as "pad" (small buffers only; the host issues memsets for large ones)
   for (int i = threadIdx.x; i < init_rows; i += blockDim.x) { token_of_row[i] = -1; gate_of_row[i] = 0.f; }
 
-  // phase 1: exclusive scan over the router blocks for every (slot, expert) sequence
+  // phase 1: exclusive scan over the router blocks for every (slot, expert) sequence; a warp takes one sequence and
+  // loads up to 8 x 32 counts before it starts scanning, so the global-memory latency is paid once per 256 blocks
   for (int q = warp; q < kE; q += nwarps) {
     int run = 0;
-    for (int b0 = 0; b0 < nblk; b0 += 32) {
-      const int b = b0 + lane;
-      const int v = (b < nblk) ? block_counts[static_cast<size_t>(b) * kE + q] : 0;
-      int inc = v;
+    for (int b0 = 0; b0 < nblk; b0 += 256) {
+      int v[8];
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int n = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += n;
+      for (int u = 0; u < 8; ++u) {
+        const int b = b0 + u * 32 + lane;
+        v[u] = (b < nblk) ? block_counts[static_cast<size_t>(b) * kE + q] : 0;
       }
-      if (b < nblk) block_counts[static_cast<size_t>(b) * kE + q] = run + inc - v;
-      run += __shfl_sync(0xffffffffu, inc, 31);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int b = b0 + u * 32 + lane;
+        int inc = v[u];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int n = __shfl_up_sync(0xffffffffu, inc, o);
+          if (lane >= o) inc += n;
+        }
+        if (b < nblk) block_counts[static_cast<size_t>(b) * kE + q] = run + inc - v[u];
+        run += __shfl_sync(0xffffffffu, inc, 31);
+      }
     }
     if (lane == 0) total_s[q] = run;
   }
-  // loss statistics: one warp per column of block_stats, lanes stride the blocks, fixed shuffle tree
+  // loss statistics: one warp per column of block_stats, lanes stride the blocks (8 loads in flight), fixed order
   for (int e = warp; e <= E; e += nwarps) {
     float s = 0.f;
-    for (int b = lane; b < nblk; b += 32) s += block_stats[static_cast<size_t>(b) * (E + 1) + e];
+    for (int b0 = 0; b0 < nblk; b0 += 256) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int b = b0 + u * 32 + lane;
+        v[u] = (b < nblk) ? block_stats[static_cast<size_t>(b) * (E + 1) + e] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) s += v[u];
+    }
     s = warp_sum(s);
     if (lane == 0) P_s[e] = s;
   }
@@ -112,18 +130,13 @@ plan_scan_kernel(int32_t* __restrict__ block_counts, const float* __restrict__ b
   __syncthreads();
   for (int i = threadIdx.x; i <= E; i += blockDim.x) expert_offsets[i] = off_s[i];
 
-  // phase 4: absolute bases for the assign kernel
+  // phase 4: absolute first row and limit of every (slot, expert) for the assign kernel (slot_limit [2][k*E])
   for (int q = threadIdx.x; q < kE; q += blockDim.x) {
     const int e = q % E;
     const int pos = expert_order ? expert_order[e] : e;
     const int first = off_s[pos] + rowbase_s[q];
-    rowbase_s[q] = first;
     slot_limit[q] = first + keptslot_s[q];
-  }
-  __syncthreads();
-  for (int q = warp; q < kE; q += nwarps) {
-    const int first = rowbase_s[q];
-    for (int b = lane; b < nblk; b += 32) block_counts[static_cast<size_t>(b) * kE + q] += first;
+    slot_limit[kE + q] = first;
   }
   if (tile_expert) {
     const int ntiles_cap = rows_cap / kRowPad;
@@ -162,7 +175,7 @@ plan_assign_kernel(const int32_t* __restrict__ topk_idx, const float* __restrict
       int rank = rank_in_warp;
       for (int w = 0; w < warp; ++w) rank += wc[w][e];
       const int q = s * E + e;
-      const int row = block_base[static_cast<size_t>(blockIdx.x) * k * E + q] + rank;
+      const int row = slot_limit[k * E + q] + block_base[static_cast<size_t>(blockIdx.x) * k * E + q] + rank;
       const bool keep = row < slot_limit[q];
       row_of_assignment[static_cast<size_t>(t) * k + s] = keep ? row : -1;
       if (keep) {

@@ -28,7 +28,8 @@ template <int EP>
 struct RouterCfg {
   static constexpr int kWBytes = 2 * EP * 64 * 2;           // hi rows then lo rows, [2*EP][64] bf16
   static constexpr int kStageBytes = kRtXBytes + kWBytes;
-  static constexpr int kStages = (EP == 64) ? 6 : 8;
+  static constexpr int kStages = (EP == 64) ? 6 : (EP == 32 ? 4 : 5);   // EP <= 32: two CTAs per SM
+  static constexpr int kCtasPerSm = (EP == 64) ? 1 : 2;
   static constexpr int kTail = 2 * 4 * (EP + 1) * 4 /*stat_s*/ + 2 * 8 * 64 * 4 /*cnt_s*/ + 256 /*barriers*/;
   static constexpr int kTotal = kStages * kStageBytes + kTail + 1024;
   static constexpr uint32_t kTmemCols = 2 * EP < 32 ? 32 : 2 * EP;
@@ -55,7 +56,7 @@ struct RouterArgs {
 };
 
 template <int EP>
-__global__ void __launch_bounds__(kRtThreads, 1)
+__global__ void __launch_bounds__(kRtThreads, RouterCfg<EP>::kCtasPerSm)
 router_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                   const RouterArgs a) {
   using Cfg = RouterCfg<EP>;
@@ -147,6 +148,14 @@ router_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     uint32_t acc_phase = 0;
     int buf = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int t = tile * kRtTile + quarter * 32 + lane;
+      const bool live = t < T;
+      const float* cb = (a.ctx_bias && live) ? a.ctx_bias + static_cast<size_t>(t / a.tokens_per_image) * E : nullptr;
+      float cbv[EP <= 16 ? EP : 1];               // small E: context bias fetched ahead of the accumulator wait
+      if (EP <= 16) {
+#pragma unroll
+        for (int e = 0; e < EP; ++e) cbv[EP <= 16 ? e : 0] = (cb && e < E) ? __ldg(cb + e) : 0.f;
+      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * EP;
@@ -162,63 +171,21 @@ router_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
       mbar_arrive(&tempty_bar[acc]);              // accumulator is in registers: the MMA warp may reuse it
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
 
-      const int t = tile * kRtTile + quarter * 32 + lane;
-      const bool live = t < T;
-      const float* cb = (a.ctx_bias && live) ? a.ctx_bias + static_cast<size_t>(t / a.tokens_per_image) * E : nullptr;
+      // logits (A.2) and their row maximum
       float lg[EP];
       float mx = -INFINITY;
 #pragma unroll
       for (int e = 0; e < EP; ++e) {
-        float v = __uint_as_float(raw[e]);
+        float v = -INFINITY;
         if (e < E) {
-          if (cb) v += __ldg(cb + e);
-          mx = fmaxf(mx, v);
-        } else {
-          v = -INFINITY;
+          v = __uint_as_float(raw[e]);
+          if (EP <= 16) v += cbv[EP <= 16 ? e : 0];
+          else if (cb) v += __ldg(cb + e);
         }
+        mx = fmaxf(mx, v);
         lg[e] = v;
       }
-      float p[EP];
-      float ssum = 0.f;
-#pragma unroll
-      for (int e = 0; e < EP; ++e) {
-        p[e] = (e < E) ? expf(lg[e] - mx) : 0.f;
-        ssum += p[e];
-      }
-      const float inv = 1.0f / ssum;
-      const float lse = mx + logf(ssum);
-      // top-k by (logit desc, index asc)
-      unsigned long long taken = 0ull;
-      int sel[8];
-      float gate[8];
-      float gsum = 0.f;
-#pragma unroll
-      for (int s = 0; s < 8; ++s) {
-        if (s < k) {
-          float best = -INFINITY;
-          int bi = 0;
-          bool found = false;
-          float pb = 0.f;
-#pragma unroll
-          for (int e = 0; e < EP; ++e) {
-            const bool ok = (e < E) && !((taken >> e) & 1ull) && (!found || lg[e] > best);
-            if (ok) { best = lg[e]; bi = e; found = true; pb = p[e]; }
-          }
-          taken |= 1ull << bi;
-          sel[s] = bi;
-          gate[s] = pb * inv;
-          gsum += gate[s];
-        }
-      }
       if (live) {
-#pragma unroll
-        for (int s = 0; s < 8; ++s) {
-          if (s < k) {
-            a.topk_idx[static_cast<size_t>(t) * k + s] = sel[s];
-            a.topk_gate[static_cast<size_t>(t) * k + s] = a.normalize ? gate[s] / (gsum + 1e-9f) : gate[s];
-            atomicAdd(&cnt_s[buf * 512 + s * E + sel[s]], 1);
-          }
-        }
         float* lo = a.logits + static_cast<size_t>(t) * E;
         if ((E & 3) == 0) {
 #pragma unroll
@@ -230,18 +197,74 @@ router_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
             if (e < E) lo[e] = lg[e];
         }
       }
-      // tile statistics: shuffle tree per expert, then the four warps in a fixed order
+      // softmax normaliser, then the tile statistics (shuffle tree per expert, the four warps in a fixed order later);
+      // p is recomputed rather than kept: registers are the scarce resource here
+      float ssum = 0.f;
+#pragma unroll
+      for (int e = 0; e < EP; ++e) ssum += (e < E) ? expf(lg[e] - mx) : 0.f;
+      const float inv = 1.0f / ssum;
+      const float lse = mx + logf(ssum);
       float* st = stat_s + (buf * 4 + quarter) * (EP + 1);
 #pragma unroll
       for (int e = 0; e < EP; ++e) {
         if (e < E) {
-          const float s = warp_sum(live ? p[e] * inv : 0.f);
+          const float s = warp_sum(live ? expf(lg[e] - mx) * inv : 0.f);
           if (lane == (e & 31)) st[e] = s;
         }
       }
       {
         const float z = warp_sum(live ? lse * lse : 0.f);
         if (lane == 0) st[EP] = z;
+      }
+      // top-k by (logit desc, index asc): order-preserving 32-bit image of the fp32 logit (0 = below everything, used
+      // for padding and for experts already taken), a max tree over (image, 63 - index) per slot instead of a serial
+      // compare chain
+      uint32_t ord[EP];
+#pragma unroll
+      for (int e = 0; e < EP; ++e) {
+        const uint32_t u = __float_as_uint(lg[e]);
+        ord[e] = (e < E) ? ((u & 0x80000000u) ? ~u : (u | 0x80000000u)) : 0u;
+      }
+      int sel[8];
+      float gate[8];
+      float gsum = 0.f;
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        if (s < k) {
+          unsigned long long m[EP / 2];
+#pragma unroll
+          for (int i = 0; i < EP / 2; ++i) {
+            const unsigned long long ka = (static_cast<unsigned long long>(ord[i]) << 32) | static_cast<unsigned>(63 - i);
+            const unsigned long long kb =
+                (static_cast<unsigned long long>(ord[i + EP / 2]) << 32) | static_cast<unsigned>(63 - i - EP / 2);
+            m[i] = ka > kb ? ka : kb;
+          }
+#pragma unroll
+          for (int w = EP / 4; w >= 1; w >>= 1) {
+#pragma unroll
+            for (int i = 0; i < w; ++i) m[i] = m[i] > m[i + w] ? m[i] : m[i + w];
+          }
+          const int bi = 63 - static_cast<int>(m[0] & 63ull);
+          const uint32_t o = static_cast<uint32_t>(m[0] >> 32);
+          const float best = __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
+#pragma unroll
+          for (int e = 0; e < EP; ++e) ord[e] = (e == bi) ? 0u : ord[e];
+          sel[s] = bi;
+          gate[s] = expf(best - mx) * inv;        // p of the winner, bit for bit what the statistics used
+          gsum += gate[s];
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < 8; ++s) {
+        if (s < k) {
+          // assignment counts: one shared-memory atomic per distinct expert of the warp (match_any), not per token
+          const unsigned same = __match_any_sync(0xffffffffu, live ? sel[s] : 64 + lane);
+          if (live) {
+            a.topk_idx[static_cast<size_t>(t) * k + s] = sel[s];
+            a.topk_gate[static_cast<size_t>(t) * k + s] = a.normalize ? gate[s] / (gsum + 1e-9f) : gate[s];
+            if (lane == __ffs(same) - 1) atomicAdd(&cnt_s[buf * 512 + s * E + sel[s]], __popc(same));
+          }
+        }
       }
       epi_bar_sync();
       for (int e = et; e <= E; e += 128) {
@@ -300,7 +323,8 @@ static int launch_router(const void* x, const void* wsplit, const RouterArgs& a,
     configured = true;
   }
   const int ntiles = (a.T + kRtTile - 1) / kRtTile;
-  const int grid = ntiles < kNumSMs ? ntiles : kNumSMs;
+  const int max_ctas = kNumSMs * Cfg::kCtasPerSm;
+  const int grid = ntiles < max_ctas ? ntiles : max_ctas;
   kern<<<grid, kRtThreads, Cfg::kTotal, st>>>(tmX, tmW, a);
   return check_launch("router_fwd");
 }

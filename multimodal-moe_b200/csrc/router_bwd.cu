@@ -82,66 +82,121 @@ router_dlogits_kernel(const float* __restrict__ logits, const int32_t* __restric
     if (e < E) dlogits[static_cast<size_t>(t) * E + e] = p[e] * (dp[e] - dot) + zc * p[e];
 }
 
-// stage 1: block (token chunk c, column slab j) -> scratch[c][e][col] ; thread owns one column and E accumulators
-constexpr int kDwgTok = 64;   // minimum tokens per chunk
-template <int EP>
-__global__ void __launch_bounds__(256)
+// dWg = dlogits^T x in two fixed-order stages (deterministic, no atomics).
+// stage 1: block = (token chunk, 256-column slab, group of 16 experts), 4 warps.  A lane owns two 4-column pieces of
+//   the slab (c, c+128) and a [16 experts][8 columns] register tile; the warps take every 4th token of the chunk, the
+//   chunk's dlogits pass through shared memory in batches of 64 tokens (broadcast reads), so one 16-byte read of x
+//   feeds 128 FMAs.  The four warps' tiles are then summed in order through shared memory -> scratch[chunk][e][col].
+// stage 2: sum over the chunks; the same launch also reduces dctx_bias[b,e] = sum of dlogits over the tokens of image b.
+constexpr int kDwgEG = 16;
+constexpr int kDwgBatch = 64;
+constexpr int kDwgRedBytes = 4 * kDwgEG * 256 * 4;
+
+__global__ void __launch_bounds__(128)
 router_dwg_partial_kernel(const float* __restrict__ dlogits, const __nv_bfloat16* __restrict__ x, int T, int d, int E,
                           int tok_per_chunk, float* __restrict__ scratch) {
-  __shared__ float dl_s[64][EP];
-  const int col = blockIdx.y * 256 + threadIdx.x;
+  extern __shared__ __align__(16) float red_s[];      // [4][16][256]
+  __shared__ __align__(16) float dl_s[kDwgBatch][kDwgEG];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slab0 = blockIdx.y * 256, e0 = blockIdx.z * kDwgEG;
+  const int c0 = slab0 + lane * 4, c1 = c0 + 128;
+  const bool has0 = c0 < d, has1 = c1 < d;
   const int t_begin = blockIdx.x * tok_per_chunk;
   const int t_end = min(T, t_begin + tok_per_chunk);
-  float acc[EP];
+  float acc[kDwgEG][8];
 #pragma unroll
-  for (int e = 0; e < EP; ++e) acc[e] = 0.f;
-  for (int tb = t_begin; tb < t_end; tb += 64) {
-    const int nt = min(64, t_end - tb);
-    __syncthreads();
-    for (int i = threadIdx.x; i < nt * E; i += blockDim.x) dl_s[i / E][i % E] = dlogits[static_cast<size_t>(tb) * E + i];
-    __syncthreads();
-    if (col < d) {
-      for (int i = 0; i < nt; ++i) {
-        const float xv = __bfloat162float(x[static_cast<size_t>(tb + i) * d + col]);
+  for (int e = 0; e < kDwgEG; ++e)
 #pragma unroll
-        for (int e = 0; e < EP; ++e)
-          if (e < E) acc[e] = fmaf(dl_s[i][e], xv, acc[e]);
+    for (int j = 0; j < 8; ++j) acc[e][j] = 0.f;
+
+  for (int tb = t_begin; tb < t_end; tb += kDwgBatch) {
+    const int nt = min(kDwgBatch, t_end - tb);
+    __syncthreads();
+    for (int i = threadIdx.x; i < kDwgBatch * kDwgEG; i += 128) {
+      const int tt = i / kDwgEG, e = e0 + (i % kDwgEG);
+      dl_s[tt][i % kDwgEG] = (tt < nt && e < E) ? dlogits[static_cast<size_t>(tb + tt) * E + e] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int i = warp; i < nt; i += 4) {
+      const __nv_bfloat16* xr = x + static_cast<size_t>(tb + i) * d;
+      const uint2 ra = has0 ? __ldg(reinterpret_cast<const uint2*>(xr + c0)) : make_uint2(0, 0);
+      const uint2 rb = has1 ? __ldg(reinterpret_cast<const uint2*>(xr + c1)) : make_uint2(0, 0);
+      float xv[8];
+      float2 f;
+      f = bf16x2_to_float2(ra.x); xv[0] = f.x; xv[1] = f.y;
+      f = bf16x2_to_float2(ra.y); xv[2] = f.x; xv[3] = f.y;
+      f = bf16x2_to_float2(rb.x); xv[4] = f.x; xv[5] = f.y;
+      f = bf16x2_to_float2(rb.y); xv[6] = f.x; xv[7] = f.y;
+#pragma unroll
+      for (int e4 = 0; e4 < kDwgEG; e4 += 4) {
+        const float4 g = *reinterpret_cast<const float4*>(&dl_s[i][e4]);
+        const float gv[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+          for (int j = 0; j < 8; ++j) acc[e4 + q][j] = fmaf(gv[q], xv[j], acc[e4 + q][j]);
       }
     }
   }
-  if (col < d) {
+  // warps in fixed order
 #pragma unroll
-    for (int e = 0; e < EP; ++e)
-      if (e < E) scratch[(static_cast<size_t>(blockIdx.x) * E + e) * d + col] = acc[e];
+  for (int e = 0; e < kDwgEG; ++e) {
+    float* r = red_s + (warp * kDwgEG + e) * 256;
+    *reinterpret_cast<float4*>(r + lane * 4) = make_float4(acc[e][0], acc[e][1], acc[e][2], acc[e][3]);
+    *reinterpret_cast<float4*>(r + 128 + lane * 4) = make_float4(acc[e][4], acc[e][5], acc[e][6], acc[e][7]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < kDwgEG * 256; i += 128) {
+    const int e = e0 + (i >> 8), col = slab0 + (i & 255);
+    if (e < E && col < d) {
+      const float v = ((red_s[i] + red_s[kDwgEG * 256 + i]) + red_s[2 * kDwgEG * 256 + i]) + red_s[3 * kDwgEG * 256 + i];
+      scratch[(static_cast<size_t>(blockIdx.x) * E + e) * d + col] = v;
+    }
   }
 }
 
+// blocks [0, nred): dwg[i] = sum over chunks of scratch[c][i];  blocks [nred, nred + B): dctx[b,:] for image b
 __global__ void __launch_bounds__(256)
-router_dwg_reduce_kernel(const float* __restrict__ scratch, int nchunks, int n, float* __restrict__ dwg) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  float s = 0.f;
-  for (int c = 0; c < nchunks; ++c) s += scratch[static_cast<size_t>(c) * n + i];
-  dwg[i] = s;
-}
-
-// dctx[b, e] = sum over the tokens of image b.  One block per image, warp w handles experts w, w+8, ...
-__global__ void __launch_bounds__(256)
-router_dctx_kernel(const float* __restrict__ dlogits, int T, int E, int tpi, float* __restrict__ dctx) {
-  const int b = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int t0 = b * tpi, t1 = min(T, t0 + tpi);
-  for (int e = warp; e < E; e += 8) {
+router_dwg_reduce_kernel(const float* __restrict__ scratch, int nchunks, int n, float* __restrict__ dwg, int nred,
+                         const float* __restrict__ dlogits, int T, int E, int tpi, float* __restrict__ dctx) {
+  if (static_cast<int>(blockIdx.x) < nred) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
     float s = 0.f;
-    for (int t = t0 + lane; t < t1; t += 32) s += dlogits[static_cast<size_t>(t) * E + e];
-    s = warp_sum(s);
-    if (lane == 0) dctx[static_cast<size_t>(b) * E + e] = s;
+    int c = 0;
+    for (; c + 4 <= nchunks; c += 4) {
+      const float a0 = scratch[static_cast<size_t>(c) * n + i], a1 = scratch[static_cast<size_t>(c + 1) * n + i];
+      const float a2 = scratch[static_cast<size_t>(c + 2) * n + i], a3 = scratch[static_cast<size_t>(c + 3) * n + i];
+      s = (((s + a0) + a1) + a2) + a3;
+    }
+    for (; c < nchunks; ++c) s += scratch[static_cast<size_t>(c) * n + i];
+    dwg[i] = s;
+    return;
+  }
+  // dctx: thread (phase, e) strides the image's tokens; consecutive threads read consecutive addresses
+  __shared__ float part[256];
+  const int b = blockIdx.x - nred;
+  const int nphase = 256 / E;
+  const int ph = threadIdx.x / E, e = threadIdx.x - ph * E;
+  const int t0 = b * tpi, t1 = min(T, t0 + tpi);
+  float s = 0.f;
+  if (ph < nphase)
+    for (int t = t0 + ph; t < t1; t += nphase) s += dlogits[static_cast<size_t>(t) * E + e];
+  part[threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.x < E) {
+    float r = 0.f;
+    for (int q = 0; q < nphase; ++q) r += part[q * E + threadIdx.x];
+    dctx[static_cast<size_t>(b) * E + threadIdx.x] = r;
   }
 }
 
-static int dwg_chunks(int T) {
-  int chunks = (T + kDwgTok - 1) / kDwgTok;
-  const int cap = kNumSMs * 4;
-  if (chunks > cap) chunks = cap;
+static int dwg_chunks(int T, int d, int E) {
+  const int slabs = (d + 255) / 256, groups = (E + kDwgEG - 1) / kDwgEG;
+  int chunks = (4 * kNumSMs + slabs * groups - 1) / (slabs * groups);
+  const int max_chunks = (T + 15) / 16;
+  if (chunks > max_chunks) chunks = max_chunks;
   return chunks < 1 ? 1 : chunks;
 }
 
@@ -171,36 +226,51 @@ extern "C" int b200moe_router_bwd_dlogits(const float* logits, const int32_t* to
 }
 
 extern "C" int64_t b200moe_dwg_scratch_floats(int T, int d, int E) {
-  return static_cast<int64_t>(dwg_chunks(T)) * E * d;
+  return static_cast<int64_t>(dwg_chunks(T, d, E)) * E * d;
+}
+
+extern "C" int b200moe_router_bwd_params(const float* dlogits, const void* x, int T, int d, int E,
+                                         int tokens_per_image, float* scratch, float* dwg, float* dctx_bias,
+                                         void* stream) {
+  B200MOE_REQUIRE(E >= 1 && E <= 64 && d > 0 && d % 128 == 0, B200MOE_EINVAL, "router_bwd_params: bad E=%d / d=%d", E, d);
+  B200MOE_REQUIRE(dctx_bias == nullptr || tokens_per_image > 0, B200MOE_EINVAL, "router_bwd_params: tokens_per_image <= 0");
+  B200MOE_REQUIRE(dwg == nullptr || (scratch != nullptr && x != nullptr), B200MOE_EINVAL, "router_bwd_params: NULL scratch / x");
+  if (T == 0 || (dwg == nullptr && dctx_bias == nullptr)) return B200MOE_OK;
+  if (int rc = b200moe_check_device()) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int chunks = 0;
+  if (dwg) {
+    chunks = dwg_chunks(T, d, E);
+    int tpc = (T + chunks - 1) / chunks;
+    tpc = (tpc + 3) / 4 * 4;
+    chunks = (T + tpc - 1) / tpc;
+    static bool configured = false;
+    if (!configured) {
+      cudaError_t e = cudaFuncSetAttribute(router_dwg_partial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDwgRedBytes);
+      B200MOE_REQUIRE(e == cudaSuccess, B200MOE_ECUDA, "router_bwd_params: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      configured = true;
+    }
+    dim3 grid(chunks, (d + 255) / 256, (E + kDwgEG - 1) / kDwgEG);
+    router_dwg_partial_kernel<<<grid, 128, kDwgRedBytes, st>>>(dlogits, static_cast<const __nv_bfloat16*>(x), T, d, E, tpc,
+                                                               scratch);
+    if (int rc = check_launch("router_dwg_partial")) return rc;
+  }
+  const int n = E * d;
+  const int nred = dwg ? (n + 255) / 256 : 0;
+  const int B = dctx_bias ? (T + tokens_per_image - 1) / tokens_per_image : 0;
+  router_dwg_reduce_kernel<<<nred + B, 256, 0, st>>>(scratch, chunks, n, dwg, nred, dlogits, T, E,
+                                                     tokens_per_image > 0 ? tokens_per_image : T, dctx_bias);
+  return check_launch("router_dwg_reduce");
 }
 
 extern "C" int b200moe_router_bwd_dwg(const float* dlogits, const void* x, int T, int d, int E, float* scratch,
                                       float* dwg, void* stream) {
-  B200MOE_REQUIRE(E >= 1 && E <= 64 && d > 0, B200MOE_EINVAL, "router_bwd_dwg: bad E=%d / d=%d", E, d);
-  if (int rc = b200moe_check_device()) return rc;
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int chunks = dwg_chunks(T);
-  const int tpc = (T + chunks - 1) / chunks;
-  dim3 grid(chunks, (d + 255) / 256);
-  auto xb = static_cast<const __nv_bfloat16*>(x);
-#define CASE(EP) router_dwg_partial_kernel<EP><<<grid, 256, 0, st>>>(dlogits, xb, T, d, E, tpc, scratch)
-  if (E <= 8) CASE(8);
-  else if (E <= 16) CASE(16);
-  else if (E <= 32) CASE(32);
-  else CASE(64);
-#undef CASE
-  if (int rc = check_launch("router_dwg_partial")) return rc;
-  const int n = E * d;
-  router_dwg_reduce_kernel<<<(n + 255) / 256, 256, 0, st>>>(scratch, chunks, n, dwg);
-  return check_launch("router_dwg_reduce");
+  B200MOE_REQUIRE(dwg != nullptr, B200MOE_EINVAL, "router_bwd_dwg: dwg is NULL");
+  return b200moe_router_bwd_params(dlogits, x, T, d, E, 0, scratch, dwg, nullptr, stream);
 }
 
 extern "C" int b200moe_router_bwd_dctx(const float* dlogits, int T, int E, int tokens_per_image, float* dctx_bias,
                                        void* stream) {
-  B200MOE_REQUIRE(tokens_per_image > 0, B200MOE_EINVAL, "router_bwd_dctx: tokens_per_image <= 0");
-  if (T == 0) return B200MOE_OK;
-  if (int rc = b200moe_check_device()) return rc;
-  const int B = (T + tokens_per_image - 1) / tokens_per_image;
-  router_dctx_kernel<<<B, 256, 0, static_cast<cudaStream_t>(stream)>>>(dlogits, T, E, tokens_per_image, dctx_bias);
-  return check_launch("router_dctx");
+  B200MOE_REQUIRE(tokens_per_image > 0 && dctx_bias != nullptr, B200MOE_EINVAL, "router_bwd_dctx: bad arguments");
+  return b200moe_router_bwd_params(dlogits, nullptr, T, 128, E, tokens_per_image, nullptr, nullptr, dctx_bias, stream);
 }

@@ -11,3 +11,5 @@ for s in j.get("sweep", []):
     print(s["workload"], s["tokens"], "ms=%.3f" % s["ms_per_step"], "graph", s["cuda_graph"], "tok/s=%.3g" % s["tokens_per_s"],
           "gemm_ms=%.3f" % s["gemm_ms"], "TF=%.0f" % s["gemm_tflops"], "frac=%.3f" % s["gemm_frac_of_peak"])
     print("    ", {k: round(v, 3) for k, v in s["per_call_ms"].items()})
+    if "hbm_kernels" in s:
+        print("     hbm:", {k: (v["gbs"], v["frac"]) for k, v in s["hbm_kernels"].items()})
