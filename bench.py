@@ -338,6 +338,8 @@ def main():
     dist_on = world > 1
     ep_group = None
     if dist_on:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ.pop("NCCL_DEBUG")          # its banner goes to stdout, which carries the ONE JSON line
         dist.init_process_group("nccl", device_id=device)
         ep_group = dist.group.WORLD
 
@@ -411,8 +413,20 @@ def main():
                     sweep.append({"workload": name, "tokens": B * HW, "error": repr(ex)})
                 torch.cuda.empty_cache()
             line["sweep"] = sweep
+    if dist_on:
+        # the same workload on ONE GPU (all experts local, this rank's tokens), measured by rank 0 in the same run, so
+        # that value / (n_gpus * scaling_reference.value) is the weak-scaling efficiency on identical per-GPU work
+        if rank == 0:
+            try:
+                r1 = measure_layer(w, min(args.steps, 10), 3, device, want_e2e=False, want_roofline=False)
+                ms1 = sum(r1["ms"]) / len(r1["ms"])
+                line["scaling_reference"] = {"n_gpus": 1, "workload": w["name"], "ms_per_step": ms1,
+                                             "value": r1["T"] / (ms1 * 1e-3), "cuda_graph": r1["graph"]}
+            except Exception as ex:  # noqa: BLE001
+                line["scaling_reference"] = {"error": repr(ex)}
+        dist.barrier()
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if dist_on:
         dist.destroy_process_group()
 

@@ -160,6 +160,17 @@ int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assignment, con
 int b200moe_ep_recv_plan(const int32_t* recv_counts, const int32_t* seg_expert, int n_seg, int E_local,
                          int rows_cap, int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert,
                          int32_t* src_of_row, void* stream);
+/* Expert-parallel routing tables on the device (no host round trip before the split sizes are needed).
+ *   ep_hist        : out [k*E+1] = per-(slot, expert) assignment counts of this rank (sum of block_counts over the
+ *                    router blocks), then T: the message of the histogram all-gather.
+ *   ep_route_tables: all_hist [W, k*E+1] (gathered); capacity_factor < 0 = no limit.  Outputs: global_offset [k,E] for
+ *                    b200moe_plan; kept [W*E+2] = rows every rank sends to every expert, then the global capacity and
+ *                    the global token count (copy this to the host for the all-to-all split sizes); recv_counts
+ *                    [C][W][experts_per_chunk] = rows this rank receives per (chunk of local experts, source, expert). */
+int b200moe_ep_hist(const int32_t* block_counts, int nblk, int k, int E, int T, int32_t* out, void* stream);
+int b200moe_ep_route_tables(const int32_t* all_hist, int W, int k, int E, int rank, double capacity_factor,
+                            int experts_per_chunk, int32_t* global_offset, int32_t* kept, int32_t* recv_counts,
+                            void* stream);
 /* Inverse row gather used on the EP return path: out[src_of_row[r],:] = in[r,:] for r < meta[0], src >= 0. */
 int b200moe_scatter_rows(const void* in, const int32_t* src_of_row, const int32_t* meta, int rows_cap, int d,
                          void* out, void* stream);

@@ -50,6 +50,8 @@ SIGNATURES = {
     "b200moe_unpermute_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
     "b200moe_ep_recv_plan": [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P],
     "b200moe_scatter_rows": [_P, _P, _P, _I, _I, _P, _P],
+    "b200moe_ep_hist": [_P, _I, _I, _I, _I, _P, _P],
+    "b200moe_ep_route_tables": [_P, _I, _I, _I, _I, C.c_double, _I, _P, _P, _P, _P],
 }
 _RESTYPE = {"b200moe_last_error": C.c_char_p, "b200moe_dwg_scratch_floats": C.c_int64,
             "b200moe_router_scratch_bytes": C.c_int64, "b200moe_layer_ws_layout": C.c_int64,
@@ -109,7 +111,7 @@ KERNELS_PER_CALL = {
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
     "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
     "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,
-    "b200moe_unpermute_bwd": 1, "b200moe_ep_recv_plan": 1, "b200moe_scatter_rows": 1,
+    "b200moe_unpermute_bwd": 1, "b200moe_ep_recv_plan": 1, "b200moe_ep_hist": 1, "b200moe_ep_route_tables": 1, "b200moe_scatter_rows": 1,
 }
 
 

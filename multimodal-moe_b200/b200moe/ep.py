@@ -23,7 +23,7 @@ from typing import List, Optional, Tuple
 import torch
 import torch.distributed as dist
 
-from . import ops
+from . import _lib, ops
 
 
 def route_tables(hist_all: torch.Tensor, tokens_all: torch.Tensor, rank: int, capacity_factor: Optional[float],
@@ -75,6 +75,36 @@ def split_sizes(kept: torch.Tensor, rank: int, W: int, C: int = 1):
     return send, recv, recv_counts, seg_expert
 
 
+def split_sizes_np(kept, rank: int, W: int, C: int = 1):
+    """numpy twin of split_sizes for the hot path: kept [W,E] int array -> (send_splits[c][W], recv_splits[c][W])."""
+    E = kept.shape[1]
+    EL = E // W
+    ELc = EL // C
+    out_view = kept[rank].reshape(W, C, ELc)
+    in_view = kept[:, rank * EL:(rank + 1) * EL].reshape(W, C, ELc)
+    send = [out_view[:, c].sum(-1).tolist() for c in range(C)]
+    recv = [in_view[:, c].sum(-1).tolist() for c in range(C)]
+    return send, recv
+
+
+def _ep_static(mod, dev, E: int, W: int):
+    """Per-module constants of the EP layout, kept on the device: (C, ELc, expert order, segment -> local expert)."""
+    key = (str(dev), E, W, getattr(mod, "ep_chunks", 1))
+    hit = mod.__dict__.get("_ep_static")
+    if hit is None or hit[0] != key:
+        C, ELc, order = chunk_layout(E, W, getattr(mod, "ep_chunks", 1))
+        seg = torch.arange(ELc, dtype=torch.int32).repeat(W)
+        hit = mod.__dict__["_ep_static"] = (key, (C, ELc, order.to(dev), seg.to(dev)))
+    return hit[1]
+
+
+def _pinned(mod, n: int) -> torch.Tensor:
+    t = mod.__dict__.get("_ep_pinned")
+    if t is None or t.numel() != n:
+        t = mod.__dict__["_ep_pinned"] = torch.empty((n,), dtype=torch.int32).pin_memory()
+    return t
+
+
 def _a2a_into(out: torch.Tensor, buf: torch.Tensor, in_splits: List[int], out_splits: List[int], group):
     dist.all_to_all_single(out, buf, output_split_sizes=out_splits, input_split_sizes=in_splits, group=group)
 
@@ -107,32 +137,44 @@ class _EPFunction(torch.autograd.Function):
         T, d = x2.shape
         E, k, EL = mod.num_experts, mod.top_k, mod.num_local_experts
         need_grad = any(ctx.needs_input_grad)
-        w1b, w2b = mod._bf16_weight("w1", w1), mod._bf16_weight("w2", w2)
+        w1b, w2b, wsplit, wgf = mod._prepared(w1, w2, wg)          # one launch: bf16 operands + gate hi/lo split
         b1f, b2f = b1.float().contiguous(), b2.float().contiguous()
-        wgf = wg.float().contiguous()
         cb = ctx_bias.float().contiguous() if ctx_bias is not None else None
         dev = x2.device
         comp, comm = torch.cuda.current_stream(), _comm_stream(mod, dev)
+        st = _lib.stream_ptr()
+        i32 = torch.int32
 
-        r = ops.router_fwd(x2, wgf, cb, tokens_per_image, k, mod.normalize_topk)
-        # histograms of every rank (+ token counts) in one small all-gather
-        mine = torch.cat([r.block_counts.sum(0, dtype=torch.int32).reshape(-1),
-                          torch.tensor([T], dtype=torch.int32, device=dev)])
-        allh = torch.empty((W, mine.numel()), dtype=torch.int32, device=dev)
+        r = ops.router_fwd(x2, None, cb, tokens_per_image, k, mod.normalize_topk, wg_split=wsplit, E=E)
+        # histograms of every rank (+ token counts): one kernel, one small all-gather, one kernel for the global
+        # routing tables; only the kept counts travel to the host (the one sync of the pass: all-to-all split sizes)
+        C, ELc, order_dev, seg_dev = _ep_static(mod, dev, E, W)
+        mine = torch.empty((k * E + 1,), dtype=i32, device=dev)
+        _lib.call("b200moe_ep_hist", r.block_counts.data_ptr(), r.block_counts.shape[0], k, E, T, mine.data_ptr(), st)
+        allh = torch.empty((W, k * E + 1), dtype=i32, device=dev)
         dist.all_gather_into_tensor(allh, mine, group=group)
-        hist_all, tokens_all = allh[:, :-1].reshape(W, k, E), allh[:, -1]
-        goff, cap, kept = route_tables(hist_all, tokens_all, rank, mod.capacity_factor, k)
-        kept_h = kept.cpu()                                  # the one host sync of the pass: all-to-all split sizes
-        C, ELc, order = chunk_layout(E, W, getattr(mod, "ep_chunks", 2))
-        send_splits, recv_splits, recv_counts, seg_expert = split_sizes(kept_h, rank, W, C)
+        goff = torch.empty((k, E), dtype=i32, device=dev)
+        kept_dev = torch.empty((W * E + 2,), dtype=i32, device=dev)
+        recv_counts_dev = torch.empty((C, W * ELc), dtype=i32, device=dev)
+        cf = -1.0 if mod.capacity_factor is None else float(mod.capacity_factor)
+        _lib.call("b200moe_ep_route_tables", allh.data_ptr(), W, k, E, rank, cf, ELc, goff.data_ptr(),
+                  kept_dev.data_ptr(), recv_counts_dev.data_ptr(), st)
+        kept_pin = _pinned(mod, W * E + 2)
+        kept_pin.copy_(kept_dev, non_blocking=True)
+        done_ev = torch.cuda.Event()
+        done_ev.record(comp)
+        send_cap = ops.rows_upper_bound(T, k, E, -1)            # host work that does not need the counts
+        done_ev.synchronize()
+        kept_np = kept_pin.numpy()
+        cap = int(kept_np[W * E])
+        send_splits, recv_splits = split_sizes_np(kept_np[:W * E].reshape(W, E), rank, W, C)
         send_off = _cumsum0([sum(s_) for s_ in send_splits])
         n_send = send_off[-1]
 
-        send_cap = ops.rows_upper_bound(T, k, E, -1)
-        p = ops.plan(r, T, k, E, cap, mod.aux_loss_weight, mod.z_loss_weight, global_offset=goff.to(dev),
-                     expert_order=order.to(dev), row_pad=1, rows_cap=send_cap)
+        p = ops.plan(r, T, k, E, cap, mod.aux_loss_weight, mod.z_loss_weight, global_offset=goff,
+                     expert_order=order_dev, row_pad=1, rows_cap=send_cap)
         xs = ops.permute(x2, p.token_of_row, p.meta, send_cap)
-        seg_dev = seg_expert.to(dev)
+        recv_counts = [recv_counts_dev[c] for c in range(C)]
 
         # dispatch all groups on the communication stream
         ready = torch.cuda.Event()
@@ -158,7 +200,7 @@ class _EPFunction(torch.autograd.Function):
             xr = ch.xp
             xr.record_stream(comp)
             ch.cap = max(128, (ch.n_recv + ELc * 127 + 127) // 128 * 128)
-            ch.offs, ch.meta, ch.tile_e, ch.src = ops.ep_recv_plan(recv_counts[c].to(dev), seg_dev, ELc, ch.cap)
+            ch.offs, ch.meta, ch.tile_e, ch.src = ops.ep_recv_plan(recv_counts[c], seg_dev, ELc, ch.cap)
             ch.xp = ops.permute(xr, ch.src, ch.meta, ch.cap)
             ch.pre, ch.h = ops.ffn_up(ch.xp, w1b[ch.lo:ch.hi], b1f[ch.lo:ch.hi], ch.meta, ch.tile_e,
                                       save_pre=need_grad)
@@ -219,8 +261,8 @@ class _EPFunction(torch.autograd.Function):
         # router gradient does not depend on the experts: it fills the bubble while the first rows travel
         dlogits = ops.router_bwd_dlogits(r.logits, r.topk_idx, p.row_of_assignment, dgate_row, p.tokens_per_expert,
                                          d_aux_t, mod.normalize_topk, mod.aux_loss_weight, mod.z_loss_weight)
-        dwg = ops.router_bwd_dwg(dlogits, x2) if need[2] else None
-        dctx = ops.router_bwd_dctx(dlogits, ctx.tpi) if (ctx.has_ctx and need[1]) else None
+        dwg, dctx = ops.router_bwd_params(dlogits, x2, ctx.tpi, want_dwg=need[2],
+                                          want_dctx=bool(ctx.has_ctx and need[1]))
 
         f32 = torch.float32
         dw1 = torch.empty((EL, F, d), dtype=f32, device=dev) if need[3] else None
@@ -246,11 +288,13 @@ class _EPFunction(torch.autograd.Function):
                               group)
             if need[5]:
                 ops.ffn_wgrad(dyp, ch.h, ch.offs, n, out=dw2[ch.lo:ch.hi])
-            if need[6]:
-                ops.colsum(dyp, ch.offs, n, out=db2[ch.lo:ch.hi])
             if need[3]:
                 ops.ffn_wgrad(dhpre, ch.xp, ch.offs, n, out=dw1[ch.lo:ch.hi])
-            if need[4]:
+            if need[6] and need[4]:
+                ops.colsum(dyp, ch.offs, n, out=db2[ch.lo:ch.hi], a1=dhpre, out1=db1[ch.lo:ch.hi])
+            elif need[6]:
+                ops.colsum(dyp, ch.offs, n, out=db2[ch.lo:ch.hi])
+            elif need[4]:
                 ops.colsum(dhpre, ch.offs, n, out=db1[ch.lo:ch.hi])
         dx = None
         if need[0]:

@@ -108,6 +108,36 @@ class _Aux(Mapping):
         return len(self._KEYS)
 
 
+class _CtxBiasFunction(torch.autograd.Function):
+    """A.2 context bias as one kernel each way (used by the expert-parallel path, whose layer pass is not a single
+    C call): ctx_bias[B,E] = concat_i Embed_i(context[:, i]) @ Wc^T."""
+
+    @staticmethod
+    def forward(ctx, context, wc, mod, *tables):
+        B, E = context.shape[0], wc.shape[0]
+        tabs = [_f32c(t) for t in tables]
+        wcf = _f32c(wc)
+        cb = torch.empty((B, E), dtype=torch.float32, device=wc.device)
+        tp, vp = mod._ctx_arrays(tabs)
+        _lib.call("b200moe_ctx_bias_fwd", context.data_ptr(), tp, vp, len(tabs), mod.context_dim, wcf.data_ptr(), B, E,
+                  cb.data_ptr(), _lib.stream_ptr())
+        ctx.mod, ctx.saved = mod, (context, tabs, wcf)
+        return cb
+
+    @staticmethod
+    def backward(ctx, dcb):
+        context, tabs, wcf = ctx.saved
+        mod = ctx.mod
+        dcb = _f32c(dcb)
+        dwc = torch.empty_like(wcf)
+        dtabs = [torch.empty_like(t) for t in tabs]
+        tp, vp = mod._ctx_arrays(tabs)
+        dp = (C.c_void_p * len(tabs))(*[t.data_ptr() for t in dtabs])
+        _lib.call("b200moe_ctx_bias_bwd", context.data_ptr(), dcb.data_ptr(), tp, vp, len(tabs), mod.context_dim,
+                  wcf.data_ptr(), context.shape[0], wcf.shape[0], C.addressof(dp), dwc.data_ptr(), _lib.stream_ptr())
+        return (None, dwc, None, *dtabs)
+
+
 class _MoEFunction(torch.autograd.Function):
     """One C call each way: b200moe_layer_fwd (router -> plan -> permute -> up(+GELU) -> down -> combine) and
     b200moe_layer_bwd (mirror, incl. the A.12 router gradient); the context bias of A.2 and its gradient are one
@@ -229,7 +259,8 @@ class ContextMoE(nn.Module):
         self.context_vocab_sizes = tuple(context_vocab_sizes)
         self.context_dim = context_dim
         self.ep_group = ep_group
-        self.ep_chunks = 2            # groups of local experts whose all-to-all overlaps the other groups' GEMMs
+        self.ep_chunks = 1            # groups of local experts whose all-to-all overlaps the other groups' GEMMs
+        # (measured at 2 GPUs, workload D: 1 group 3.72 ms, 2 groups 4.00 ms, 4 groups 4.91 ms per step)
         self.ep_size, self.ep_rank = 1, 0
         if ep_group is not None:
             import torch.distributed as dist
@@ -259,7 +290,7 @@ class ContextMoE(nn.Module):
         new = self.__class__.__new__(self.__class__)
         memo[id(self)] = new
         for k_, v in self.__dict__.items():
-            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep"):
+            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned"):
                 continue
             if k_ in ("_wcache", "last_aux", "_plans"):
                 new.__dict__[k_] = {}
@@ -274,7 +305,7 @@ class ContextMoE(nn.Module):
     def __getstate__(self):
         s = dict(self.__dict__)
         s["_wcache"], s["last_aux"], s["aux_loss"], s["ep_group"], s["_plans"] = {}, {}, torch.zeros(()), None, {}
-        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep"):
+        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned"):
             s.pop(k_, None)
         return s
 
@@ -383,7 +414,11 @@ class ContextMoE(nn.Module):
             xb = xb.contiguous()
         if self.ep_size > 1:
             from .ep import ep_forward
-            y, aux, stats = ep_forward(self, xb, self.context_bias(context), tpi)
+            cb = None
+            if context is not None and self.ctx_proj is not None:
+                cb = _CtxBiasFunction.apply(context.long().contiguous(), self.ctx_proj.weight, self,
+                                            *[m_.weight for m_ in self.ctx_embed])
+            y, aux, stats = ep_forward(self, xb, cb, tpi)
             self.aux_loss = aux
             r, p = self._last
             self.last_aux = {"load_balance": stats[1], "z_loss": stats[2], "tokens_per_expert": p.tokens_per_expert,

@@ -51,10 +51,12 @@ class Routing:
     block_stats: torch.Tensor   # [nblk,E+1] fp32
 
 
-def router_fwd(x: torch.Tensor, wg: torch.Tensor, ctx_bias: Optional[torch.Tensor], tokens_per_image: int,
-               k: int, normalize: bool) -> Routing:
+def router_fwd(x: torch.Tensor, wg: Optional[torch.Tensor], ctx_bias: Optional[torch.Tensor],
+               tokens_per_image: int, k: int, normalize: bool, wg_split: Optional[torch.Tensor] = None,
+               E: Optional[int] = None) -> Routing:
+    """wg [E,d] fp32, split into bf16 hi/lo inside the call; or wg=None with wg_split from prepare_weights (and E)."""
     T, d = x.shape
-    E = wg.shape[0]
+    E = wg.shape[0] if wg is not None else E
     dev = x.device
     nblk = _lib.load().b200moe_num_router_blocks(T)
     r = Routing(_empty((T, E), torch.float32, dev), _empty((T, k), torch.int32, dev),
@@ -63,7 +65,7 @@ def router_fwd(x: torch.Tensor, wg: torch.Tensor, ctx_bias: Optional[torch.Tenso
     nscratch = _lib.load().b200moe_router_scratch_bytes(d, E)
     if nscratch < 0:
         raise RuntimeError(f"router_fwd: num_experts={E} outside [1,64]")
-    wsplit = _empty((nscratch // 2,), torch.bfloat16, dev)
+    wsplit = wg_split if wg_split is not None else _empty((nscratch // 2,), torch.bfloat16, dev)
     call("b200moe_router_fwd", ptr(x), ptr(ctx_bias), tokens_per_image, ptr(wg), ptr(wsplit), T, d, E, k,
          int(normalize),
          ptr(r.logits), ptr(r.topk_idx), ptr(r.topk_gate), ptr(r.block_counts), ptr(r.block_stats), stream_ptr())
@@ -219,6 +221,25 @@ def router_bwd_dwg(dlogits, x):
     dwg = _empty((E, d), torch.float32, x.device)
     call("b200moe_router_bwd_dwg", ptr(dlogits), ptr(x), T, d, E, ptr(scratch), ptr(dwg), stream_ptr())
     return dwg
+
+
+def router_bwd_params(dlogits, x, tokens_per_image: int, want_dwg: bool = True, want_dctx: bool = True):
+    """(dwg [E,d] or None, dctx_bias [B,E] or None) in two launches."""
+    T, E = dlogits.shape
+    d = x.shape[1]
+    dev = x.device
+    dwg = scratch = dctx = None
+    if want_dwg:
+        n = _lib.load().b200moe_dwg_scratch_floats(T, d, E)
+        scratch = _empty((n,), torch.float32, dev)
+        dwg = _empty((E, d), torch.float32, dev)
+    if want_dctx:
+        B = (T + tokens_per_image - 1) // tokens_per_image
+        dctx = _empty((B, E), torch.float32, dev)
+    if want_dwg or want_dctx:
+        call("b200moe_router_bwd_params", ptr(dlogits), ptr(x), T, d, E, tokens_per_image, ptr(scratch), ptr(dwg),
+             ptr(dctx), stream_ptr())
+    return dwg, dctx
 
 
 def router_bwd_dctx(dlogits, tokens_per_image: int):

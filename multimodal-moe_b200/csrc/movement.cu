@@ -375,7 +375,7 @@ extern "C" int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assi
   B200MOE_REQUIRE(dlogits == nullptr || wg != nullptr, B200MOE_EINVAL, "unpermute_bwd: dlogits without wg");
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
-  const bool big = T >= 64 * 2 * kNumSMs;
+  const bool big = T >= 64 * kNumSMs;   // 8 tokens per warp once 64-token blocks still cover the SMs
   const int tok = big ? 64 : 16;
   const size_t smem = dlogits ? sizeof(float) * (static_cast<size_t>(E) * 256 + tok * E) : 0;
   static bool configured = false;
