@@ -99,3 +99,15 @@ def test_ep_tables_world2(T, E, k, cf, chunks):
         p.join(120)
         assert p.exitcode == 0
     assert out.get() == "ok"
+
+
+def test_split_sizes_numpy_twin():
+    """The numpy split-size helper of the hot path agrees with the torch one the gloo test pins."""
+    from b200moe.ep import split_sizes, split_sizes_np
+    g = torch.Generator().manual_seed(4)
+    for W, E, C in ((2, 8, 1), (4, 16, 2), (8, 64, 4), (1, 4, 2)):
+        kept = torch.randint(0, 500, (W, E), generator=g)
+        for rank in range(W):
+            send, recv, _, _ = split_sizes(kept, rank, W, C)
+            send_np, recv_np = split_sizes_np(kept.numpy(), rank, W, C)
+            assert send == send_np and recv == recv_np
