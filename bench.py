@@ -305,6 +305,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, choices=[None, "A", "C", "D"])
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-pdl", action="store_true", help="plain stream-ordered launches inside the whole-layer calls")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -343,6 +344,9 @@ def main():
         dist.init_process_group("nccl", device_id=device)
         ep_group = dist.group.WORLD
 
+    if args.no_pdl:
+        from b200moe import _lib as _l
+        _l.load().b200moe_layer_pdl(0)
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()

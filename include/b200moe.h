@@ -228,6 +228,9 @@ int b200moe_layer_bwd(const b200moe_layer_desc* desc, const void* x, const float
 /* Per-step CUDA-event timing of the two calls above (measurement aid): enable, run, synchronize the stream, then read
  * entries 0,1,... until the call returns B200MOE_EINVAL.  b200moe_layer_profile(x) also clears earlier entries. */
 int b200moe_layer_profile(int enable);
+/* Programmatic dependent launch between the kernels of a whole-layer call (default on): every kernel of the path runs
+ * its prologue while its predecessor drains and executes griddepcontrol.wait before touching global memory. */
+int b200moe_layer_pdl(int enable);
 int b200moe_layer_profile_read(int index, const char** name, float* ms);
 
 #ifdef __cplusplus

@@ -7,6 +7,7 @@
 namespace b200moe {
 
 static thread_local char g_err[512] = "";
+thread_local bool g_pdl = false;
 
 void set_error(const char* fmt, ...) {
   va_list ap;

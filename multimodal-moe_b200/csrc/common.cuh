@@ -22,6 +22,34 @@ int check_launch(const char* what);
     }                                         \
   } while (0)
 
+// Programmatic dependent launch (PDL): inside the whole-layer calls every kernel is launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, so its blocks may be scheduled (and run their prologue:
+// barrier init, TMEM allocation, descriptor prefetch) while the previous kernel of the stream drains.  Every kernel
+// of the layer path executes pdl_sync() before its first global-memory access: griddepcontrol.wait returns only when
+// the prerequisite grid has completed and flushed, so data dependencies are exactly those of plain stream order.
+// Without the attribute both instructions are no-ops.
+extern thread_local bool g_pdl;
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_sync() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = g_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 constexpr int kNumSMs = 148;
 constexpr int kRowPad = 128;          // every expert segment of the permuted buffer starts at a multiple of this
 constexpr int kRouterTokPerBlock = 128;  // max tokens per router/plan block (granularity of the priority scan)

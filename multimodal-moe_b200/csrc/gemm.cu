@@ -97,6 +97,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_sync();                                   // prologue done; everything below reads the previous kernel's output
 
   // ---- tile schedule (identical in every role) -------------------------------------------------------------
   const int tiles_n = args.N / BN;

@@ -14,6 +14,7 @@ struct ProfEntry { const char* name; cudaEvent_t a, b; };
 static bool g_prof_on = false;
 static ProfEntry g_prof[kMaxProf];
 static int g_prof_n = 0;
+static bool g_pdl_enabled = true;
 
 struct ProfScope {
   cudaStream_t st;
@@ -31,6 +32,13 @@ struct ProfScope {
     cudaEventRecord(g_prof[g_prof_n].b, st);
     ++g_prof_n;
   }
+};
+// PDL on for the kernels launched inside one whole-layer call (off while the per-step profile is recording: the
+// events between the kernels serialise them anyway and the timings should be those of isolated kernels)
+struct PdlScope {
+  bool prev;
+  PdlScope() : prev(g_pdl) { g_pdl = !g_prof_on && g_pdl_enabled; }
+  ~PdlScope() { g_pdl = prev; }
 };
 #define STEP(name, call)            \
   do {                              \
@@ -161,6 +169,11 @@ extern "C" int b200moe_ctx_bias_bwd(const int64_t* context, const float* dctx_bi
   return check_launch("ctx_bias_bwd");
 }
 
+extern "C" int b200moe_layer_pdl(int enable) {
+  g_pdl_enabled = enable != 0;
+  return B200MOE_OK;
+}
+
 extern "C" int b200moe_layer_profile(int enable) {
   for (int i = 0; i < g_prof_n; ++i) { cudaEventDestroy(g_prof[i].a); cudaEventDestroy(g_prof[i].b); }
   g_prof_n = 0;
@@ -234,6 +247,7 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
   const int32_t* meta = WS(int32_t, B200MOE_WS_META);
   const int32_t* tile_expert = WS(int32_t, B200MOE_WS_TILE_EXPERT);
   int rc;
+  PdlScope pdl_;
   STEP("router_fwd",
        b200moe_router_fwd(x, ctx_bias, q->tokens_per_image, nullptr, const_cast<void*>(wg_split), T, d, E, k,
                           q->normalize_topk, WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX),
@@ -279,6 +293,7 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
   void* dhpre = BWS(void, B200MOE_BWS_DHPRE);
   float* dlogits = BWS(float, B200MOE_BWS_DLOGITS);
   int rc;
+  PdlScope pdl_;
   STEP("combine_bwd",
        b200moe_combine_bwd(dy, WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_TOKEN_OF_ROW),
                            WS(float, B200MOE_WS_GATE_OF_ROW), meta, R, d, dyp, BWS(float, B200MOE_BWS_DGATE_ROW), stream));

@@ -26,6 +26,7 @@ __device__ __forceinline__ uint4 pack8(const float (&v)[8]) {
 __global__ void __launch_bounds__(kMoveThreads)
 permute_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ token_of_row,
                const int32_t* __restrict__ meta, int d, __nv_bfloat16* __restrict__ xp) {
+  pdl_sync();
   const int R = meta[0];
   const int nchunk = d >> 3;
   const int lane = threadIdx.x & 31;
@@ -61,6 +62,7 @@ scatter_rows_kernel(const __nv_bfloat16* __restrict__ in, const int32_t* __restr
 __global__ void __launch_bounds__(kMoveThreads)
 combine_kernel(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ row_of_assignment,
                const float* __restrict__ topk_gate, int T, int k, int d, __nv_bfloat16* __restrict__ y) {
+  pdl_sync();
   const int nchunk = d >> 3;
   const int lane = threadIdx.x & 31;
   for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps) {
@@ -86,6 +88,7 @@ combine_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
                    const int32_t* __restrict__ token_of_row, const float* __restrict__ gate_of_row,
                    const int32_t* __restrict__ meta, int d, __nv_bfloat16* __restrict__ dyp,
                    float* __restrict__ dgate_row) {
+  pdl_sync();
   const int R = meta[0];
   const int nchunk = d >> 3;
   const int lane = threadIdx.x & 31;
@@ -129,6 +132,7 @@ unpermute_bwd_kernel(const __nv_bfloat16* __restrict__ dxp, const int32_t* __res
                      const float* __restrict__ dlogits, const float* __restrict__ wg, int T, int k, int d, int E,
                      __nv_bfloat16* __restrict__ dx) {
   constexpr int kTok = 8 * TT;         // tokens per block
+  pdl_sync();
   extern __shared__ __align__(16) float unp_s[];
   float* wg_s = unp_s;                 // [E][256]
   float* dl_s = unp_s + E * 256;       // [kTok][E]
@@ -235,6 +239,7 @@ __global__ void __launch_bounds__(8 * kColsumPhases)
 colsum_kernel(const ColsumJob j0, const ColsumJob j1, const int32_t* __restrict__ expert_offsets, int accumulate) {
   __shared__ float part[kColsumPhases][65];
   __shared__ float part2[8][64];
+  pdl_sync();
   const int slabs0 = j0.ncols >> 6;
   const bool second = static_cast<int>(blockIdx.x) >= slabs0;
   const ColsumJob j = second ? j1 : j0;
@@ -337,7 +342,7 @@ extern "C" int b200moe_permute(const void* x, const int32_t* token_of_row, const
                                void* xp, void* stream) {
   B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "permute: d=%d must be a multiple of 8", d);
   if (int rc = b200moe_check_device()) return rc;
-  permute_kernel<<<move_grid(rows_cap), kMoveThreads, 0, ST(stream)>>>(BF(x), token_of_row, meta, d, BFW(xp));
+  launch_k(permute_kernel, move_grid(rows_cap), kMoveThreads, 0, ST(stream), BF(x), token_of_row, meta, d, BFW(xp));
   return check_launch("permute");
 }
 
@@ -354,7 +359,7 @@ extern "C" int b200moe_combine(const void* yo, const int32_t* row_of_assignment,
   B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "combine: d=%d must be a multiple of 8", d);
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
-  combine_kernel<<<move_grid(T), kMoveThreads, 0, ST(stream)>>>(BF(yo), row_of_assignment, topk_gate, T, k, d, BFW(y));
+  launch_k(combine_kernel, move_grid(T), kMoveThreads, 0, ST(stream), BF(yo), row_of_assignment, topk_gate, T, k, d, BFW(y));
   return check_launch("combine");
 }
 
@@ -363,8 +368,8 @@ extern "C" int b200moe_combine_bwd(const void* dy, const void* yo, const int32_t
                                    float* dgate_row, void* stream) {
   B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "combine_bwd: d=%d must be a multiple of 8", d);
   if (int rc = b200moe_check_device()) return rc;
-  combine_bwd_kernel<<<move_grid(rows_cap), kMoveThreads, 0, ST(stream)>>>(BF(dy), BF(yo), token_of_row, gate_of_row,
-                                                                           meta, d, BFW(dyp), dgate_row);
+  launch_k(combine_bwd_kernel, move_grid(rows_cap), kMoveThreads, 0, ST(stream), BF(dy), BF(yo), token_of_row,
+           gate_of_row, meta, d, BFW(dyp), dgate_row);
   return check_launch("combine_bwd");
 }
 
@@ -388,9 +393,9 @@ extern "C" int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assi
   }
   dim3 grid((T + tok - 1) / tok, (d + 255) / 256);
   if (big)
-    unpermute_bwd_kernel<8><<<grid, 256, smem, ST(stream)>>>(BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx));
+    launch_k(unpermute_bwd_kernel<8>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx));
   else
-    unpermute_bwd_kernel<2><<<grid, 256, smem, ST(stream)>>>(BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx));
+    launch_k(unpermute_bwd_kernel<2>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx));
   return check_launch("unpermute_bwd");
 }
 
@@ -417,7 +422,7 @@ extern "C" int b200moe_colsum(const void* a0, int ncols0, float* db0, const void
   ColsumJob j0{BF(a0), db0, ncols0};
   ColsumJob j1{BF(a1), db1, a1 ? ncols1 : 0};
   dim3 grid((ncols0 >> 6) + (a1 ? (ncols1 >> 6) : 0), E);
-  colsum_kernel<<<grid, 8 * kColsumPhases, 0, ST(stream)>>>(j0, j1, expert_offsets, accumulate);
+  launch_k(colsum_kernel, grid, 8 * kColsumPhases, 0, ST(stream), j0, j1, expert_offsets, accumulate);
   return check_launch("colsum");
 }
 

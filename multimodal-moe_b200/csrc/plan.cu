@@ -28,6 +28,7 @@ plan_scan_kernel(int32_t* __restrict__ block_counts, const float* __restrict__ b
   __shared__ float P_s[65];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = kScanThreads / 32;
   const int kE = k * E;
+  pdl_sync();
 
   // row maps start as "pad" (small buffers only; the host issues memsets for large ones)
   for (int i = threadIdx.x; i < init_rows; i += blockDim.x) { token_of_row[i] = -1; gate_of_row[i] = 0.f; }
@@ -163,6 +164,7 @@ plan_assign_kernel(const int32_t* __restrict__ topk_idx, const float* __restrict
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = t < T;
+  pdl_sync();
   for (int s = 0; s < k; ++s) {
     for (int i = threadIdx.x; i < (kRouterTokPerBlock / 32) * 64; i += blockDim.x) (&wc[0][0])[i] = 0;
     __syncthreads();
@@ -211,13 +213,12 @@ extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int
     cudaMemsetAsync(token_of_row, 0xFF, sizeof(int32_t) * static_cast<size_t>(rows_cap), st);
     cudaMemsetAsync(gate_of_row, 0, sizeof(float) * static_cast<size_t>(rows_cap), st);
   }
-  plan_scan_kernel<<<1, kScanThreads, 0, st>>>(block_counts, block_stats, nblk, T, k, E, capacity, global_offset,
-                                               expert_order, row_pad, rows_cap, aux_loss_weight, z_loss_weight,
-                                               expert_offsets, meta, tile_expert, tokens_per_expert,
-                                               kept_per_expert, losses, slot_limit, token_of_row, gate_of_row,
-                                               init_in_kernel ? rows_cap : 0);
+  launch_k(plan_scan_kernel, 1, kScanThreads, 0, st, block_counts, block_stats, nblk, T, k, E, capacity, global_offset,
+           expert_order, row_pad, rows_cap, aux_loss_weight, z_loss_weight, expert_offsets, meta, tile_expert,
+           tokens_per_expert, kept_per_expert, losses, slot_limit, token_of_row, gate_of_row,
+           init_in_kernel ? rows_cap : 0);
   if (int rc = check_launch("plan_scan")) return rc;
-  plan_assign_kernel<<<nblk, tb, 0, st>>>(topk_idx, topk_gate, block_counts, slot_limit, T, k, E,
-                                                          row_of_assignment, token_of_row, gate_of_row);
+  launch_k(plan_assign_kernel, nblk, tb, 0, st, topk_idx, topk_gate, block_counts, slot_limit, T, k, E,
+           row_of_assignment, token_of_row, gate_of_row);
   return check_launch("plan_assign");
 }

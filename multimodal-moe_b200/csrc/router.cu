@@ -93,6 +93,7 @@ router_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_sync();                                   // prologue done; inputs of the previous kernel from here on
 
   if (warp == 0) {
     // ======================= TMA producer =======================
@@ -325,7 +326,7 @@ static int launch_router(const void* x, const void* wsplit, const RouterArgs& a,
   const int ntiles = (a.T + kRtTile - 1) / kRtTile;
   const int max_ctas = kNumSMs * Cfg::kCtasPerSm;
   const int grid = ntiles < max_ctas ? ntiles : max_ctas;
-  kern<<<grid, kRtThreads, Cfg::kTotal, st>>>(tmX, tmW, a);
+  launch_k(kern, grid, kRtThreads, Cfg::kTotal, st, tmX, tmW, a);
   return check_launch("router_fwd");
 }
 

@@ -19,6 +19,7 @@ router_dlogits_kernel(const float* __restrict__ logits, const int32_t* __restric
                       const int32_t* __restrict__ tokens_per_expert, const float* __restrict__ d_aux, int T, int E,
                       int k, int normalize, float aux_w, float z_w, float* __restrict__ dlogits) {
   __shared__ float f_s[64];
+  pdl_sync();
   if (threadIdx.x < E)
     f_s[threadIdx.x] = static_cast<float>(tokens_per_expert[threadIdx.x]) / static_cast<float>(static_cast<long long>(T) * k);
   __syncthreads();
@@ -98,6 +99,7 @@ router_dwg_partial_kernel(const float* __restrict__ dlogits, const __nv_bfloat16
   extern __shared__ __align__(16) float red_s[];      // [4][16][256]
   __shared__ __align__(16) float dl_s[kDwgBatch][kDwgEG];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_sync();
   const int slab0 = blockIdx.y * 256, e0 = blockIdx.z * kDwgEG;
   const int c0 = slab0 + lane * 4, c1 = c0 + 128;
   const bool has0 = c0 < d, has1 = c1 < d;
@@ -160,6 +162,7 @@ router_dwg_partial_kernel(const float* __restrict__ dlogits, const __nv_bfloat16
 __global__ void __launch_bounds__(256)
 router_dwg_reduce_kernel(const float* __restrict__ scratch, int nchunks, int n, float* __restrict__ dwg, int nred,
                          const float* __restrict__ dlogits, int T, int E, int tpi, float* __restrict__ dctx) {
+  pdl_sync();
   if (static_cast<int>(blockIdx.x) < nred) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -215,8 +218,8 @@ extern "C" int b200moe_router_bwd_dlogits(const float* logits, const int32_t* to
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int grid = (T + 127) / 128;
 #define CASE(EP)                                                                                                  \
-  router_dlogits_kernel<EP><<<grid, 128, 0, st>>>(logits, topk_idx, row_of_assignment, dgate_row, tokens_per_expert, \
-                                                  d_aux, T, E, k, normalize_topk, aux_loss_weight, z_loss_weight, dlogits)
+  launch_k(router_dlogits_kernel<EP>, grid, 128, 0, st, logits, topk_idx, row_of_assignment, dgate_row,            \
+           tokens_per_expert, d_aux, T, E, k, normalize_topk, aux_loss_weight, z_loss_weight, dlogits)
   if (E <= 8) CASE(8);
   else if (E <= 16) CASE(16);
   else if (E <= 32) CASE(32);
@@ -251,15 +254,15 @@ extern "C" int b200moe_router_bwd_params(const float* dlogits, const void* x, in
       configured = true;
     }
     dim3 grid(chunks, (d + 255) / 256, (E + kDwgEG - 1) / kDwgEG);
-    router_dwg_partial_kernel<<<grid, 128, kDwgRedBytes, st>>>(dlogits, static_cast<const __nv_bfloat16*>(x), T, d, E, tpc,
-                                                               scratch);
+    launch_k(router_dwg_partial_kernel, grid, 128, kDwgRedBytes, st, dlogits, static_cast<const __nv_bfloat16*>(x), T, d,
+             E, tpc, scratch);
     if (int rc = check_launch("router_dwg_partial")) return rc;
   }
   const int n = E * d;
   const int nred = dwg ? (n + 255) / 256 : 0;
   const int B = dctx_bias ? (T + tokens_per_image - 1) / tokens_per_image : 0;
-  router_dwg_reduce_kernel<<<nred + B, 256, 0, st>>>(scratch, chunks, n, dwg, nred, dlogits, T, E,
-                                                     tokens_per_image > 0 ? tokens_per_image : T, dctx_bias);
+  launch_k(router_dwg_reduce_kernel, nred + B, 256, 0, st, scratch, chunks, n, dwg, nred, dlogits, T, E,
+           tokens_per_image > 0 ? tokens_per_image : T, dctx_bias);
   return check_launch("router_dwg_reduce");
 }
 
