@@ -1,9 +1,14 @@
 """b200moe — B200-native context-gated MoE FFN layer (host side of libb200moe.so).
 
-Public API: ContextMoE (drop-in nn.Module), ops (tensor-level wrappers of the C ABI), load_library().
+Public API: ContextMoE (drop-in nn.Module), MoEEncoderLayer / upcycle_encoder (encoder-layer glue), context (scene-context
+vocabulary and wire-through), checkpoint (expert-parallel state dicts), ops (tensor-level wrappers of the C ABI),
+load_library().
 """
 from ._lib import LIB_PATH, SIGNATURES, load as load_library  # noqa: F401
 from . import ops  # noqa: F401
 from .layer import ContextMoE  # noqa: F401
+from .encoder import MoEEncoderLayer, upcycle_encoder  # noqa: F401
+from . import checkpoint, context  # noqa: F401
 
-__all__ = ["ContextMoE", "ops", "load_library", "LIB_PATH", "SIGNATURES"]
+__all__ = ["ContextMoE", "MoEEncoderLayer", "upcycle_encoder", "context", "checkpoint", "ops", "load_library",
+           "LIB_PATH", "SIGNATURES"]

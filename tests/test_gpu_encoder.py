@@ -1,0 +1,105 @@
+"""GPU: encoder-layer glue.  A dense stand-in with the attribute names and forward of
+the vendored TransformerEncoderLayer (hybrid_encoder.py:116-161) is upcycled in place; with identical experts,
+renormalised gates and no capacity limit the swapped layer must reproduce the dense one (K1 anchor) and train."""
+import copy
+
+import pytest
+import torch
+import torch.nn as nn
+
+pytestmark = pytest.mark.gpu
+
+
+class TransformerEncoderLayer(nn.Module):           # name matters: upcycle_encoder matches the vendored class name
+    def __init__(self, d_model, nhead, dim_feedforward, normalize_before=False):
+        super().__init__()
+        self.normalize_before = normalize_before
+        self.self_attn = nn.MultiheadAttention(d_model, nhead, 0.0, batch_first=True)
+        self.linear1, self.linear2 = nn.Linear(d_model, dim_feedforward), nn.Linear(dim_feedforward, d_model)
+        self.norm1, self.norm2 = nn.LayerNorm(d_model), nn.LayerNorm(d_model)
+        self.dropout, self.dropout1, self.dropout2 = nn.Dropout(0.0), nn.Dropout(0.0), nn.Dropout(0.0)
+        self.activation = nn.GELU()
+
+    def forward(self, src, src_mask=None, pos_embed=None):
+        residual = src
+        if self.normalize_before:
+            src = self.norm1(src)
+        q = k = src if pos_embed is None else src + pos_embed
+        src, _ = self.self_attn(q, k, value=src, attn_mask=src_mask)
+        src = residual + self.dropout1(src)
+        if not self.normalize_before:
+            src = self.norm1(src)
+        residual = src
+        if self.normalize_before:
+            src = self.norm2(src)
+        src = self.linear2(self.dropout(self.activation(self.linear1(src))))
+        src = residual + self.dropout2(src)
+        if not self.normalize_before:
+            src = self.norm2(src)
+        return src
+
+
+class Detector(nn.Module):
+    def __init__(self, layer):
+        super().__init__()
+        self.encoder = nn.ModuleList([copy.deepcopy(layer)])      # hybrid_encoder.py:167 deep-copies the layer
+
+    def forward(self, x, targets=None):
+        for l_ in self.encoder:
+            x = l_(x)
+        return x
+
+
+@pytest.mark.parametrize("pre_norm", [False, True])
+def test_upcycled_encoder_layer_matches_dense_and_trains(pre_norm):
+    import b200moe
+    from b200moe import context as cx
+    torch.manual_seed(0)
+    B, HW, d, F = 4, 400, 256, 1024
+    dense = Detector(TransformerEncoderLayer(d, 8, F, pre_norm)).cuda()
+    moe = copy.deepcopy(dense)
+    n = b200moe.upcycle_encoder(moe, num_experts=8, top_k=2, capacity_factor=None,
+                                context_vocab_sizes=cx.CONTEXT_VOCAB_SIZES)
+    assert n == 1 and isinstance(moe.encoder[0], b200moe.MoEEncoderLayer)
+    hook = cx.install_context_hook(moe)
+    x = torch.randn(B, HW, d, device="cuda")
+    targets = [cx.attach_context({}, {"time_of_day": "night", "scraped_weather": "rain"}) for _ in range(B)]
+    with torch.no_grad():
+        yd = dense(x)
+    xm = x.clone().requires_grad_(True)
+    ym = moe(xm, targets=targets)
+    assert moe.encoder[0]._context.shape == (B, 5)
+    rel = float((ym.float() - yd).norm() / yd.norm())
+    assert rel <= 1e-2, rel                                         # bf16 experts vs the fp32 dense FFN
+    aux = cx.collect_aux_loss(moe)
+    assert aux is not None and aux.requires_grad
+    (ym.float().pow(2).mean() + aux).backward()
+    layer = moe.encoder[0]
+    for p in (layer.moe.w1, layer.moe.w2, layer.moe.gate.weight, layer.moe.ctx_proj.weight, layer.norm2.weight):
+        assert p.grad is not None and torch.isfinite(p.grad).all() and p.grad.abs().sum() > 0
+    assert xm.grad is not None and torch.isfinite(xm.grad).all()
+    tel = cx.router_telemetry(moe)
+    assert tel["moe0/dropped"] == 0 and 0.0 < tel["moe0/max_expert_share"] <= 1.0
+    hook.remove()
+    copy.deepcopy(moe)                                              # EMA / hybrid_encoder.py:167 deep-copy the module
+
+
+def test_decoder_ffn_site_shape():
+    """§8(f) rank 4: the decoder FFN (rtdetrv2_decoder.py:186-189: d=256, ffn=1024, 300 queries per image) is the same
+    layer at a smaller token count; per-expert row counts fall below one 128-row tile."""
+    import b200moe
+    from oracle import moe_ref as R
+    torch.manual_seed(1)
+    B, Q, d, F, E, k = 8, 300, 256, 1024, 8, 2
+    ref = R.ContextMoERef(d, F, E, k, 1.25)
+    with torch.no_grad():
+        for p in (ref.w1, ref.w2):
+            p.copy_(p.to(torch.bfloat16).float())
+    m = b200moe.ContextMoE(d, F, E, k, 1.25)
+    m.load_state_dict(ref.state_dict())
+    m = m.cuda()
+    x = torch.randn(B, Q, d).to(torch.bfloat16)
+    y = m(x.cuda())
+    yr = ref(x.float(), None, logits_value=m.last_aux["logits"].cpu())
+    assert torch.equal(m.last_aux["topk_idx"].cpu().long(), ref.last_aux["topk_idx"])
+    assert float((y.float().cpu() - yr).norm() / yr.norm()) <= 1e-2
