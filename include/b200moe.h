@@ -210,6 +210,34 @@ enum {
   B200MOE_BWS_DYP = 0, B200MOE_BWS_DGATE_ROW, B200MOE_BWS_DHPRE, B200MOE_BWS_DXP, B200MOE_BWS_DLOGITS,
   B200MOE_BWS_DWG_SCRATCH, B200MOE_BWS_COUNT
 };
+/* Optional fused post-norm of the encoder layer (hybrid_encoder.py:158-160): with a non-NULL b200moe_postnorm the last
+ * kernel of the forward computes out = LayerNorm(residual + combine(yo)) instead of y = combine(yo) (the [T,d]
+ * intermediates y and y + residual are never written), and the backward starts from d(out).                   */
+typedef struct b200moe_postnorm {
+  const void* residual;     /* [T,d] bf16 */
+  const float* gamma;       /* [d] LayerNorm weight */
+  const float* beta;        /* [d] LayerNorm bias */
+  float eps;
+  float* mean_rstd;         /* [T,2] fp32, written by the forward, read by the backward */
+} b200moe_postnorm;
+typedef struct b200moe_postnorm_bwd {
+  const void* residual;     /* [T,d] bf16 */
+  const float* gamma;
+  const float* mean_rstd;   /* from the forward */
+  void* dv;                 /* [T,d] bf16 out: gradient of the pre-norm sum = d(residual) = d(MoE output) */
+  float* scratch;           /* b200moe_ln_scratch_floats(T, d) floats */
+  float* dgamma;            /* [d] out */
+  float* dbeta;             /* [d] out */
+} b200moe_postnorm_bwd;
+int b200moe_combine_ln_fwd(const void* yo, const int32_t* row_of_assignment, const float* topk_gate,
+                           const void* residual, const float* gamma, const float* beta, float eps, int T, int k,
+                           int d, void* out, float* mean_rstd, void* stream);
+int64_t b200moe_ln_scratch_floats(int T, int d);
+int b200moe_combine_ln_bwd(const void* dout, const void* yo, const int32_t* row_of_assignment,
+                           const float* topk_gate, const void* residual, const float* gamma,
+                           const float* mean_rstd, int T, int k, int d, void* dv, float* scratch, float* dgamma,
+                           float* dbeta, void* stream);
+
 int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* desc, int64_t* offsets /* [B200MOE_WS_COUNT] */);
 int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* desc, int64_t* offsets /* [B200MOE_BWS_COUNT] */);
 /* router -> plan -> permute -> up(+GELU) -> down -> combine.  x [T,d] bf16; ctx_bias [B,E] fp32 or NULL; wg_split
@@ -217,14 +245,15 @@ int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* desc, int64_t* off
  * save_for_backward == 0 skips the pre-activation store. */
 int b200moe_layer_fwd(const b200moe_layer_desc* desc, const void* x, const float* ctx_bias, const void* wg_split,
                       const void* w1, const float* b1, const void* w2, const float* b2, void* ws, void* y,
-                      int save_for_backward, void* stream);
+                      int save_for_backward, const b200moe_postnorm* postnorm /* or NULL */, void* stream);
 /* Mirror of the forward incl. the A.12 router gradient.  dy [T,d] bf16; d_aux: device scalar (gradient of the
  * weighted auxiliary loss) or NULL.  Any of the gradient outputs may be NULL (not computed):
  * dx [T,d] bf16, dctx_bias [B,E], dwg [E,d], dw1 [E,F,d], db1 [E,F], dw2 [E,d,F], db2 [E,d] (all fp32).      */
 int b200moe_layer_bwd(const b200moe_layer_desc* desc, const void* x, const float* wg, const void* w1,
                       const void* w2, const void* ws, void* bws, const void* dy, const float* d_aux, void* dx,
                       float* dctx_bias, float* dwg, float* dw1, float* db1, float* dw2, float* db2,
-                      int has_ctx_bias, void* stream);
+                      int has_ctx_bias, const b200moe_postnorm_bwd* postnorm /* or NULL: dy is then d(out) */,
+                      void* stream);
 /* Per-step CUDA-event timing of the two calls above (measurement aid): enable, run, synchronize the stream, then read
  * entries 0,1,... until the call returns B200MOE_EINVAL.  b200moe_layer_profile(x) also clears earlier entries. */
 int b200moe_layer_profile(int enable);

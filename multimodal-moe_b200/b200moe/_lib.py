@@ -41,8 +41,11 @@ SIGNATURES = {
     "b200moe_layer_profile_read": [_I, _P, _P],
     "b200moe_layer_ws_layout": [_P, _P],
     "b200moe_layer_bwd_ws_layout": [_P, _P],
-    "b200moe_layer_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P],
-    "b200moe_layer_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P],
+    "b200moe_layer_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P],
+    "b200moe_layer_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P],
+    "b200moe_combine_ln_fwd": [_P, _P, _P, _P, _P, _P, _F, _I, _I, _I, _P, _P, _P],
+    "b200moe_ln_scratch_floats": [_I, _I],
+    "b200moe_combine_ln_bwd": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P],
     "b200moe_router_bwd_dlogits": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _P, _P],
     "b200moe_dwg_scratch_floats": [_I, _I, _I],
     "b200moe_router_bwd_dwg": [_P, _P, _I, _I, _I, _P, _P, _P],
@@ -56,7 +59,19 @@ SIGNATURES = {
 }
 _RESTYPE = {"b200moe_last_error": C.c_char_p, "b200moe_dwg_scratch_floats": C.c_int64,
             "b200moe_router_scratch_bytes": C.c_int64, "b200moe_layer_ws_layout": C.c_int64,
-            "b200moe_layer_bwd_ws_layout": C.c_int64}
+            "b200moe_layer_bwd_ws_layout": C.c_int64, "b200moe_ln_scratch_floats": C.c_int64}
+
+
+class PostNorm(C.Structure):
+    """b200moe_postnorm of include/b200moe.h."""
+    _fields_ = [("residual", C.c_void_p), ("gamma", C.c_void_p), ("beta", C.c_void_p), ("eps", C.c_float),
+                ("mean_rstd", C.c_void_p)]
+
+
+class PostNormBwd(C.Structure):
+    """b200moe_postnorm_bwd of include/b200moe.h."""
+    _fields_ = [("residual", C.c_void_p), ("gamma", C.c_void_p), ("mean_rstd", C.c_void_p), ("dv", C.c_void_p),
+                ("scratch", C.c_void_p), ("dgamma", C.c_void_p), ("dbeta", C.c_void_p)]
 
 
 class LayerDesc(C.Structure):
@@ -108,7 +123,7 @@ def stream_ptr() -> int:
 # kernels launched by each entry point (memset nodes not counted); used for bench.py's gpu_launches
 KERNELS_PER_CALL = {
     "b200moe_cast_f32_bf16": 1, "b200moe_prepare_weights": 1, "b200moe_ctx_bias_fwd": 1, "b200moe_ctx_bias_bwd": 1,
-    "b200moe_layer_fwd": 7, "b200moe_layer_bwd": 11, "b200moe_router_bwd_params": 2, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
+    "b200moe_layer_fwd": 7, "b200moe_layer_bwd": 11, "b200moe_combine_ln_fwd": 1, "b200moe_combine_ln_bwd": 2, "b200moe_router_bwd_params": 2, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
     "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
     "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,

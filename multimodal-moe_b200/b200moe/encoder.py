@@ -55,6 +55,9 @@ class MoEEncoderLayer(nn.Module):
         ctx = self._context
         if ctx is not None and ctx.device != src.device:
             ctx = ctx.to(src.device)
+        if not self.normalize_before and (self.dropout2.p == 0.0 or not self.training):
+            # post-norm (the vendored default): residual add + LayerNorm ride the combine kernel (:157-160 in one pass)
+            return self.moe.forward_post_norm(src, residual, self.norm2, ctx)
         src = self.moe(src, ctx)                     # hybrid_encoder.py:157; dropped tokens give 0, the residual carries them
         src = residual + self.dropout2(src)
         if not self.normalize_before:

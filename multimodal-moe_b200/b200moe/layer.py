@@ -144,7 +144,7 @@ class _MoEFunction(torch.autograd.Function):
     more small kernel each."""
 
     @staticmethod
-    def forward(ctx, x2, context, wg, wc, w1, b1, w2, b2, mod, tpi, *tables):
+    def forward(ctx, x2, context, wg, wc, w1, b1, w2, b2, mod, tpi, residual, ln_w, ln_b, ln_eps, *tables):
         T, d = x2.shape
         dev = x2.device
         E = mod.num_experts
@@ -165,9 +165,17 @@ class _MoEFunction(torch.autograd.Function):
             ctx.ctx_saved = (context, tabs, wcf)
         ws = torch.empty((pl.ws_bytes,), dtype=torch.uint8, device=dev)
         y = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
+        pn_ptr = None
+        ctx.ln = None
+        if residual is not None:                     # fused post-norm: y = LayerNorm(residual + MoE(x))
+            gam, bet = _f32c(ln_w), _f32c(ln_b)
+            mean_rstd = torch.empty((T, 2), dtype=torch.float32, device=dev)
+            pn = _lib.PostNorm(residual.data_ptr(), gam.data_ptr(), bet.data_ptr(), float(ln_eps), mean_rstd.data_ptr())
+            pn_ptr = C.addressof(pn)
+            ctx.ln = (residual, gam, mean_rstd, ln_w.dtype, ln_b.dtype)
         _lib.call("b200moe_layer_fwd", pl.desc_ptr, x2.data_ptr(), cb.data_ptr() if cb is not None else None,
                   wsplit.data_ptr(), w1b.data_ptr(), b1f.data_ptr(), w2b.data_ptr(), b2f.data_ptr(), ws.data_ptr(),
-                  y.data_ptr(), int(need_grad), st)
+                  y.data_ptr(), int(need_grad), pn_ptr, st)
         ctx.mod, ctx.pl, ctx.has_ctx = mod, pl, cb is not None
         ctx.dtypes = (wg.dtype, w1.dtype, b1.dtype, w2.dtype, b2.dtype)
         ctx.save_for_backward(x2, wgf, w1b, w2b, ws)
@@ -185,7 +193,7 @@ class _MoEFunction(torch.autograd.Function):
         T, d = x2.shape
         E, F = mod.num_experts, mod.dim_feedforward
         dev = x2.device
-        need = ctx.needs_input_grad      # x2, context, wg, wc, w1, b1, w2, b2, mod, tpi, *tables
+        need = ctx.needs_input_grad      # x2, context, wg, wc, w1, b1, w2, b2, mod, tpi, residual, ln_w, ln_b, eps, *tables
         if dy is None:
             dy = torch.zeros_like(x2)
         dy = dy.contiguous().to(torch.bfloat16)
@@ -197,7 +205,7 @@ class _MoEFunction(torch.autograd.Function):
         db1 = torch.empty((E, F), dtype=f32, device=dev) if need[5] else None
         dw2 = torch.empty((E, d, F), dtype=f32, device=dev) if need[6] else None
         db2 = torch.empty((E, d), dtype=f32, device=dev) if need[7] else None
-        want_ctx = ctx.has_ctx and (need[3] or any(need[10:]))
+        want_ctx = ctx.has_ctx and (need[3] or any(need[14:]))
         dcb = None
         if want_ctx:
             B = ctx.ctx_saved[0].shape[0]
@@ -205,9 +213,20 @@ class _MoEFunction(torch.autograd.Function):
         bws = torch.empty((pl.bws_bytes,), dtype=torch.uint8, device=dev)
         p = lambda t: t.data_ptr() if t is not None else None  # noqa: E731
         st = _lib.stream_ptr()
+        pn_ptr, dres, dgam, dbet = None, None, None, None
+        if ctx.ln is not None:
+            residual, gam, mean_rstd, t_lw, t_lb = ctx.ln
+            dres = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
+            dgam, dbet = torch.empty((d,), dtype=f32, device=dev), torch.empty((d,), dtype=f32, device=dev)
+            scr = torch.empty((_lib.load().b200moe_ln_scratch_floats(T, d),), dtype=f32, device=dev)
+            pn = _lib.PostNormBwd(residual.data_ptr(), gam.data_ptr(), mean_rstd.data_ptr(), dres.data_ptr(),
+                                  scr.data_ptr(), dgam.data_ptr(), dbet.data_ptr())
+            pn_ptr = C.addressof(pn)
         _lib.call("b200moe_layer_bwd", pl.desc_ptr, x2.data_ptr(), wgf.data_ptr(), w1b.data_ptr(), w2b.data_ptr(),
                   ws.data_ptr(), bws.data_ptr(), dy.data_ptr(), p(d_aux_t), p(dx), p(dcb), p(dwg), p(dw1), p(db1),
-                  p(dw2), p(db2), int(ctx.has_ctx), st)
+                  p(dw2), p(db2), int(ctx.has_ctx), pn_ptr, st)
+        if ctx.ln is not None:
+            dgam, dbet = (dgam if dgam.dtype == t_lw else dgam.to(t_lw)), (dbet if dbet.dtype == t_lb else dbet.to(t_lb))
         dwc, dtabs = None, ()
         if want_ctx:
             context, tabs, wcf = ctx.ctx_saved
@@ -226,11 +245,11 @@ class _MoEFunction(torch.autograd.Function):
 
         def cast(g, dt):
             return g if g is None or g.dtype == dt else g.to(dt)
-        n_tab = len(need) - 10
+        n_tab = len(need) - 14
         if not dtabs:
             dtabs = (None,) * n_tab
         return (dx, None, cast(dwg, t_wg), dwc, cast(dw1, t_w1), cast(db1, t_b1), cast(dw2, t_w2), cast(db2, t_b2),
-                None, None, *dtabs)
+                None, None, dres, dgam, dbet, None, *dtabs)
 
 
 class ContextMoE(nn.Module):
@@ -394,7 +413,13 @@ class ContextMoE(nn.Module):
             emb = torch.cat([m(context[:, i]) for i, m in enumerate(self.ctx_embed)], dim=-1)
             return torch.nn.functional.linear(emb.float(), self.ctx_proj.weight.float())
 
-    def forward(self, x: torch.Tensor, context: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def forward_post_norm(self, x: torch.Tensor, residual: torch.Tensor, norm: nn.LayerNorm,
+                          context: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """`norm(residual + self(x, context))` (hybrid_encoder.py:157-160 with dropout 0) with the residual add and the
+        LayerNorm fused into the combine kernel, forward and backward.  Returns a tensor of x's shape and dtype."""
+        return self.forward(x, context, _post=(residual, norm))
+
+    def forward(self, x: torch.Tensor, context: Optional[torch.Tensor] = None, _post=None) -> torch.Tensor:
         if not x.is_cuda:
             raise RuntimeError("b200moe.ContextMoE runs on a B200 (sm_100a) only; there is no CPU fallback")
         if x.shape[-1] != self.d_model:
@@ -404,7 +429,10 @@ class ContextMoE(nn.Module):
         T = x2.shape[0]
         if T == 0:
             self.aux_loss = x.new_zeros((), dtype=torch.float32)
-            return x.clone()
+            return x.clone() if _post is None else _post[1](_post[0] + x)
+        if _post is not None and (self.ep_size > 1 or self.d_model > 1024 or not isinstance(_post[1], nn.LayerNorm)
+                                  or _post[1].weight is None or _post[1].bias is None):
+            return _post[1](_post[0] + self.forward(x, context))        # shapes the fused kernel does not cover
         B = shape[0] if x.dim() == 3 else 1
         if context is not None and context.shape[0] != B:
             raise ValueError("context must have one row per image")
@@ -430,9 +458,19 @@ class ContextMoE(nn.Module):
         use_ctx = context is not None and self.ctx_proj is not None
         ctx_ids = context.long().contiguous() if use_ctx else None
         tables = [m.weight for m in self.ctx_embed] if use_ctx else []
+        res_b = ln_w = ln_b = None
+        ln_eps = 0.0
+        if _post is not None:
+            res, norm = _post
+            if res.shape != x.shape:
+                raise ValueError("residual must have the shape of x")
+            res_b = res.reshape(-1, self.d_model)
+            res_b = res_b if res_b.dtype == torch.bfloat16 else res_b.to(torch.bfloat16)
+            res_b = res_b if res_b.is_contiguous() else res_b.contiguous()
+            ln_w, ln_b, ln_eps = norm.weight, norm.bias, norm.eps
         y, aux, _stats = _MoEFunction.apply(xb, ctx_ids, self.gate.weight,
                                             self.ctx_proj.weight if use_ctx else None, self.w1, self.b1, self.w2,
-                                            self.b2, self, tpi, *tables)
+                                            self.b2, self, tpi, res_b, ln_w, ln_b, ln_eps, *tables)
         # plain attributes: bypass nn.Module.__setattr__ (several microseconds per assignment)
         self.__dict__["aux_loss"] = aux
         self.__dict__["last_aux"] = _Aux(*self._last_ws)

@@ -237,7 +237,8 @@ extern "C" int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* q, int6
 
 extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, const float* ctx_bias,
                                  const void* wg_split, const void* w1, const float* b1, const void* w2,
-                                 const float* b2, void* ws, void* y, int save_for_backward, void* stream) {
+                                 const float* b2, void* ws, void* y, int save_for_backward,
+                                 const b200moe_postnorm* pn, void* stream) {
   if (int rc = check_desc(q, "layer_fwd")) return rc;
   B200MOE_REQUIRE(x && wg_split && w1 && b1 && w2 && b2 && ws && y, B200MOE_EINVAL, "layer_fwd: NULL argument");
   int64_t off[B200MOE_WS_COUNT];
@@ -267,15 +268,21 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                                 save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H), stream));
   STEP("ffn_down", b200moe_ffn_down(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert, R, d, F, E,
                                     WS(void, B200MOE_WS_YO), stream));
-  STEP("combine", b200moe_combine(WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
-                                  WS(float, B200MOE_WS_TOPK_GATE), T, k, d, y, stream));
+  if (pn) {
+    STEP("combine_ln", b200moe_combine_ln_fwd(WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
+                                              WS(float, B200MOE_WS_TOPK_GATE), pn->residual, pn->gamma, pn->beta,
+                                              pn->eps, T, k, d, y, pn->mean_rstd, stream));
+  } else {
+    STEP("combine", b200moe_combine(WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
+                                    WS(float, B200MOE_WS_TOPK_GATE), T, k, d, y, stream));
+  }
   return B200MOE_OK;
 }
 
 extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, const float* wg, const void* w1,
                                  const void* w2, const void* ws, void* bws, const void* dy, const float* d_aux,
                                  void* dx, float* dctx_bias, float* dwg, float* dw1, float* db1, float* dw2,
-                                 float* db2, int has_ctx_bias, void* stream) {
+                                 float* db2, int has_ctx_bias, const b200moe_postnorm_bwd* pn, void* stream) {
   if (int rc = check_desc(q, "layer_bwd")) return rc;
   B200MOE_REQUIRE(x && wg && w1 && w2 && ws && bws && dy, B200MOE_EINVAL, "layer_bwd: NULL argument");
   int64_t off[B200MOE_WS_COUNT], boff[B200MOE_BWS_COUNT];
@@ -294,6 +301,12 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
   float* dlogits = BWS(float, B200MOE_BWS_DLOGITS);
   int rc;
   PdlScope pdl_;
+  if (pn) {
+    STEP("combine_ln_bwd",
+         b200moe_combine_ln_bwd(dy, WS(void, B200MOE_WS_YO), roa, WS(float, B200MOE_WS_TOPK_GATE), pn->residual,
+                                pn->gamma, pn->mean_rstd, T, k, d, pn->dv, pn->scratch, pn->dgamma, pn->dbeta, stream));
+    dy = pn->dv;
+  }
   STEP("combine_bwd",
        b200moe_combine_bwd(dy, WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_TOKEN_OF_ROW),
                            WS(float, B200MOE_WS_GATE_OF_ROW), meta, R, d, dyp, BWS(float, B200MOE_BWS_DGATE_ROW), stream));

@@ -323,6 +323,189 @@ prepare_weights_kernel(const float* __restrict__ w1, __nv_bfloat16* __restrict__
   }
 }
 
+// ---- fused post-norm (hybrid_encoder.py:158-160): out = LayerNorm(residual + combine(yo)) ---------------------------
+// One warp per token; a lane owns the 16-byte chunks lane, lane+32, ... of the row (d <= 1024: at most four), so the
+// gate-weighted sum, the residual add, both LayerNorm moments and the affine output never leave registers and the
+// token's [T,d] intermediate (y, y + residual) is never written.  mean / rstd are kept for the backward pass.
+constexpr int kLnMaxI = 4;
+template <int NI>
+__device__ __forceinline__ void ln_gather_sum(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ roa,
+                                              const float* __restrict__ gate, const __nv_bfloat16* __restrict__ res,
+                                              int t, int k, int d, int lane, float (&v)[NI][8]) {
+  const int nchunk = d >> 3;
+#pragma unroll
+  for (int i = 0; i < NI; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+  for (int s = 0; s < k; ++s) {
+    const int r = roa[static_cast<size_t>(t) * k + s];
+    if (r < 0) continue;
+    const float g = gate[static_cast<size_t>(t) * k + s];
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nchunk) {
+        float a[8];
+        unpack8(ldg128(yo + static_cast<size_t>(r) * d + c * 8), a);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[i][j] = fmaf(g, a[j], v[i][j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NI; ++i) {
+    const int c = lane + 32 * i;
+    if (c < nchunk) {
+      float a[8];
+      unpack8(ldg128(res + static_cast<size_t>(t) * d + c * 8), a);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) v[i][j] += a[j];
+    }
+  }
+}
+
+template <int NI>
+__global__ void __launch_bounds__(kMoveThreads)
+combine_ln_fwd_kernel(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ roa,
+                      const float* __restrict__ gate, const __nv_bfloat16* __restrict__ res,
+                      const float* __restrict__ gamma, const float* __restrict__ beta, float eps, int T, int k, int d,
+                      __nv_bfloat16* __restrict__ out, float* __restrict__ mean_rstd) {
+  pdl_sync();
+  const int lane = threadIdx.x & 31, nchunk = d >> 3;
+  const float invd = 1.0f / static_cast<float>(d);
+  for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps) {
+    float v[NI][8];
+    ln_gather_sum<NI>(yo, roa, gate, res, t, k, d, lane, v);
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < NI; ++i)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += v[i][j];          // missing chunks are zero
+    const float mean = warp_sum(s) * invd;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < NI; ++i)
+      if (lane + 32 * i < nchunk)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float c_ = v[i][j] - mean; q = fmaf(c_, c_, q); }
+    const float rstd = rsqrtf(warp_sum(q) * invd + eps);
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nchunk) {
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c * 8)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c * 8) + 1);
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c * 8)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c * 8) + 1);
+        const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bt[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = fmaf((v[i][j] - mean) * rstd, gm[j], bt[j]);
+        stg128(out + static_cast<size_t>(t) * d + c * 8, pack8(o));
+      }
+    }
+    if (lane == 0) { mean_rstd[2 * static_cast<size_t>(t)] = mean; mean_rstd[2 * static_cast<size_t>(t) + 1] = rstd; }
+  }
+}
+
+// Backward: recomputes the pre-norm sum v and xhat from the same inputs, dv = rstd (dxhat - mean(dxhat) - xhat
+// mean(dxhat xhat)) with dxhat = dout gamma; dv is both the residual's gradient and the MoE output's gradient.
+// dgamma / dbeta: per-lane partial sums over the warp's tokens, the block's warps in fixed order, one row of scratch
+// per block; a second launch sums the blocks in order (deterministic).
+template <int NI>
+__global__ void __launch_bounds__(kMoveThreads)
+combine_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ yo,
+                      const int32_t* __restrict__ roa, const float* __restrict__ gate,
+                      const __nv_bfloat16* __restrict__ res, const float* __restrict__ gamma,
+                      const float* __restrict__ mean_rstd, int T, int k, int d, __nv_bfloat16* __restrict__ dv,
+                      float* __restrict__ scratch) {
+  extern __shared__ __align__(16) float lnb_s[];       // [8 warps][2][d]
+  pdl_sync();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nchunk = d >> 3;
+  const float invd = 1.0f / static_cast<float>(d);
+  float dg[NI][8], db[NI][8];
+#pragma unroll
+  for (int i = 0; i < NI; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { dg[i][j] = 0.f; db[i][j] = 0.f; }
+  for (int t = blockIdx.x * kMoveWarps + warp; t < T; t += gridDim.x * kMoveWarps) {
+    float v[NI][8], dy[NI][8];
+    ln_gather_sum<NI>(yo, roa, gate, res, t, k, d, lane, v);
+    const float mean = mean_rstd[2 * static_cast<size_t>(t)], rstd = mean_rstd[2 * static_cast<size_t>(t) + 1];
+    float m1 = 0.f, m2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nchunk) {
+        float a[8];
+        unpack8(ldg128(dout + static_cast<size_t>(t) * d + c * 8), a);
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c * 8)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c * 8) + 1);
+        const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float xh = (v[i][j] - mean) * rstd;
+          v[i][j] = xh;
+          dg[i][j] = fmaf(a[j], xh, dg[i][j]);
+          db[i][j] += a[j];
+          dy[i][j] = a[j] * gm[j];
+          m1 += dy[i][j];
+          m2 = fmaf(dy[i][j], xh, m2);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) dy[i][j] = 0.f;
+      }
+    }
+    m1 = warp_sum(m1) * invd;
+    m2 = warp_sum(m2) * invd;
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nchunk) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (dy[i][j] - m1 - v[i][j] * m2);
+        stg128(dv + static_cast<size_t>(t) * d + c * 8, pack8(o));
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < NI; ++i) {
+    const int c = lane + 32 * i;
+    if (c < nchunk) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        lnb_s[(warp * 2 + 0) * d + c * 8 + j] = dg[i][j];
+        lnb_s[(warp * 2 + 1) * d + c * 8 + j] = db[i][j];
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * d; i += blockDim.x) {
+    float sum = 0.f;
+#pragma unroll
+    for (int w = 0; w < kMoveWarps; ++w) sum += lnb_s[w * 2 * d + i];
+    scratch[static_cast<size_t>(blockIdx.x) * 2 * d + i] = sum;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+ln_param_reduce_kernel(const float* __restrict__ scratch, int nblk, int d, float* __restrict__ dgamma,
+                       float* __restrict__ dbeta) {
+  pdl_sync();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 2 * d) return;
+  float s = 0.f;
+  for (int b = 0; b < nblk; ++b) s += scratch[static_cast<size_t>(b) * 2 * d + i];
+  if (i < d) dgamma[i] = s;
+  else dbeta[i - d] = s;
+}
+
+static inline int ln_bwd_blocks(int T) {
+  int b = (T + kMoveWarps - 1) / kMoveWarps;
+  if (b > kNumSMs * 2) b = kNumSMs * 2;
+  return b < 1 ? 1 : b;
+}
+
 static inline int move_grid(long long rows) {
   long long b = (rows + kMoveWarps - 1) / kMoveWarps;
   const long long cap = static_cast<long long>(kNumSMs) * 8;
@@ -441,4 +624,58 @@ extern "C" int b200moe_prepare_weights(const float* w1, void* w1_bf16, int64_t n
   prepare_weights_kernel<<<static_cast<int>(blocks), 256, 0, ST(stream)>>>(
       w1, BFW(w1_bf16), n1 / 8, w2, BFW(w2_bf16), n2 / 8, wg, BFW(wg_split), E, EP, d);
   return check_launch("prepare_weights");
+}
+
+extern "C" int b200moe_combine_ln_fwd(const void* yo, const int32_t* row_of_assignment, const float* topk_gate,
+                                      const void* residual, const float* gamma, const float* beta, float eps, int T,
+                                      int k, int d, void* out, float* mean_rstd, void* stream) {
+  B200MOE_REQUIRE(d > 0 && d % 8 == 0 && d <= 1024, B200MOE_EINVAL, "combine_ln_fwd: d=%d must be a multiple of 8, <= 1024", d);
+  B200MOE_REQUIRE(yo && row_of_assignment && topk_gate && residual && gamma && beta && out && mean_rstd, B200MOE_EINVAL,
+                  "combine_ln_fwd: NULL argument");
+  if (T == 0) return B200MOE_OK;
+  if (int rc = b200moe_check_device()) return rc;
+  const int ni = (d / 8 + 31) / 32;
+#define LNF(NI)                                                                                                       \
+  launch_k(combine_ln_fwd_kernel<NI>, move_grid(T), kMoveThreads, 0, ST(stream), BF(yo), row_of_assignment, topk_gate, \
+           BF(residual), gamma, beta, eps, T, k, d, BFW(out), mean_rstd)
+  if (ni == 1) LNF(1);
+  else if (ni == 2) LNF(2);
+  else LNF(4);
+#undef LNF
+  return check_launch("combine_ln_fwd");
+}
+
+extern "C" int64_t b200moe_ln_scratch_floats(int T, int d) { return static_cast<int64_t>(ln_bwd_blocks(T)) * 2 * d; }
+
+extern "C" int b200moe_combine_ln_bwd(const void* dout, const void* yo, const int32_t* row_of_assignment,
+                                      const float* topk_gate, const void* residual, const float* gamma,
+                                      const float* mean_rstd, int T, int k, int d, void* dv, float* scratch,
+                                      float* dgamma, float* dbeta, void* stream) {
+  B200MOE_REQUIRE(d > 0 && d % 8 == 0 && d <= 1024, B200MOE_EINVAL, "combine_ln_bwd: d=%d must be a multiple of 8, <= 1024", d);
+  B200MOE_REQUIRE(dout && yo && row_of_assignment && topk_gate && residual && gamma && mean_rstd && dv && scratch &&
+                      dgamma && dbeta, B200MOE_EINVAL, "combine_ln_bwd: NULL argument");
+  if (T == 0) return B200MOE_OK;
+  if (int rc = b200moe_check_device()) return rc;
+  const int ni = (d / 8 + 31) / 32, nblk = ln_bwd_blocks(T);
+  const size_t smem = sizeof(float) * kMoveWarps * 2 * d;
+  static bool configured = false;
+  if (!configured) {
+    const int mx = static_cast<int>(sizeof(float) * kMoveWarps * 2 * 1024);
+    cudaError_t e1 = cudaFuncSetAttribute(combine_ln_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    cudaError_t e2 = cudaFuncSetAttribute(combine_ln_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    cudaError_t e3 = cudaFuncSetAttribute(combine_ln_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    B200MOE_REQUIRE(e1 == cudaSuccess && e2 == cudaSuccess && e3 == cudaSuccess, B200MOE_ECUDA, "combine_ln_bwd: cudaFuncSetAttribute failed");
+    configured = true;
+  }
+#define LNB(NI)                                                                                                     \
+  launch_k(combine_ln_bwd_kernel<NI>, nblk, kMoveThreads, smem, ST(stream), BF(dout), BF(yo), row_of_assignment,      \
+           topk_gate, BF(residual), gamma, mean_rstd, T, k, d, BFW(dv), scratch)
+  if (ni == 1) LNB(1);
+  else if (ni == 2) LNB(2);
+  else LNB(4);
+#undef LNB
+  if (int rc = check_launch("combine_ln_bwd")) return rc;
+  launch_k(ln_param_reduce_kernel, (2 * d + 255) / 256, 256, 0, ST(stream), static_cast<const float*>(scratch), nblk, d,
+           dgamma, dbeta);
+  return check_launch("ln_param_reduce");
 }

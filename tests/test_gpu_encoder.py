@@ -103,3 +103,44 @@ def test_decoder_ffn_site_shape():
     yr = ref(x.float(), None, logits_value=m.last_aux["logits"].cpu())
     assert torch.equal(m.last_aux["topk_idx"].cpu().long(), ref.last_aux["topk_idx"])
     assert float((y.float().cpu() - yr).norm() / yr.norm()) <= 1e-2
+
+
+@pytest.mark.parametrize("B,HW,d,F,E,cf", [(8, 400, 256, 1024, 8, 1.25), (3, 231, 512, 1024, 16, 0.5), (2, 100, 128, 256, 4, None),
+                                           (2, 77, 1024, 1024, 8, 1.0)])
+def test_fused_post_norm_matches_unfused(B, HW, d, F, E, cf):
+    """LayerNorm(residual + MoE(x)) through the fused combine kernel (forward and backward) against the same module
+    with torch's add + LayerNorm around the plain forward.  Both run the same expert kernels on the same routing, so
+    the only differences are the bf16 rounding of y that the fused path skips and summation order."""
+    import b200moe
+    torch.manual_seed(B * HW)
+    m = b200moe.ContextMoE(d, F, E, 2, cf, context_vocab_sizes=(6, 10, 4, 6, 4)).cuda()
+    norm = nn.LayerNorm(d).cuda()
+    with torch.no_grad():
+        norm.weight.uniform_(0.5, 1.5)
+        norm.bias.uniform_(-0.2, 0.2)
+    x = torch.randn(B, HW, d, device="cuda").to(torch.bfloat16)
+    res = torch.randn(B, HW, d, device="cuda").to(torch.bfloat16)
+    go = torch.randn(B, HW, d, device="cuda")
+    ctx = torch.stack([torch.randint(0, v, (B,)) for v in (6, 10, 4, 6, 4)], 1).cuda()
+
+    def run(fused):
+        for p in list(m.parameters()) + list(norm.parameters()):
+            p.grad = None
+        xa, ra = x.clone().requires_grad_(True), res.clone().requires_grad_(True)
+        out = m.forward_post_norm(xa, ra, norm, ctx) if fused else norm((ra + m(xa, ctx)).float()).to(torch.bfloat16)
+        ((out.float() * go).sum() + m.aux_loss).backward()
+        grads = {n: p.grad.clone() for n, p in list(m.named_parameters()) + [("ln." + n_, p_) for n_, p_ in norm.named_parameters()]}
+        return out.detach(), xa.grad, ra.grad, grads
+
+    of, dxf, drf, gf = run(True)
+    ou, dxu, dru, gu = run(False)
+
+    def rel(a, b):
+        return float((a.float() - b.float()).norm() / (b.float().norm() + 1e-12))
+    assert of.dtype == torch.bfloat16 and rel(of, ou) <= 6e-3
+    assert rel(dxf, dxu) <= 1e-2 and rel(drf, dru) <= 1e-2
+    for n in gu:
+        assert rel(gf[n], gu[n]) <= 2e-2, n
+    # deterministic
+    of2, dxf2, _, gf2 = run(True)
+    assert torch.equal(of, of2) and torch.equal(dxf, dxf2) and torch.equal(gf["ln.weight"], gf2["ln.weight"])
