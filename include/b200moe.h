@@ -42,6 +42,10 @@ int b200moe_check_device(void);
 
 /* Upper bound (multiple of 128) on rows of the permuted buffer: min(T*k, E*capacity) + E*127, rounded up. */
 int b200moe_rows_upper_bound(int T, int k, int E, int capacity);
+/* Row padding of the expert segments the whole-layer calls use for this problem (128, or 256 when the GEMMs are large
+ * enough for CTA pairs) and the matching bound on the rows of the permuted buffer (multiple of row_pad). */
+int b200moe_layer_row_pad(int T, int k, int E, int capacity, int d, int F);
+int b200moe_layer_rows_cap(int T, int k, int E, int capacity, int d, int F);
 /* Tokens per router block (128 = one tcgen05 M tile of the router) and the resulting block count
  * ceil(T / block): first dimension of block_counts / block_stats. */
 int b200moe_router_block(int T);
@@ -72,7 +76,7 @@ int b200moe_router_fwd(const void* x, const float* ctx_bias, int tokens_per_imag
 /* A.5 + A.8-A.10.  Slot-major / token-major priority scan, capacity clamp, padded expert offsets, row maps, losses.
  *   global_offset [k,E] int32 or NULL: earlier-priority assignments owned by other ranks (expert parallelism)
  *   expert_order  [E] int32 or NULL : position of expert e in the row layout (NULL = identity)
- *   row_pad: 128 on one GPU (GEMM tiles), 1 for an all-to-all send buffer
+ *   row_pad: 128 or 256 on one GPU (GEMM tiles / CTA-pair tiles), 1 for an all-to-all send buffer
  *   out: expert_offsets [E+1] (in layout order: offsets[i] is the first row of the expert at position i)
  *        meta [B200MOE_META_INTS]; tile_expert [rows_cap/128] (expert of each 128-row tile, -1 beyond R)
  *        tokens_per_expert [E] (pre-drop); kept_per_expert [E]
@@ -103,13 +107,16 @@ int b200moe_combine_bwd(const void* dy, const void* yo, const int32_t* token_of_
 /* Expert FFN, forward (A.6).  Grouped bf16 GEMMs on tcgen05/TMEM fed by TMA.
  *   up  : pre = xp @ w1[e]^T + b1[e];  h = gelu_erf(pre)      w1 [E,F,d] bf16, b1 [E,F] fp32
  *   down: yo  = h  @ w2[e]^T + b2[e]                          w2 [E,d,F] bf16, b2 [E,d] fp32
- *   pre may be NULL (inference: nothing saved for backward).                                         */
+ *   pre may be NULL (inference: nothing saved for backward).
+ *   row_pad = the padding b200moe_plan laid the expert segments out with: 128, or 256 -- then 256-row tiles never
+ *   straddle experts and large problems run on CTA pairs (tcgen05 cta_group::2: two SMs share one 256 x 256 tile,
+ *   each loading half of the weight tile).  The weight-gradient GEMM pairs along the weight rows by itself.   */
 int b200moe_ffn_up(const void* xp, const void* w1, const float* b1, const int32_t* meta,
                    const int32_t* tile_expert, int rows_cap, int d, int F, int E,
-                   void* pre, void* h, void* stream);
+                   void* pre, void* h, int row_pad, void* stream);
 int b200moe_ffn_down(const void* h, const void* w2, const float* b2, const int32_t* meta,
                      const int32_t* tile_expert, int rows_cap, int d, int F, int E,
-                     void* yo, void* stream);
+                     void* yo, int row_pad, void* stream);
 
 /* Expert FFN, backward.
  *   dgrad_down: dhpre = (dyp @ w2[e]) * gelu_erf'(pre)        [R,F]
@@ -119,10 +126,10 @@ int b200moe_ffn_down(const void* h, const void* w2, const float* b2, const int32
  *   colsum    : db[e,:] = sum over rows of e of a[r,:]        (db2 from dyp, db1 from dhpre)  */
 int b200moe_ffn_dgrad_down(const void* dyp, const void* w2, const void* pre, const int32_t* meta,
                            const int32_t* tile_expert, int rows_cap, int d, int F, int E,
-                           void* dhpre, void* stream);
+                           void* dhpre, int row_pad, void* stream);
 int b200moe_ffn_dgrad_up(const void* dhpre, const void* w1, const int32_t* meta,
                          const int32_t* tile_expert, int rows_cap, int d, int F, int E,
-                         void* dxp, void* stream);
+                         void* dxp, int row_pad, void* stream);
 int b200moe_ffn_wgrad(const void* a, const void* b, const int32_t* expert_offsets, int rows_cap,
                       int M, int N, int E, float* dw, int accumulate, void* stream);
 /* Bias gradients of both projections in ONE launch (a1 may be NULL): db0[e,:] = column sums of a0 over the rows of

@@ -18,6 +18,8 @@ SIGNATURES = {
     "b200moe_last_error": [],
     "b200moe_check_device": [],
     "b200moe_rows_upper_bound": [_I, _I, _I, _I],
+    "b200moe_layer_row_pad": [_I, _I, _I, _I, _I, _I],
+    "b200moe_layer_rows_cap": [_I, _I, _I, _I, _I, _I],
     "b200moe_router_block": [_I],
     "b200moe_num_router_blocks": [_I],
     "b200moe_cast_f32_bf16": [_P, _P, _L, _P],
@@ -27,10 +29,10 @@ SIGNATURES = {
     "b200moe_permute": [_P, _P, _P, _I, _I, _P, _P],
     "b200moe_combine": [_P, _P, _P, _I, _I, _I, _P, _P],
     "b200moe_combine_bwd": [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P],
-    "b200moe_ffn_up": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _P],
-    "b200moe_ffn_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
-    "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
-    "b200moe_ffn_dgrad_up": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
+    "b200moe_ffn_up": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _P],
+    "b200moe_ffn_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
+    "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
+    "b200moe_ffn_dgrad_up": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
     "b200moe_ffn_wgrad": [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
     "b200moe_colsum": [_P, _I, _P, _P, _I, _P, _P, _I, _I, _P],
     "b200moe_prepare_weights": [_P, _P, _L, _P, _P, _L, _P, _P, _I, _I, _P],

@@ -45,7 +45,9 @@ class _LayerPlan:
         lib = _lib.load()
         E, k, d, F = mod.num_experts, mod.top_k, mod.d_model, mod.dim_feedforward
         cap = ops.capacity_of(mod.capacity_factor, T, k, E)
-        rows_cap = ops.rows_upper_bound(T, k, E, cap)
+        rows_cap = lib.b200moe_layer_rows_cap(T, k, E, cap, d, F)
+        if rows_cap <= 0:
+            raise RuntimeError(f"b200moe: bad layer shape T={T} k={k} E={E}")
         self.desc = _lib.LayerDesc(T, d, F, E, k, tpi, cap, rows_cap, int(mod.normalize_topk),
                                    mod.aux_loss_weight, mod.z_loss_weight)
         self.desc_ptr = C.addressof(self.desc)

@@ -138,40 +138,40 @@ def combine_bwd(dy: torch.Tensor, yo: Optional[torch.Tensor], token_of_row: torc
     return dyp, dgate_row
 
 
-def ffn_up(xp, w1, b1, meta, tile_expert, save_pre: bool = True):
+def ffn_up(xp, w1, b1, meta, tile_expert, save_pre: bool = True, row_pad: int = ROW_PAD):
     rows_cap, d = xp.shape
     E, F, _ = w1.shape
     pre = _empty((rows_cap, F), torch.bfloat16, xp.device) if save_pre else None
     h = _empty((rows_cap, F), torch.bfloat16, xp.device)
     call("b200moe_ffn_up", ptr(xp), ptr(w1), ptr(b1), ptr(meta), ptr(tile_expert), rows_cap, d, F, E, ptr(pre),
-         ptr(h), stream_ptr())
+         ptr(h), row_pad, stream_ptr())
     return pre, h
 
 
-def ffn_down(h, w2, b2, meta, tile_expert):
+def ffn_down(h, w2, b2, meta, tile_expert, row_pad: int = ROW_PAD):
     rows_cap, F = h.shape
     E, d, _ = w2.shape
     yo = _empty((rows_cap, d), torch.bfloat16, h.device)
     call("b200moe_ffn_down", ptr(h), ptr(w2), ptr(b2), ptr(meta), ptr(tile_expert), rows_cap, d, F, E, ptr(yo),
-         stream_ptr())
+         row_pad, stream_ptr())
     return yo
 
 
-def ffn_dgrad_down(dyp, w2, pre, meta, tile_expert):
+def ffn_dgrad_down(dyp, w2, pre, meta, tile_expert, row_pad: int = ROW_PAD):
     rows_cap, d = dyp.shape
     E, _, F = w2.shape
     dhpre = _empty((rows_cap, F), torch.bfloat16, dyp.device)
     call("b200moe_ffn_dgrad_down", ptr(dyp), ptr(w2), ptr(pre), ptr(meta), ptr(tile_expert), rows_cap, d, F, E,
-         ptr(dhpre), stream_ptr())
+         ptr(dhpre), row_pad, stream_ptr())
     return dhpre
 
 
-def ffn_dgrad_up(dhpre, w1, meta, tile_expert):
+def ffn_dgrad_up(dhpre, w1, meta, tile_expert, row_pad: int = ROW_PAD):
     rows_cap, F = dhpre.shape
     E, _, d = w1.shape
     dxp = _empty((rows_cap, d), torch.bfloat16, dhpre.device)
     call("b200moe_ffn_dgrad_up", ptr(dhpre), ptr(w1), ptr(meta), ptr(tile_expert), rows_cap, d, F, E, ptr(dxp),
-         stream_ptr())
+         row_pad, stream_ptr())
     return dxp
 
 

@@ -59,6 +59,26 @@ int b200moe_rows_upper_bound(int T, int k, int E, int capacity) {
   return static_cast<int>(rows);
 }
 
+int b200moe_layer_row_pad(int T, int k, int E, int capacity, int d, int F) {
+  if (T <= 0 || k <= 0 || E <= 0 || d % 256 != 0 || F % 256 != 0) return B200MOE_ROW_PAD;
+  long long kept = 1LL * T * k;
+  if (capacity >= 0 && 1LL * E * capacity < kept) kept = 1LL * E * capacity;
+  // CTA pairs pay off once the narrower GEMM (N = d) still has two waves of 256 x 256 tiles
+  return (kept / 256) * (d / 256) >= 2LL * 148 ? 256 : B200MOE_ROW_PAD;
+}
+
+int b200moe_layer_rows_cap(int T, int k, int E, int capacity, int d, int F) {
+  const int pad = b200moe_layer_row_pad(T, k, E, capacity, d, F);
+  if (pad == B200MOE_ROW_PAD) return b200moe_rows_upper_bound(T, k, E, capacity);
+  if (T < 0 || k <= 0 || E <= 0) return B200MOE_EINVAL;
+  long long kept = 1LL * T * k;
+  if (capacity >= 0 && 1LL * E * capacity < kept) kept = 1LL * E * capacity;
+  long long rows = kept + 1LL * E * (pad - 1);
+  rows = (rows + pad - 1) / pad * pad;
+  if (rows > 0x7fffff00LL) return B200MOE_EINVAL;
+  return static_cast<int>(rows);
+}
+
 int b200moe_router_block(int T) { return b200moe::router_block_tokens(T); }
 
 int b200moe_num_router_blocks(int T) {

@@ -47,30 +47,37 @@ struct GemmArgs {
   int accumulate;
 };
 
-template <int BN>
+template <int BN, bool CTA2>
 struct SmemCfg {
+  static constexpr int kBLoad = CTA2 ? BN / 2 : BN;                        // B rows / columns this CTA loads
   static constexpr int kABytes = BM * BK * 2;
-  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kBBytes = kBLoad * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = (BN == 256) ? 4 : 6;
+  static constexpr int kStages = (kStageBytes > 32768) ? 4 : 6;
   static constexpr int kOutBytes = 8 * 4096;                               // epilogue staging: 8 x 4 KB or 16 x 2 KB
   static constexpr int kBarBytes = 256;
   static constexpr int kTotal = kStages * kStageBytes + kOutBytes + kBarBytes + 1024;  // + alignment slack
 };
 
-template <int BN, bool A_MN, bool B_MN, int EPI>
+// CTA2: clusters of two CTAs share one 256 x BN tile (tcgen05 cta_group::2).  Each CTA loads its own 128 rows of A and
+// HALF of the B tile, CTA 0 issues one M=256 MMA that reads both halves, and each CTA's TMEM receives its own 128
+// output rows: per FLOP the pair pulls 2/3 of the operand bytes through L2 that two independent CTAs would -- the
+// 128 x 256 tiles are L2-bandwidth-bound (ncu: ~14 TB/s of L2->SM traffic at 58-72 % tensor-pipe activity).
+template <int BN, bool A_MN, bool B_MN, int EPI, bool CTA2>
 __global__ void __launch_bounds__(gemm_threads(EPI), 1)
 grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC0, const __grid_constant__ CUtensorMap tmC1,
                     const GemmArgs args) {
-  using Cfg = SmemCfg<BN>;
+  using Cfg = SmemCfg<BN, CTA2>;
   constexpr int kStages = Cfg::kStages;
   constexpr bool kWgrad = (EPI == EPI_WGRAD);
+  constexpr int kBLoad = Cfg::kBLoad;
+  constexpr int kTileM = CTA2 ? 2 * BM : BM;                               // rows of one scheduled tile
   constexpr int kEpiWarps = epi_warps(EPI);
   constexpr int kEpiThreads = kEpiWarps * 32;
   constexpr int kStgBytes = Cfg::kOutBytes / kEpiWarps;                    // 4 KB (wgrad) or 2 KB
   constexpr uint32_t kTmemCols = 2 * BN;  // 256 or 512: power of two
-  constexpr uint32_t kIdesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+  constexpr uint32_t kIdesc = make_idesc_bf16(kTileM, BN, A_MN, B_MN);
 
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -82,6 +89,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta_rank = CTA2 ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
@@ -89,20 +98,26 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmC0);
     if (EPI == EPI_UP) tma_prefetch_desc(&tmC1);
     for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], kEpiThreads); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], (CTA2 ? 2 : 1) * kEpiThreads); }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc<kTmemCols>(tmem_slot);
+  if (warp == 1) {
+    if (CTA2) tmem_alloc2<kTmemCols>(tmem_slot);
+    else tmem_alloc<kTmemCols>(tmem_slot);
+  }
   tc_fence_before();
   __syncthreads();
+  if (CTA2) cluster_sync_all();                 // the peer's barriers exist before anything signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_sync();                                   // prologue done; everything below reads the previous kernel's output
 
   // ---- tile schedule (identical in every role) -------------------------------------------------------------
   const int tiles_n = args.N / BN;
-  const int tiles_m = kWgrad ? args.M / BM : 0;
-  const int total_tiles = kWgrad ? args.E * tiles_m * tiles_n : args.meta[1] * tiles_n;
+  const int tiles_m = kWgrad ? args.M / kTileM : 0;
+  const int total_tiles = kWgrad ? args.E * tiles_m * tiles_n : (args.meta[1] / (kTileM / BM)) * tiles_n;
+  const int worker = CTA2 ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+  const int nworkers = CTA2 ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
 
   auto decode = [&](int tile, int& e, int& m_tile, int& n_tile, int& krow0, int& kblocks) {
     if (kWgrad) {
@@ -111,12 +126,14 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int r = tile - e * per_e;
       m_tile = r / tiles_n;
       n_tile = r - m_tile * tiles_n;
+      if (CTA2) m_tile = 2 * m_tile + static_cast<int>(cta_rank);         // this CTA's 128 rows of the 256-row tile
       const int r0 = args.expert_offsets[e], r1 = args.expert_offsets[e + 1];
       krow0 = r0;
       kblocks = (r1 - r0) / BK;
     } else {
       m_tile = tile / tiles_n;
       n_tile = tile - m_tile * tiles_n;
+      if (CTA2) m_tile = 2 * m_tile + static_cast<int>(cta_rank);         // both 128-row tiles belong to one expert
       e = args.tile_expert[m_tile];
       krow0 = 0;
       kblocks = args.K / BK;
@@ -128,28 +145,32 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = worker; tile < total_tiles; tile += nworkers) {
         int e, m_tile, n_tile, krow0, kblocks;
         decode(tile, e, m_tile, n_tile, krow0, kblocks);
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           unsigned char* sa = smem + stage * Cfg::kStageBytes;
           unsigned char* sb = sa + Cfg::kABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], Cfg::kStageBytes);
+          // the bytes of BOTH CTAs land on CTA 0's barrier, armed by CTA 0 alone
+          if (leader) mbar_arrive_expect_tx(&full_bar[stage], (CTA2 ? 2 : 1) * Cfg::kStageBytes);
+          auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
+            if (CTA2) tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
+            else tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
+          };
           if (A_MN) {
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j)
-              tma_load_2d(sa + j * 8192, &tmA, &full_bar[stage], m_tile * BM + j * 64, krow0 + kb * BK);
+            for (int j = 0; j < BM / 64; ++j) load(sa + j * 8192, &tmA, m_tile * BM + j * 64, krow0 + kb * BK);
           } else {
-            tma_load_2d(sa, &tmA, &full_bar[stage], kb * BK, m_tile * BM);
+            load(sa, &tmA, kb * BK, m_tile * BM);
           }
+          const int n0 = n_tile * BN + static_cast<int>(cta_rank) * kBLoad;      // this CTA's share of the B tile
           if (B_MN) {
             const int krow = kWgrad ? krow0 + kb * BK : e * args.K + kb * BK;
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(sb + j * 8192, &tmB, &full_bar[stage], n_tile * BN + j * 64, krow);
+            for (int j = 0; j < kBLoad / 64; ++j) load(sb + j * 8192, &tmB, n0 + j * 64, krow);
           } else {
-            tma_load_2d(sb, &tmB, &full_bar[stage], kb * BK, e * args.N + n_tile * BN);
+            load(sb, &tmB, kb * BK, e * args.N + n0);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
@@ -157,12 +178,12 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (warp == 1) {
     // ======================= MMA issuer =======================
-    if (lane == 0) {
+    if (lane == 0 && leader) {
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = worker; tile < total_tiles; tile += nworkers) {
         int e, m_tile, n_tile, krow0, kblocks;
         decode(tile, e, m_tile, n_tile, krow0, kblocks);
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
@@ -179,13 +200,21 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           for (int ks = 0; ks < BK / 16; ++ks) {
             const uint64_t a_k = da + static_cast<uint64_t>(ks * (A_MN ? 128 : 2));
             const uint64_t b_k = db + static_cast<uint64_t>(ks * (B_MN ? 128 : 2));
-            umma_bf16_ss(tmem_d, a_k, b_k, kIdesc, (kb | ks) != 0 ? 1u : 0u);
+            if (CTA2) umma_bf16_ss_pair(tmem_d, a_k, b_k, kIdesc, (kb | ks) != 0 ? 1u : 0u);
+            else umma_bf16_ss(tmem_d, a_k, b_k, kIdesc, (kb | ks) != 0 ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);   // frees the smem slot once these MMAs have read it
+          // frees the smem slot (of both CTAs) once these MMAs have read it
+          if (CTA2) umma_commit_pair(&empty_bar[stage]);
+          else umma_commit(&empty_bar[stage]);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        if (kblocks > 0) umma_commit(&tfull_bar[acc]);   // accumulator complete
-        else mbar_arrive(&tfull_bar[acc]);               // empty expert: nothing to wait for
+        if (kblocks > 0) {                               // accumulator complete (in both CTAs' TMEM)
+          if (CTA2) umma_commit_pair(&tfull_bar[acc]);
+          else umma_commit(&tfull_bar[acc]);
+        } else {                                         // empty expert: nothing to wait for
+          mbar_arrive(&tfull_bar[acc]);
+          if (CTA2) mbar_arrive_remote(&tfull_bar[acc], 1);
+        }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -200,7 +229,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     unsigned char* stg = stage_out + (warp - 2) * kStgBytes;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int tile = worker; tile < total_tiles; tile += nworkers) {
       int e, m_tile, n_tile, krow0, kblocks;
       decode(tile, e, m_tile, n_tile, krow0, kblocks);
       mbar_wait(&tfull_bar[acc], acc_phase);
@@ -306,7 +335,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
       tc_fence_before();
-      mbar_arrive(&tempty_bar[acc]);
+      if (CTA2 && !leader) mbar_arrive_remote(&tempty_bar[acc], 0);   // the MMA issuer lives in CTA 0
+      else mbar_arrive(&tempty_bar[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (lane == 0) tma_store_wait_all0();      // staging smem must outlive the bulk stores that read it
@@ -314,9 +344,11 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   tc_fence_before();
   __syncthreads();
+  if (CTA2) cluster_sync_all();                 // neither CTA leaves while the other may still touch its smem / TMEM
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<kTmemCols>(tmem_base);
+    if (CTA2) tmem_dealloc2<kTmemCols>(tmem_base);
+    else tmem_dealloc<kTmemCols>(tmem_base);
   }
 }
 

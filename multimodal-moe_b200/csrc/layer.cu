@@ -56,8 +56,8 @@ static int check_desc(const b200moe_layer_desc* q, const char* what) {
                   "%s: bad num_experts=%d / top_k=%d", what, q->E, q->k);
   B200MOE_REQUIRE(q->capacity >= 0, B200MOE_EINVAL, "%s: negative capacity", what);
   B200MOE_REQUIRE(q->rows_cap > 0 && q->rows_cap % kRowPad == 0 &&
-                      q->rows_cap >= b200moe_rows_upper_bound(q->T, q->k, q->E, q->capacity),
-                  B200MOE_EINVAL, "%s: rows_cap=%d is not b200moe_rows_upper_bound(T,k,E,capacity)", what, q->rows_cap);
+                      q->rows_cap >= b200moe_layer_rows_cap(q->T, q->k, q->E, q->capacity, q->d, q->F),
+                  B200MOE_EINVAL, "%s: rows_cap=%d is below b200moe_layer_rows_cap(T,k,E,capacity,d,F)", what, q->rows_cap);
   return B200MOE_OK;
 }
 
@@ -247,6 +247,7 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
   const int T = q->T, d = q->d, F = q->F, E = q->E, k = q->k, R = q->rows_cap;
   const int32_t* meta = WS(int32_t, B200MOE_WS_META);
   const int32_t* tile_expert = WS(int32_t, B200MOE_WS_TILE_EXPERT);
+  const int pad = b200moe_layer_row_pad(T, k, E, q->capacity, d, F);
   int rc;
   PdlScope pdl_;
   STEP("router_fwd",
@@ -257,7 +258,7 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
   STEP("plan",
        b200moe_plan(WS(int32_t, B200MOE_WS_TOPK_IDX), WS(float, B200MOE_WS_TOPK_GATE),
                     WS(int32_t, B200MOE_WS_BLOCK_COUNTS), WS(float, B200MOE_WS_BLOCK_STATS), T, k, E, q->capacity,
-                    nullptr, nullptr, kRowPad, R, q->aux_loss_weight, q->z_loss_weight,
+                    nullptr, nullptr, pad, R, q->aux_loss_weight, q->z_loss_weight,
                     WS(int32_t, B200MOE_WS_EXPERT_OFFSETS), WS(int32_t, B200MOE_WS_META),
                     WS(int32_t, B200MOE_WS_TILE_EXPERT), WS(int32_t, B200MOE_WS_TOKENS_PER_EXPERT),
                     WS(int32_t, B200MOE_WS_KEPT_PER_EXPERT), WS(float, B200MOE_WS_LOSSES),
@@ -265,9 +266,9 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                     WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW), stream));
   STEP("permute", b200moe_permute(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP), stream));
   STEP("ffn_up", b200moe_ffn_up(WS(void, B200MOE_WS_XP), w1, b1, meta, tile_expert, R, d, F, E,
-                                save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H), stream));
+                                save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H), pad, stream));
   STEP("ffn_down", b200moe_ffn_down(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert, R, d, F, E,
-                                    WS(void, B200MOE_WS_YO), stream));
+                                    WS(void, B200MOE_WS_YO), pad, stream));
   if (pn) {
     STEP("combine_ln", b200moe_combine_ln_fwd(WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
                                               WS(float, B200MOE_WS_TOPK_GATE), pn->residual, pn->gamma, pn->beta,
@@ -299,6 +300,7 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
   void* dyp = BWS(void, B200MOE_BWS_DYP);
   void* dhpre = BWS(void, B200MOE_BWS_DHPRE);
   float* dlogits = BWS(float, B200MOE_BWS_DLOGITS);
+  const int pad = b200moe_layer_row_pad(T, k, E, q->capacity, d, F);
   int rc;
   PdlScope pdl_;
   if (pn) {
@@ -311,7 +313,7 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
        b200moe_combine_bwd(dy, WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_TOKEN_OF_ROW),
                            WS(float, B200MOE_WS_GATE_OF_ROW), meta, R, d, dyp, BWS(float, B200MOE_BWS_DGATE_ROW), stream));
   STEP("ffn_dgrad_down",
-       b200moe_ffn_dgrad_down(dyp, w2, WS(void, B200MOE_WS_PRE), meta, tile_expert, R, d, F, E, dhpre, stream));
+       b200moe_ffn_dgrad_down(dyp, w2, WS(void, B200MOE_WS_PRE), meta, tile_expert, R, d, F, E, dhpre, pad, stream));
   if (dw2) { STEP("ffn_wgrad", b200moe_ffn_wgrad(dyp, WS(void, B200MOE_WS_H), offs, R, d, F, E, dw2, 0, stream)); }
   if (dw1) { STEP("ffn_wgrad", b200moe_ffn_wgrad(dhpre, WS(void, B200MOE_WS_XP), offs, R, F, d, E, dw1, 0, stream)); }
   if (db2 && db1) {
@@ -327,7 +329,7 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
                                   T, E, k, q->normalize_topk, q->aux_loss_weight, q->z_loss_weight, dlogits, stream));
   if (dx) {
     void* dxp = BWS(void, B200MOE_BWS_DXP);
-    STEP("ffn_dgrad_up", b200moe_ffn_dgrad_up(dhpre, w1, meta, tile_expert, R, d, F, E, dxp, stream));
+    STEP("ffn_dgrad_up", b200moe_ffn_dgrad_up(dhpre, w1, meta, tile_expert, R, d, F, E, dxp, pad, stream));
     STEP("unpermute_bwd", b200moe_unpermute_bwd(dxp, roa, dlogits, wg, T, k, d, E, dx, stream));
   }
   {

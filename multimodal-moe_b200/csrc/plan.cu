@@ -201,7 +201,8 @@ extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int
   using namespace b200moe;
   B200MOE_REQUIRE(T > 0, B200MOE_EINVAL, "plan: T=%d must be positive", T);
   B200MOE_REQUIRE(E >= 1 && E <= 64 && k >= 1 && k <= 8 && k <= E, B200MOE_EINVAL, "plan: bad E=%d / k=%d", E, k);
-  B200MOE_REQUIRE(row_pad == 1 || row_pad == kRowPad, B200MOE_EINVAL, "plan: row_pad must be 1 or 128");
+  B200MOE_REQUIRE(row_pad == 1 || row_pad == kRowPad || row_pad == 2 * kRowPad, B200MOE_EINVAL,
+                  "plan: row_pad must be 1, 128 or 256");
   B200MOE_REQUIRE(capacity >= 0, B200MOE_EINVAL, "plan: negative capacity");
   B200MOE_REQUIRE(rows_cap > 0 && rows_cap % kRowPad == 0, B200MOE_EINVAL, "plan: rows_cap must be a multiple of 128");
   if (int rc = b200moe_check_device()) return rc;

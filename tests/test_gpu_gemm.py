@@ -17,11 +17,11 @@ def ops():
     return b200moe.ops
 
 
-def _layout(E, rows_per_expert, seed=0):
-    """Hand-built plan: expert e owns rows_per_expert[e] rows, segments padded to 128."""
+def _layout(E, rows_per_expert, pad=128):
+    """Hand-built plan: expert e owns rows_per_expert[e] rows, segments padded to `pad` (128, or 256 = CTA-pair layout)."""
     offs = [0]
     for n in rows_per_expert:
-        offs.append(offs[-1] + (n + 127) // 128 * 128)
+        offs.append(offs[-1] + (n + pad - 1) // pad * pad)
     R = offs[-1]
     rows_cap = R + 256                                       # spare tiles beyond R must be skipped
     meta = torch.zeros(8, dtype=torch.int32)
@@ -41,17 +41,20 @@ def _rel(a, b):
 
 
 CASES = [
-    (8, 256, 1024, [800, 790, 1, 0, 128, 129, 300, 555]),     # config A shape, ragged incl. an empty expert
-    (4, 128, 256, [5, 200, 0, 130]),                          # smallest tile-able shape
-    (16, 512, 2048, [400] * 16),                              # config C shape
-    (2, 1024, 4096, [3000, 2500]),                            # config D shape, BN=256 path
+    (8, 256, 1024, [800, 790, 1, 0, 128, 129, 300, 555], 128),     # config A shape, ragged incl. an empty expert
+    (4, 128, 256, [5, 200, 0, 130], 128),                          # smallest tile-able shape
+    (16, 512, 2048, [400] * 16, 128),                              # config C shape
+    (2, 1024, 4096, [3000, 2500], 128),                            # config D shape, BN=256 path
+    (4, 512, 1024, [6000, 5000, 0, 8100], 256),                    # CTA-pair layout: every GEMM on cta_group::2 tiles
+    (2, 1024, 4096, [3000, 2500], 256),                            # CTA pairs for up / dgrad_down only
+    (8, 1024, 2048, [300, 200, 0, 129, 520, 64, 1, 700], 128),     # weight-gradient GEMMs on CTA pairs (ragged K, empty expert)
 ]
 
 
-@pytest.mark.parametrize("E,d,F,rows", CASES)
-def test_ffn_forward_stages(ops, E, d, F, rows):
+@pytest.mark.parametrize("E,d,F,rows,pad", CASES)
+def test_ffn_forward_stages(ops, E, d, F, rows, pad):
     g = torch.Generator().manual_seed(E * 1000 + d)
-    offs, meta, te, valid, rexp, R, rows_cap = _layout(E, rows)
+    offs, meta, te, valid, rexp, R, rows_cap = _layout(E, rows, pad)
     xp = torch.randn(rows_cap, d, generator=g).to(torch.bfloat16)
     xp[~valid] = 0
     w1 = (torch.randn(E, F, d, generator=g) * d ** -0.5).to(torch.bfloat16)
@@ -59,8 +62,8 @@ def test_ffn_forward_stages(ops, E, d, F, rows):
     w2 = (torch.randn(E, d, F, generator=g) * F ** -0.5).to(torch.bfloat16)
     b2 = torch.randn(E, d, generator=g) * 0.1
     dev = "cuda"
-    pre, h = ops.ffn_up(xp.to(dev), w1.to(dev), b1.to(dev), meta.to(dev), te.to(dev))
-    yo = ops.ffn_down(h, w2.to(dev), b2.to(dev), meta.to(dev), te.to(dev))
+    pre, h = ops.ffn_up(xp.to(dev), w1.to(dev), b1.to(dev), meta.to(dev), te.to(dev), row_pad=pad)
+    yo = ops.ffn_down(h, w2.to(dev), b2.to(dev), meta.to(dev), te.to(dev), row_pad=pad)
     torch.cuda.synchronize()
     pre, h, yo = pre.cpu()[:R], h.cpu()[:R], yo.cpu()[:R]
     for e in range(E):
@@ -76,10 +79,10 @@ def test_ffn_forward_stages(ops, E, d, F, rows):
         assert float((yo[sl].float() - yo_ref).abs().max()) < 0.05 * float(yo_ref.abs().max())
 
 
-@pytest.mark.parametrize("E,d,F,rows", CASES)
-def test_ffn_backward_stages(ops, E, d, F, rows):
+@pytest.mark.parametrize("E,d,F,rows,pad", CASES)
+def test_ffn_backward_stages(ops, E, d, F, rows, pad):
     g = torch.Generator().manual_seed(E * 1000 + d + 1)
-    offs, meta, te, valid, rexp, R, rows_cap = _layout(E, rows)
+    offs, meta, te, valid, rexp, R, rows_cap = _layout(E, rows, pad)
     dev = "cuda"
     dyp = torch.randn(rows_cap, d, generator=g).to(torch.bfloat16)
     dyp[~valid] = 0
@@ -91,8 +94,8 @@ def test_ffn_backward_stages(ops, E, d, F, rows):
     w2 = (torch.randn(E, d, F, generator=g) * F ** -0.5).to(torch.bfloat16)
     md, ted, od = meta.to(dev), te.to(dev), offs.to(dev)
 
-    dhpre = ops.ffn_dgrad_down(dyp.to(dev), w2.to(dev), pre.to(dev), md, ted)
-    dxp = ops.ffn_dgrad_up(dhpre, w1.to(dev), md, ted)
+    dhpre = ops.ffn_dgrad_down(dyp.to(dev), w2.to(dev), pre.to(dev), md, ted, row_pad=pad)
+    dxp = ops.ffn_dgrad_up(dhpre, w1.to(dev), md, ted, row_pad=pad)
     dw2 = ops.ffn_wgrad(dyp.to(dev), h.to(dev), od, E)
     dw1 = ops.ffn_wgrad(dhpre, xp.to(dev), od, E)
     db2 = ops.colsum(dyp.to(dev), od, E)
