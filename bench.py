@@ -49,6 +49,15 @@ def peaks():
     return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
 
 
+def ncu_traffic(workload):
+    """DRAM bytes per launch of the GEMM family from the committed ncu capture (profiles/r01_traffic.json), or None."""
+    try:
+        j = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))[workload]
+        return j["gemm_family_dram_bytes_per_step"] / j["gemm_launches_per_step"]
+    except Exception:  # noqa: BLE001
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -387,7 +396,8 @@ def main():
             line["roofline"] = {"bound": "tensor", "kernel": "grouped_gemm_kernel (6 launches: up, down, 2 dgrad, 2 wgrad)",
                                 "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                                 "peak_source": pk["src"] + (" burst" if ms_per_step < 1.0 else " sustained"),
-                                "flops_per_step": fl, "gemm_ms_per_step": res["gemm_ms"], "traffic": None}
+                                "flops_per_step": fl, "gemm_ms_per_step": res["gemm_ms"],
+                                "launches": res.get("gemm_launches"), "traffic": ncu_traffic(wl_name)}
         line["per_call_ms"] = res["per_call_ms"]
         if world == 1:
             line["hbm_kernels"] = hbm_kernels(w, res["T"], res["kept"], res["per_call_ms"], pk["hbm"])

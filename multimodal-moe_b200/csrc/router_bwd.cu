@@ -164,17 +164,31 @@ router_dwg_reduce_kernel(const float* __restrict__ scratch, int nchunks, int n, 
                          const float* __restrict__ dlogits, int T, int E, int tpi, float* __restrict__ dctx) {
   pdl_sync();
   if (static_cast<int>(blockIdx.x) < nred) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    // 32 outputs x 8 phases per block: phase p sums chunks p, p+8, ... (eight loads in flight), then the phases are
+    // added in order -- a fixed summation order with 8x the memory parallelism of one thread per output
+    __shared__ float ph_s[8][33];
+    const int o = threadIdx.x & 31, p = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + o;
     float s = 0.f;
-    int c = 0;
-    for (; c + 4 <= nchunks; c += 4) {
-      const float a0 = scratch[static_cast<size_t>(c) * n + i], a1 = scratch[static_cast<size_t>(c + 1) * n + i];
-      const float a2 = scratch[static_cast<size_t>(c + 2) * n + i], a3 = scratch[static_cast<size_t>(c + 3) * n + i];
-      s = (((s + a0) + a1) + a2) + a3;
+    if (i < n) {
+      int c = p;
+      for (; c + 56 < nchunks; c += 64) {
+        float a[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) a[u] = scratch[static_cast<size_t>(c + 8 * u) * n + i];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) s += a[u];
+      }
+      for (; c < nchunks; c += 8) s += scratch[static_cast<size_t>(c) * n + i];
     }
-    for (; c < nchunks; ++c) s += scratch[static_cast<size_t>(c) * n + i];
-    dwg[i] = s;
+    ph_s[p][o] = s;
+    __syncthreads();
+    if (p == 0 && i < n) {
+      float r = 0.f;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) r += ph_s[q][o];
+      dwg[i] = r;
+    }
     return;
   }
   // dctx: thread (phase, e) strides the image's tokens; consecutive threads read consecutive addresses
@@ -259,7 +273,7 @@ extern "C" int b200moe_router_bwd_params(const float* dlogits, const void* x, in
     if (int rc = check_launch("router_dwg_partial")) return rc;
   }
   const int n = E * d;
-  const int nred = dwg ? (n + 255) / 256 : 0;
+  const int nred = dwg ? (n + 31) / 32 : 0;
   const int B = dctx_bias ? (T + tokens_per_image - 1) / tokens_per_image : 0;
   launch_k(router_dwg_reduce_kernel, nred + B, 256, 0, st, scratch, chunks, n, dwg, nred, dlogits, T, E,
            tokens_per_image > 0 ? tokens_per_image : T, dctx_bias);
