@@ -1,0 +1,131 @@
+"""CUDA-graph replay of a ContextMoE for fixed-shape training (RT-DETR trains at one resolution unless multi-scale is
+on: configs/rtdetrv2/include/dataloader.yml:22, so the S5 encoder level sees the same [B, HW, d] every step).
+
+At the reference's shapes (8 x 400 tokens, d = 256) one forward + backward of the layer is ~0.13 ms of device work
+behind ~0.5 ms of Python / autograd / allocator time when launched call by call.  `GraphedMoE` captures the forward
+(weight preparation, context bias, b200moe_layer_fwd) and the backward (b200moe_layer_bwd, context-bias gradients)
+once each into CUDA graphs that share one memory pool, and replays them from a thin autograd node: per step the host
+copies the inputs into the captured buffers, launches one graph each way and hands out the captured outputs.
+
+    moe = ContextMoE(...).cuda()
+    fast = GraphedMoE(moe, x_example, context_example)      # captures; x_example gives shape and dtype
+    y = fast(x, context); loss = crit(y) + fast.aux_loss; loss.backward()      # as with the module itself
+
+Semantics are those of `torch.cuda.make_graphed_callables`: the returned tensors (and the parameter gradients autograd
+accumulates from) are the captured buffers, valid until the next replay; shapes, dtypes, `requires_grad` pattern and the
+parameter storage must not change (in-place optimizer steps are fine; weights are re-cast inside the graph every step).
+Anything else — other shapes, no-grad evaluation, expert parallelism (its pass has a host sync) — falls through to the
+eager module.  Parity with the eager module is bit-exact (tests/test_gpu_layer.py::test_graphed_matches_eager).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from .layer import ContextMoE
+
+
+class _Replay(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, g, x, context, *params):
+        g.x_s.copy_(x)
+        if context is not None:
+            g.ctx_s.copy_(context)
+        g.fwd_graph.replay()
+        ctx.g = g
+        y, aux = g.y_s.detach(), g.aux_s.detach()
+        return y, aux
+
+    @staticmethod
+    def backward(ctx, dy, daux):
+        g = ctx.g
+        if dy is None:
+            g.dy_s.zero_()
+        else:
+            g.dy_s.copy_(dy)
+        if daux is None:
+            g.daux_s.zero_()
+        else:
+            g.daux_s.copy_(daux)
+        for p, s in zip(g._params, g.dparams_s):
+            # autograd adopts a returned buffer as p.grad when it can; if a gradient from an earlier step still lives
+            # there (accumulation over micro-batches, zero_grad(set_to_none=False)), move it out before the replay
+            if s is not None and p.grad is not None and p.grad.data_ptr() == s.data_ptr():
+                p.grad = p.grad.clone()
+        g.bwd_graph.replay()
+        return (None, g.dx_s.detach() if g.dx_s is not None else None, None,
+                *[p.detach() if p is not None else None for p in g.dparams_s])
+
+
+class GraphedMoE(nn.Module):
+    def __init__(self, moe: ContextMoE, x_example: torch.Tensor, context_example: Optional[torch.Tensor] = None,
+                 warmup: int = 3):
+        super().__init__()
+        if not isinstance(moe, ContextMoE):
+            raise TypeError("GraphedMoE wraps a b200moe.ContextMoE")
+        if moe.ep_size > 1:
+            raise ValueError("the expert-parallel pass synchronises with the host once per step and cannot be captured")
+        if not x_example.is_cuda:
+            raise RuntimeError("b200moe runs on a B200 (sm_100a) only; there is no CPU fallback")
+        self.moe = moe
+        self._shape, self._dtype = tuple(x_example.shape), x_example.dtype
+        self._has_ctx = context_example is not None
+        self._params = [p for p in moe.parameters() if p.requires_grad]
+        self._capture(x_example, context_example, warmup)
+
+    @property
+    def aux_loss(self) -> torch.Tensor:
+        return self.moe.aux_loss
+
+    @property
+    def last_aux(self):
+        return self.moe.last_aux
+
+    def _capture(self, x_example, context_example, warmup):
+        moe, params = self.moe, self._params
+        dev = x_example.device
+        self.x_s = torch.zeros_like(x_example).requires_grad_(True)
+        with torch.no_grad():
+            self.x_s.copy_(x_example)
+        self.ctx_s = context_example.clone() if self._has_ctx else None
+        self.dy_s = torch.zeros_like(x_example)
+        self.daux_s = torch.ones((), dtype=torch.float32, device=dev)
+        inputs = (self.x_s, *params)
+
+        def fwd():
+            moe._wcache.clear()                    # the fp32 -> bf16 weight preparation belongs to the graph
+            y = moe(self.x_s, self.ctx_s)
+            return y, moe.aux_loss
+
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(max(warmup, 1)):
+                y, aux = fwd()
+                torch.autograd.grad((y, aux), inputs, (self.dy_s, self.daux_s), allow_unused=True)
+            del y, aux
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+
+        pool = torch.cuda.graph_pool_handle()
+        self.fwd_graph, self.bwd_graph = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.fwd_graph, pool=pool):
+            y, aux = fwd()
+        with torch.cuda.graph(self.bwd_graph, pool=pool):
+            grads = torch.autograd.grad((y, aux), inputs, (self.dy_s, self.daux_s), allow_unused=True)
+        self.y_s, self.aux_s = y, aux
+        self.dx_s, self.dparams_s = grads[0], list(grads[1:])
+        self._telemetry = moe.last_aux             # views into the captured workspace: refreshed by every replay
+        torch.cuda.synchronize(dev)
+
+    def forward(self, x: torch.Tensor, context: Optional[torch.Tensor] = None) -> torch.Tensor:
+        moe = self.moe
+        if (not torch.is_grad_enabled() or tuple(x.shape) != self._shape or x.dtype != self._dtype
+                or (context is not None) != self._has_ctx
+                or (context is not None and context.shape != self.ctx_s.shape)):
+            return moe(x, context)
+        y, aux = _Replay.apply(self, x, context, *self._params)
+        moe.aux_loss, moe.last_aux = aux, self._telemetry
+        return y

@@ -47,6 +47,36 @@ struct PdlScope {
   } while (0);                      \
   if (rc) return rc
 
+// Backward-pass fork: the weight gradients / bias sums and the router's parameter gradients do not feed dx, so at
+// latency-bound sizes they run on two library-owned side streams, joined to the caller's stream before the call returns
+// (plain event fork/join, so the pattern is captured into a CUDA graph as parallel branches).
+struct ForkState {
+  bool ok = false;
+  cudaStream_t s1 = nullptr, s2 = nullptr;
+  cudaEvent_t ev[5] = {};
+};
+static ForkState g_fork[16];
+static int g_fork_mode = 1;   // 0 never, 1 when the pass is latency-bound, 2 always
+static ForkState* fork_state() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+  ForkState& f = g_fork[dev];
+  if (!f.ok) {
+    if (cudaStreamCreateWithFlags(&f.s1, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaStreamCreateWithFlags(&f.s2, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    for (auto& e : f.ev)
+      if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    f.ok = true;
+  }
+  return &f;
+}
+// a kernel that directly follows a cross-stream wait is launched without the programmatic-serialization attribute
+struct NoPdl {
+  bool prev;
+  NoPdl() : prev(g_pdl) { g_pdl = false; }
+  ~NoPdl() { g_pdl = prev; }
+};
+
 static int check_desc(const b200moe_layer_desc* q, const char* what) {
   B200MOE_REQUIRE(q != nullptr, B200MOE_EINVAL, "%s: NULL descriptor", what);
   B200MOE_REQUIRE(q->T > 0, B200MOE_EINVAL, "%s: T=%d must be positive", what, q->T);
@@ -309,35 +339,73 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
                                 pn->gamma, pn->mean_rstd, T, k, d, pn->dv, pn->scratch, pn->dgamma, pn->dbeta, stream));
     dy = pn->dv;
   }
+  // fork when every GEMM of the pass is about one wave of tiles (kernel latency, not throughput, sets the time)
+  ForkState* fk = nullptr;
+  if (!g_prof_on && g_fork_mode && (g_fork_mode == 2 || static_cast<int64_t>(R / 128) * (F / 256) <= 4 * kNumSMs))
+    fk = fork_state();
+  cudaStream_t main_s = static_cast<cudaStream_t>(stream);
+  void* s1 = fk ? static_cast<void*>(fk->s1) : stream;   // router gradients
+  void* s2 = fk ? static_cast<void*>(fk->s2) : stream;   // weight gradients, bias sums
+  float* dctx = (dctx_bias && has_ctx_bias) ? dctx_bias : nullptr;
   STEP("combine_bwd",
        b200moe_combine_bwd(dy, WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_TOKEN_OF_ROW),
                            WS(float, B200MOE_WS_GATE_OF_ROW), meta, R, d, dyp, BWS(float, B200MOE_BWS_DGATE_ROW), stream));
+  if (fk) {
+    cudaEventRecord(fk->ev[0], main_s);
+    cudaStreamWaitEvent(fk->s1, fk->ev[0], 0);
+    cudaStreamWaitEvent(fk->s2, fk->ev[0], 0);
+  }
   STEP("ffn_dgrad_down",
        b200moe_ffn_dgrad_down(dyp, w2, WS(void, B200MOE_WS_PRE), meta, tile_expert, R, d, F, E, dhpre, pad, stream));
-  if (dw2) { STEP("ffn_wgrad", b200moe_ffn_wgrad(dyp, WS(void, B200MOE_WS_H), offs, R, d, F, E, dw2, 0, stream)); }
-  if (dw1) { STEP("ffn_wgrad", b200moe_ffn_wgrad(dhpre, WS(void, B200MOE_WS_XP), offs, R, F, d, E, dw1, 0, stream)); }
-  if (db2 && db1) {
-    STEP("colsum", b200moe_colsum(dyp, d, db2, dhpre, F, db1, offs, E, 0, stream));
-  } else if (db2) {
-    STEP("colsum", b200moe_colsum(dyp, d, db2, nullptr, 0, nullptr, offs, E, 0, stream));
-  } else if (db1) {
-    STEP("colsum", b200moe_colsum(dhpre, F, db1, nullptr, 0, nullptr, offs, E, 0, stream));
+  if (fk) cudaEventRecord(fk->ev[1], main_s);
+  {
+    NoPdl np_;
+    if (!fk) np_.~NoPdl(), new (&np_) NoPdl(), g_pdl = np_.prev;   // single stream: keep PDL as it was
+    STEP("router_bwd_dlogits",
+         b200moe_router_bwd_dlogits(WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX), roa,
+                                    BWS(float, B200MOE_BWS_DGATE_ROW), WS(int32_t, B200MOE_WS_TOKENS_PER_EXPERT), d_aux,
+                                    T, E, k, q->normalize_topk, q->aux_loss_weight, q->z_loss_weight, dlogits, s1));
   }
-  STEP("router_bwd_dlogits",
-       b200moe_router_bwd_dlogits(WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX), roa,
-                                  BWS(float, B200MOE_BWS_DGATE_ROW), WS(int32_t, B200MOE_WS_TOKENS_PER_EXPERT), d_aux,
-                                  T, E, k, q->normalize_topk, q->aux_loss_weight, q->z_loss_weight, dlogits, stream));
+  if (fk) cudaEventRecord(fk->ev[2], fk->s1);
+  if (dwg || dctx) {
+    STEP("router_bwd_params", b200moe_router_bwd_params(dlogits, x, T, d, E, q->tokens_per_image,
+                                                        BWS(float, B200MOE_BWS_DWG_SCRATCH), dwg, dctx, s1));
+  }
+  if (dw2) {
+    NoPdl np_;
+    if (!fk) g_pdl = np_.prev;
+    STEP("ffn_wgrad", b200moe_ffn_wgrad(dyp, WS(void, B200MOE_WS_H), offs, R, d, F, E, dw2, 0, s2));
+  }
+  if (fk) cudaStreamWaitEvent(fk->s2, fk->ev[1], 0);
+  if (dw1) {
+    NoPdl np_;
+    if (!fk) g_pdl = np_.prev;
+    STEP("ffn_wgrad", b200moe_ffn_wgrad(dhpre, WS(void, B200MOE_WS_XP), offs, R, F, d, E, dw1, 0, s2));
+  }
+  {
+    NoPdl np_;
+    if (!fk || dw1) g_pdl = np_.prev;
+    if (db2 && db1) {
+      STEP("colsum", b200moe_colsum(dyp, d, db2, dhpre, F, db1, offs, E, 0, s2));
+    } else if (db2) {
+      STEP("colsum", b200moe_colsum(dyp, d, db2, nullptr, 0, nullptr, offs, E, 0, s2));
+    } else if (db1) {
+      STEP("colsum", b200moe_colsum(dhpre, F, db1, nullptr, 0, nullptr, offs, E, 0, s2));
+    }
+  }
   if (dx) {
     void* dxp = BWS(void, B200MOE_BWS_DXP);
     STEP("ffn_dgrad_up", b200moe_ffn_dgrad_up(dhpre, w1, meta, tile_expert, R, d, F, E, dxp, pad, stream));
+    if (fk) cudaStreamWaitEvent(main_s, fk->ev[2], 0);
+    NoPdl np_;
+    if (!fk) g_pdl = np_.prev;
     STEP("unpermute_bwd", b200moe_unpermute_bwd(dxp, roa, dlogits, wg, T, k, d, E, dx, stream));
   }
-  {
-    float* dctx = (dctx_bias && has_ctx_bias) ? dctx_bias : nullptr;
-    if (dwg || dctx) {
-      STEP("router_bwd_params", b200moe_router_bwd_params(dlogits, x, T, d, E, q->tokens_per_image,
-                                                          BWS(float, B200MOE_BWS_DWG_SCRATCH), dwg, dctx, stream));
-    }
+  if (fk) {
+    cudaEventRecord(fk->ev[3], fk->s1);
+    cudaEventRecord(fk->ev[4], fk->s2);
+    cudaStreamWaitEvent(main_s, fk->ev[3], 0);
+    cudaStreamWaitEvent(main_s, fk->ev[4], 0);
   }
   return B200MOE_OK;
 #undef BWS

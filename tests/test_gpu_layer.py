@@ -140,3 +140,63 @@ def test_cpu_input_raises():
     m = b200moe.ContextMoE(128, 128, 4, 2)
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         m(torch.randn(4, 128))
+
+
+@pytest.mark.parametrize("ctx", [False, True])
+def test_graphed_matches_eager(ctx):
+    """GraphedMoE (forward and backward replayed from CUDA graphs) against the eager module: bit-exact outputs,
+    auxiliary loss and every gradient, over several steps with the weights changed in place between them."""
+    import b200moe
+    B, HW, d, F, E, k = 4, 200, 256, 512, 8, 2
+    _, m = _pair(d, F, E, k, 1.25, ctx=ctx, seed=11)
+    ref = copy.deepcopy(m)
+    g = torch.Generator().manual_seed(4)
+    xs = [torch.randn(B, HW, d, generator=g).to(torch.bfloat16).cuda() for _ in range(3)]
+    cs = [torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1).cuda()
+          if ctx else None for _ in range(3)]
+    go = torch.randn(B, HW, d, generator=g).cuda()
+    fast = b200moe.GraphedMoE(m, xs[0], cs[0])
+    for step in range(3):
+        outs = []
+        for mod, call in ((ref, ref), (m, fast)):
+            mod.zero_grad(set_to_none=True)
+            xg = xs[step].clone().requires_grad_(True)
+            y = call(xg, cs[step])
+            loss = (y.float() * go).sum() + 3.0 * call.aux_loss
+            loss.backward()
+            outs.append((y.detach().clone(), call.aux_loss.detach().clone(), xg.grad.clone(),
+                         {n: p.grad.clone() for n, p in mod.named_parameters() if p.grad is not None},
+                         mod.last_aux["topk_idx"].clone()))
+        (y0, a0, dx0, g0, i0), (y1, a1, dx1, g1, i1) = outs
+        assert torch.equal(y0, y1) and torch.equal(a0, a1) and torch.equal(dx0, dx1) and torch.equal(i0, i1)
+        assert g0.keys() == g1.keys() and len(g0) >= 5
+        for n in g0:
+            assert torch.equal(g0[n], g1[n]), n
+        with torch.no_grad():                                  # an optimizer step, in place, on both copies
+            for p, q in zip(ref.parameters(), m.parameters()):
+                if p.grad is not None:
+                    p.add_(p.grad, alpha=-1e-3)
+                    q.add_(q.grad, alpha=-1e-3)
+    # other shapes and no-grad calls fall through to the eager module
+    with torch.no_grad():
+        assert torch.equal(fast(xs[0], cs[0]), ref(xs[0], cs[0]))
+    assert fast(xs[0][:2], None if cs[0] is None else cs[0][:2]).shape == (2, HW, d)
+
+
+def test_graphed_gradient_accumulation():
+    """Two micro-batches without zeroing in between: p.grad must be the sum, although every replay writes the gradients
+    into the same captured buffers."""
+    import b200moe
+    B, HW, d, F, E, k = 2, 128, 128, 256, 4, 2
+    _, m = _pair(d, F, E, k, 1.25, seed=5)
+    ref = copy.deepcopy(m)
+    g = torch.Generator().manual_seed(8)
+    xs = [torch.randn(B, HW, d, generator=g).to(torch.bfloat16).cuda() for _ in range(2)]
+    fast = b200moe.GraphedMoE(m, xs[0])
+    for mod, call in ((ref, ref), (m, fast)):
+        mod.zero_grad(set_to_none=True)
+        for x in xs:
+            (call(x).float().sum() + call.aux_loss).backward()
+    for (n, p), q in zip(ref.named_parameters(), m.parameters()):
+        if p.grad is not None:
+            assert torch.allclose(p.grad, q.grad, rtol=1e-6, atol=1e-6), n
