@@ -326,6 +326,8 @@ def main():
     ap.add_argument("--workload", default=None, choices=[None, "A", "C", "D"])
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-pdl", action="store_true", help="plain stream-ordered launches inside the whole-layer calls")
+    ap.add_argument("--fork", type=int, default=1, choices=[0, 1, 2],
+                    help="backward-pass side streams: 0 never, 1 at latency-bound sizes (default), 2 always")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
@@ -367,6 +369,9 @@ def main():
     if args.no_pdl:
         from b200moe import _lib as _l
         _l.load().b200moe_layer_pdl(0)
+    if args.fork != 1:
+        from b200moe import _lib as _l
+        _l.load().b200moe_layer_fork(args.fork)
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()

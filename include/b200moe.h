@@ -267,6 +267,10 @@ int b200moe_layer_profile(int enable);
 /* Programmatic dependent launch between the kernels of a whole-layer call (default on): every kernel of the path runs
  * its prologue while its predecessor drains and executes griddepcontrol.wait before touching global memory. */
 int b200moe_layer_pdl(int enable);
+/* Backward-pass fork/join: weight gradients + bias sums and the router's parameter gradients run on two library-owned
+ * side streams next to the dgrad chain and are joined to `stream` before b200moe_layer_bwd returns (capturable).
+ * mode 0 = never, 1 = when every GEMM of the pass is about one wave of tiles (default), 2 = always. */
+int b200moe_layer_fork(int mode);
 int b200moe_layer_profile_read(int index, const char** name, float* ms);
 
 #ifdef __cplusplus

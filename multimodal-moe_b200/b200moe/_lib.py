@@ -40,6 +40,7 @@ SIGNATURES = {
     "b200moe_ctx_bias_bwd": [_P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P, _P],
     "b200moe_layer_profile": [_I],
     "b200moe_layer_pdl": [_I],
+    "b200moe_layer_fork": [_I],
     "b200moe_layer_profile_read": [_I, _P, _P],
     "b200moe_layer_ws_layout": [_P, _P],
     "b200moe_layer_bwd_ws_layout": [_P, _P],

@@ -71,10 +71,10 @@ static ForkState* fork_state() {
   return &f;
 }
 // a kernel that directly follows a cross-stream wait is launched without the programmatic-serialization attribute
-struct NoPdl {
+struct PdlOffIf {
   bool prev;
-  NoPdl() : prev(g_pdl) { g_pdl = false; }
-  ~NoPdl() { g_pdl = prev; }
+  explicit PdlOffIf(bool off) : prev(g_pdl) { if (off) g_pdl = false; }
+  ~PdlOffIf() { g_pdl = prev; }
 };
 
 static int check_desc(const b200moe_layer_desc* q, const char* what) {
@@ -201,6 +201,12 @@ extern "C" int b200moe_ctx_bias_bwd(const int64_t* context, const float* dctx_bi
 
 extern "C" int b200moe_layer_pdl(int enable) {
   g_pdl_enabled = enable != 0;
+  return B200MOE_OK;
+}
+
+extern "C" int b200moe_layer_fork(int mode) {
+  B200MOE_REQUIRE(mode >= 0 && mode <= 2, B200MOE_EINVAL, "layer_fork: mode=%d must be 0, 1 or 2", mode);
+  g_fork_mode = mode;
   return B200MOE_OK;
 }
 
@@ -359,8 +365,7 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
        b200moe_ffn_dgrad_down(dyp, w2, WS(void, B200MOE_WS_PRE), meta, tile_expert, R, d, F, E, dhpre, pad, stream));
   if (fk) cudaEventRecord(fk->ev[1], main_s);
   {
-    NoPdl np_;
-    if (!fk) np_.~NoPdl(), new (&np_) NoPdl(), g_pdl = np_.prev;   // single stream: keep PDL as it was
+    PdlOffIf np_(fk != nullptr);
     STEP("router_bwd_dlogits",
          b200moe_router_bwd_dlogits(WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX), roa,
                                     BWS(float, B200MOE_BWS_DGATE_ROW), WS(int32_t, B200MOE_WS_TOKENS_PER_EXPERT), d_aux,
@@ -372,19 +377,16 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
                                                         BWS(float, B200MOE_BWS_DWG_SCRATCH), dwg, dctx, s1));
   }
   if (dw2) {
-    NoPdl np_;
-    if (!fk) g_pdl = np_.prev;
+    PdlOffIf np_(fk != nullptr);
     STEP("ffn_wgrad", b200moe_ffn_wgrad(dyp, WS(void, B200MOE_WS_H), offs, R, d, F, E, dw2, 0, s2));
   }
   if (fk) cudaStreamWaitEvent(fk->s2, fk->ev[1], 0);
   if (dw1) {
-    NoPdl np_;
-    if (!fk) g_pdl = np_.prev;
+    PdlOffIf np_(fk != nullptr);
     STEP("ffn_wgrad", b200moe_ffn_wgrad(dhpre, WS(void, B200MOE_WS_XP), offs, R, F, d, E, dw1, 0, s2));
   }
   {
-    NoPdl np_;
-    if (!fk || dw1) g_pdl = np_.prev;
+    PdlOffIf np_(fk != nullptr && !dw1);
     if (db2 && db1) {
       STEP("colsum", b200moe_colsum(dyp, d, db2, dhpre, F, db1, offs, E, 0, s2));
     } else if (db2) {
@@ -397,8 +399,7 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
     void* dxp = BWS(void, B200MOE_BWS_DXP);
     STEP("ffn_dgrad_up", b200moe_ffn_dgrad_up(dhpre, w1, meta, tile_expert, R, d, F, E, dxp, pad, stream));
     if (fk) cudaStreamWaitEvent(main_s, fk->ev[2], 0);
-    NoPdl np_;
-    if (!fk) g_pdl = np_.prev;
+    PdlOffIf np_(fk != nullptr);
     STEP("unpermute_bwd", b200moe_unpermute_bwd(dxp, roa, dlogits, wg, T, k, d, E, dx, stream));
   }
   if (fk) {
