@@ -326,8 +326,8 @@ def main():
     ap.add_argument("--workload", default=None, choices=[None, "A", "C", "D"])
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-pdl", action="store_true", help="plain stream-ordered launches inside the whole-layer calls")
-    ap.add_argument("--fork", type=int, default=1, choices=[0, 1, 2],
-                    help="backward-pass side streams: 0 never, 1 at latency-bound sizes (default), 2 always")
+    ap.add_argument("--fork", type=int, default=1, choices=[0, 1],
+                    help="backward-pass side streams (weight / router gradients next to the dgrad chain): 0 off, 1 on")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 

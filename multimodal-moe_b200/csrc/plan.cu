@@ -189,6 +189,165 @@ plan_assign_kernel(const int32_t* __restrict__ topk_idx, const float* __restrict
   }
 }
 
+// Small problems (<= kFusedMaxBlocks router blocks): one launch.  Every block redoes the (tiny) scan for itself --
+// totals and its own exclusive base from the nblk x k x E counts -- and the capacity / offset arithmetic in shared
+// memory, then assigns the rows of its 128 tokens; block 0 also writes the plan's global outputs and the losses, and
+// the blocks share the initialisation of the pad rows (rows no assignment lands on), so no second kernel and no
+// single-block stage sits on the critical path of a latency-bound step.
+constexpr int kFusedMaxBlocks = 64;
+
+__global__ void __launch_bounds__(kRouterTokPerBlock)
+plan_fused_kernel(const int32_t* __restrict__ topk_idx, const float* __restrict__ topk_gate,
+                  const int32_t* __restrict__ block_counts, const float* __restrict__ block_stats, int nblk, int T,
+                  int k, int E, int capacity, const int32_t* __restrict__ global_offset,
+                  const int32_t* __restrict__ expert_order, int row_pad, int rows_cap, float aux_w, float z_w,
+                  int32_t* __restrict__ expert_offsets, int32_t* __restrict__ meta, int32_t* __restrict__ tile_expert,
+                  int32_t* __restrict__ tokens_per_expert, int32_t* __restrict__ kept_per_expert,
+                  float* __restrict__ losses, int32_t* __restrict__ slot_limit,
+                  int32_t* __restrict__ row_of_assignment, int32_t* __restrict__ token_of_row,
+                  float* __restrict__ gate_of_row) {
+  __shared__ int total_s[8 * 64], base_s[8 * 64], first_s[8 * 64], keptslot_s[8 * 64];
+  __shared__ int kept_s[64], count_s[64], off_s[65], expert_at_s[64];
+  __shared__ float P_s[65];
+  __shared__ int wc[kRouterTokPerBlock / 32][64];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = kRouterTokPerBlock / 32;
+  const int kE = k * E;
+  const bool lead = blockIdx.x == 0;
+  pdl_sync();
+
+  for (int q = threadIdx.x; q < kE; q += blockDim.x) {
+    int tot = 0, base = 0;
+    for (int b = 0; b < nblk; ++b) {
+      const int c = block_counts[static_cast<size_t>(b) * kE + q];
+      base += (b < static_cast<int>(blockIdx.x)) ? c : 0;
+      tot += c;
+    }
+    total_s[q] = tot;
+    base_s[q] = base;
+  }
+  if (lead) {   // loss statistics, summed in the order plan_scan_kernel uses
+    for (int e = warp; e <= E; e += nwarps) {
+      float s = 0.f;
+      for (int b0 = 0; b0 < nblk; b0 += 256) {
+        float v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const int b = b0 + u * 32 + lane;
+          v[u] = (b < nblk) ? block_stats[static_cast<size_t>(b) * (E + 1) + e] : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) s += v[u];
+      }
+      s = warp_sum(s);
+      if (lane == 0) P_s[e] = s;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < E) {
+    const int e = threadIdx.x;
+    int lower = 0, kept = 0, count = 0;
+    for (int s = 0; s < k; ++s) {
+      const int n = total_s[s * E + e];
+      const int base = global_offset ? global_offset[s * E + e] : lower;
+      int room = capacity - base;
+      room = room < 0 ? 0 : room;
+      const int ks = n < room ? n : room;
+      keptslot_s[s * E + e] = ks;
+      first_s[s * E + e] = kept;          // relative to the expert segment until the offsets are known
+      kept += ks;
+      lower += n;
+      count += n;
+    }
+    kept_s[e] = kept;
+    count_s[e] = count;
+    expert_at_s[expert_order ? expert_order[e] : e] = e;
+    if (lead) {
+      tokens_per_expert[e] = count;
+      kept_per_expert[e] = kept;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int off = 0, kept_total = 0, count_total = 0;
+    for (int i = 0; i < E; ++i) {
+      off_s[i] = off;
+      const int e = expert_at_s[i];
+      off += (kept_s[e] + row_pad - 1) / row_pad * row_pad;
+      kept_total += kept_s[e];
+      count_total += count_s[e];
+    }
+    off_s[E] = off;
+    if (lead) {
+      meta[0] = off;
+      meta[1] = (off + kRowPad - 1) / kRowPad;
+      meta[2] = count_total - kept_total;
+      meta[3] = kept_total;
+      meta[4] = capacity;
+      meta[5] = meta[6] = meta[7] = 0;
+      float lb = 0.f;
+      const float invT = T > 0 ? 1.0f / static_cast<float>(T) : 0.f;
+      for (int e = 0; e < E; ++e)
+        lb += (static_cast<float>(count_s[e]) / static_cast<float>(static_cast<long long>(T) * k)) * (P_s[e] * invT);
+      lb *= static_cast<float>(E);
+      const float z = P_s[E] * invT;
+      losses[0] = aux_w * lb + z_w * z;
+      losses[1] = lb;
+      losses[2] = z;
+    }
+  }
+  __syncthreads();
+  for (int q = threadIdx.x; q < kE; q += blockDim.x) {
+    const int e = q % E;
+    const int pos = expert_order ? expert_order[e] : e;
+    const int first = off_s[pos] + first_s[q];
+    first_s[q] = first;
+    if (lead) {
+      slot_limit[q] = first + keptslot_s[q];
+      slot_limit[kE + q] = first;
+    }
+  }
+  if (lead)
+    for (int i = threadIdx.x; i <= E; i += blockDim.x) expert_offsets[i] = off_s[i];
+  // pad rows and tile -> expert map, shared between the blocks
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows_cap; r += gridDim.x * blockDim.x) {
+    int pos = -1;
+    if (r < off_s[E]) {
+      pos = 0;
+      while (pos + 1 < E && off_s[pos + 1] <= r) ++pos;
+    }
+    const int e = pos >= 0 ? expert_at_s[pos] : -1;
+    if (pos < 0 || r >= off_s[pos] + kept_s[e]) { token_of_row[r] = -1; gate_of_row[r] = 0.f; }
+    if (tile_expert && (r % kRowPad) == 0) tile_expert[r / kRowPad] = e;
+  }
+  __syncthreads();
+
+  // rows of this block's assignments (as plan_assign_kernel)
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = t < T;
+  for (int s = 0; s < k; ++s) {
+    for (int i = threadIdx.x; i < (kRouterTokPerBlock / 32) * 64; i += blockDim.x) (&wc[0][0])[i] = 0;
+    __syncthreads();
+    const int e = live ? topk_idx[static_cast<size_t>(t) * k + s] : (0x40000000 + lane);
+    const unsigned same = __match_any_sync(0xffffffffu, e);
+    const int rank_in_warp = __popc(same & ((1u << lane) - 1u));
+    if (live && rank_in_warp == 0) wc[warp][e] = __popc(same);
+    __syncthreads();
+    if (live) {
+      int rank = rank_in_warp;
+      for (int w = 0; w < warp; ++w) rank += wc[w][e];
+      const int q = s * E + e;
+      const int row = first_s[q] + base_s[q] + rank;
+      const bool keep = row < first_s[q] + keptslot_s[q];
+      row_of_assignment[static_cast<size_t>(t) * k + s] = keep ? row : -1;
+      if (keep) {
+        token_of_row[row] = t;
+        gate_of_row[row] = topk_gate[static_cast<size_t>(t) * k + s];
+      }
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace b200moe
 
 extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int32_t* block_counts,
@@ -209,6 +368,13 @@ extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int tb = router_block_tokens(T);
   const int nblk = (T + tb - 1) / tb;
+  if (nblk <= kFusedMaxBlocks) {
+    launch_k(plan_fused_kernel, nblk, tb, 0, st, topk_idx, topk_gate, static_cast<const int32_t*>(block_counts),
+             block_stats, nblk, T, k, E, capacity, global_offset, expert_order, row_pad, rows_cap, aux_loss_weight,
+             z_loss_weight, expert_offsets, meta, tile_expert, tokens_per_expert, kept_per_expert, losses, slot_limit,
+             row_of_assignment, token_of_row, gate_of_row);
+    return check_launch("plan_fused");
+  }
   const bool init_in_kernel = rows_cap <= 16 * 1024;
   if (!init_in_kernel) {
     cudaMemsetAsync(token_of_row, 0xFF, sizeof(int32_t) * static_cast<size_t>(rows_cap), st);

@@ -17,6 +17,7 @@
 //     assignment counts per (slot, expert) and sum_t p[t,e] / sum_t lse^2, reduced in a fixed order (warp shuffle
 //     tree, then the four warps in order): deterministic, no float atomics.  The plan kernel scans the tiles.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -408,9 +409,12 @@ static int launch_router(const void* x, const void* wsplit, RouterArgs a, cudaSt
     configured = true;
   }
   a.stages = Cfg::stages(a.k);
+  static const int stage_cap = [] { const char* e = getenv("B200MOE_ROUTER_STAGES"); return e ? atoi(e) : 0; }();
+  static const int cta_cap = [] { const char* e = getenv("B200MOE_ROUTER_CTAS"); return e ? atoi(e) : 0; }();
+  if (stage_cap >= 2 && stage_cap < a.stages) a.stages = stage_cap;
   B200MOE_REQUIRE(a.stages >= 2, B200MOE_EINVAL, "router_fwd: no shared memory left for the load ring (top_k=%d)", a.k);
   const int ntiles = (a.T + kRtTile - 1) / kRtTile;
-  const int max_ctas = kNumSMs * Cfg::kCtasPerSm;
+  const int max_ctas = cta_cap > 0 ? cta_cap : kNumSMs * Cfg::kCtasPerSm;
   const int grid = ntiles < max_ctas ? ntiles : max_ctas;
   launch_k(kern, grid, Cfg::kThreads, Cfg::total(a.k), st, tmX, tmW, a);
   return check_launch("router_fwd");
