@@ -182,6 +182,39 @@ int b200moe_ep_route_tables(const int32_t* all_hist, int W, int k, int E, int ra
 int b200moe_scatter_rows(const void* in, const int32_t* src_of_row, const int32_t* meta, int rows_cap, int d,
                          void* out, void* stream);
 
+/* ---- Expert parallelism over peer memory (NVLink loads / stores inside the row-movement kernels) ----------------
+ * Every rank owns an arena holding row buffers [rows_cap, d] bf16 in the padded expert-major layout (xp, yo, dyp,
+ * dxp at byte offsets the host chooses); `peers` is a DEVICE array of W arena base addresses as mapped on this GPU
+ * (symmetric memory).  A remote row is named dest = rank * rows_cap + row.  The host places one device-side barrier
+ * over the ranks between a producer and its remote consumers; nothing here synchronises.
+ *   ep_p2p_tables      : kept [W*E+2] from b200moe_ep_route_tables -> dest_off [E] (first row, on rank e / E_local, of
+ *                        this rank's rows for expert e), this rank's expert_offsets [E_local+1] / meta / tile_expert
+ *                        (as b200moe_plan writes them); meta[5] = 1 if some rank's rows exceed rows_cap.
+ *   ep_p2p_zero_pads   : zero the pad rows of up to two local buffers (a, b may be NULL).
+ *   ep_p2p_dispatch    : peers' xp[dest] = x[token_of_row[r]] for every send row r (send layout = b200moe_plan with
+ *                        row_pad 1); writes dest_of_row [send_rows_cap] for the calls below.
+ *   ep_p2p_combine     : y[t] = sum_s gate[t,s] * peers' yo[dest_of_row[row_of_assignment[t,s]]].
+ *   ep_p2p_combine_bwd : peers' dyp[dest] = gate_of_row[r] * dy[token]; dgate_row[r] = <dy[token], peers' yo[dest]>.
+ *   ep_p2p_unpermute_bwd: b200moe_unpermute_bwd with the dxp rows loaded from the peers.                        */
+int b200moe_ep_p2p_tables(const int32_t* kept, int W, int E, int rank, int rows_cap, int32_t* dest_off,
+                          int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert, void* stream);
+int b200moe_ep_p2p_zero_pads(const int32_t* kept, const int32_t* expert_offsets, int W, int E, int rank, int d,
+                             void* a, void* b, void* stream);
+int b200moe_ep_p2p_dispatch(const void* x, const int32_t* token_of_row, const int32_t* send_offsets,
+                            const int32_t* send_meta, const int32_t* dest_off, const void* const* peers,
+                            int64_t buf_offset_bytes, int rows_cap, int send_rows_cap, int E, int E_local, int d,
+                            int32_t* dest_of_row, void* stream);
+int b200moe_ep_p2p_combine(const void* const* peers, int64_t buf_offset_bytes, int rows_cap,
+                           const int32_t* dest_of_row, const int32_t* row_of_assignment, const float* topk_gate,
+                           int T, int k, int d, void* y, void* stream);
+int b200moe_ep_p2p_combine_bwd(const void* dy, const void* const* peers, int64_t yo_offset_bytes,
+                               int64_t dyp_offset_bytes, int rows_cap, const int32_t* dest_of_row,
+                               const int32_t* token_of_row, const float* gate_of_row, const int32_t* send_meta,
+                               int send_rows_cap, int d, float* dgate_row, void* stream);
+int b200moe_ep_p2p_unpermute_bwd(const void* const* peers, int64_t buf_offset_bytes, int rows_cap,
+                                 const int32_t* dest_of_row, const int32_t* row_of_assignment, const float* dlogits,
+                                 const float* wg, int T, int k, int d, int E, void* dx, void* stream);
+
 /* ---- Context bias (A.2): ctx_bias[b,e] = sum_i Embed_i[context[b,i],:] . Wc[e, i*cd:(i+1)*cd] ------------------
  * context [B,n_fields] int64 (device); tables: HOST array of n_fields device pointers, table i is [vocab[i], cd]
  * fp32; vocab: HOST array; wc [E, n_fields*cd] fp32.  Ids outside [0, vocab[i]) contribute nothing.

@@ -1,0 +1,195 @@
+"""Expert parallelism over peer memory: the row-movement kernels of the layer load and store rows in
+the other ranks' HBM over NVLink, so there is no all-to-all, no send / receive buffer and no host synchronisation in
+the pass (csrc/ep_p2p.cu has the data flow; b200moe/ep.py is the NCCL all-to-all path this replaces on one NVSwitch box
+and remains the fallback).
+
+Per module one symmetric arena (torch.distributed._symmetric_memory: cuMem allocations mapped into every rank of the
+group, plus signal pads for a device-side barrier) holds xp | yo | dyp | dxp, each [rows_cap, d] bf16 with
+rows_cap = E_local * pad128(capacity for T_cap tokens per rank).  T_cap is agreed once (max over the ranks at the
+first call); a later call with more tokens on some rank raises on that rank.
+
+Forward : router -> histogram all-gather -> ep_route_tables -> plan (send layout) -> ep_p2p_tables ->
+          ep_p2p_dispatch (gather x rows, store them into the expert ranks' xp) -> barrier -> up -> down (into yo)
+          -> barrier -> ep_p2p_combine (load the k rows of a token from the expert ranks' yo).
+Backward: ep_p2p_combine_bwd (store gate * dy into the expert ranks' dyp; load yo rows for the gate gradient) ->
+          router gradients (fill the wait) -> barrier -> dgrad_down -> dgrad_up (into dxp) -> weight gradients ->
+          barrier -> ep_p2p_unpermute_bwd (load dxp rows from the expert ranks).
+Reuse of the arena across steps is ordered by the histogram all-gather of the next forward (every rank has finished
+the previous backward before any rank's all-gather completes).
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import _lib, ops
+
+_BIG = 1 << 30
+
+
+class P2PUnavailable(RuntimeError):
+    pass
+
+
+class _Arena:
+    def __init__(self, mod, group, T_cap: int, dev):
+        try:
+            import torch.distributed._symmetric_memory as symm
+        except Exception as e:  # noqa: BLE001
+            raise P2PUnavailable(f"torch symmetric memory is not importable: {e!r}") from e
+        W = dist.get_world_size(group)
+        E, k, d = mod.num_experts, mod.top_k, mod.d_model
+        t = torch.tensor([T_cap], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+        self.T_cap = int(t.item())
+        cap = ops.capacity_of(mod.capacity_factor, self.T_cap * W, k, E)
+        self.rows_cap = mod.num_local_experts * ((cap + 127) // 128 * 128)
+        self.buf_bytes = self.rows_cap * d * 2
+        self.mem = symm.empty(4 * self.buf_bytes, dtype=torch.uint8, device=dev)
+        self.hdl = symm.rendezvous(self.mem, group)
+        self.peers = torch.tensor(list(self.hdl.buffer_ptrs), dtype=torch.int64, device=dev)
+        bf = self.mem.view(torch.bfloat16).view(4, self.rows_cap, d)
+        self.xp, self.yo, self.dyp, self.dxp = bf[0], bf[1], bf[2], bf[3]
+        self.off = [i * self.buf_bytes for i in range(4)]
+        self.pending = False           # a forward whose backward has not run yet owns the arena
+
+    def barrier(self, channel: int):
+        self.hdl.barrier(channel=channel)
+
+
+def arena_for(mod, T: int, dev) -> _Arena:
+    a = mod.__dict__.get("_p2p_arena")
+    if a is None:
+        a = mod.__dict__["_p2p_arena"] = _Arena(mod, mod.ep_group, T, dev)
+    if T > a.T_cap:
+        raise RuntimeError(f"expert-parallel peer-memory arena was sized for {a.T_cap} tokens per rank, got {T}; "
+                           f"construct the layer with ep_p2p=False or call with the largest batch first")
+    return a
+
+
+class _P2PFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x2, ctx_bias, wg, w1, b1, w2, b2, mod, tokens_per_image, ar):
+        group = mod.ep_group
+        W, rank = dist.get_world_size(group), dist.get_rank(group)
+        T, d = x2.shape
+        E, k, EL = mod.num_experts, mod.top_k, mod.num_local_experts
+        need_grad = any(ctx.needs_input_grad)
+        w1b, w2b, wsplit, wgf = mod._prepared(w1, w2, wg)
+        b1f, b2f = b1.float().contiguous(), b2.float().contiguous()
+        cb = ctx_bias.float().contiguous() if ctx_bias is not None else None
+        dev = x2.device
+        st = _lib.stream_ptr()
+        i32 = torch.int32
+
+        r = ops.router_fwd(x2, None, cb, tokens_per_image, k, mod.normalize_topk, wg_split=wsplit, E=E)
+        mine = torch.empty((k * E + 1,), dtype=i32, device=dev)
+        _lib.call("b200moe_ep_hist", r.block_counts.data_ptr(), r.block_counts.shape[0], k, E, T, mine.data_ptr(), st)
+        allh = torch.empty((W, k * E + 1), dtype=i32, device=dev)
+        dist.all_gather_into_tensor(allh, mine, group=group)
+        goff = torch.empty((k, E), dtype=i32, device=dev)
+        kept = torch.empty((W * E + 2,), dtype=i32, device=dev)
+        recv_counts = torch.empty((W * EL,), dtype=i32, device=dev)
+        cf = -1.0 if mod.capacity_factor is None else float(mod.capacity_factor)
+        _lib.call("b200moe_ep_route_tables", allh.data_ptr(), W, k, E, rank, cf, EL, goff.data_ptr(), kept.data_ptr(),
+                  recv_counts.data_ptr(), st)
+        # the plan kernel takes the capacity from the host; the global capacity lives on the device (kept[W*E]), so the
+        # offsets are shifted instead: room = BIG - (offset + BIG - capacity) = capacity - offset
+        goff_shift = goff + (_BIG - kept[W * E])
+        send_cap = ops.rows_upper_bound(T, k, E, -1)
+        p = ops.plan(r, T, k, E, _BIG, mod.aux_loss_weight, mod.z_loss_weight, global_offset=goff_shift,
+                     expert_order=None, row_pad=1, rows_cap=send_cap)
+        R = ar.rows_cap
+        dest_off = torch.empty((E,), dtype=i32, device=dev)
+        offs = torch.empty((EL + 1,), dtype=i32, device=dev)
+        meta = torch.empty((8,), dtype=i32, device=dev)
+        tile_e = torch.empty((R // 128,), dtype=i32, device=dev)
+        _lib.call("b200moe_ep_p2p_tables", kept.data_ptr(), W, E, rank, R, dest_off.data_ptr(), offs.data_ptr(),
+                  meta.data_ptr(), tile_e.data_ptr(), st)
+        _lib.call("b200moe_ep_p2p_zero_pads", kept.data_ptr(), offs.data_ptr(), W, E, rank, d, ar.xp.data_ptr(),
+                  ar.dyp.data_ptr() if need_grad else None, st)
+        dest_of_row = torch.empty((send_cap,), dtype=i32, device=dev)
+        _lib.call("b200moe_ep_p2p_dispatch", x2.data_ptr(), p.token_of_row.data_ptr(), p.expert_offsets.data_ptr(),
+                  p.meta.data_ptr(), dest_off.data_ptr(), ar.peers.data_ptr(), ar.off[0], R, send_cap, E, EL, d,
+                  dest_of_row.data_ptr(), st)
+        ar.barrier(0)                                   # every rank's rows have landed in xp
+        pre, h = ops.ffn_up(ar.xp, w1b, b1f, meta, tile_e, save_pre=need_grad)
+        ops.ffn_down(h, w2b, b2f, meta, tile_e, out=ar.yo)
+        ar.barrier(1)                                   # every rank's yo is complete
+        y = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
+        _lib.call("b200moe_ep_p2p_combine", ar.peers.data_ptr(), ar.off[1], R, dest_of_row.data_ptr(),
+                  p.row_of_assignment.data_ptr(), r.topk_gate.data_ptr(), T, k, d, y.data_ptr(), st)
+
+        ctx.mod, ctx.tpi, ctx.plan, ctx.routing, ctx.ar = mod, tokens_per_image, p, r, ar
+        ctx.has_ctx = ctx_bias is not None
+        ctx.dtypes = (w1.dtype, b1.dtype, w2.dtype, b2.dtype, wg.dtype)
+        ctx.tabs = (dest_of_row, offs, meta, tile_e, send_cap, pre, h)
+        ctx.save_for_backward(x2, wgf, w1b, w2b)
+        ar.pending = need_grad
+        aux = p.losses[0]
+        stats = p.losses.detach()
+        ctx.mark_non_differentiable(stats)
+        mod._stash(r, p)
+        return y, aux, stats
+
+    @staticmethod
+    def backward(ctx, dy, d_aux, _d_stats):
+        x2, wgf, w1b, w2b = ctx.saved_tensors
+        mod, p, r, ar = ctx.mod, ctx.plan, ctx.routing, ctx.ar
+        dest_of_row, offs, meta, tile_e, send_cap, pre, h = ctx.tabs
+        T, d = x2.shape
+        E, k, EL, F = mod.num_experts, mod.top_k, mod.num_local_experts, mod.dim_feedforward
+        need = ctx.needs_input_grad
+        dev = x2.device
+        st = _lib.stream_ptr()
+        R = ar.rows_cap
+        if dy is None:
+            dy = torch.zeros_like(x2)
+        dy = dy.contiguous().to(torch.bfloat16)
+        d_aux_t = d_aux.float().contiguous() if d_aux is not None else None
+        f32 = torch.float32
+
+        dgate_row = torch.empty((send_cap,), dtype=f32, device=dev)
+        _lib.call("b200moe_ep_p2p_combine_bwd", dy.data_ptr(), ar.peers.data_ptr(), ar.off[1], ar.off[2], R,
+                  dest_of_row.data_ptr(), p.token_of_row.data_ptr(), p.gate_of_row.data_ptr(), p.meta.data_ptr(),
+                  send_cap, d, dgate_row.data_ptr(), st)
+        # the router gradients need nothing from the other ranks: they run while the slowest rank's rows arrive
+        dlogits = ops.router_bwd_dlogits(r.logits, r.topk_idx, p.row_of_assignment, dgate_row, p.tokens_per_expert,
+                                         d_aux_t, mod.normalize_topk, mod.aux_loss_weight, mod.z_loss_weight)
+        dwg, dctx = ops.router_bwd_params(dlogits, x2, ctx.tpi, want_dwg=need[2],
+                                          want_dctx=bool(ctx.has_ctx and need[1]))
+        ar.barrier(2)                                   # every rank's dyp rows have landed
+        dhpre = ops.ffn_dgrad_down(ar.dyp, w2b, pre, meta, tile_e)
+        if need[0]:
+            ops.ffn_dgrad_up(dhpre, w1b, meta, tile_e, out=ar.dxp)
+        dw1 = torch.empty((EL, F, d), dtype=f32, device=dev) if need[3] else None
+        db1 = torch.empty((EL, F), dtype=f32, device=dev) if need[4] else None
+        dw2 = torch.empty((EL, d, F), dtype=f32, device=dev) if need[5] else None
+        db2 = torch.empty((EL, d), dtype=f32, device=dev) if need[6] else None
+        if need[5]:
+            ops.ffn_wgrad(ar.dyp, h, offs, EL, out=dw2)
+        if need[3]:
+            ops.ffn_wgrad(dhpre, ar.xp, offs, EL, out=dw1)
+        if need[6] and need[4]:
+            ops.colsum(ar.dyp, offs, EL, out=db2, a1=dhpre, out1=db1)
+        elif need[6]:
+            ops.colsum(ar.dyp, offs, EL, out=db2)
+        elif need[4]:
+            ops.colsum(dhpre, offs, EL, out=db1)
+        dx = None
+        ar.barrier(3)                                   # every rank's dxp is complete (and its reads of xp / dyp are queued)
+        if need[0]:
+            dx = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
+            _lib.call("b200moe_ep_p2p_unpermute_bwd", ar.peers.data_ptr(), ar.off[3], R, dest_of_row.data_ptr(),
+                      p.row_of_assignment.data_ptr(), dlogits.data_ptr(), wgf.data_ptr(), T, k, d, E, dx.data_ptr(), st)
+        ar.pending = False
+        t_w1, t_b1, t_w2, t_b2, t_wg = ctx.dtypes
+
+        def cast(g, dt):
+            return g if g is None or g.dtype == dt else g.to(dt)
+        return (dx, dctx, cast(dwg, t_wg), cast(dw1, t_w1), cast(db1, t_b1), cast(dw2, t_w2), cast(db2, t_b2),
+                None, None, None)
+
+
+def p2p_forward(mod, xb, cb, tpi, ar):
+    return _P2PFunction.apply(xb, cb, mod.gate.weight, mod.w1, mod.b1, mod.w2, mod.b2, mod, tpi, ar)

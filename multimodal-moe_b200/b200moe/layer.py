@@ -262,7 +262,8 @@ class ContextMoE(nn.Module):
     def __init__(self, d_model: int, dim_feedforward: int, num_experts: int, top_k: int = 2,
                  capacity_factor: Optional[float] = 1.25, context_vocab_sizes: Sequence[int] = (),
                  context_dim: int = 32, activation: str = "gelu", aux_loss_weight: float = 1e-2,
-                 z_loss_weight: float = 1e-3, normalize_topk: bool = True, ep_group=None):
+                 z_loss_weight: float = 1e-3, normalize_topk: bool = True, ep_group=None,
+                 ep_p2p: Optional[bool] = None):
         super().__init__()
         if activation != "gelu":
             raise ValueError("only exact-erf GELU is defined for this layer (zoo/rtdetr/utils.py:160-161)")
@@ -280,6 +281,7 @@ class ContextMoE(nn.Module):
         self.context_vocab_sizes = tuple(context_vocab_sizes)
         self.context_dim = context_dim
         self.ep_group = ep_group
+        self.ep_p2p = ep_p2p          # None: peer-memory dispatch when available; False: NCCL all-to-all; True: required
         self.ep_chunks = 1            # groups of local experts whose all-to-all overlaps the other groups' GEMMs
         # (measured at 2 GPUs, workload D: 1 group 3.72 ms, 2 groups 4.00 ms, 4 groups 4.91 ms per step)
         self.ep_size, self.ep_rank = 1, 0
@@ -311,7 +313,7 @@ class ContextMoE(nn.Module):
         new = self.__class__.__new__(self.__class__)
         memo[id(self)] = new
         for k_, v in self.__dict__.items():
-            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned"):
+            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena"):
                 continue
             if k_ in ("_wcache", "last_aux", "_plans"):
                 new.__dict__[k_] = {}
@@ -326,7 +328,7 @@ class ContextMoE(nn.Module):
     def __getstate__(self):
         s = dict(self.__dict__)
         s["_wcache"], s["last_aux"], s["aux_loss"], s["ep_group"], s["_plans"] = {}, {}, torch.zeros(()), None, {}
-        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned"):
+        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena"):
             s.pop(k_, None)
         return s
 
@@ -397,6 +399,23 @@ class ContextMoE(nn.Module):
         self._wcache["prep"] = (key, out)
         return out
 
+    def _ep_call(self, ep_forward, xb, cb, tpi):
+        """Expert-parallel pass: over peer memory (b200moe/ep_p2p.py) when the group's GPUs can map each other's memory,
+        a capacity factor bounds the rows per rank and no unfinished backward owns the arena; else NCCL all-to-alls."""
+        import os
+        if (self.ep_p2p is not False and self.capacity_factor is not None and self.ep_chunks == 1
+                and os.environ.get("B200MOE_EP_P2P", "1") != "0"):
+            from . import ep_p2p
+            try:
+                ar = ep_p2p.arena_for(self, xb.shape[0], xb.device)
+            except ep_p2p.P2PUnavailable:
+                if self.ep_p2p:
+                    raise
+                self.ep_p2p, ar = False, None
+            if ar is not None and not ar.pending:
+                return ep_p2p.p2p_forward(self, xb, cb, tpi, ar)
+        return ep_forward(self, xb, cb, tpi)
+
     def _ctx_arrays(self, tabs):
         """HOST arrays (device pointers of the embedding tables, their vocabulary sizes) for the ctx_bias calls."""
         key = tuple(t.data_ptr() for t in tabs)
@@ -448,7 +467,7 @@ class ContextMoE(nn.Module):
             if context is not None and self.ctx_proj is not None:
                 cb = _CtxBiasFunction.apply(context.long().contiguous(), self.ctx_proj.weight, self,
                                             *[m_.weight for m_ in self.ctx_embed])
-            y, aux, stats = ep_forward(self, xb, cb, tpi)
+            y, aux, stats = self._ep_call(ep_forward, xb, cb, tpi)
             self.aux_loss = aux
             r, p = self._last
             self.last_aux = {"load_balance": stats[1], "z_loss": stats[2], "tokens_per_expert": p.tokens_per_expert,

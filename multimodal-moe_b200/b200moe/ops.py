@@ -148,10 +148,10 @@ def ffn_up(xp, w1, b1, meta, tile_expert, save_pre: bool = True, row_pad: int = 
     return pre, h
 
 
-def ffn_down(h, w2, b2, meta, tile_expert, row_pad: int = ROW_PAD):
+def ffn_down(h, w2, b2, meta, tile_expert, row_pad: int = ROW_PAD, out: Optional[torch.Tensor] = None):
     rows_cap, F = h.shape
     E, d, _ = w2.shape
-    yo = _empty((rows_cap, d), torch.bfloat16, h.device)
+    yo = out if out is not None else _empty((rows_cap, d), torch.bfloat16, h.device)
     call("b200moe_ffn_down", ptr(h), ptr(w2), ptr(b2), ptr(meta), ptr(tile_expert), rows_cap, d, F, E, ptr(yo),
          row_pad, stream_ptr())
     return yo
@@ -166,10 +166,10 @@ def ffn_dgrad_down(dyp, w2, pre, meta, tile_expert, row_pad: int = ROW_PAD):
     return dhpre
 
 
-def ffn_dgrad_up(dhpre, w1, meta, tile_expert, row_pad: int = ROW_PAD):
+def ffn_dgrad_up(dhpre, w1, meta, tile_expert, row_pad: int = ROW_PAD, out: Optional[torch.Tensor] = None):
     rows_cap, F = dhpre.shape
     E, _, d = w1.shape
-    dxp = _empty((rows_cap, d), torch.bfloat16, dhpre.device)
+    dxp = out if out is not None else _empty((rows_cap, d), torch.bfloat16, dhpre.device)
     call("b200moe_ffn_dgrad_up", ptr(dhpre), ptr(w1), ptr(meta), ptr(tile_expert), rows_cap, d, F, E, ptr(dxp),
          row_pad, stream_ptr())
     return dxp

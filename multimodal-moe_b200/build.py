@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 OUT_DIR = os.path.join(HERE, "b200moe")
 LIB = os.path.join(OUT_DIR, "libb200moe.so")
 OBJ_DIR = os.path.join(HERE, "build")
-SOURCES = ["api.cu", "router.cu", "router_bwd.cu", "plan.cu", "movement.cu", "gemm.cu", "ep.cu", "layer.cu"]
+SOURCES = ["api.cu", "router.cu", "router_bwd.cu", "plan.cu", "movement.cu", "gemm.cu", "ep.cu", "ep_p2p.cu", "layer.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]

@@ -105,6 +105,34 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+__device__ __forceinline__ void unpack8(const uint4& r, float (&v)[8]) {
+  float2 f;
+  f = bf16x2_to_float2(r.x); v[0] = f.x; v[1] = f.y;
+  f = bf16x2_to_float2(r.y); v[2] = f.x; v[3] = f.y;
+  f = bf16x2_to_float2(r.z); v[4] = f.x; v[5] = f.y;
+  f = bf16x2_to_float2(r.w); v[6] = f.x; v[7] = f.y;
+}
+__device__ __forceinline__ uint4 pack8(const float (&v)[8]) {
+  uint4 r;
+  r.x = float2_to_bf16x2(v[0], v[1]); r.y = float2_to_bf16x2(v[2], v[3]);
+  r.z = float2_to_bf16x2(v[4], v[5]); r.w = float2_to_bf16x2(v[6], v[7]);
+  return r;
+}
+
+// Rows that live in a peer GPU's memory (expert parallelism over NVLink, ep_p2p.cu): every rank maps the arenas of all
+// ranks (symmetric allocation); a row is named by dest = rank * rows_cap + row inside that rank's buffer.
+struct PeerRows {
+  const unsigned char* const* peers;   // device array [W] of arena base addresses (as mapped on this GPU); NULL = local
+  long long off_bytes;                 // offset of the buffer inside every arena
+  const int32_t* dest_of_row;          // [send rows] -> rank * rows_cap + row
+  int rows_cap;                        // rows of the buffer on every rank
+};
+__device__ __forceinline__ __nv_bfloat16* peer_row(const PeerRows& pr, int dest, int d) {
+  const int w = dest / pr.rows_cap, row = dest - w * pr.rows_cap;
+  return reinterpret_cast<__nv_bfloat16*>(const_cast<unsigned char*>(pr.peers[w]) + pr.off_bytes) +
+         static_cast<size_t>(row) * d;
+}
+
 // erf-GELU (hybrid_encoder.py:157 with utils.py:160-161 -> nn.GELU()) for the GEMM epilogues.
 // The epilogue has ~16 issue slots per output element before it, not the tensor pipe, bounds the up-projection
 // (DESIGN.md), and erff() alone costs ~25.  Phi(x) = 0.5 (1 + erf(x / sqrt 2)) is evaluated as

@@ -8,20 +8,6 @@ namespace b200moe {
 constexpr int kMoveWarps = 8;
 constexpr int kMoveThreads = kMoveWarps * 32;
 
-__device__ __forceinline__ void unpack8(const uint4& r, float (&v)[8]) {
-  float2 f;
-  f = bf16x2_to_float2(r.x); v[0] = f.x; v[1] = f.y;
-  f = bf16x2_to_float2(r.y); v[2] = f.x; v[3] = f.y;
-  f = bf16x2_to_float2(r.z); v[4] = f.x; v[5] = f.y;
-  f = bf16x2_to_float2(r.w); v[6] = f.x; v[7] = f.y;
-}
-__device__ __forceinline__ uint4 pack8(const float (&v)[8]) {
-  uint4 r;
-  r.x = float2_to_bf16x2(v[0], v[1]); r.y = float2_to_bf16x2(v[2], v[3]);
-  r.z = float2_to_bf16x2(v[4], v[5]); r.w = float2_to_bf16x2(v[6], v[7]);
-  return r;
-}
-
 // xp[r] = x[token_of_row[r]] or 0
 __global__ void __launch_bounds__(kMoveThreads)
 permute_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ token_of_row,
@@ -130,7 +116,7 @@ template <int TT>
 __global__ void __launch_bounds__(256)
 unpermute_bwd_kernel(const __nv_bfloat16* __restrict__ dxp, const int32_t* __restrict__ row_of_assignment,
                      const float* __restrict__ dlogits, const float* __restrict__ wg, int T, int k, int d, int E,
-                     __nv_bfloat16* __restrict__ dx) {
+                     __nv_bfloat16* __restrict__ dx, const PeerRows pr) {
   constexpr int kTok = 8 * TT;         // tokens per block
   pdl_sync();
   extern __shared__ __align__(16) float unp_s[];
@@ -147,7 +133,7 @@ unpermute_bwd_kernel(const __nv_bfloat16* __restrict__ dxp, const int32_t* __res
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[tt][j] = 0.f;
   // gathers first (independent of the router part): all loads of up to 4 tokens in flight at once
-  if (dxp) {
+  if (dxp || pr.peers) {
 #pragma unroll
     for (int h = 0; h < TT; h += 4) {
       constexpr int kG = TT < 4 ? TT : 4;
@@ -156,8 +142,14 @@ unpermute_bwd_kernel(const __nv_bfloat16* __restrict__ dxp, const int32_t* __res
 #pragma unroll
         for (int q = 0; q < kG; ++q) {
           const int t = t0 + warp * TT + h + q;
-          const int r = t < T ? row_of_assignment[static_cast<size_t>(t) * k + s] : -1;
-          const __nv_bfloat16* src = dxp + static_cast<size_t>(r < 0 ? 0 : r) * d;
+          int r = t < T ? row_of_assignment[static_cast<size_t>(t) * k + s] : -1;
+          const __nv_bfloat16* src;
+          if (pr.peers) {                 // expert parallelism: the row lives on the expert's rank (ep_p2p.cu)
+            r = r >= 0 ? pr.dest_of_row[r] : -1;
+            src = r >= 0 ? peer_row(pr, r, d) : nullptr;
+          } else {
+            src = dxp + static_cast<size_t>(r < 0 ? 0 : r) * d;
+          }
           va[q] = r >= 0 ? __ldg(reinterpret_cast<const uint2*>(src + c0)) : make_uint2(0, 0);
           vb[q] = (r >= 0 && has1) ? __ldg(reinterpret_cast<const uint2*>(src + c1)) : make_uint2(0, 0);
         }
@@ -556,8 +548,10 @@ extern "C" int b200moe_combine_bwd(const void* dy, const void* yo, const int32_t
   return check_launch("combine_bwd");
 }
 
-extern "C" int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assignment, const float* dlogits,
-                                     const float* wg, int T, int k, int d, int E, void* dx, void* stream) {
+static int unpermute_bwd_impl(const void* dxp, const b200moe::PeerRows& pr, const int32_t* row_of_assignment,
+                              const float* dlogits, const float* wg, int T, int k, int d, int E, void* dx,
+                              void* stream) {
+  using namespace b200moe;
   B200MOE_REQUIRE(d > 0 && d % 128 == 0, B200MOE_EINVAL, "unpermute_bwd: d=%d must be a multiple of 128", d);
   B200MOE_REQUIRE(E >= 1 && E <= 64, B200MOE_EINVAL, "unpermute_bwd: num_experts=%d outside [1,64]", E);
   B200MOE_REQUIRE(dlogits == nullptr || wg != nullptr, B200MOE_EINVAL, "unpermute_bwd: dlogits without wg");
@@ -576,10 +570,25 @@ extern "C" int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assi
   }
   dim3 grid((T + tok - 1) / tok, (d + 255) / 256);
   if (big)
-    launch_k(unpermute_bwd_kernel<8>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx));
+    launch_k(unpermute_bwd_kernel<8>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx), pr);
   else
-    launch_k(unpermute_bwd_kernel<2>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx));
+    launch_k(unpermute_bwd_kernel<2>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx), pr);
   return check_launch("unpermute_bwd");
+}
+
+extern "C" int b200moe_unpermute_bwd(const void* dxp, const int32_t* row_of_assignment, const float* dlogits,
+                                     const float* wg, int T, int k, int d, int E, void* dx, void* stream) {
+  return unpermute_bwd_impl(dxp, b200moe::PeerRows{nullptr, 0, nullptr, 1}, row_of_assignment, dlogits, wg, T, k, d, E,
+                            dx, stream);
+}
+
+extern "C" int b200moe_ep_p2p_unpermute_bwd(const void* const* peers, int64_t buf_offset_bytes, int rows_cap,
+                                            const int32_t* dest_of_row, const int32_t* row_of_assignment,
+                                            const float* dlogits, const float* wg, int T, int k, int d, int E,
+                                            void* dx, void* stream) {
+  B200MOE_REQUIRE(peers && dest_of_row && rows_cap > 0, B200MOE_EINVAL, "ep_p2p_unpermute_bwd: bad arguments");
+  b200moe::PeerRows pr{reinterpret_cast<const unsigned char* const*>(peers), buf_offset_bytes, dest_of_row, rows_cap};
+  return unpermute_bwd_impl(nullptr, pr, row_of_assignment, dlogits, wg, T, k, d, E, dx, stream);
 }
 
 extern "C" int b200moe_cast_f32_bf16(const float* src, void* dst, int64_t n, void* stream) {

@@ -30,11 +30,14 @@ def main():
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     ok = True
-    for (B, HW, d, F, E, k, cf) in [(2, 300, 256, 512, 8, 2, 1.0), (1, 777, 512, 1024, 16, 2, 1.25),
-                                    (2, 64, 128, 256, 2 * world, 1, 0.5), (4, 400, 256, 1024, 8, 2, None)]:
+    cases = [(2, 300, 256, 512, 8, 2, 1.0), (1, 777, 512, 1024, 16, 2, 1.25), (2, 64, 128, 256, 2 * world, 1, 0.5),
+             (4, 400, 256, 1024, 8, 2, None)]
+    # every case over peer memory (the default where available; cf=None has no row bound and uses NCCL) and over NCCL
+    for (B, HW, d, F, E, k, cf), p2p in [(c, m) for c in cases for m in (None, False)]:
         vs = (6, 10, 4, 6, 4)
         torch.manual_seed(7)
-        m_ep = b200moe.ContextMoE(d, F, E, k, cf, context_vocab_sizes=vs, ep_group=dist.group.WORLD).to(dev)
+        m_ep = b200moe.ContextMoE(d, F, E, k, cf, context_vocab_sizes=vs, ep_group=dist.group.WORLD,
+                                  ep_p2p=p2p).to(dev)
         torch.manual_seed(7)
         m_1 = b200moe.ContextMoE(d, F, E, k, cf, context_vocab_sizes=vs).to(dev)
         with torch.no_grad():                                       # skew the router so that capacity bites
@@ -46,10 +49,13 @@ def main():
         c_all = torch.stack([torch.randint(0, v, (world * B,), generator=g) for v in vs], 1).to(dev)
         sl = slice(rank * B, (rank + 1) * B)
 
-        x = x_all[sl].clone().requires_grad_(True)
-        y = m_ep(x, c_all[sl])
-        y.backward(go_all[sl])
+        for _ in range(2):                                          # twice: the second pass reuses the peer arena
+            m_ep.zero_grad(set_to_none=True)
+            x = x_all[sl].clone().requires_grad_(True)
+            y = m_ep(x, c_all[sl])
+            y.backward(go_all[sl])
         a_ep = dict(m_ep.last_aux)
+        path = "p2p" if "_p2p_arena" in m_ep.__dict__ else "nccl"
 
         x1 = x_all.clone().requires_grad_(True)
         y1 = m_1(x1, c_all)
@@ -78,7 +84,7 @@ def main():
         dist.all_reduce(dcp)
         checks["dctx_proj (sum over ranks)"] = rel(dcp, m_1.ctx_proj.weight.grad) < 2e-2
         bad = [n for n, v in checks.items() if not v]
-        print(f"[rank {rank}] B={B} HW={HW} d={d} F={F} E={E} k={k} cf={cf}: dropped(ep local)={int(a_ep['dropped'])} "
+        print(f"[rank {rank}] {path} B={B} HW={HW} d={d} F={F} E={E} k={k} cf={cf}: dropped(ep local)={int(a_ep['dropped'])} "
               f"dropped(1gpu)={int(a_1['dropped'])} rel_y={rel(y, y1[sl]):.2e} rel_dx={rel(x.grad, x1.grad[sl]):.2e} "
               f"{'OK' if not bad else 'FAILED ' + str(bad)}", flush=True)
         ok = ok and not bad
