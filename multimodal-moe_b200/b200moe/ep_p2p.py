@@ -27,6 +27,22 @@ from . import _lib, ops
 _BIG = 1 << 30
 
 
+def p2p_layout(kept: torch.Tensor, rank: int, row_pad: int = 128):
+    """Host twin of b200moe_ep_p2p_tables (pure integer logic, pinned on CPU with gloo and against the kernel on GPU).
+    kept [W,E]: rows every rank sends to every expert.  Returns (dest_off [E]: first row, inside the buffer of rank
+    e // E_local, of `rank`'s rows for expert e; expert_offsets [W, E_local+1]: the padded segments of every rank)."""
+    W, E = kept.shape
+    EL = E // W
+    kept = kept.to(torch.int64)
+    tot = kept.sum(0)
+    seg = ((tot + row_pad - 1) // row_pad * row_pad).view(W, EL)
+    start = seg.cumsum(1) - seg                                  # [W,EL] first row of a local expert on its rank
+    before = kept.cumsum(0) - kept                               # [W,E] rows of the lower ranks (rank-major in an expert)
+    dest_off = start.reshape(E) + before[rank]
+    offsets = torch.cat([start, seg.sum(1, keepdim=True)], 1)
+    return dest_off.to(torch.int32), offsets.to(torch.int32)
+
+
 class P2PUnavailable(RuntimeError):
     pass
 

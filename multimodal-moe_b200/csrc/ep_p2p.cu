@@ -23,7 +23,8 @@ constexpr int kP2pThreads = kP2pWarps * 32;
 //   dest_off[e]       : first row, inside the buffer of rank e / EL, of the rows THIS rank sends to expert e
 //                       (segment of expert e on its rank + rows of the lower ranks: rank-major inside an expert)
 //   expert_offsets[j] : this rank's own padded segments (local expert j), meta / tile_expert as b200moe_plan writes them
-//   meta[5] = 1 if some rank's rows do not fit rows_cap (the pass is then invalid; the host checks the flag lazily)
+//   meta[5] = 1 if some rank's rows do not fit rows_cap (cannot happen while every rank stays within the token count the
+//   arena was sized for -- the host enforces that; rows beyond rows_cap are never stored, the flag is the evidence)
 __global__ void __launch_bounds__(64)
 ep_p2p_tables_kernel(const int32_t* __restrict__ kept, int W, int E, int rank, int rows_cap,
                      int32_t* __restrict__ dest_off, int32_t* __restrict__ expert_offsets, int32_t* __restrict__ meta,

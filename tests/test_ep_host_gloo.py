@@ -111,3 +111,68 @@ def test_split_sizes_numpy_twin():
             send, recv, _, _ = split_sizes(kept, rank, W, C)
             send_np, recv_np = split_sizes_np(kept.numpy(), rank, W, C)
             assert send == send_np and recv == recv_np
+
+
+def _p2p_worker(rank, world, port, T, E, k, cf, out):
+    """Peer-memory dispatch on CPU: the 'stores into the expert rank's buffer' are emulated by gathering
+    (destination rank, destination row, payload) triples; the layout must be a bijection onto the unpadded part of
+    every expert segment, in global priority order (rank-major inside an expert)."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from b200moe import ep, ep_p2p
+        g = torch.Generator().manual_seed(200 + rank)
+        logits = torch.randn(T, E, generator=g)
+        logits[:, 1] += 1.0
+        _, idx, _ = R.route(logits, k)
+        hist = torch.stack([torch.bincount(idx[:, s], minlength=E) for s in range(k)]).to(torch.int32)
+        mine = torch.cat([hist.reshape(-1), torch.tensor([T], dtype=torch.int32)])
+        allh = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allh, mine)
+        allh = torch.stack(allh)
+        goff, cap, kept = ep.route_tables(allh[:, :-1].reshape(world, k, E), allh[:, -1], rank, cf, k)
+        dest_off, offsets = ep_p2p.p2p_layout(kept, rank)
+        EL = E // world
+        _, keep = R.assign_slots(idx, E, cap, global_offset=goff.long())
+        offs, kept_l, soa, tor = R.permutation(idx, keep, E, pad_to=1)          # send order: experts back to back
+        triples = []
+        for e in range(E):
+            seg = tor[int(offs[e]):int(offs[e + 1])]
+            for i, t in enumerate(seg.tolist()):
+                triples.append((e // EL, int(dest_off[e]) + i, rank * T + t, e))
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (triples, offsets.tolist(), kept.tolist()))
+        if rank == 0:
+            for g_ in gathered:
+                assert g_[1] == gathered[0][1] and g_[2] == gathered[0][2]      # every rank derived the same layout
+            offsets_all, kept_all = torch.tensor(gathered[0][1]), torch.tensor(gathered[0][2])
+            tot = kept_all.sum(0)
+            for w in range(world):
+                rows = sorted((row, tok, e) for g_ in gathered for (dw, row, tok, e) in g_[0] if dw == w)
+                want_rows = [r_ for j in range(EL) for r_ in range(int(offsets_all[w, j]),
+                                                                   int(offsets_all[w, j]) + int(tot[w * EL + j]))]
+                assert [r_[0] for r_ in rows] == want_rows                       # bijection onto the unpadded rows
+                for row, tok, e in rows:
+                    j = e - w * EL
+                    assert int(offsets_all[w, j]) <= row < int(offsets_all[w, j + 1])
+                for j in range(EL):                                              # rank-major inside an expert
+                    toks = [tok // T for row, tok, e in rows if e == w * EL + j]
+                    assert toks == sorted(toks)
+                assert int(offsets_all[w, EL]) % 128 == 0
+            out.put("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("T,E,k,cf", [(257, 8, 2, 1.0), (64, 4, 1, 0.5), (300, 16, 2, 1.25)])
+def test_p2p_layout_world2(T, E, k, cf):
+    ctx = mp.get_context("spawn")
+    out = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_p2p_worker, args=(r, 2, port, T, E, k, cf, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert out.get() == "ok"
