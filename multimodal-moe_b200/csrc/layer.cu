@@ -132,34 +132,37 @@ ctx_bias_fwd_kernel(const int64_t* __restrict__ context, const CtxTables tb, int
 }
 
 // dwc[e, i] = sum_b dctx[b,e] * emb_b[i];  dtable_f[v, j] = sum_{b: ctx[b,f]=v} sum_e dctx[b,e] * wc[e, f*cd+j]
-// One thread per output element, images in increasing order (deterministic).
+// One warp per output element: the lanes stride the images, then a fixed shuffle tree (deterministic).
 __global__ void __launch_bounds__(256)
 ctx_bias_bwd_kernel(const int64_t* __restrict__ context, const float* __restrict__ dctx, const CtxTables tb, int n,
                     int cd, const float* __restrict__ wc, int B, int E, float* __restrict__ dwc, int n_dwc,
                     int n_tab) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
   if (i < n_dwc) {
     const int e = i / (n * cd), c = i - e * (n * cd);
     const int f = c / cd, j = c - f * cd;
     float s = 0.f;
-    for (int b = 0; b < B; ++b) {
+    for (int b = lane; b < B; b += 32) {
       const long long id = context[static_cast<size_t>(b) * n + f];
       if (id >= 0 && id < tb.vocab[f]) s = fmaf(dctx[static_cast<size_t>(b) * E + e], tb.table[f][static_cast<size_t>(id) * cd + j], s);
     }
-    dwc[i] = s;
+    s = warp_sum(s);
+    if (lane == 0) dwc[i] = s;
   } else if (i < n_dwc + n_tab) {
     int r = i - n_dwc;
     int f = 0;
     while (r >= tb.vocab[f] * cd) { r -= tb.vocab[f] * cd; ++f; }
     const int v = r / cd, j = r - v * cd;
     float s = 0.f;
-    for (int b = 0; b < B; ++b) {
+    for (int b = lane; b < B; b += 32) {
       if (context[static_cast<size_t>(b) * n + f] != v) continue;
       float g = 0.f;
       for (int e = 0; e < E; ++e) g = fmaf(dctx[static_cast<size_t>(b) * E + e], wc[static_cast<size_t>(e) * n * cd + f * cd + j], g);
       s += g;
     }
-    tb.dtable[f][r] = s;
+    s = warp_sum(s);
+    if (lane == 0) tb.dtable[f][r] = s;
   }
 }
 
@@ -206,7 +209,7 @@ extern "C" int b200moe_ctx_bias_bwd(const int64_t* context, const float* dctx_bi
   for (int i = 0; i < n_fields; ++i) n_tab += vocab[i] * context_dim;
   const int n_dwc = E * n_fields * context_dim;
   const int total = n_dwc + n_tab;
-  ctx_bias_bwd_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  ctx_bias_bwd_kernel<<<(total + 7) / 8, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       context, dctx_bias, tb, n_fields, context_dim, wc, B, E, dwc, n_dwc, n_tab);
   return check_launch("ctx_bias_bwd");
 }

@@ -159,12 +159,35 @@ __global__ void __launch_bounds__(kRouterTokPerBlock)
 plan_assign_kernel(const int32_t* __restrict__ topk_idx, const float* __restrict__ topk_gate,
                    const int32_t* __restrict__ block_base, const int32_t* __restrict__ slot_limit, int T, int k,
                    int E, int32_t* __restrict__ row_of_assignment, int32_t* __restrict__ token_of_row,
-                   float* __restrict__ gate_of_row) {
+                   float* __restrict__ gate_of_row, const int32_t* __restrict__ expert_offsets,
+                   const int32_t* __restrict__ kept_per_expert, const int32_t* __restrict__ expert_order,
+                   int rows_cap) {
   __shared__ int wc[kRouterTokPerBlock / 32][64];
+  __shared__ int off_s[65], end_s[64];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = t < T;
   pdl_sync();
+  // pad rows (rows no assignment lands on) are marked here, a slice per block: no memset launches before the plan
+  for (int i = threadIdx.x; i <= E; i += blockDim.x) off_s[i] = expert_offsets[i];
+  for (int e = threadIdx.x; e < E; e += blockDim.x) {
+    const int pos = expert_order ? expert_order[e] : e;
+    end_s[pos] = expert_offsets[pos] + kept_per_expert[e];
+  }
+  __syncthreads();
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows_cap; r += gridDim.x * blockDim.x) {
+    bool pad = r >= off_s[E];
+    if (!pad) {
+      int lo = 0, hi = E;
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (off_s[mid] <= r) lo = mid; else hi = mid;
+      }
+      while (lo + 1 < E && off_s[lo + 1] <= r) ++lo;     // skip empty segments that start at the same row
+      pad = r >= end_s[lo];
+    }
+    if (pad) { token_of_row[r] = -1; gate_of_row[r] = 0.f; }
+  }
   for (int s = 0; s < k; ++s) {
     for (int i = threadIdx.x; i < (kRouterTokPerBlock / 32) * 64; i += blockDim.x) (&wc[0][0])[i] = 0;
     __syncthreads();
@@ -375,17 +398,12 @@ extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int
              row_of_assignment, token_of_row, gate_of_row);
     return check_launch("plan_fused");
   }
-  const bool init_in_kernel = rows_cap <= 16 * 1024;
-  if (!init_in_kernel) {
-    cudaMemsetAsync(token_of_row, 0xFF, sizeof(int32_t) * static_cast<size_t>(rows_cap), st);
-    cudaMemsetAsync(gate_of_row, 0, sizeof(float) * static_cast<size_t>(rows_cap), st);
-  }
   launch_k(plan_scan_kernel, 1, kScanThreads, 0, st, block_counts, block_stats, nblk, T, k, E, capacity, global_offset,
            expert_order, row_pad, rows_cap, aux_loss_weight, z_loss_weight, expert_offsets, meta, tile_expert,
-           tokens_per_expert, kept_per_expert, losses, slot_limit, token_of_row, gate_of_row,
-           init_in_kernel ? rows_cap : 0);
+           tokens_per_expert, kept_per_expert, losses, slot_limit, token_of_row, gate_of_row, 0);
   if (int rc = check_launch("plan_scan")) return rc;
   launch_k(plan_assign_kernel, nblk, tb, 0, st, topk_idx, topk_gate, block_counts, slot_limit, T, k, E,
-           row_of_assignment, token_of_row, gate_of_row);
+           row_of_assignment, token_of_row, gate_of_row, static_cast<const int32_t*>(expert_offsets),
+           static_cast<const int32_t*>(kept_per_expert), expert_order, rows_cap);
   return check_launch("plan_assign");
 }
