@@ -112,7 +112,7 @@ combine_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
 // 256 contiguous bytes per warp access in global memory), so every wg value read from shared memory feeds 8 FMAs
 // per token x 8 tokens.  The k gathered rows of dxp are added in slot order in fp32.
 // TT = tokens per warp (8 for large batches; 2 for small ones so that the grid still covers the SMs).
-template <int TT>
+template <int TT, bool P2P>
 __global__ void __launch_bounds__(256)
 unpermute_bwd_kernel(const __nv_bfloat16* __restrict__ dxp, const int32_t* __restrict__ row_of_assignment,
                      const float* __restrict__ dlogits, const float* __restrict__ wg, int T, int k, int d, int E,
@@ -133,7 +133,7 @@ unpermute_bwd_kernel(const __nv_bfloat16* __restrict__ dxp, const int32_t* __res
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[tt][j] = 0.f;
   // gathers first (independent of the router part): all loads of up to 4 tokens in flight at once
-  if (dxp || pr.peers) {
+  if (P2P || dxp) {
 #pragma unroll
     for (int h = 0; h < TT; h += 4) {
       constexpr int kG = TT < 4 ? TT : 4;
@@ -144,7 +144,7 @@ unpermute_bwd_kernel(const __nv_bfloat16* __restrict__ dxp, const int32_t* __res
           const int t = t0 + warp * TT + h + q;
           int r = t < T ? row_of_assignment[static_cast<size_t>(t) * k + s] : -1;
           const __nv_bfloat16* src;
-          if (pr.peers) {                 // expert parallelism: the row lives on the expert's rank (ep_p2p.cu)
+          if (P2P) {                      // expert parallelism: the row lives on the expert's rank (ep_p2p.cu)
             r = r >= 0 ? pr.dest_of_row[r] : -1;
             src = r >= 0 ? peer_row(pr, r, d) : nullptr;
           } else {
@@ -563,16 +563,24 @@ static int unpermute_bwd_impl(const void* dxp, const b200moe::PeerRows& pr, cons
   static bool configured = false;
   if (!configured) {
     const int mx = static_cast<int>(sizeof(float) * (64 * 256 + 64 * 64));
-    cudaError_t e1 = cudaFuncSetAttribute(unpermute_bwd_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
-    cudaError_t e2 = cudaFuncSetAttribute(unpermute_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
-    B200MOE_REQUIRE(e1 == cudaSuccess && e2 == cudaSuccess, B200MOE_ECUDA, "unpermute_bwd: cudaFuncSetAttribute failed");
+    cudaError_t e1 = cudaFuncSetAttribute(unpermute_bwd_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    cudaError_t e2 = cudaFuncSetAttribute(unpermute_bwd_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    cudaError_t e3 = cudaFuncSetAttribute(unpermute_bwd_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    cudaError_t e4 = cudaFuncSetAttribute(unpermute_bwd_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    B200MOE_REQUIRE(e1 == cudaSuccess && e2 == cudaSuccess && e3 == cudaSuccess && e4 == cudaSuccess, B200MOE_ECUDA,
+                    "unpermute_bwd: cudaFuncSetAttribute failed");
     configured = true;
   }
   dim3 grid((T + tok - 1) / tok, (d + 255) / 256);
-  if (big)
-    launch_k(unpermute_bwd_kernel<8>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx), pr);
-  else
-    launch_k(unpermute_bwd_kernel<2>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, d, E, BFW(dx), pr);
+  const bool p2p = pr.peers != nullptr;
+#define UNP_LAUNCH(TT_, P_)                                                                                          \
+  launch_k(unpermute_bwd_kernel<TT_, P_>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, \
+           d, E, BFW(dx), pr)
+  if (big && p2p) UNP_LAUNCH(8, true);
+  else if (big) UNP_LAUNCH(8, false);
+  else if (p2p) UNP_LAUNCH(2, true);
+  else UNP_LAUNCH(2, false);
+#undef UNP_LAUNCH
   return check_launch("unpermute_bwd");
 }
 

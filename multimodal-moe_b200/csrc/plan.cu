@@ -20,62 +20,84 @@ plan_scan_kernel(int32_t* __restrict__ block_counts, const float* __restrict__ b
                  int32_t* __restrict__ expert_offsets, int32_t* __restrict__ meta, int32_t* __restrict__ tile_expert,
                  int32_t* __restrict__ tokens_per_expert, int32_t* __restrict__ kept_per_expert,
                  float* __restrict__ losses, int32_t* __restrict__ slot_limit, int32_t* __restrict__ token_of_row,
-                 float* __restrict__ gate_of_row, int init_rows) {
+                 float* __restrict__ gate_of_row) {
   __shared__ int total_s[8 * 64];      // [k][E] assignments per (slot, expert) on this rank
   __shared__ int rowbase_s[8 * 64];    // [k][E] first row (relative to the expert segment) of slot s
   __shared__ int keptslot_s[8 * 64];
   __shared__ int kept_s[64], count_s[64], off_s[65], expert_at_s[64];
   __shared__ float P_s[65];
+  __shared__ float scan_s[(kScanThreads / 32) * 32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = kScanThreads / 32;
   const int kE = k * E;
   pdl_sync();
 
-  // row maps start as "pad" (small buffers only; the host issues memsets for large ones)
-  for (int i = threadIdx.x; i < init_rows; i += blockDim.x) { token_of_row[i] = -1; gate_of_row[i] = 0.f; }
-
-  // phase 1: exclusive scan over the router blocks for every (slot, expert) sequence; a warp takes one sequence and
-  // loads up to 8 x 32 counts before it starts scanning, so the global-memory latency is paid once per 256 blocks
-  for (int q = warp; q < kE; q += nwarps) {
-    int run = 0;
-    for (int b0 = 0; b0 < nblk; b0 += 256) {
-      int v[8];
+  // phase 1: exclusive scan over the router blocks for every (slot, expert) column.  Lanes run along the columns (one
+  // 128-byte line per block and warp: a lane-per-block layout made every load and store touch 32 lines and the one
+  // SM's load/store unit, not memory latency, set the time: 30 us at 512 blocks), the 32 warps split the blocks into
+  // contiguous chunks: chunk sums -> shared memory -> prefix over the chunks -> second pass writes the bases.
+  {
+    int* chunk_s = reinterpret_cast<int*>(scan_s);                 // [nwarps][32]
+    const int ch = (nblk + nwarps - 1) / nwarps;
+    const int b_lo = warp * ch, b_hi = (b_lo + ch < nblk) ? b_lo + ch : nblk;
+    for (int q0 = 0; q0 < kE; q0 += 32) {
+      const int q = q0 + lane;
+      const bool on = q < kE;
+      int sum = 0;
+      for (int b0 = b_lo; b0 < b_hi; b0 += 8) {
+        int v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int b = b0 + u * 32 + lane;
-        v[u] = (b < nblk) ? block_counts[static_cast<size_t>(b) * kE + q] : 0;
+        for (int u = 0; u < 8; ++u) v[u] = (on && b0 + u < b_hi) ? block_counts[static_cast<size_t>(b0 + u) * kE + q] : 0;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) sum += v[u];
       }
+      chunk_s[warp * 32 + lane] = sum;
+      __syncthreads();
+      int run = 0, tot = 0;
+      for (int w = 0; w < nwarps; ++w) {
+        const int c = chunk_s[w * 32 + lane];
+        run += (w < warp) ? c : 0;
+        tot += c;
+      }
+      if (warp == 0 && on) total_s[q] = tot;
+      for (int b0 = b_lo; b0 < b_hi; b0 += 8) {
+        int v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int b = b0 + u * 32 + lane;
-        int inc = v[u];
+        for (int u = 0; u < 8; ++u) v[u] = (on && b0 + u < b_hi) ? block_counts[static_cast<size_t>(b0 + u) * kE + q] : 0;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-          const int n = __shfl_up_sync(0xffffffffu, inc, o);
-          if (lane >= o) inc += n;
+        for (int u = 0; u < 8; ++u) {
+          if (on && b0 + u < b_hi) block_counts[static_cast<size_t>(b0 + u) * kE + q] = run;
+          run += v[u];
         }
-        if (b < nblk) block_counts[static_cast<size_t>(b) * kE + q] = run + inc - v[u];
-        run += __shfl_sync(0xffffffffu, inc, 31);
       }
+      __syncthreads();
     }
-    if (lane == 0) total_s[q] = run;
   }
-  // loss statistics: one warp per column of block_stats, lanes stride the blocks (8 loads in flight), fixed order
-  for (int e = warp; e <= E; e += nwarps) {
-    float s = 0.f;
-    for (int b0 = 0; b0 < nblk; b0 += 256) {
-      float v[8];
+  // loss statistics: lanes along the columns of block_stats, warps split the blocks, then the chunks in a fixed order
+  {
+    float* fchunk_s = scan_s;                                       // [nwarps][32]
+    const int ch = (nblk + nwarps - 1) / nwarps;
+    const int b_lo = warp * ch, b_hi = (b_lo + ch < nblk) ? b_lo + ch : nblk;
+    for (int e0 = 0; e0 <= E; e0 += 32) {
+      const int e = e0 + lane;
+      const bool on = e <= E;
+      float sum = 0.f;
+      for (int b0 = b_lo; b0 < b_hi; b0 += 8) {
+        float v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int b = b0 + u * 32 + lane;
-        v[u] = (b < nblk) ? block_stats[static_cast<size_t>(b) * (E + 1) + e] : 0.f;
+        for (int u = 0; u < 8; ++u) v[u] = (on && b0 + u < b_hi) ? block_stats[static_cast<size_t>(b0 + u) * (E + 1) + e] : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) sum += v[u];
       }
-#pragma unroll
-      for (int u = 0; u < 8; ++u) s += v[u];
+      fchunk_s[warp * 32 + lane] = sum;
+      __syncthreads();
+      if (warp == 0 && on) {
+        float s = 0.f;
+        for (int w = 0; w < nwarps; ++w) s += fchunk_s[w * 32 + lane];
+        P_s[e] = s;
+      }
+      __syncthreads();
     }
-    s = warp_sum(s);
-    if (lane == 0) P_s[e] = s;
   }
-  __syncthreads();
 
   // phase 2: per expert, slot bases against the capacity
   if (threadIdx.x < E) {
@@ -248,7 +270,7 @@ plan_fused_kernel(const int32_t* __restrict__ topk_idx, const float* __restrict_
     total_s[q] = tot;
     base_s[q] = base;
   }
-  if (lead) {   // loss statistics, summed in the order plan_scan_kernel uses
+  if (lead) {   // loss statistics: one warp per column, lanes stride the blocks, fixed order
     for (int e = warp; e <= E; e += nwarps) {
       float s = 0.f;
       for (int b0 = 0; b0 < nblk; b0 += 256) {
@@ -400,7 +422,7 @@ extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int
   }
   launch_k(plan_scan_kernel, 1, kScanThreads, 0, st, block_counts, block_stats, nblk, T, k, E, capacity, global_offset,
            expert_order, row_pad, rows_cap, aux_loss_weight, z_loss_weight, expert_offsets, meta, tile_expert,
-           tokens_per_expert, kept_per_expert, losses, slot_limit, token_of_row, gate_of_row, 0);
+           tokens_per_expert, kept_per_expert, losses, slot_limit, token_of_row, gate_of_row);
   if (int rc = check_launch("plan_scan")) return rc;
   launch_k(plan_assign_kernel, nblk, tb, 0, st, topk_idx, topk_gate, block_counts, slot_limit, T, k, E,
            row_of_assignment, token_of_row, gate_of_row, static_cast<const int32_t*>(expert_offsets),

@@ -71,7 +71,7 @@ def test_router_all_ties_pick_lowest_index(ops):
 
 @pytest.mark.parametrize("T,E,k,cf", [(3200, 8, 2, None), (3200, 8, 2, 1.25), (1000, 16, 2, 0.5), (777, 64, 2, 1.0),
                                       (130, 4, 1, 0.25), (5000, 8, 3, 1.25), (128, 8, 2, 1.25), (1, 8, 2, None),
-                                      (40000, 8, 2, 1.25), (20000, 16, 2, 1.0)])
+                                      (40000, 8, 2, 1.25), (20000, 16, 2, 1.0), (9000, 64, 4, 1.0), (8321, 40, 3, 0.75)])
 def test_plan_matches_oracle(ops, T, E, k, cf):
     d = 256
     x, wg = _mk(T, d, E, seed=7 + T)
