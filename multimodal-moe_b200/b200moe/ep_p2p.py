@@ -76,7 +76,17 @@ class _Arena:
 def arena_for(mod, T: int, dev) -> _Arena:
     a = mod.__dict__.get("_p2p_arena")
     if a is None:
-        a = mod.__dict__["_p2p_arena"] = _Arena(mod, mod.ep_group, T, dev)
+        # every rank must take the same transport: agree on the outcome of the (collective) set-up
+        err = None
+        try:
+            a = _Arena(mod, mod.ep_group, T, dev)
+        except Exception as e:  # noqa: BLE001
+            err = e
+        ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=mod.ep_group)
+        if int(ok.item()) == 0:
+            raise P2PUnavailable(f"peer-memory arena could not be set up on every rank: {err!r}")
+        mod.__dict__["_p2p_arena"] = a
     if T > a.T_cap:
         raise RuntimeError(f"expert-parallel peer-memory arena was sized for {a.T_cap} tokens per rank, got {T}; "
                            f"construct the layer with ep_p2p=False or call with the largest batch first")

@@ -55,7 +55,7 @@ struct SmemCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = (kStageBytes > 32768) ? 4 : 6;
   static constexpr int kOutBytes = 8 * 4096;                               // epilogue staging: 8 x 4 KB or 16 x 2 KB
-  static constexpr int kBarBytes = 256;
+  static constexpr int kBarBytes = 512;
   static constexpr int kTotal = kStages * kStageBytes + kOutBytes + kBarBytes + 1024;  // + alignment slack
 };
 
@@ -87,6 +87,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tfull_bar = empty_bar + kStages;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* ld_bar = reinterpret_cast<uint64_t*>(tmem_slot + 2);           // EPI_DGRAD_DOWN: one per epilogue warp
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta_rank = CTA2 ? cluster_ctarank() : 0u;
@@ -96,7 +97,9 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC0);
-    if (EPI == EPI_UP) tma_prefetch_desc(&tmC1);
+    if (EPI == EPI_UP || EPI == EPI_DGRAD_DOWN) tma_prefetch_desc(&tmC1);
+    if (EPI == EPI_DGRAD_DOWN)
+      for (int w = 0; w < kEpiWarps; ++w) mbar_init(&ld_bar[w], 1);
     for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], (CTA2 ? 2 : 1) * kEpiThreads); }
     fence_mbar_init();
@@ -229,25 +232,37 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     unsigned char* stg = stage_out + (warp - 2) * kStgBytes;
     int acc = 0;
     uint32_t acc_phase = 0;
+    uint32_t ld_phase = 0;
     for (int tile = worker; tile < total_tiles; tile += nworkers) {
       int e, m_tile, n_tile, krow0, kblocks;
       decode(tile, e, m_tile, n_tile, krow0, kblocks);
+      const int row0 = m_tile * BM + quarter * 32;                 // first of this warp's 32 output rows
+      const size_t grow = static_cast<size_t>(row0) + lane;        // this thread's output row
+      // EPI_DGRAD_DOWN: the pre-activation box of a chunk travels by TMA into this warp's staging box (the same box the
+      // result leaves from; a thread reads and writes only its own row of it).  Per-thread 16-byte loads of 64-byte row
+      // pieces cost 8 load instructions x 32 lines per chunk and kept the SM's load/store unit busy; the first box is
+      // requested before the wait for the accumulator.
+      if (EPI == EPI_DGRAD_DOWN && lane == 0) {
+        tma_store_wait_read0();
+        mbar_arrive_expect_tx(&ld_bar[warp - 2], kStgBytes);
+        tma_load_2d(stg, &tmC1, &ld_bar[warp - 2], n_tile * BN + cgroup * kChunksPerWarp * 32, row0);
+      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
-      const int row0 = m_tile * BM + quarter * 32;                 // first of this warp's 32 output rows
-      const size_t grow = static_cast<size_t>(row0) + lane;        // this thread's output row
 #pragma unroll 1
-      for (int c = cgroup * kChunksPerWarp; c < (cgroup + 1) * kChunksPerWarp; ++c) {
+      for (int cc = 0; cc < kChunksPerWarp; ++cc) {
+        const int c = cgroup * kChunksPerWarp + cc;
         const int col0 = n_tile * BN + c * 32;
         uint32_t v[32];
         tmem_ld32(taddr + c * 32, v);
         uint4 pr[4];
-        if (EPI == EPI_DGRAD_DOWN) {           // pre-activation row chunk (64 contiguous bytes), overlaps the TMEM load
-          const __nv_bfloat16* ap = args.aux + grow * args.N + col0;
+        if (EPI == EPI_DGRAD_DOWN) {
+          mbar_wait(&ld_bar[warp - 2], ld_phase);
+          ld_phase ^= 1;
+          const uint32_t swz_l = (lane >> 1) & 3;
 #pragma unroll
-          for (int j = 0; j < 4; ++j) pr[j] = __ldg(reinterpret_cast<const uint4*>(ap) + j);   // L1-allocating: the
-          // other half of the 128-byte line is this thread's next chunk
+          for (int j = 0; j < 4; ++j) pr[j] = *reinterpret_cast<const uint4*>(stg + lane * 64 + ((j ^ swz_l) << 4));
         }
         float4 bv[8];
         if (EPI == EPI_UP || EPI == EPI_DOWN) {
@@ -331,6 +346,11 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (lane == 0) {
             tma_store_2d(&tmC0, stg, col0, row0);
             tma_store_commit();
+            if (EPI == EPI_DGRAD_DOWN && cc + 1 < kChunksPerWarp) {   // next pre-activation box, once the store has read this one
+              tma_store_wait_read0();
+              mbar_arrive_expect_tx(&ld_bar[warp - 2], kStgBytes);
+              tma_load_2d(stg, &tmC1, &ld_bar[warp - 2], col0 + 32, row0);
+            }
           }
         }
       }
