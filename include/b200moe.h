@@ -195,7 +195,9 @@ int b200moe_scatter_rows(const void* in, const int32_t* src_of_row, const int32_
  *                        row_pad 1); writes dest_of_row [send_rows_cap] for the calls below.
  *   ep_p2p_combine     : y[t] = sum_s gate[t,s] * peers' yo[dest_of_row[row_of_assignment[t,s]]].
  *   ep_p2p_combine_bwd : peers' dyp[dest] = gate_of_row[r] * dy[token]; dgate_row[r] = <dy[token], peers' yo[dest]>.
- *   ep_p2p_unpermute_bwd: b200moe_unpermute_bwd with the dxp rows loaded from the peers.                        */
+ *   ep_p2p_unpermute_bwd: b200moe_unpermute_bwd with the dxp rows loaded from the peers.
+ *   ep_p2p_pull_rows   : out[r] = peers' buffer[dest_of_row[r]] for every send row (plain copy, no shared memory: runs
+ *                        next to the weight-gradient GEMMs on a side stream; b200moe_unpermute_bwd then reads `out`). */
 int b200moe_ep_p2p_tables(const int32_t* kept, int W, int E, int rank, int rows_cap, int32_t* dest_off,
                           int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert, void* stream);
 int b200moe_ep_p2p_zero_pads(const int32_t* kept, const int32_t* expert_offsets, int W, int E, int rank, int d,
@@ -211,6 +213,9 @@ int b200moe_ep_p2p_combine_bwd(const void* dy, const void* const* peers, int64_t
                                int64_t dyp_offset_bytes, int rows_cap, const int32_t* dest_of_row,
                                const int32_t* token_of_row, const float* gate_of_row, const int32_t* send_meta,
                                int send_rows_cap, int d, float* dgate_row, void* stream);
+int b200moe_ep_p2p_pull_rows(const void* const* peers, int64_t buf_offset_bytes, int rows_cap,
+                             const int32_t* dest_of_row, const int32_t* send_meta, int send_rows_cap, int d, void* out,
+                             void* stream);
 int b200moe_ep_p2p_unpermute_bwd(const void* const* peers, int64_t buf_offset_bytes, int rows_cap,
                                  const int32_t* dest_of_row, const int32_t* row_of_assignment, const float* dlogits,
                                  const float* wg, int T, int k, int d, int E, void* dx, void* stream);

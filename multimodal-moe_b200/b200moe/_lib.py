@@ -43,6 +43,7 @@ SIGNATURES = {
     "b200moe_ep_p2p_dispatch": [_P, _P, _P, _P, _P, _P, _L, _I, _I, _I, _I, _I, _P, _P],
     "b200moe_ep_p2p_combine": [_P, _L, _I, _P, _P, _P, _I, _I, _I, _P, _P],
     "b200moe_ep_p2p_combine_bwd": [_P, _P, _L, _L, _I, _P, _P, _P, _P, _I, _I, _P, _P],
+    "b200moe_ep_p2p_pull_rows": [_P, _L, _I, _P, _P, _I, _I, _P, _P],
     "b200moe_ep_p2p_unpermute_bwd": [_P, _L, _I, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
     "b200moe_layer_profile": [_I],
     "b200moe_layer_pdl": [_I],

@@ -12,8 +12,9 @@ Forward : router -> histogram all-gather -> ep_route_tables -> plan (send layout
           ep_p2p_dispatch (gather x rows, store them into the expert ranks' xp) -> barrier -> up -> down (into yo)
           -> barrier -> ep_p2p_combine (load the k rows of a token from the expert ranks' yo).
 Backward: ep_p2p_combine_bwd (store gate * dy into the expert ranks' dyp; load yo rows for the gate gradient) ->
-          router gradients (fill the wait) -> barrier -> dgrad_down -> dgrad_up (into dxp) -> weight gradients ->
-          barrier -> ep_p2p_unpermute_bwd (load dxp rows from the expert ranks).
+          router gradients (fill the wait) -> barrier -> dgrad_down -> dgrad_up (into dxp) ->
+          barrier -> ep_p2p_pull_rows on a side stream (copy the dxp rows home over NVLink) next to the weight
+          gradients on the main stream -> unpermute_bwd.
 Reuse of the arena across steps is ordered by the histogram all-gather of the next forward (every rank has finished
 the previous backward before any rank's all-gather completes).
 """
@@ -25,6 +26,13 @@ import torch.distributed as dist
 from . import _lib, ops
 
 _BIG = 1 << 30
+
+
+def _side_stream(mod, dev) -> torch.cuda.Stream:
+    s = mod.__dict__.get("_p2p_side")
+    if s is None or s.device != dev:
+        s = mod.__dict__["_p2p_side"] = torch.cuda.Stream(device=dev)
+    return s
 
 
 def p2p_layout(kept: torch.Tensor, rank: int, row_pad: int = 128):
@@ -186,8 +194,19 @@ class _P2PFunction(torch.autograd.Function):
                                           want_dctx=bool(ctx.has_ctx and need[1]))
         ar.barrier(2)                                   # every rank's dyp rows have landed
         dhpre = ops.ffn_dgrad_down(ar.dyp, w2b, pre, meta, tile_e)
+        comp = torch.cuda.current_stream()
+        dxs = None
         if need[0]:
             ops.ffn_dgrad_up(dhpre, w1b, meta, tile_e, out=ar.dxp)
+            ar.barrier(3)                               # every rank's dxp is complete
+            # the rows come home on a side stream (a plain copy kernel: no shared memory, so it runs on the SMs next to
+            # the persistent weight-gradient CTAs) while the tensor-bound kernels below keep the main stream busy
+            side = _side_stream(mod, dev)
+            side.wait_stream(comp)
+            dxs = torch.empty((send_cap, d), dtype=torch.bfloat16, device=dev)
+            with torch.cuda.stream(side):
+                _lib.call("b200moe_ep_p2p_pull_rows", ar.peers.data_ptr(), ar.off[3], R, dest_of_row.data_ptr(),
+                          p.meta.data_ptr(), send_cap, d, dxs.data_ptr(), side.cuda_stream)
         dw1 = torch.empty((EL, F, d), dtype=f32, device=dev) if need[3] else None
         db1 = torch.empty((EL, F), dtype=f32, device=dev) if need[4] else None
         dw2 = torch.empty((EL, d, F), dtype=f32, device=dev) if need[5] else None
@@ -203,11 +222,9 @@ class _P2PFunction(torch.autograd.Function):
         elif need[4]:
             ops.colsum(dhpre, offs, EL, out=db1)
         dx = None
-        ar.barrier(3)                                   # every rank's dxp is complete (and its reads of xp / dyp are queued)
         if need[0]:
-            dx = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
-            _lib.call("b200moe_ep_p2p_unpermute_bwd", ar.peers.data_ptr(), ar.off[3], R, dest_of_row.data_ptr(),
-                      p.row_of_assignment.data_ptr(), dlogits.data_ptr(), wgf.data_ptr(), T, k, d, E, dx.data_ptr(), st)
+            comp.wait_stream(side)
+            dx = ops.unpermute_bwd(dxs, p.row_of_assignment, dlogits, wgf, T, k, d)
         ar.pending = False
         t_w1, t_b1, t_w2, t_b2, t_wg = ctx.dtypes
 

@@ -313,7 +313,7 @@ class ContextMoE(nn.Module):
         new = self.__class__.__new__(self.__class__)
         memo[id(self)] = new
         for k_, v in self.__dict__.items():
-            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena"):
+            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side"):
                 continue
             if k_ in ("_wcache", "last_aux", "_plans"):
                 new.__dict__[k_] = {}
@@ -328,7 +328,7 @@ class ContextMoE(nn.Module):
     def __getstate__(self):
         s = dict(self.__dict__)
         s["_wcache"], s["last_aux"], s["aux_loss"], s["ep_group"], s["_plans"] = {}, {}, torch.zeros(()), None, {}
-        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena"):
+        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side"):
             s.pop(k_, None)
         return s
 

@@ -195,6 +195,25 @@ ep_p2p_combine_bwd_kernel(const __nv_bfloat16* __restrict__ dy, PeerRows yo, Pee
   }
 }
 
+// out[r] = peers' buffer[dest_of_row[r]]: the return trip of the input gradients as a plain row copy.  No shared memory
+// and few registers, so its blocks co-reside with the persistent weight-gradient GEMM CTAs: the NVLink transfer runs
+// under the tensor-bound kernels instead of after them.
+__global__ void __launch_bounds__(kP2pThreads)
+ep_p2p_pull_rows_kernel(PeerRows pr, const int32_t* __restrict__ send_meta, int d, __nv_bfloat16* __restrict__ out) {
+  const int R = send_meta[0];
+  const int nchunk = d >> 3, lane = threadIdx.x & 31;
+  for (int r = blockIdx.x * kP2pWarps + (threadIdx.x >> 5); r < R; r += gridDim.x * kP2pWarps) {
+    const int dest = pr.dest_of_row[r];
+    __nv_bfloat16* dst = out + static_cast<size_t>(r) * d;
+    if (dest < 0) {
+      for (int c = lane; c < nchunk; c += 32) stg128(dst + c * 8, make_uint4(0, 0, 0, 0));
+      continue;
+    }
+    const __nv_bfloat16* src = peer_row(pr, dest, d);
+    for (int c = lane; c < nchunk; c += 32) stg128(dst + c * 8, ldg128(src + c * 8));
+  }
+}
+
 static int p2p_grid(int rows) {
   int g = (rows + kP2pWarps - 1) / kP2pWarps;
   const int mx = kNumSMs * 8;
@@ -264,4 +283,15 @@ extern "C" int b200moe_ep_p2p_combine_bwd(const void* dy, const void* const* pee
   ep_p2p_combine_bwd_kernel<<<p2p_grid(send_rows_cap), kP2pThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), yo, dyp, token_of_row, gate_of_row, send_meta, d, dgate_row);
   return check_launch("ep_p2p_combine_bwd");
+}
+
+extern "C" int b200moe_ep_p2p_pull_rows(const void* const* peers, int64_t buf_offset_bytes, int rows_cap,
+                                        const int32_t* dest_of_row, const int32_t* send_meta, int send_rows_cap, int d,
+                                        void* out, void* stream) {
+  B200MOE_REQUIRE(peers && dest_of_row && out && d % 8 == 0, B200MOE_EINVAL, "ep_p2p_pull_rows: bad arguments");
+  if (int rc = b200moe_check_device()) return rc;
+  PeerRows pr{reinterpret_cast<const unsigned char* const*>(peers), buf_offset_bytes, dest_of_row, rows_cap};
+  ep_p2p_pull_rows_kernel<<<p2p_grid(send_rows_cap), kP2pThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      pr, send_meta, d, static_cast<__nv_bfloat16*>(out));
+  return check_launch("ep_p2p_pull_rows");
 }
