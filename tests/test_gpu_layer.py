@@ -200,3 +200,46 @@ def test_graphed_gradient_accumulation():
     for (n, p), q in zip(ref.named_parameters(), m.parameters()):
         if p.grad is not None:
             assert torch.allclose(p.grad, q.grad, rtol=1e-6, atol=1e-6), n
+
+
+def test_backward_fork_and_pdl_do_not_change_results():
+    """The side streams of b200moe_layer_bwd (weight / router gradients next to the dgrad chain) and programmatic
+    dependent launch reorder execution only: every output and gradient is bit-identical with both switched off."""
+    from b200moe import _lib
+    B, HW, d, F, E, k = 4, 333, 256, 512, 8, 2
+    _, m = _pair(d, F, E, k, 1.0, ctx=True, seed=21)
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(B, HW, d, generator=g).to(torch.bfloat16).cuda()
+    c = torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1).cuda()
+    go = torch.randn(B, HW, d, generator=g).cuda()
+    lib = _lib.load()
+    outs = []
+    try:
+        for fork, pdl in ((1, 1), (0, 0), (1, 0), (0, 1)):
+            lib.b200moe_layer_fork(fork)
+            lib.b200moe_layer_pdl(pdl)
+            m.zero_grad(set_to_none=True)
+            xg = x.clone().requires_grad_(True)
+            y = m(xg, c)
+            ((y.float() * go).sum() + m.aux_loss).backward()
+            torch.cuda.synchronize()
+            outs.append([y.detach().clone(), xg.grad.clone()] + [p.grad.clone() for p in m.parameters() if p.grad is not None])
+    finally:
+        lib.b200moe_layer_fork(1)
+        lib.b200moe_layer_pdl(1)
+    for other in outs[1:]:
+        assert len(other) == len(outs[0])
+        for a, b in zip(outs[0], other):
+            assert torch.equal(a, b)
+
+
+def test_empty_batch_and_eval_mode():
+    import b200moe
+    _, m = _pair(128, 256, 4, 2, 1.25, seed=1)
+    x0 = torch.zeros(0, 7, 128, dtype=torch.bfloat16, device="cuda")
+    assert m(x0).shape == (0, 7, 128) and float(m.aux_loss) == 0.0
+    x = torch.randn(2, 50, 128, device="cuda").to(torch.bfloat16)
+    m.eval()
+    with torch.no_grad():
+        y1, y2 = m(x), m(x)
+    assert torch.equal(y1, y2) and y1.shape == x.shape and torch.isfinite(y1.float()).all()

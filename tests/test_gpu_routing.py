@@ -28,7 +28,7 @@ def _mk(T, d, E, seed=0, zero_gate=False):
 
 
 @pytest.mark.parametrize("T,d,E,k", [(3200, 256, 8, 2), (1000, 512, 16, 2), (777, 1024, 64, 2), (130, 128, 4, 1),
-                                     (513, 256, 5, 3), (4096, 256, 32, 4)])
+                                     (513, 256, 5, 3), (4096, 256, 32, 4), (777, 512, 64, 8), (300, 128, 9, 8), (1, 128, 2, 2)])
 def test_router_matches_oracle(ops, T, d, E, k):
     x, wg = _mk(T, d, E, seed=T)
     B = 1 if T % 8 else 8
@@ -71,7 +71,7 @@ def test_router_all_ties_pick_lowest_index(ops):
 
 @pytest.mark.parametrize("T,E,k,cf", [(3200, 8, 2, None), (3200, 8, 2, 1.25), (1000, 16, 2, 0.5), (777, 64, 2, 1.0),
                                       (130, 4, 1, 0.25), (5000, 8, 3, 1.25), (128, 8, 2, 1.25), (1, 8, 2, None),
-                                      (40000, 8, 2, 1.25), (20000, 16, 2, 1.0), (9000, 64, 4, 1.0), (8321, 40, 3, 0.75)])
+                                      (40000, 8, 2, 1.25), (20000, 16, 2, 1.0), (9000, 64, 4, 1.0), (8321, 40, 3, 0.75), (777, 64, 8, 1.0), (8300, 64, 8, 0.5)])
 def test_plan_matches_oracle(ops, T, E, k, cf):
     d = 256
     x, wg = _mk(T, d, E, seed=7 + T)

@@ -56,6 +56,17 @@ def main():
             y.backward(go_all[sl])
         a_ep = dict(m_ep.last_aux)
         path = "p2p" if "_p2p_arena" in m_ep.__dict__ else "nccl"
+        if path == "p2p":
+            # a second forward before the first backward must not touch the arena the pending backward reads
+            xa = x_all[sl].clone().requires_grad_(True)
+            ya = m_ep(xa, c_all[sl])
+            with torch.no_grad():
+                yb = m_ep(x_all[sl], c_all[sl])                     # eval-style call in between (NCCL path)
+            m_ep.zero_grad(set_to_none=True)
+            ya.backward(go_all[sl])
+            ok = ok and torch.equal(ya, y) and torch.equal(yb, y) and torch.equal(xa.grad, x.grad)
+            if not (torch.equal(ya, y) and torch.equal(yb, y) and torch.equal(xa.grad, x.grad)):
+                print(f"[rank {rank}] FAILED interleaved forward on the p2p path", flush=True)
 
         x1 = x_all.clone().requires_grad_(True)
         y1 = m_1(x1, c_all)
