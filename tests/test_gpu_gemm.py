@@ -141,3 +141,32 @@ def test_bad_shapes_fail_loudly(ops):
     b1 = torch.zeros(2, 256, device="cuda")
     with pytest.raises(RuntimeError, match="multiple of 128"):
         ops.ffn_up(xp, w1, b1, meta.cuda(), te.cuda())
+
+
+def test_gelu_saturates_for_large_preactivations(ops):
+    """|pre| far beyond 8 (where the tanh-form fit of Phi is clamped): h -> pre or 0, GELU' -> 1 or 0, nothing NaN."""
+    E, d, F, rows, pad = 2, 128, 256, [256, 128], 128
+    g = torch.Generator().manual_seed(77)
+    offs, meta, te, valid, rexp, R, rows_cap = _layout(E, rows, pad)
+    xp = (torch.randn(rows_cap, d, generator=g) * 6.0).to(torch.bfloat16)
+    xp[~valid] = 0
+    w1 = (torch.randn(E, F, d, generator=g) * d ** -0.5 * 4.0).to(torch.bfloat16)      # pre ~ N(0, 24^2)
+    b1 = torch.zeros(E, F)
+    dev = "cuda"
+    pre, h = ops.ffn_up(xp.to(dev), w1.to(dev), b1.to(dev), meta.to(dev), te.to(dev), row_pad=pad)
+    pre_c, h_c = pre.cpu()[:R].float(), h.cpu()[:R].float()
+    assert float(pre_c.abs().max()) > 40 and torch.isfinite(h_c).all()
+    h_ref = torch.nn.functional.gelu(pre_c)
+    assert _rel(h_c, h_ref) < 6e-3
+    big = pre_c.abs() > 9
+    assert torch.equal(h_c[big & (pre_c > 0)], pre_c[big & (pre_c > 0)]) and float(h_c[big & (pre_c < 0)].abs().max()) == 0.0
+    w2 = (torch.randn(E, d, F, generator=g) * F ** -0.5).to(torch.bfloat16)
+    dyp = torch.randn(rows_cap, d, generator=g).to(torch.bfloat16)
+    dyp[~valid] = 0
+    dhpre = ops.ffn_dgrad_down(dyp.to(dev), w2.to(dev), pre, meta.to(dev), te.to(dev), row_pad=pad).cpu()[:R].float()
+    assert torch.isfinite(dhpre).all()
+    for e in range(E):
+        sl = slice(int(offs[e]), int(offs[e + 1]))
+        pf = pre_c[sl].clone().requires_grad_(True)
+        torch.nn.functional.gelu(pf).backward(dyp[sl].float() @ w2[e].float())
+        assert _rel(dhpre[sl], pf.grad) < 6e-3
