@@ -198,8 +198,8 @@ int b200moe_scatter_rows(const void* in, const int32_t* src_of_row, const int32_
  *   ep_p2p_unpermute_bwd: b200moe_unpermute_bwd with the dxp rows loaded from the peers.
  *   ep_p2p_pull_rows   : out[r] = peers' buffer[dest_of_row[r]] for every send row (plain copy, no shared memory: runs
  *                        next to the weight-gradient GEMMs on a side stream; b200moe_unpermute_bwd then reads `out`). */
-int b200moe_ep_p2p_tables(const int32_t* kept, int W, int E, int rank, int rows_cap, int32_t* dest_off,
-                          int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert, void* stream);
+int b200moe_ep_p2p_tables(const int32_t* kept, int W, int E, int rank, int rows_cap, int row_pad /* 128 | 256 */,
+                          int32_t* dest_off, int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert, void* stream);
 int b200moe_ep_p2p_zero_pads(const int32_t* kept, const int32_t* expert_offsets, int W, int E, int rank, int d,
                              void* a, void* b, void* stream);
 int b200moe_ep_p2p_dispatch(const void* x, const int32_t* token_of_row, const int32_t* send_offsets,

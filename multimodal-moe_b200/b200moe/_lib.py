@@ -38,7 +38,7 @@ SIGNATURES = {
     "b200moe_prepare_weights": [_P, _P, _L, _P, _P, _L, _P, _P, _I, _I, _P],
     "b200moe_ctx_bias_fwd": [_P, _P, _P, _I, _I, _P, _I, _I, _P, _P],
     "b200moe_ctx_bias_bwd": [_P, _P, _P, _P, _I, _I, _P, _I, _I, _P, _P, _P],
-    "b200moe_ep_p2p_tables": [_P, _I, _I, _I, _I, _P, _P, _P, _P, _P],
+    "b200moe_ep_p2p_tables": [_P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P],
     "b200moe_ep_p2p_zero_pads": [_P, _P, _I, _I, _I, _I, _P, _P, _P],
     "b200moe_ep_p2p_dispatch": [_P, _P, _P, _P, _P, _P, _L, _I, _I, _I, _I, _I, _P, _P],
     "b200moe_ep_p2p_combine": [_P, _L, _I, _P, _P, _P, _I, _I, _I, _P, _P],

@@ -67,7 +67,10 @@ class _Arena:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
         self.T_cap = int(t.item())
         cap = ops.capacity_of(mod.capacity_factor, self.T_cap * W, k, E)
-        self.rows_cap = mod.num_local_experts * ((cap + 127) // 128 * 128)
+        # 256-row segments (CTA-pair GEMM tiles) when a balanced share of the rows still fills two waves of them
+        self.row_pad = int(_lib.load().b200moe_layer_row_pad(self.T_cap, k, mod.num_local_experts, -1, d,
+                                                             mod.dim_feedforward))
+        self.rows_cap = mod.num_local_experts * ((cap + self.row_pad - 1) // self.row_pad * self.row_pad)
         self.buf_bytes = self.rows_cap * d * 2
         self.mem = symm.empty(4 * self.buf_bytes, dtype=torch.uint8, device=dev)
         self.hdl = symm.rendezvous(self.mem, group)
@@ -138,7 +141,7 @@ class _P2PFunction(torch.autograd.Function):
         offs = torch.empty((EL + 1,), dtype=i32, device=dev)
         meta = torch.empty((8,), dtype=i32, device=dev)
         tile_e = torch.empty((R // 128,), dtype=i32, device=dev)
-        _lib.call("b200moe_ep_p2p_tables", kept.data_ptr(), W, E, rank, R, dest_off.data_ptr(), offs.data_ptr(),
+        _lib.call("b200moe_ep_p2p_tables", kept.data_ptr(), W, E, rank, R, ar.row_pad, dest_off.data_ptr(), offs.data_ptr(),
                   meta.data_ptr(), tile_e.data_ptr(), st)
         _lib.call("b200moe_ep_p2p_zero_pads", kept.data_ptr(), offs.data_ptr(), W, E, rank, d, ar.xp.data_ptr(),
                   ar.dyp.data_ptr() if need_grad else None, st)
@@ -147,8 +150,8 @@ class _P2PFunction(torch.autograd.Function):
                   p.meta.data_ptr(), dest_off.data_ptr(), ar.peers.data_ptr(), ar.off[0], R, send_cap, E, EL, d,
                   dest_of_row.data_ptr(), st)
         ar.barrier(0)                                   # every rank's rows have landed in xp
-        pre, h = ops.ffn_up(ar.xp, w1b, b1f, meta, tile_e, save_pre=need_grad)
-        ops.ffn_down(h, w2b, b2f, meta, tile_e, out=ar.yo)
+        pre, h = ops.ffn_up(ar.xp, w1b, b1f, meta, tile_e, save_pre=need_grad, row_pad=ar.row_pad)
+        ops.ffn_down(h, w2b, b2f, meta, tile_e, row_pad=ar.row_pad, out=ar.yo)
         ar.barrier(1)                                   # every rank's yo is complete
         y = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
         _lib.call("b200moe_ep_p2p_combine", ar.peers.data_ptr(), ar.off[1], R, dest_of_row.data_ptr(),
@@ -193,11 +196,11 @@ class _P2PFunction(torch.autograd.Function):
         dwg, dctx = ops.router_bwd_params(dlogits, x2, ctx.tpi, want_dwg=need[2],
                                           want_dctx=bool(ctx.has_ctx and need[1]))
         ar.barrier(2)                                   # every rank's dyp rows have landed
-        dhpre = ops.ffn_dgrad_down(ar.dyp, w2b, pre, meta, tile_e)
+        dhpre = ops.ffn_dgrad_down(ar.dyp, w2b, pre, meta, tile_e, row_pad=ar.row_pad)
         comp = torch.cuda.current_stream()
         dxs = None
         if need[0]:
-            ops.ffn_dgrad_up(dhpre, w1b, meta, tile_e, out=ar.dxp)
+            ops.ffn_dgrad_up(dhpre, w1b, meta, tile_e, row_pad=ar.row_pad, out=ar.dxp)
             ar.barrier(3)                               # every rank's dxp is complete
             # the rows come home on a side stream (a plain copy kernel: no shared memory, so it runs on the SMs next to
             # the persistent weight-gradient CTAs) while the tensor-bound kernels below keep the main stream busy

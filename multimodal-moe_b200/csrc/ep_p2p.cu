@@ -26,7 +26,7 @@ constexpr int kP2pThreads = kP2pWarps * 32;
 //   meta[5] = 1 if some rank's rows do not fit rows_cap (cannot happen while every rank stays within the token count the
 //   arena was sized for -- the host enforces that; rows beyond rows_cap are never stored, the flag is the evidence)
 __global__ void __launch_bounds__(64)
-ep_p2p_tables_kernel(const int32_t* __restrict__ kept, int W, int E, int rank, int rows_cap,
+ep_p2p_tables_kernel(const int32_t* __restrict__ kept, int W, int E, int rank, int rows_cap, int row_pad,
                      int32_t* __restrict__ dest_off, int32_t* __restrict__ expert_offsets, int32_t* __restrict__ meta,
                      int32_t* __restrict__ tile_expert) {
   __shared__ int tot_s[64], off_s[65], real_s[1], bad_s[1];
@@ -42,13 +42,13 @@ ep_p2p_tables_kernel(const int32_t* __restrict__ kept, int W, int E, int rank, i
   if (e < E) {
     const int w = e / EL;
     int off = 0;
-    for (int j = w * EL; j < e; ++j) off += (tot_s[j] + kRowPad - 1) / kRowPad * kRowPad;
+    for (int j = w * EL; j < e; ++j) off += (tot_s[j] + row_pad - 1) / row_pad * row_pad;
     int before = 0;
     for (int s = 0; s < rank; ++s) before += kept[s * E + e];
     dest_off[e] = off + before;
     if (w == rank) off_s[e - w * EL] = off;
     if (e == w * EL + EL - 1) {       // last expert of rank w: total rows of that rank
-      const int total = off + (tot_s[e] + kRowPad - 1) / kRowPad * kRowPad;
+      const int total = off + (tot_s[e] + row_pad - 1) / row_pad * row_pad;
       if (total > rows_cap) bad_s[0] = 1;
       if (w == rank) off_s[EL] = total;
     }
@@ -224,13 +224,15 @@ static int p2p_grid(int rows) {
 
 using namespace b200moe;
 
-extern "C" int b200moe_ep_p2p_tables(const int32_t* kept, int W, int E, int rank, int rows_cap, int32_t* dest_off,
-                                     int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert, void* stream) {
+extern "C" int b200moe_ep_p2p_tables(const int32_t* kept, int W, int E, int rank, int rows_cap, int row_pad,
+                                     int32_t* dest_off, int32_t* expert_offsets, int32_t* meta, int32_t* tile_expert,
+                                     void* stream) {
+  B200MOE_REQUIRE(row_pad == kRowPad || row_pad == 2 * kRowPad, B200MOE_EINVAL, "ep_p2p_tables: row_pad must be 128 or 256");
   B200MOE_REQUIRE(W >= 1 && W <= 8 && E >= 1 && E <= 64 && E % W == 0 && rank >= 0 && rank < W, B200MOE_EINVAL,
                   "ep_p2p_tables: bad world=%d / num_experts=%d / rank=%d", W, E, rank);
   B200MOE_REQUIRE(rows_cap > 0 && rows_cap % kRowPad == 0, B200MOE_EINVAL, "ep_p2p_tables: rows_cap must be a multiple of 128");
   if (int rc = b200moe_check_device()) return rc;
-  ep_p2p_tables_kernel<<<1, 64, 0, static_cast<cudaStream_t>(stream)>>>(kept, W, E, rank, rows_cap, dest_off,
+  ep_p2p_tables_kernel<<<1, 64, 0, static_cast<cudaStream_t>(stream)>>>(kept, W, E, rank, rows_cap, row_pad, dest_off,
                                                                         expert_offsets, meta, tile_expert);
   return check_launch("ep_p2p_tables");
 }

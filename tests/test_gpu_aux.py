@@ -149,8 +149,8 @@ def test_ep_hist(ops):
     assert torch.equal(out[:-1].cpu(), bc.sum(0).reshape(-1).cpu().int()) and int(out[-1]) == T
 
 
-@pytest.mark.parametrize("W,E", [(2, 8), (4, 16), (8, 64), (1, 4)])
-def test_ep_p2p_tables_match_host_twin(ops, W, E):
+@pytest.mark.parametrize("W,E,pad", [(2, 8, 128), (4, 16, 256), (8, 64, 128), (1, 4, 256)])
+def test_ep_p2p_tables_match_host_twin(ops, W, E, pad):
     from b200moe import _lib
     from b200moe.ep_p2p import p2p_layout
     g = torch.Generator().manual_seed(W * 7 + E)
@@ -159,13 +159,13 @@ def test_ep_p2p_tables_match_host_twin(ops, W, E):
     kd = torch.cat([kept.reshape(-1), torch.tensor([0, 0], dtype=torch.int32)]).cuda()
     EL = E // W
     for rank in range(W):
-        dest_ref, offs_ref = p2p_layout(kept, rank)
+        dest_ref, offs_ref = p2p_layout(kept, rank, pad)
         rows_cap = int(offs_ref[:, -1].max())
         dest = torch.empty(E, dtype=torch.int32, device="cuda")
         offs = torch.empty(EL + 1, dtype=torch.int32, device="cuda")
         meta = torch.empty(8, dtype=torch.int32, device="cuda")
         tile_e = torch.empty(rows_cap // 128, dtype=torch.int32, device="cuda")
-        _call("b200moe_ep_p2p_tables", kd.data_ptr(), W, E, rank, rows_cap, dest.data_ptr(), offs.data_ptr(),
+        _call("b200moe_ep_p2p_tables", kd.data_ptr(), W, E, rank, rows_cap, pad, dest.data_ptr(), offs.data_ptr(),
               meta.data_ptr(), tile_e.data_ptr(), _lib.stream_ptr())
         assert torch.equal(dest.cpu(), dest_ref) and torch.equal(offs.cpu(), offs_ref[rank])
         m = meta.cpu()
@@ -182,6 +182,6 @@ def test_ep_p2p_tables_match_host_twin(ops, W, E):
             assert int(te[t]) == want
         # too small a buffer is flagged, not overrun
         if rows_cap > 128:
-            _call("b200moe_ep_p2p_tables", kd.data_ptr(), W, E, rank, rows_cap - 128, dest.data_ptr(), offs.data_ptr(),
+            _call("b200moe_ep_p2p_tables", kd.data_ptr(), W, E, rank, rows_cap - 128, pad, dest.data_ptr(), offs.data_ptr(),
                   meta.data_ptr(), tile_e.data_ptr(), _lib.stream_ptr())
             assert int(meta.cpu()[5]) == 1
