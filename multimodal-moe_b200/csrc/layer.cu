@@ -111,7 +111,7 @@ struct CtxTables {
 };
 
 // one block per image, thread per expert-strided output; the n*cd-long embedding row sits in shared memory
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(512)
 ctx_bias_fwd_kernel(const int64_t* __restrict__ context, const CtxTables tb, int n, int cd,
                     const float* __restrict__ wc, int E, float* __restrict__ out) {
   extern __shared__ float emb_s[];   // [n*cd]
@@ -123,7 +123,7 @@ ctx_bias_fwd_kernel(const int64_t* __restrict__ context, const CtxTables tb, int
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int e = warp; e < E; e += 4) {
+  for (int e = warp; e < E; e += (blockDim.x >> 5)) {
     float s = 0.f;
     for (int i = lane; i < n * cd; i += 32) s = fmaf(emb_s[i], wc[static_cast<size_t>(e) * n * cd + i], s);
     s = warp_sum(s);
@@ -191,7 +191,8 @@ extern "C" int b200moe_ctx_bias_fwd(const int64_t* context, const float* const* 
   B200MOE_REQUIRE(context_dim > 0 && n_fields * context_dim <= 8192 && B > 0 && E >= 1 && E <= 64, B200MOE_EINVAL,
                   "ctx_bias_fwd: bad shape (context_dim=%d, B=%d, E=%d)", context_dim, B, E);
   if (int rc = b200moe_check_device()) return rc;
-  ctx_bias_fwd_kernel<<<B, 128, sizeof(float) * n_fields * context_dim, static_cast<cudaStream_t>(stream)>>>(
+  const int threads = E <= 4 ? 128 : (E <= 8 ? 256 : 512);      // a warp per expert, up to 16 warps
+  ctx_bias_fwd_kernel<<<B, threads, sizeof(float) * n_fields * context_dim, static_cast<cudaStream_t>(stream)>>>(
       context, tb, n_fields, context_dim, wc, E, ctx_bias);
   return check_launch("ctx_bias_fwd");
 }

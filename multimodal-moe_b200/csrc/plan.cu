@@ -26,77 +26,69 @@ plan_scan_kernel(int32_t* __restrict__ block_counts, const float* __restrict__ b
   __shared__ int keptslot_s[8 * 64];
   __shared__ int kept_s[64], count_s[64], off_s[65], expert_at_s[64];
   __shared__ float P_s[65];
-  __shared__ float scan_s[(kScanThreads / 32) * 32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = kScanThreads / 32;
   const int kE = k * E;
   pdl_sync();
 
-  // phase 1: exclusive scan over the router blocks for every (slot, expert) column.  Lanes run along the columns (one
-  // 128-byte line per block and warp: a lane-per-block layout made every load and store touch 32 lines and the one
-  // SM's load/store unit, not memory latency, set the time: 30 us at 512 blocks), the 32 warps split the blocks into
-  // contiguous chunks: chunk sums -> shared memory -> prefix over the chunks -> second pass writes the bases.
+  // phase 1: exclusive scan over the router blocks for every (slot, expert) column, and the column sums of the loss
+  // statistics.  Lanes run along the columns (one 128-byte line per block and warp: a lane-per-block layout made every
+  // load and store touch 32 lines and the one SM's load/store unit, not memory latency, set the time: 30 us at 512
+  // blocks), the 32 warps split the blocks into contiguous chunks: chunk sums of every column -> shared memory -> one
+  // barrier -> prefix over the chunks -> second pass writes the bases.
   {
-    int* chunk_s = reinterpret_cast<int*>(scan_s);                 // [nwarps][32]
+    extern __shared__ int scan_dyn[];
+    int* chunk_s = scan_dyn;                                                  // [nwarps][kE]
+    float* fchunk_s = reinterpret_cast<float*>(scan_dyn + nwarps * kE);       // [nwarps][E+1]
     const int ch = (nblk + nwarps - 1) / nwarps;
     const int b_lo = warp * ch, b_hi = (b_lo + ch < nblk) ? b_lo + ch : nblk;
-    for (int q0 = 0; q0 < kE; q0 += 32) {
-      const int q = q0 + lane;
-      const bool on = q < kE;
+    for (int q = lane; q < kE; q += 32) {
       int sum = 0;
       for (int b0 = b_lo; b0 < b_hi; b0 += 8) {
         int v[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = (on && b0 + u < b_hi) ? block_counts[static_cast<size_t>(b0 + u) * kE + q] : 0;
+        for (int u = 0; u < 8; ++u) v[u] = (b0 + u < b_hi) ? block_counts[static_cast<size_t>(b0 + u) * kE + q] : 0;
 #pragma unroll
         for (int u = 0; u < 8; ++u) sum += v[u];
       }
-      chunk_s[warp * 32 + lane] = sum;
-      __syncthreads();
-      int run = 0, tot = 0;
-      for (int w = 0; w < nwarps; ++w) {
-        const int c = chunk_s[w * 32 + lane];
-        run += (w < warp) ? c : 0;
-        tot += c;
-      }
-      if (warp == 0 && on) total_s[q] = tot;
-      for (int b0 = b_lo; b0 < b_hi; b0 += 8) {
-        int v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = (on && b0 + u < b_hi) ? block_counts[static_cast<size_t>(b0 + u) * kE + q] : 0;
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-          if (on && b0 + u < b_hi) block_counts[static_cast<size_t>(b0 + u) * kE + q] = run;
-          run += v[u];
-        }
-      }
-      __syncthreads();
+      chunk_s[warp * kE + q] = sum;
     }
-  }
-  // loss statistics: lanes along the columns of block_stats, warps split the blocks, then the chunks in a fixed order
-  {
-    float* fchunk_s = scan_s;                                       // [nwarps][32]
-    const int ch = (nblk + nwarps - 1) / nwarps;
-    const int b_lo = warp * ch, b_hi = (b_lo + ch < nblk) ? b_lo + ch : nblk;
-    for (int e0 = 0; e0 <= E; e0 += 32) {
-      const int e = e0 + lane;
-      const bool on = e <= E;
+    for (int e = lane; e <= E; e += 32) {
       float sum = 0.f;
       for (int b0 = b_lo; b0 < b_hi; b0 += 8) {
         float v[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) v[u] = (on && b0 + u < b_hi) ? block_stats[static_cast<size_t>(b0 + u) * (E + 1) + e] : 0.f;
+        for (int u = 0; u < 8; ++u) v[u] = (b0 + u < b_hi) ? block_stats[static_cast<size_t>(b0 + u) * (E + 1) + e] : 0.f;
 #pragma unroll
         for (int u = 0; u < 8; ++u) sum += v[u];
       }
-      fchunk_s[warp * 32 + lane] = sum;
-      __syncthreads();
-      if (warp == 0 && on) {
-        float s = 0.f;
-        for (int w = 0; w < nwarps; ++w) s += fchunk_s[w * 32 + lane];
-        P_s[e] = s;
-      }
-      __syncthreads();
+      fchunk_s[warp * (E + 1) + e] = sum;
     }
+    __syncthreads();
+    for (int q = lane; q < kE; q += 32) {
+      int run = 0, tot = 0;
+      for (int w = 0; w < nwarps; ++w) {
+        const int c = chunk_s[w * kE + q];
+        run += (w < warp) ? c : 0;
+        tot += c;
+      }
+      if (warp == 0) total_s[q] = tot;
+      for (int b0 = b_lo; b0 < b_hi; b0 += 8) {
+        int v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = (b0 + u < b_hi) ? block_counts[static_cast<size_t>(b0 + u) * kE + q] : 0;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (b0 + u < b_hi) block_counts[static_cast<size_t>(b0 + u) * kE + q] = run;
+          run += v[u];
+        }
+      }
+    }
+    for (int e = threadIdx.x; e <= E; e += blockDim.x) {      // the chunks in a fixed order
+      float sacc = 0.f;
+      for (int w = 0; w < nwarps; ++w) sacc += fchunk_s[w * (E + 1) + e];
+      P_s[e] = sacc;
+    }
+    __syncthreads();
   }
 
   // phase 2: per expert, slot bases against the capacity
@@ -420,7 +412,13 @@ extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int
              row_of_assignment, token_of_row, gate_of_row);
     return check_launch("plan_fused");
   }
-  launch_k(plan_scan_kernel, 1, kScanThreads, 0, st, block_counts, block_stats, nblk, T, k, E, capacity, global_offset,
+  const size_t scan_smem = sizeof(int) * (kScanThreads / 32) * (static_cast<size_t>(k) * E + E + 1);
+  static bool scan_configured = false;
+  if (!scan_configured) {
+    cudaFuncSetAttribute(plan_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * (8 * 64 + 65) * 4);
+    scan_configured = true;
+  }
+  launch_k(plan_scan_kernel, 1, kScanThreads, scan_smem, st, block_counts, block_stats, nblk, T, k, E, capacity, global_offset,
            expert_order, row_pad, rows_cap, aux_loss_weight, z_loss_weight, expert_offsets, meta, tile_expert,
            tokens_per_expert, kept_per_expert, losses, slot_limit, token_of_row, gate_of_row);
   if (int rc = check_launch("plan_scan")) return rc;
