@@ -225,8 +225,9 @@ def measure_layer(w, steps, warmup, device, ep_group=None, dist_on=False, want_e
 
     # (1) eager: every kernel launched from Python through the C ABI (host launch latency included)
     _lib.Counters.reset()
+    _lib.load().b200moe_launch_count(1)                      # counted inside the library, at every launch site
     ms_eager = time_steps(step, steps, warmup, flush, dist_on)
-    launches = _lib.Counters.launches // (steps + warmup)
+    launches = int(_lib.load().b200moe_launch_count(0)) // (steps + warmup)
     res = {"ms_eager": ms_eager, "T": T, "launches_per_step": launches,
            "kept": int(m.last_aux["meta"][3]), "dropped": int(m.last_aux["meta"][2])}
 

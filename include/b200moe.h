@@ -36,6 +36,9 @@ extern "C" {
 #define B200MOE_META_INTS 8          /* meta[0]=R (padded rows in use) meta[1]=R/128 meta[2]=dropped meta[3]=kept */
 
 int b200moe_version(void);
+/* Kernels launched by the library since load (or since the last call with reset != 0): the evidence behind a
+ * benchmark's launch count. */
+int64_t b200moe_launch_count(int reset);
 const char* b200moe_last_error(void);
 /* 0 when the current device is compute capability 10.x, else B200MOE_EARCH. */
 int b200moe_check_device(void);

@@ -15,6 +15,7 @@ _P, _I, _F, _L = C.c_void_p, C.c_int, C.c_float, C.c_int64
 # name -> argtypes (return type is int unless listed in _RESTYPE); mirrors include/b200moe.h one to one
 SIGNATURES = {
     "b200moe_version": [],
+    "b200moe_launch_count": [_I],
     "b200moe_last_error": [],
     "b200moe_check_device": [],
     "b200moe_rows_upper_bound": [_I, _I, _I, _I],
@@ -67,7 +68,7 @@ SIGNATURES = {
     "b200moe_ep_hist": [_P, _I, _I, _I, _I, _P, _P],
     "b200moe_ep_route_tables": [_P, _I, _I, _I, _I, C.c_double, _I, _P, _P, _P, _P],
 }
-_RESTYPE = {"b200moe_last_error": C.c_char_p, "b200moe_dwg_scratch_floats": C.c_int64,
+_RESTYPE = {"b200moe_last_error": C.c_char_p, "b200moe_launch_count": C.c_int64, "b200moe_dwg_scratch_floats": C.c_int64,
             "b200moe_router_scratch_bytes": C.c_int64, "b200moe_layer_ws_layout": C.c_int64,
             "b200moe_layer_bwd_ws_layout": C.c_int64, "b200moe_ln_scratch_floats": C.c_int64}
 

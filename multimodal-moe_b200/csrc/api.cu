@@ -16,12 +16,15 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
+static long long g_launches = 0;   // kernels launched by this library (every launch site ends in check_launch)
+
 int check_launch(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("%s: %s", what, cudaGetErrorString(e));
     return B200MOE_ECUDA;
   }
+  ++g_launches;
   return B200MOE_OK;
 }
 
@@ -30,6 +33,12 @@ int check_launch(const char* what) {
 extern "C" {
 
 int b200moe_version(void) { return 100; }
+
+int64_t b200moe_launch_count(int reset) {
+  const long long n = b200moe::g_launches;
+  if (reset) b200moe::g_launches = 0;
+  return n;
+}
 
 const char* b200moe_last_error(void) { return b200moe::g_err; }
 
