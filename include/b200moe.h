@@ -293,7 +293,10 @@ int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* desc, int64_t* off
  * save_for_backward == 0 skips the pre-activation store. */
 int b200moe_layer_fwd(const b200moe_layer_desc* desc, const void* x, const float* ctx_bias, const void* wg_split,
                       const void* w1, const float* b1, const void* w2, const float* b2, void* ws, void* y,
-                      int save_for_backward, const b200moe_postnorm* postnorm /* or NULL */, void* stream);
+                      int save_for_backward, const b200moe_postnorm* postnorm /* or NULL */,
+                      void* weights_ready /* cudaEvent_t recorded after w1 / w2 were prepared on another stream, or NULL:
+                                             waited for just before the up-projection */,
+                      void* stream);
 /* Mirror of the forward incl. the A.12 router gradient.  dy [T,d] bf16; d_aux: device scalar (gradient of the
  * weighted auxiliary loss) or NULL.  Any of the gradient outputs may be NULL (not computed):
  * dx [T,d] bf16, dctx_bias [B,E], dwg [E,d], dw1 [E,F,d], db1 [E,F], dw2 [E,d,F], db2 [E,d] (all fp32).      */

@@ -52,7 +52,7 @@ SIGNATURES = {
     "b200moe_layer_profile_read": [_I, _P, _P],
     "b200moe_layer_ws_layout": [_P, _P],
     "b200moe_layer_bwd_ws_layout": [_P, _P],
-    "b200moe_layer_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P],
+    "b200moe_layer_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P],
     "b200moe_layer_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P],
     "b200moe_combine_ln_fwd": [_P, _P, _P, _P, _P, _P, _F, _I, _I, _I, _P, _P, _P],
     "b200moe_ln_scratch_floats": [_I, _I],

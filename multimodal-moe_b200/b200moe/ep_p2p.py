@@ -112,7 +112,7 @@ class _P2PFunction(torch.autograd.Function):
         T, d = x2.shape
         E, k, EL = mod.num_experts, mod.top_k, mod.num_local_experts
         need_grad = any(ctx.needs_input_grad)
-        w1b, w2b, wsplit, wgf = mod._prepared(w1, w2, wg)
+        w1b, w2b, wsplit, wgf, _ = mod._prepared(w1, w2, wg)
         b1f, b2f = b1.float().contiguous(), b2.float().contiguous()
         cb = ctx_bias.float().contiguous() if ctx_bias is not None else None
         dev = x2.device

@@ -152,7 +152,7 @@ class _MoEFunction(torch.autograd.Function):
         E = mod.num_experts
         need_grad = any(ctx.needs_input_grad)   # forward runs under no_grad: ask autograd, not the grad mode
         pl = mod._layer_plan(T, tpi)
-        w1b, w2b, wsplit, wgf = mod._prepared(w1, w2, wg)
+        w1b, w2b, wsplit, wgf, ready = mod._prepared(w1, w2, wg, overlap=True)
         b1f, b2f = _f32c(b1), _f32c(b2)
         st = _lib.stream_ptr()
         cb = None
@@ -177,7 +177,7 @@ class _MoEFunction(torch.autograd.Function):
             ctx.ln = (residual, gam, mean_rstd, ln_w.dtype, ln_b.dtype)
         _lib.call("b200moe_layer_fwd", pl.desc_ptr, x2.data_ptr(), cb.data_ptr() if cb is not None else None,
                   wsplit.data_ptr(), w1b.data_ptr(), b1f.data_ptr(), w2b.data_ptr(), b2f.data_ptr(), ws.data_ptr(),
-                  y.data_ptr(), int(need_grad), pn_ptr, st)
+                  y.data_ptr(), int(need_grad), pn_ptr, ready.cuda_event if ready is not None else None, st)
         ctx.mod, ctx.pl, ctx.has_ctx = mod, pl, cb is not None
         ctx.dtypes = (wg.dtype, w1.dtype, b1.dtype, w2.dtype, b2.dtype)
         ctx.save_for_backward(x2, wgf, w1b, w2b, ws)
@@ -313,7 +313,8 @@ class ContextMoE(nn.Module):
         new = self.__class__.__new__(self.__class__)
         memo[id(self)] = new
         for k_, v in self.__dict__.items():
-            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side"):
+            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side", "_prep_stream",
+                      "_prep_keep"):
                 continue
             if k_ in ("_wcache", "last_aux", "_plans"):
                 new.__dict__[k_] = {}
@@ -328,7 +329,8 @@ class ContextMoE(nn.Module):
     def __getstate__(self):
         s = dict(self.__dict__)
         s["_wcache"], s["last_aux"], s["aux_loss"], s["ep_group"], s["_plans"] = {}, {}, torch.zeros(()), None, {}
-        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side"):
+        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side", "_prep_stream",
+                      "_prep_keep"):
             s.pop(k_, None)
         return s
 
@@ -375,13 +377,15 @@ class ContextMoE(nn.Module):
             pl = self._plans[(T, tpi)] = _LayerPlan(self, T, tpi)
         return pl
 
-    def _prepared(self, w1, w2, wg):
-        """bf16 operand copies of w1 / w2 and the bf16 hi/lo split of the gate (one launch), redone only when a
-        parameter changed (version counters).  Returns (w1_bf16, w2_bf16, wg_split, wg_fp32)."""
+    def _prepared(self, w1, w2, wg, overlap: bool = False):
+        """bf16 operand copies of w1 / w2 and the bf16 hi/lo split of the gate, redone only when a parameter changed
+        (version counters).  Returns (w1_bf16, w2_bf16, wg_split, wg_fp32, ready): with `overlap` the two big casts run
+        on a side stream next to the router / plan / permute, and `ready` is the CUDA event b200moe_layer_fwd waits for
+        just before the up-projection (None when nothing is in flight); without it, one launch on the current stream."""
         key = (w1.data_ptr(), w1._version, w2.data_ptr(), w2._version, wg.data_ptr(), wg._version, str(w1.device))
         hit = self._wcache.get("prep")
         if hit is not None and hit[0] == key:
-            return hit[1]
+            return (*hit[1], None)
         dev, bf = w1.device, torch.bfloat16
         w1d, w2d = w1.detach().contiguous(), w2.detach().contiguous()
         wgf = wg.detach().float().contiguous()
@@ -391,13 +395,29 @@ class ContextMoE(nn.Module):
         wsplit = torch.empty((nsplit,), dtype=bf, device=dev)
         w1f = w1d.float() if w1d.dtype not in (bf, torch.float32) else w1d
         w2f = w2d.float() if w2d.dtype not in (bf, torch.float32) else w2d
-        _lib.call("b200moe_prepare_weights",
-                  w1f.data_ptr() if w1b is not w1d else None, w1b.data_ptr(), w1f.numel() if w1b is not w1d else 0,
-                  w2f.data_ptr() if w2b is not w2d else None, w2b.data_ptr(), w2f.numel() if w2b is not w2d else 0,
-                  wgf.data_ptr(), wsplit.data_ptr(), self.d_model, self.num_experts, _lib.stream_ptr())
+        a1 = (w1f.data_ptr(), w1b.data_ptr(), w1f.numel()) if w1b is not w1d else (None, w1b.data_ptr(), 0)
+        a2 = (w2f.data_ptr(), w2b.data_ptr(), w2f.numel()) if w2b is not w2d else (None, w2b.data_ptr(), 0)
+        ready = None
+        if overlap and (a1[2] or a2[2]):
+            cur = torch.cuda.current_stream(dev)
+            _lib.call("b200moe_prepare_weights", None, w1b.data_ptr(), 0, None, w2b.data_ptr(), 0, wgf.data_ptr(),
+                      wsplit.data_ptr(), self.d_model, self.num_experts, _lib.stream_ptr())
+            side = self.__dict__.get("_prep_stream")
+            if side is None or side.device != dev:
+                side = self.__dict__["_prep_stream"] = torch.cuda.Stream(device=dev)
+            side.wait_stream(cur)
+            with torch.cuda.stream(side):
+                _lib.call("b200moe_prepare_weights", *a1, *a2, None, None, self.d_model, self.num_experts,
+                          _lib.stream_ptr())
+                ready = torch.cuda.Event()
+                ready.record(side)
+            self.__dict__["_prep_keep"] = (w1f, w2f)      # read on the side stream: keep them until the next call
+        else:
+            _lib.call("b200moe_prepare_weights", *a1, *a2, wgf.data_ptr(), wsplit.data_ptr(), self.d_model,
+                      self.num_experts, _lib.stream_ptr())
         out = (w1b, w2b, wsplit, wgf)
         self._wcache["prep"] = (key, out)
-        return out
+        return (*out, ready)
 
     def _ep_call(self, ep_forward, xb, cb, tpi):
         """Expert-parallel pass: over peer memory (b200moe/ep_p2p.py) when the group's GPUs can map each other's memory,

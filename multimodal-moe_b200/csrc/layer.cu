@@ -290,7 +290,7 @@ extern "C" int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* q, int6
 extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, const float* ctx_bias,
                                  const void* wg_split, const void* w1, const float* b1, const void* w2,
                                  const float* b2, void* ws, void* y, int save_for_backward,
-                                 const b200moe_postnorm* pn, void* stream) {
+                                 const b200moe_postnorm* pn, void* weights_ready, void* stream) {
   if (int rc = check_desc(q, "layer_fwd")) return rc;
   B200MOE_REQUIRE(x && wg_split && w1 && b1 && w2 && b2 && ws && y, B200MOE_EINVAL, "layer_fwd: NULL argument");
   int64_t off[B200MOE_WS_COUNT];
@@ -317,8 +317,15 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                     WS(int32_t, B200MOE_WS_SLOT_LIMIT), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
                     WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW), stream));
   STEP("permute", b200moe_permute(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP), stream));
-  STEP("ffn_up", b200moe_ffn_up(WS(void, B200MOE_WS_XP), w1, b1, meta, tile_expert, R, d, F, E,
-                                save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H), pad, stream));
+  {
+    // the bf16 expert weights may still be in preparation on another stream (the router, the plan and the permute do
+    // not need them): join here, just before their first reader
+    if (weights_ready)
+      cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), static_cast<cudaEvent_t>(weights_ready), 0);
+    PdlOffIf np_(weights_ready != nullptr);
+    STEP("ffn_up", b200moe_ffn_up(WS(void, B200MOE_WS_XP), w1, b1, meta, tile_expert, R, d, F, E,
+                                  save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H), pad, stream));
+  }
   STEP("ffn_down", b200moe_ffn_down(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert, R, d, F, E,
                                     WS(void, B200MOE_WS_YO), pad, stream));
   if (pn) {
