@@ -1,6 +1,8 @@
 // HBM-bound row movement: dispatch (permute), combine, their backward passes, casts, column sums.
 // One warp moves one row with 128-bit loads/stores (a row of d bf16 is d/8 16-byte chunks, lanes stride them),
 // so every request is a run of full 32-byte sectors and consecutive lanes touch consecutive addresses.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace b200moe {
@@ -557,8 +559,13 @@ static int unpermute_bwd_impl(const void* dxp, const b200moe::PeerRows& pr, cons
   B200MOE_REQUIRE(dlogits == nullptr || wg != nullptr, B200MOE_EINVAL, "unpermute_bwd: dlogits without wg");
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
-  const bool big = T >= 64 * kNumSMs;   // 8 tokens per warp once 64-token blocks still cover the SMs
-  const int tok = big ? 64 : 16;
+  // 8 tokens per warp (each shared-memory read of wg feeds 64 FMAs) only where the router term is the limit: many
+  // experts and enough tokens that 64-token blocks still cover the SMs; below that the kernel is latency-bound and
+  // small blocks win (tools/unp_bench.py: 76 vs 86 us at E=16 / 65533 tokens, 88 vs 141 us at E=64 / 16384)
+  const bool big = T >= 64 * kNumSMs && E > 16;
+  static const int tt_env = [] { const char* e = getenv("B200MOE_UNP_TT"); return e ? atoi(e) : 0; }();   // experiments
+  const int tt = (tt_env == 2 || tt_env == 4 || tt_env == 8) ? tt_env : (big ? 8 : 2);
+  const int tok = 8 * tt;
   const size_t smem = dlogits ? sizeof(float) * (static_cast<size_t>(E) * 256 + tok * E) : 0;
   static bool configured = false;
   if (!configured) {
@@ -567,6 +574,8 @@ static int unpermute_bwd_impl(const void* dxp, const b200moe::PeerRows& pr, cons
     cudaError_t e2 = cudaFuncSetAttribute(unpermute_bwd_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
     cudaError_t e3 = cudaFuncSetAttribute(unpermute_bwd_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
     cudaError_t e4 = cudaFuncSetAttribute(unpermute_bwd_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    cudaFuncSetAttribute(unpermute_bwd_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
+    cudaFuncSetAttribute(unpermute_bwd_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
     B200MOE_REQUIRE(e1 == cudaSuccess && e2 == cudaSuccess && e3 == cudaSuccess && e4 == cudaSuccess, B200MOE_ECUDA,
                     "unpermute_bwd: cudaFuncSetAttribute failed");
     configured = true;
@@ -576,8 +585,10 @@ static int unpermute_bwd_impl(const void* dxp, const b200moe::PeerRows& pr, cons
 #define UNP_LAUNCH(TT_, P_)                                                                                          \
   launch_k(unpermute_bwd_kernel<TT_, P_>, grid, 256, smem, ST(stream), BF(dxp), row_of_assignment, dlogits, wg, T, k, \
            d, E, BFW(dx), pr)
-  if (big && p2p) UNP_LAUNCH(8, true);
-  else if (big) UNP_LAUNCH(8, false);
+  if (tt == 8 && p2p) UNP_LAUNCH(8, true);
+  else if (tt == 8) UNP_LAUNCH(8, false);
+  else if (tt == 4 && p2p) UNP_LAUNCH(4, true);
+  else if (tt == 4) UNP_LAUNCH(4, false);
   else if (p2p) UNP_LAUNCH(2, true);
   else UNP_LAUNCH(2, false);
 #undef UNP_LAUNCH
