@@ -198,8 +198,6 @@ int b200moe_scatter_rows(const void* in, const int32_t* src_of_row, const int32_
  *                        row_pad 1); writes dest_of_row [send_rows_cap] for the calls below.
  *   ep_p2p_combine     : y[t] = sum_s gate[t,s] * peers' yo[dest_of_row[row_of_assignment[t,s]]].
  *   ep_p2p_combine_bwd : peers' dyp[dest] = gate_of_row[r] * dy[token]; dgate_row[r] = <dy[token], peers' yo[dest]>.
- *                        dgate_row == NULL: stores only; dyp_offset_bytes < 0: dot products only (the two halves can
- *                        then run on different streams).
  *   ep_p2p_unpermute_bwd: b200moe_unpermute_bwd with the dxp rows loaded from the peers.
  *   ep_p2p_pull_rows   : out[r] = peers' buffer[dest_of_row[r]] for every send row (plain copy, no shared memory: runs
  *                        next to the weight-gradient GEMMs on a side stream; b200moe_unpermute_bwd then reads `out`). */

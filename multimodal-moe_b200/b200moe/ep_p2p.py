@@ -187,24 +187,17 @@ class _P2PFunction(torch.autograd.Function):
         f32 = torch.float32
 
         dgate_row = torch.empty((send_cap,), dtype=f32, device=dev)
-        comp = torch.cuda.current_stream()
-        side = _side_stream(mod, dev)
-        side.wait_stream(comp)
-        with torch.cuda.stream(side):                   # stores of gate * dy into the expert ranks (NVLink out) ...
-            _lib.call("b200moe_ep_p2p_combine_bwd", dy.data_ptr(), ar.peers.data_ptr(), ar.off[1], ar.off[2], R,
-                      dest_of_row.data_ptr(), p.token_of_row.data_ptr(), p.gate_of_row.data_ptr(), p.meta.data_ptr(),
-                      send_cap, d, None, side.cuda_stream)
-        # ... next to the gate gradient (loads of the yo rows: NVLink in) and the router gradients that follow from it
-        _lib.call("b200moe_ep_p2p_combine_bwd", dy.data_ptr(), ar.peers.data_ptr(), ar.off[1], -1, R,
+        _lib.call("b200moe_ep_p2p_combine_bwd", dy.data_ptr(), ar.peers.data_ptr(), ar.off[1], ar.off[2], R,
                   dest_of_row.data_ptr(), p.token_of_row.data_ptr(), p.gate_of_row.data_ptr(), p.meta.data_ptr(),
                   send_cap, d, dgate_row.data_ptr(), st)
+        # the router gradients need nothing from the other ranks: they run while the slowest rank's rows arrive
         dlogits = ops.router_bwd_dlogits(r.logits, r.topk_idx, p.row_of_assignment, dgate_row, p.tokens_per_expert,
                                          d_aux_t, mod.normalize_topk, mod.aux_loss_weight, mod.z_loss_weight)
         dwg, dctx = ops.router_bwd_params(dlogits, x2, ctx.tpi, want_dwg=need[2],
                                           want_dctx=bool(ctx.has_ctx and need[1]))
-        comp.wait_stream(side)
         ar.barrier(2)                                   # every rank's dyp rows have landed
         dhpre = ops.ffn_dgrad_down(ar.dyp, w2b, pre, meta, tile_e, row_pad=ar.row_pad)
+        comp = torch.cuda.current_stream()
         dxs = None
         if need[0]:
             ops.ffn_dgrad_up(dhpre, w1b, meta, tile_e, row_pad=ar.row_pad, out=ar.dxp)

@@ -168,36 +168,30 @@ ep_p2p_combine_bwd_kernel(const __nv_bfloat16* __restrict__ dy, PeerRows yo, Pee
                           const int32_t* __restrict__ send_meta, int d, float* __restrict__ dgate_row) {
   const int R = send_meta[0];
   const int nchunk = d >> 3, lane = threadIdx.x & 31;
-  const bool do_dot = dgate_row != nullptr, do_push = dyp.peers != nullptr;   // either half alone, or both
   for (int r = blockIdx.x * kP2pWarps + (threadIdx.x >> 5); r < R; r += gridDim.x * kP2pWarps) {
     const int t = token_of_row[r];
     const int dest = yo.dest_of_row[r];
     if (t < 0 || dest < 0) {
-      if (lane == 0 && do_dot) dgate_row[r] = 0.f;
+      if (lane == 0) dgate_row[r] = 0.f;
       continue;
     }
     const float g = gate_of_row[r];
     const __nv_bfloat16* yrow = peer_row(yo, dest, d);
-    __nv_bfloat16* drow = do_push ? peer_row(dyp, dest, d) : nullptr;
+    __nv_bfloat16* drow = peer_row(dyp, dest, d);
     float dot = 0.f;
     for (int c = lane; c < nchunk; c += 32) {
       float a[8], b[8], o[8];
       unpack8(ldg128(dy + static_cast<size_t>(t) * d + c * 8), a);
-      if (do_dot) {
-        unpack8(ldg128(yrow + c * 8), b);
+      unpack8(ldg128(yrow + c * 8), b);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) dot = fmaf(a[j], b[j], dot);
+      for (int j = 0; j < 8; ++j) {
+        o[j] = g * a[j];
+        dot = fmaf(a[j], b[j], dot);
       }
-      if (do_push) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = g * a[j];
-        stg128(drow + c * 8, pack8(o));
-      }
+      stg128(drow + c * 8, pack8(o));
     }
-    if (do_dot) {
-      dot = warp_sum(dot);
-      if (lane == 0) dgate_row[r] = dot;
-    }
+    dot = warp_sum(dot);
+    if (lane == 0) dgate_row[r] = dot;
   }
 }
 
@@ -284,12 +278,10 @@ extern "C" int b200moe_ep_p2p_combine_bwd(const void* dy, const void* const* pee
                                           const int32_t* token_of_row, const float* gate_of_row,
                                           const int32_t* send_meta, int send_rows_cap, int d, float* dgate_row,
                                           void* stream) {
-  B200MOE_REQUIRE(dy && peers && dest_of_row && d % 8 == 0 && (dgate_row || dyp_offset_bytes >= 0), B200MOE_EINVAL,
-                  "ep_p2p_combine_bwd: bad arguments");
+  B200MOE_REQUIRE(dy && peers && dest_of_row && dgate_row && d % 8 == 0, B200MOE_EINVAL, "ep_p2p_combine_bwd: bad arguments");
   if (int rc = b200moe_check_device()) return rc;
   const unsigned char* const* pp = reinterpret_cast<const unsigned char* const*>(peers);
-  PeerRows yo{pp, yo_offset_bytes, dest_of_row, rows_cap};
-  PeerRows dyp{dyp_offset_bytes >= 0 ? pp : nullptr, dyp_offset_bytes, dest_of_row, rows_cap};   // < 0: no stores
+  PeerRows yo{pp, yo_offset_bytes, dest_of_row, rows_cap}, dyp{pp, dyp_offset_bytes, dest_of_row, rows_cap};
   ep_p2p_combine_bwd_kernel<<<p2p_grid(send_rows_cap), kP2pThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), yo, dyp, token_of_row, gate_of_row, send_meta, d, dgate_row);
   return check_launch("ep_p2p_combine_bwd");
