@@ -313,7 +313,8 @@ int b200moe_layer_profile(int enable);
 int b200moe_layer_pdl(int enable);
 /* Backward-pass fork/join: weight gradients + bias sums and the router's parameter gradients run on two library-owned
  * side streams next to the dgrad chain and are joined to `stream` before b200moe_layer_bwd returns (capturable).
- * mode 0 = off, 1 = on (default; measured 3-12 % faster per step from 3200 to 65600 tokens). */
+ * mode 0 = off, 1 = on (default; measured 3-12 % faster per step from 3200 to 65600 tokens).  The side streams and their
+ * events are per device, not per caller: whole-layer calls on one device must come from one host thread at a time. */
 int b200moe_layer_fork(int mode);
 int b200moe_layer_profile_read(int index, const char** name, float* ms);
 
