@@ -31,6 +31,11 @@ extern "C" {
 #define B200MOE_EARCH (-2)    /* not an sm_100 device */
 #define B200MOE_ECUDA (-3)    /* CUDA runtime / driver error */
 
+/* Expert activation: exact-erf GELU of the encoder FFN (hybrid_encoder.py:157 with zoo/rtdetr/utils.py:160-161) or the
+ * ReLU of the decoder FFN (rtdetrv2_decoder.py:169,187,203: activation="relu"). */
+#define B200MOE_ACT_GELU 0
+#define B200MOE_ACT_RELU 1
+
 #define B200MOE_ROW_PAD 128          /* expert segments of the permuted buffer are padded to this many rows */
 #define B200MOE_ROUTER_BLOCK 128     /* max tokens per router block (granularity of the priority scan) */
 #define B200MOE_META_INTS 8          /* meta[0]=R (padded rows in use) meta[1]=R/128 meta[2]=dropped meta[3]=kept */
@@ -97,6 +102,12 @@ int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int32_t* block
 /* Dispatch: xp[r,:] = x[token_of_row[r],:] (zero rows for pads), r < meta[0]. 128-bit loads/stores. */
 int b200moe_permute(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
                     void* xp, void* stream);
+/* The same dispatch kernel, also preparing the fused combine of b200moe_ffn_down_combine (no memset launches on the
+ * critical path): y_acc [T,d] fp32 := 0, arrive [T,d/32] int32 := 0 (may be NULL), and y[t,:] := 0 (bf16, may be NULL)
+ * for every token that kept no assignment (nothing else writes those rows).  d % 128 == 0. */
+int b200moe_permute_init(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
+                         void* xp, float* y_acc, int32_t* arrive, const int32_t* row_of_assignment, int T, int k,
+                         void* y, void* stream);
 
 /* A.7 combine: y[t,:] = sum_s gate[t,s] * yo[row_of_assignment[t,s],:] in slot order, fp32 accumulate. */
 int b200moe_combine(const void* yo, const int32_t* row_of_assignment, const float* topk_gate,
@@ -108,7 +119,7 @@ int b200moe_combine_bwd(const void* dy, const void* yo, const int32_t* token_of_
                         const int32_t* meta, int rows_cap, int d, void* dyp, float* dgate_row, void* stream);
 
 /* Expert FFN, forward (A.6).  Grouped bf16 GEMMs on tcgen05/TMEM fed by TMA.
- *   up  : pre = xp @ w1[e]^T + b1[e];  h = gelu_erf(pre)      w1 [E,F,d] bf16, b1 [E,F] fp32
+ *   up  : pre = xp @ w1[e]^T + b1[e];  h = act(pre)           w1 [E,F,d] bf16, b1 [E,F] fp32; act = B200MOE_ACT_*
  *   down: yo  = h  @ w2[e]^T + b2[e]                          w2 [E,d,F] bf16, b2 [E,d] fp32
  *   pre may be NULL (inference: nothing saved for backward).
  *   row_pad = the padding b200moe_plan laid the expert segments out with: 128, or 256 -- then 256-row tiles never
@@ -116,20 +127,34 @@ int b200moe_combine_bwd(const void* dy, const void* yo, const int32_t* token_of_
  *   each loading half of the weight tile).  The weight-gradient GEMM pairs along the weight rows by itself.   */
 int b200moe_ffn_up(const void* xp, const void* w1, const float* b1, const int32_t* meta,
                    const int32_t* tile_expert, int rows_cap, int d, int F, int E,
-                   void* pre, void* h, int row_pad, void* stream);
+                   void* pre, void* h, int activation, int row_pad, void* stream);
 int b200moe_ffn_down(const void* h, const void* w2, const float* b2, const int32_t* meta,
                      const int32_t* tile_expert, int rows_cap, int d, int F, int E,
                      void* yo, int row_pad, void* stream);
+/* Down-projection with the gate-weighted combine of A.7 FUSED INTO ITS EPILOGUE (the `linear2` half of
+ * hybrid_encoder.py:157 and the weighted sum over the selected experts in one kernel): for every live row r
+ *   y_acc[token_of_row[r], :] += gate_of_row[r] * bf16(h[r] @ w2[e]^T + b2[e])          (fp32 reductions at L2)
+ * straight from the accumulator registers.  top_k <= 2 only: two fp32 terms commute, so the result does not depend on
+ * the order in which tiles finish and is bit-identical to b200moe_ffn_down + b200moe_combine.
+ *   yo     : [R,d] bf16 expert outputs, stored as b200moe_ffn_down does, or NULL (inference: the backward is its only reader)
+ *   y_acc  : [T,d] fp32, zero on entry (b200moe_permute_init)
+ *   arrive : [T,d/32] int32, zero on entry, or NULL.  With it the thread that delivers the LAST contribution to a
+ *            (token, 32-column chunk) reads the chunk back from L2 and writes y [T,d] bf16: no combine / convert
+ *            launch follows.  Without it the caller finishes from y_acc (b200moe_combine_ln_fwd). */
+int b200moe_ffn_down_combine(const void* h, const void* w2, const float* b2, const int32_t* meta,
+                             const int32_t* tile_expert, const int32_t* token_of_row, const float* gate_of_row,
+                             const int32_t* row_of_assignment, int T, int k, int rows_cap, int d, int F, int E,
+                             void* yo, float* y_acc, int32_t* arrive, void* y, int row_pad, void* stream);
 
 /* Expert FFN, backward.
- *   dgrad_down: dhpre = (dyp @ w2[e]) * gelu_erf'(pre)        [R,F]
+ *   dgrad_down: dhpre = (dyp @ w2[e]) * act'(pre)             [R,F]
  *   dgrad_up  : dxp   = dhpre @ w1[e]                         [R,d]
  *   wgrad     : dw[e] = a[rows of e]^T @ b[rows of e]         a [R,M] bf16, b [R,N] bf16 -> dw [E,M,N] fp32
  *               (dw2 = dyp^T h, dw1 = dhpre^T xp); accumulate != 0 adds into dw
  *   colsum    : db[e,:] = sum over rows of e of a[r,:]        (db2 from dyp, db1 from dhpre)  */
 int b200moe_ffn_dgrad_down(const void* dyp, const void* w2, const void* pre, const int32_t* meta,
                            const int32_t* tile_expert, int rows_cap, int d, int F, int E,
-                           void* dhpre, int row_pad, void* stream);
+                           void* dhpre, int activation, int row_pad, void* stream);
 int b200moe_ffn_dgrad_up(const void* dhpre, const void* w1, const int32_t* meta,
                          const int32_t* tile_expert, int rows_cap, int d, int F, int E,
                          void* dxp, int row_pad, void* stream);
@@ -245,13 +270,20 @@ typedef struct b200moe_layer_desc {
   int32_t rows_cap;           /* b200moe_rows_upper_bound(T, k, E, capacity) */
   int32_t normalize_topk;
   float aux_loss_weight, z_loss_weight;
+  int32_t activation;         /* B200MOE_ACT_GELU | B200MOE_ACT_RELU */
+  int32_t flags;              /* B200MOE_LAYER_* */
 } b200moe_layer_desc;
+/* flags: the fused combine (b200moe_ffn_down_combine) is the default for top_k <= 2; this bit selects the separate
+ * b200moe_ffn_down + b200moe_combine kernels instead (the tested reference of the fused epilogue; top_k > 2 always
+ * takes them). */
+#define B200MOE_LAYER_SEPARATE_COMBINE 1
 
 enum {
   B200MOE_WS_LOGITS = 0, B200MOE_WS_TOPK_IDX, B200MOE_WS_TOPK_GATE, B200MOE_WS_BLOCK_COUNTS, B200MOE_WS_BLOCK_STATS,
   B200MOE_WS_EXPERT_OFFSETS, B200MOE_WS_META, B200MOE_WS_TILE_EXPERT, B200MOE_WS_TOKENS_PER_EXPERT,
   B200MOE_WS_KEPT_PER_EXPERT, B200MOE_WS_LOSSES, B200MOE_WS_SLOT_LIMIT, B200MOE_WS_ROW_OF_ASSIGNMENT,
   B200MOE_WS_TOKEN_OF_ROW, B200MOE_WS_GATE_OF_ROW, B200MOE_WS_XP, B200MOE_WS_PRE, B200MOE_WS_H, B200MOE_WS_YO,
+  B200MOE_WS_Y_ACC /* [T,d] fp32 */, B200MOE_WS_ARRIVE /* [T,d/32] int32 */,
   B200MOE_WS_COUNT
 };
 enum {
@@ -277,18 +309,21 @@ typedef struct b200moe_postnorm_bwd {
   float* dgamma;            /* [d] out */
   float* dbeta;             /* [d] out */
 } b200moe_postnorm_bwd;
+/* y_acc != NULL: the combine already happened in the down-projection's epilogue; the pre-norm sum is y_acc + residual
+ * (yo / row_of_assignment / topk_gate are then unused and may be NULL). */
 int b200moe_combine_ln_fwd(const void* yo, const int32_t* row_of_assignment, const float* topk_gate,
-                           const void* residual, const float* gamma, const float* beta, float eps, int T, int k,
-                           int d, void* out, float* mean_rstd, void* stream);
+                           const float* y_acc, const void* residual, const float* gamma, const float* beta, float eps,
+                           int T, int k, int d, void* out, float* mean_rstd, void* stream);
 int64_t b200moe_ln_scratch_floats(int T, int d);
 int b200moe_combine_ln_bwd(const void* dout, const void* yo, const int32_t* row_of_assignment,
-                           const float* topk_gate, const void* residual, const float* gamma,
+                           const float* topk_gate, const float* y_acc, const void* residual, const float* gamma,
                            const float* mean_rstd, int T, int k, int d, void* dv, float* scratch, float* dgamma,
                            float* dbeta, void* stream);
 
 int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* desc, int64_t* offsets /* [B200MOE_WS_COUNT] */);
 int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* desc, int64_t* offsets /* [B200MOE_BWS_COUNT] */);
-/* router -> plan -> permute -> up(+GELU) -> down -> combine.  x [T,d] bf16; ctx_bias [B,E] fp32 or NULL; wg_split
+/* router -> plan -> permute -> up(+activation) -> down with the combine fused into its epilogue (top_k <= 2; else, or with
+ * B200MOE_LAYER_SEPARATE_COMBINE: down -> combine).  x [T,d] bf16; ctx_bias [B,E] fp32 or NULL; wg_split
  * from b200moe_prepare_weights; w1 [E,F,d], w2 [E,d,F] bf16; b1 [E,F], b2 [E,d] fp32; y [T,d] bf16.
  * save_for_backward == 0 skips the pre-activation store. */
 int b200moe_layer_fwd(const b200moe_layer_desc* desc, const void* x, const float* ctx_bias, const void* wg_split,

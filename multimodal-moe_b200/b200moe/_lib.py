@@ -28,11 +28,13 @@ SIGNATURES = {
     "b200moe_router_fwd": [_P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],
     "b200moe_plan": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b200moe_permute": [_P, _P, _P, _I, _I, _P, _P],
+    "b200moe_permute_init": [_P, _P, _P, _I, _I, _P, _P, _P, _P, _I, _I, _P, _P],
     "b200moe_combine": [_P, _P, _P, _I, _I, _I, _P, _P],
     "b200moe_combine_bwd": [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P],
-    "b200moe_ffn_up": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _P],
+    "b200moe_ffn_up": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _I, _P],
     "b200moe_ffn_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
-    "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
+    "b200moe_ffn_down_combine": [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _I, _P],
+    "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _I, _P],
     "b200moe_ffn_dgrad_up": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
     "b200moe_ffn_wgrad": [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
     "b200moe_colsum": [_P, _I, _P, _P, _I, _P, _P, _I, _I, _P],
@@ -54,9 +56,9 @@ SIGNATURES = {
     "b200moe_layer_bwd_ws_layout": [_P, _P],
     "b200moe_layer_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P],
     "b200moe_layer_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P],
-    "b200moe_combine_ln_fwd": [_P, _P, _P, _P, _P, _P, _F, _I, _I, _I, _P, _P, _P],
+    "b200moe_combine_ln_fwd": [_P, _P, _P, _P, _P, _P, _P, _F, _I, _I, _I, _P, _P, _P],
     "b200moe_ln_scratch_floats": [_I, _I],
-    "b200moe_combine_ln_bwd": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P],
+    "b200moe_combine_ln_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P],
     "b200moe_router_bwd_dlogits": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _P, _P],
     "b200moe_dwg_scratch_floats": [_I, _I, _I],
     "b200moe_router_bwd_dwg": [_P, _P, _I, _I, _I, _P, _P, _P],
@@ -89,12 +91,18 @@ class LayerDesc(C.Structure):
     """b200moe_layer_desc of include/b200moe.h."""
     _fields_ = [("T", C.c_int32), ("d", C.c_int32), ("F", C.c_int32), ("E", C.c_int32), ("k", C.c_int32),
                 ("tokens_per_image", C.c_int32), ("capacity", C.c_int32), ("rows_cap", C.c_int32),
-                ("normalize_topk", C.c_int32), ("aux_loss_weight", C.c_float), ("z_loss_weight", C.c_float)]
+                ("normalize_topk", C.c_int32), ("aux_loss_weight", C.c_float), ("z_loss_weight", C.c_float),
+                ("activation", C.c_int32), ("flags", C.c_int32)]
+
+
+ACT_GELU, ACT_RELU = 0, 1                 # B200MOE_ACT_*
+ACTIVATIONS = {"gelu": ACT_GELU, "relu": ACT_RELU}
+LAYER_SEPARATE_COMBINE = 1                # B200MOE_LAYER_SEPARATE_COMBINE
 
 
 WS_NAMES = ("logits", "topk_idx", "topk_gate", "block_counts", "block_stats", "expert_offsets", "meta", "tile_expert",
             "tokens_per_expert", "kept_per_expert", "losses", "slot_limit", "row_of_assignment", "token_of_row",
-            "gate_of_row", "xp", "pre", "h", "yo")
+            "gate_of_row", "xp", "pre", "h", "yo", "y_acc", "arrive")
 BWS_NAMES = ("dyp", "dgate_row", "dhpre", "dxp", "dlogits", "dwg_scratch")
 
 _lib: Optional[C.CDLL] = None
@@ -137,6 +145,7 @@ KERNELS_PER_CALL = {
     "b200moe_layer_fwd": 7, "b200moe_layer_bwd": 11, "b200moe_combine_ln_fwd": 1, "b200moe_combine_ln_bwd": 2, "b200moe_router_bwd_params": 2, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
     "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
+    "b200moe_permute_init": 1, "b200moe_ffn_down_combine": 1,
     "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,
     "b200moe_unpermute_bwd": 1, "b200moe_ep_recv_plan": 1, "b200moe_ep_hist": 1, "b200moe_ep_route_tables": 1, "b200moe_scatter_rows": 1,
 }
@@ -161,7 +170,12 @@ class Counters:
         return out
 
 
+PROFILING = False      # per-kernel event timing is recording: the layer keeps every kernel on one stream meanwhile
+
+
 def layer_profile(enable: bool) -> None:
+    global PROFILING
+    PROFILING = bool(enable)
     load().b200moe_layer_profile(int(enable))
 
 

@@ -203,7 +203,7 @@ class _EPFunction(torch.autograd.Function):
             ch.offs, ch.meta, ch.tile_e, ch.src = ops.ep_recv_plan(recv_counts[c], seg_dev, ELc, ch.cap)
             ch.xp = ops.permute(xr, ch.src, ch.meta, ch.cap)
             ch.pre, ch.h = ops.ffn_up(ch.xp, w1b[ch.lo:ch.hi], b1f[ch.lo:ch.hi], ch.meta, ch.tile_e,
-                                      save_pre=need_grad)
+                                      save_pre=need_grad, activation=_lib.ACTIVATIONS[mod.activation])
             yo = ops.ffn_down(ch.h, w2b[ch.lo:ch.hi], b2f[ch.lo:ch.hi], ch.meta, ch.tile_e)
             yr = ops.scatter_rows(yo, ch.src, ch.meta, max(ch.n_recv, 1))
             done = torch.cuda.Event()
@@ -275,7 +275,8 @@ class _EPFunction(torch.autograd.Function):
             dyrs[c].record_stream(comp)
             n = ch.hi - ch.lo
             dyp = ops.permute(dyrs[c], ch.src, ch.meta, ch.cap)
-            dhpre = ops.ffn_dgrad_down(dyp, w2b[ch.lo:ch.hi], ch.pre, ch.meta, ch.tile_e)
+            dhpre = ops.ffn_dgrad_down(dyp, w2b[ch.lo:ch.hi], ch.pre, ch.meta, ch.tile_e,
+                                       activation=_lib.ACTIVATIONS[mod.activation])
             if need[0]:
                 dxp = ops.ffn_dgrad_up(dhpre, w1b[ch.lo:ch.hi], ch.meta, ch.tile_e)
                 dxr = ops.scatter_rows(dxp, ch.src, ch.meta, max(ch.n_recv, 1))

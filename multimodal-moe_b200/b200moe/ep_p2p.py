@@ -150,7 +150,8 @@ class _P2PFunction(torch.autograd.Function):
                   p.meta.data_ptr(), dest_off.data_ptr(), ar.peers.data_ptr(), ar.off[0], R, send_cap, E, EL, d,
                   dest_of_row.data_ptr(), st)
         ar.barrier(0)                                   # every rank's rows have landed in xp
-        pre, h = ops.ffn_up(ar.xp, w1b, b1f, meta, tile_e, save_pre=need_grad, row_pad=ar.row_pad)
+        pre, h = ops.ffn_up(ar.xp, w1b, b1f, meta, tile_e, save_pre=need_grad, row_pad=ar.row_pad,
+                            activation=_lib.ACTIVATIONS[mod.activation])
         ops.ffn_down(h, w2b, b2f, meta, tile_e, row_pad=ar.row_pad, out=ar.yo)
         ar.barrier(1)                                   # every rank's yo is complete
         y = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
@@ -196,7 +197,8 @@ class _P2PFunction(torch.autograd.Function):
         dwg, dctx = ops.router_bwd_params(dlogits, x2, ctx.tpi, want_dwg=need[2],
                                           want_dctx=bool(ctx.has_ctx and need[1]))
         ar.barrier(2)                                   # every rank's dyp rows have landed
-        dhpre = ops.ffn_dgrad_down(ar.dyp, w2b, pre, meta, tile_e, row_pad=ar.row_pad)
+        dhpre = ops.ffn_dgrad_down(ar.dyp, w2b, pre, meta, tile_e, row_pad=ar.row_pad,
+                                   activation=_lib.ACTIVATIONS[mod.activation])
         comp = torch.cuda.current_stream()
         dxs = None
         if need[0]:

@@ -27,7 +27,8 @@ _WS_DTYPES = {"logits": torch.float32, "topk_idx": torch.int32, "topk_gate": tor
               "meta": torch.int32, "tile_expert": torch.int32, "tokens_per_expert": torch.int32,
               "kept_per_expert": torch.int32, "losses": torch.float32, "slot_limit": torch.int32,
               "row_of_assignment": torch.int32, "token_of_row": torch.int32, "gate_of_row": torch.float32,
-              "xp": torch.bfloat16, "pre": torch.bfloat16, "h": torch.bfloat16, "yo": torch.bfloat16}
+              "xp": torch.bfloat16, "pre": torch.bfloat16, "h": torch.bfloat16, "yo": torch.bfloat16,
+              "y_acc": torch.float32, "arrive": torch.int32}
 
 
 def _f32c(t: torch.Tensor) -> torch.Tensor:
@@ -48,8 +49,10 @@ class _LayerPlan:
         rows_cap = lib.b200moe_layer_rows_cap(T, k, E, cap, d, F)
         if rows_cap <= 0:
             raise RuntimeError(f"b200moe: bad layer shape T={T} k={k} E={E}")
+        self.fused = bool(mod.fused_combine) and k <= 2
         self.desc = _lib.LayerDesc(T, d, F, E, k, tpi, cap, rows_cap, int(mod.normalize_topk),
-                                   mod.aux_loss_weight, mod.z_loss_weight)
+                                   mod.aux_loss_weight, mod.z_loss_weight, _lib.ACTIVATIONS[mod.activation],
+                                   0 if mod.fused_combine else _lib.LAYER_SEPARATE_COMBINE)
         self.desc_ptr = C.addressof(self.desc)
         off = (C.c_int64 * len(_lib.WS_NAMES))()
         self.ws_bytes = lib.b200moe_layer_ws_layout(self.desc_ptr, C.addressof(off))
@@ -64,7 +67,8 @@ class _LayerPlan:
                       "block_stats": (nblk, E + 1), "expert_offsets": (E + 1,), "meta": (8,),
                       "tile_expert": (R // 128,), "tokens_per_expert": (E,), "kept_per_expert": (E,), "losses": (3,),
                       "slot_limit": (2 * k * E,), "row_of_assignment": (T, k), "token_of_row": (R,),
-                      "gate_of_row": (R,), "xp": (R, d), "pre": (R, F), "h": (R, F), "yo": (R, d)}
+                      "gate_of_row": (R,), "xp": (R, d), "pre": (R, F), "h": (R, F), "yo": (R, d),
+                      "y_acc": (T, d) if self.fused else (0, d), "arrive": (T, d // 32) if self.fused else (0, d // 32)}
         self.capacity, self.rows_cap = cap, rows_cap
 
     def view(self, ws: torch.Tensor, name: str) -> torch.Tensor:
@@ -152,7 +156,9 @@ class _MoEFunction(torch.autograd.Function):
         E = mod.num_experts
         need_grad = any(ctx.needs_input_grad)   # forward runs under no_grad: ask autograd, not the grad mode
         pl = mod._layer_plan(T, tpi)
-        w1b, w2b, wsplit, wgf, ready = mod._prepared(w1, w2, wg, overlap=True)
+        # (while bench.py's per-kernel timing records, the casts stay on the current stream: a cast running next to the
+        # router / plan / permute would steal their HBM bandwidth and the numbers would not be those of isolated kernels)
+        w1b, w2b, wsplit, wgf, ready = mod._prepared(w1, w2, wg, overlap=not _lib.PROFILING)
         b1f, b2f = _f32c(b1), _f32c(b2)
         st = _lib.stream_ptr()
         cb = None
@@ -265,8 +271,9 @@ class ContextMoE(nn.Module):
                  z_loss_weight: float = 1e-3, normalize_topk: bool = True, ep_group=None,
                  ep_p2p: Optional[bool] = None):
         super().__init__()
-        if activation != "gelu":
-            raise ValueError("only exact-erf GELU is defined for this layer (zoo/rtdetr/utils.py:160-161)")
+        if activation not in _lib.ACTIVATIONS:
+            # encoder FFN: exact-erf GELU (zoo/rtdetr/utils.py:160-161); decoder FFN: ReLU (rtdetrv2_decoder.py:169)
+            raise ValueError(f"activation must be one of {sorted(_lib.ACTIVATIONS)}, got {activation!r}")
         if not 1 <= top_k <= num_experts:
             raise ValueError("top_k must be in [1, num_experts]")
         if num_experts > 64 or top_k > 8:
@@ -280,6 +287,10 @@ class ContextMoE(nn.Module):
         self.normalize_topk = bool(normalize_topk)
         self.context_vocab_sizes = tuple(context_vocab_sizes)
         self.context_dim = context_dim
+        self.activation = activation
+        # combine fused into the down-projection's epilogue (top_k <= 2); False selects the separate down + combine
+        # kernels, the tested reference of the fused epilogue
+        self.fused_combine = True
         self.ep_group = ep_group
         self.ep_p2p = ep_p2p          # None: peer-memory dispatch when available; False: NCCL all-to-all; True: required
         self.ep_chunks = 1            # groups of local experts whose all-to-all overlaps the other groups' GEMMs
@@ -354,27 +365,19 @@ class ContextMoE(nn.Module):
             if self.ctx_proj is not None:
                 nn.init.normal_(self.ctx_proj.weight, std=0.02)
 
-    def _bf16_weight(self, name: str, w: torch.Tensor) -> torch.Tensor:
-        """bf16 operand copy of a master weight, re-cast only when the parameter changed (version counter)."""
-        if w.dtype == torch.bfloat16:
-            return w.detach().contiguous()
-        key = (w.data_ptr(), w._version, tuple(w.shape))
-        hit = self._wcache.get(name)
-        if hit is not None and hit[0] == key:
-            return hit[1]
-        wb = ops.cast_bf16(w.detach())
-        self._wcache[name] = (key, wb)
-        return wb
-
     def _stash(self, r, p):
         self._last = (r, p)
 
     def _layer_plan(self, T: int, tpi: int) -> _LayerPlan:
-        pl = self._plans.get((T, tpi))
+        # everything the descriptor is built from: a later change of capacity_factor, the loss weights, ... must not
+        # be served a stale plan
+        key = (T, tpi, self.capacity_factor, self.normalize_topk, self.aux_loss_weight, self.z_loss_weight,
+               self.activation, self.fused_combine)
+        pl = self._plans.get(key)
         if pl is None:
             if len(self._plans) > 64:       # multiscale training varies T per step (dataloader.yml:22)
                 self._plans.clear()
-            pl = self._plans[(T, tpi)] = _LayerPlan(self, T, tpi)
+            pl = self._plans[key] = _LayerPlan(self, T, tpi)
         return pl
 
     def _prepared(self, w1, w2, wg, overlap: bool = False):
@@ -445,14 +448,6 @@ class ContextMoE(nn.Module):
             voc = (C.c_int32 * len(tabs))(*[t.shape[0] for t in tabs])
             keep = self.__dict__["_ctx_keep"] = (key, arr, voc, C.addressof(arr), C.addressof(voc))
         return keep[3], keep[4]
-
-    def context_bias(self, context: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
-        """A.2: ctx_bias[B,E] = concat_i Embed_i(context[:, i]) @ Wc^T (fp32 regardless of autocast)."""
-        if context is None or self.ctx_proj is None:
-            return None
-        with torch.autocast(device_type=context.device.type, enabled=False):
-            emb = torch.cat([m(context[:, i]) for i, m in enumerate(self.ctx_embed)], dim=-1)
-            return torch.nn.functional.linear(emb.float(), self.ctx_proj.weight.float())
 
     def forward_post_norm(self, x: torch.Tensor, residual: torch.Tensor, norm: nn.LayerNorm,
                           context: Optional[torch.Tensor] = None) -> torch.Tensor:

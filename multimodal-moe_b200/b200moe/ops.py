@@ -138,14 +138,42 @@ def combine_bwd(dy: torch.Tensor, yo: Optional[torch.Tensor], token_of_row: torc
     return dyp, dgate_row
 
 
-def ffn_up(xp, w1, b1, meta, tile_expert, save_pre: bool = True, row_pad: int = ROW_PAD):
+def ffn_up(xp, w1, b1, meta, tile_expert, save_pre: bool = True, row_pad: int = ROW_PAD,
+           activation: int = _lib.ACT_GELU):
     rows_cap, d = xp.shape
     E, F, _ = w1.shape
     pre = _empty((rows_cap, F), torch.bfloat16, xp.device) if save_pre else None
     h = _empty((rows_cap, F), torch.bfloat16, xp.device)
     call("b200moe_ffn_up", ptr(xp), ptr(w1), ptr(b1), ptr(meta), ptr(tile_expert), rows_cap, d, F, E, ptr(pre),
-         ptr(h), row_pad, stream_ptr())
+         ptr(h), activation, row_pad, stream_ptr())
     return pre, h
+
+
+def permute_init(x: torch.Tensor, token_of_row: torch.Tensor, meta: torch.Tensor, rows_cap: int,
+                 row_of_assignment: torch.Tensor, finalize: bool = True):
+    """Dispatch + the zero state of the fused combine: (xp, y_acc [T,d] fp32, arrive [T,d/32] | None, y [T,d] | None)."""
+    T, d = x.shape
+    k = row_of_assignment.shape[1]
+    xp = _empty((rows_cap, d), torch.bfloat16, x.device)
+    y_acc = _empty((T, d), torch.float32, x.device)
+    arrive = _empty((T, d // 32), torch.int32, x.device) if finalize else None
+    y = _empty((T, d), torch.bfloat16, x.device) if finalize else None
+    call("b200moe_permute_init", ptr(x), ptr(token_of_row), ptr(meta), rows_cap, d, ptr(xp), ptr(y_acc), ptr(arrive),
+         ptr(row_of_assignment), T, k, ptr(y), stream_ptr())
+    return xp, y_acc, arrive, y
+
+
+def ffn_down_combine(h, w2, b2, meta, tile_expert, token_of_row, gate_of_row, row_of_assignment, y_acc, arrive, y,
+                     row_pad: int = ROW_PAD, save_yo: bool = True):
+    """Down-projection with the combine fused into its epilogue (top_k <= 2).  Returns yo (or None)."""
+    rows_cap, F = h.shape
+    E, d, _ = w2.shape
+    T, k = row_of_assignment.shape
+    yo = _empty((rows_cap, d), torch.bfloat16, h.device) if save_yo else None
+    call("b200moe_ffn_down_combine", ptr(h), ptr(w2), ptr(b2), ptr(meta), ptr(tile_expert), ptr(token_of_row),
+         ptr(gate_of_row), ptr(row_of_assignment), T, k, rows_cap, d, F, E, ptr(yo), ptr(y_acc), ptr(arrive), ptr(y),
+         row_pad, stream_ptr())
+    return yo
 
 
 def ffn_down(h, w2, b2, meta, tile_expert, row_pad: int = ROW_PAD, out: Optional[torch.Tensor] = None):
@@ -157,12 +185,12 @@ def ffn_down(h, w2, b2, meta, tile_expert, row_pad: int = ROW_PAD, out: Optional
     return yo
 
 
-def ffn_dgrad_down(dyp, w2, pre, meta, tile_expert, row_pad: int = ROW_PAD):
+def ffn_dgrad_down(dyp, w2, pre, meta, tile_expert, row_pad: int = ROW_PAD, activation: int = _lib.ACT_GELU):
     rows_cap, d = dyp.shape
     E, _, F = w2.shape
     dhpre = _empty((rows_cap, F), torch.bfloat16, dyp.device)
     call("b200moe_ffn_dgrad_down", ptr(dyp), ptr(w2), ptr(pre), ptr(meta), ptr(tile_expert), rows_cap, d, F, E,
-         ptr(dhpre), row_pad, stream_ptr())
+         ptr(dhpre), activation, row_pad, stream_ptr())
     return dhpre
 
 

@@ -14,8 +14,10 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT_DIR = os.path.join(HERE, "b200moe")
-LIB = os.path.join(OUT_DIR, "libb200moe.so")
-OBJ_DIR = os.path.join(HERE, "build")
+# B200MOE_BUILD_DIR / B200MOE_LIB_OUT redirect the objects / the library (compile checks that must not replace the
+# library a queued GPU run is about to pick up)
+LIB = os.environ.get("B200MOE_LIB_OUT", os.path.join(OUT_DIR, "libb200moe.so"))
+OBJ_DIR = os.environ.get("B200MOE_BUILD_DIR", os.path.join(HERE, "build"))
 SOURCES = ["api.cu", "router.cu", "router_bwd.cu", "plan.cu", "movement.cu", "gemm.cu", "ep.cu", "ep_p2p.cu", "layer.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
@@ -37,7 +39,9 @@ def _stale(target: str, deps: list[str]) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_lib(force: bool = False, verbose: bool = False) -> str:
+def build_lib(force: bool = False, verbose: bool = False, report: list | None = None) -> str:
+    """Compile every stale (or, with `force`, every) translation unit and link.  `report` receives the names of the
+    objects that were actually rebuilt."""
     os.makedirs(OBJ_DIR, exist_ok=True)
     extra = ["-Xptxas", "-v"] if verbose else []
 
@@ -50,6 +54,8 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
                 raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
             if verbose:
                 sys.stderr.write(r.stderr)
+            if report is not None:
+                report.append(os.path.basename(obj))
         return obj
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
@@ -59,6 +65,8 @@ def build_lib(force: bool = False, verbose: bool = False) -> str:
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+        if report is not None:
+            report.append(os.path.basename(LIB))
     return LIB
 
 

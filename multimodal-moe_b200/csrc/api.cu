@@ -16,7 +16,27 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 
-static long long g_launches = 0;   // kernels launched by this library (every launch site ends in check_launch)
+static std::atomic<long long> g_launches{0};   // kernels launched by this library (every launch site ends in check_launch)
+
+int current_device() {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return -1; }
+  return dev;
+}
+
+int num_sms() {
+  static std::atomic<int> cached[64];
+  const int dev = current_device();
+  if (dev < 0 || dev >= 64) return 148;
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n > 0) return n;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    return 148;
+  }
+  cached[dev].store(n, std::memory_order_relaxed);
+  return n;
+}
 
 int check_launch(const char* what) {
   cudaError_t e = cudaGetLastError();
@@ -24,7 +44,7 @@ int check_launch(const char* what) {
     set_error("%s: %s", what, cudaGetErrorString(e));
     return B200MOE_ECUDA;
   }
-  ++g_launches;
+  g_launches.fetch_add(1, std::memory_order_relaxed);
   return B200MOE_OK;
 }
 
@@ -35,9 +55,7 @@ extern "C" {
 int b200moe_version(void) { return 100; }
 
 int64_t b200moe_launch_count(int reset) {
-  const long long n = b200moe::g_launches;
-  if (reset) b200moe::g_launches = 0;
-  return n;
+  return reset ? b200moe::g_launches.exchange(0) : b200moe::g_launches.load();
 }
 
 const char* b200moe_last_error(void) { return b200moe::g_err; }
@@ -73,7 +91,7 @@ int b200moe_layer_row_pad(int T, int k, int E, int capacity, int d, int F) {
   long long kept = 1LL * T * k;
   if (capacity >= 0 && 1LL * E * capacity < kept) kept = 1LL * E * capacity;
   // CTA pairs pay off once the narrower GEMM (N = d) still has two waves of 256 x 256 tiles
-  return (kept / 256) * (d / 256) >= 2LL * 148 ? 256 : B200MOE_ROW_PAD;
+  return (kept / 256) * (d / 256) >= 2LL * b200moe::num_sms() ? 256 : B200MOE_ROW_PAD;
 }
 
 int b200moe_layer_rows_cap(int T, int k, int E, int capacity, int d, int F) {

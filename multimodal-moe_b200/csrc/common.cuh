@@ -6,6 +6,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 #include "../../include/b200moe.h"
 
 namespace b200moe {
@@ -69,7 +71,17 @@ inline cudaError_t launch_k_pair(void (*kern)(KArgs...), dim3 grid, dim3 block, 
 }
 #endif
 
-constexpr int kNumSMs = 148;
+// Multiprocessors of the current device (148 on a B200), read once per device (api.cu); 148 when no device is visible
+// (the pure layout helpers of the ABI are callable on a CPU-only box).
+int num_sms();
+int current_device();          // cudaGetDevice; -1 on failure
+// One-time, per-device kernel configuration (cudaFuncSetAttribute is a per-device attribute): `done` is false the first
+// time a launcher runs on a device; two threads racing through it both set the same attribute, which is harmless.
+struct DeviceOnce {
+  std::atomic<unsigned long long> mask{0};
+  bool done(int dev) const { return dev >= 0 && dev < 64 && ((mask.load(std::memory_order_acquire) >> dev) & 1ull); }
+  void set(int dev) { if (dev >= 0 && dev < 64) mask.fetch_or(1ull << dev, std::memory_order_release); }
+};
 constexpr int kRowPad = 128;          // every expert segment of the permuted buffer starts at a multiple of this
 constexpr int kRouterTokPerBlock = 128;  // max tokens per router/plan block (granularity of the priority scan)
 // Tokens per router block: one 128-token tcgen05 M tile (router.cu).  Router, plan and the host wrappers all use this.
@@ -116,6 +128,21 @@ __device__ __forceinline__ uint4 pack8(const float (&v)[8]) {
   uint4 r;
   r.x = float2_to_bf16x2(v[0], v[1]); r.y = float2_to_bf16x2(v[2], v[3]);
   r.z = float2_to_bf16x2(v[4], v[5]); r.w = float2_to_bf16x2(v[6], v[7]);
+  return r;
+}
+
+// The A.7 combine y[t] = sum_s g_s * yo_s, fp32, slot order: product and sum are rounded separately (no FMA contraction)
+// and flush subnormals, which is exactly what an fp32 reduction at L2 (red.global.add.f32) does with a pre-multiplied
+// term.  A sum of k <= 2 such terms does not depend on their order, so the down-projection's fused epilogue (terms
+// arrive in tile order) and the separate combine kernels (slot order) produce the same bits.
+__device__ __forceinline__ float combine_term(float g, float v) {
+  float r;
+  asm("mul.rn.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(g), "f"(v));
+  return r;
+}
+__device__ __forceinline__ float combine_add(float acc, float term) {
+  float r;
+  asm("add.rn.ftz.f32 %0, %1, %2;" : "=f"(r) : "f"(acc), "f"(term));
   return r;
 }
 

@@ -153,7 +153,7 @@ ep_p2p_combine_kernel(PeerRows pr, const int32_t* __restrict__ row_of_assignment
         float v[8];
         unpack8(ldg128(src[s] + c * 8), v);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = fmaf(g[s], v[j], acc[j]);
+        for (int j = 0; j < 8; ++j) acc[j] = combine_add(acc[j], combine_term(g[s], v[j]));
       }
       stg128(y + static_cast<size_t>(t) * d + c * 8, pack8(acc));
     }
@@ -216,7 +216,7 @@ ep_p2p_pull_rows_kernel(PeerRows pr, const int32_t* __restrict__ send_meta, int 
 
 static int p2p_grid(int rows) {
   int g = (rows + kP2pWarps - 1) / kP2pWarps;
-  const int mx = kNumSMs * 8;
+  const int mx = num_sms() * 8;
   return g < 1 ? 1 : (g > mx ? mx : g);
 }
 

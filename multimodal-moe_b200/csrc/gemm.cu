@@ -20,7 +20,10 @@
 
 namespace b200moe {
 
-enum : int { EPI_UP = 0, EPI_DOWN = 1, EPI_DGRAD_DOWN = 2, EPI_DGRAD_UP = 3, EPI_WGRAD = 4 };
+// EPI_DOWN_COMBINE: the down-projection with the gate-weighted combine of A.7 fused into its epilogue (y accumulated in
+// fp32 straight from the accumulator registers; the expert outputs yo are stored only when the backward needs them).
+enum : int { EPI_UP = 0, EPI_DOWN = 1, EPI_DGRAD_DOWN = 2, EPI_DGRAD_UP = 3, EPI_WGRAD = 4, EPI_DOWN_COMBINE = 5 };
+enum : int { ACT_GELU = 0, ACT_RELU = 1 };   // encoder FFN (hybrid_encoder.py:157, utils.py:160-161) / decoder FFN (rtdetrv2_decoder.py:169)
 
 constexpr int BM = 128;
 constexpr int BK = 64;
@@ -45,7 +48,20 @@ struct GemmArgs {
   __nv_bfloat16* out1;            // EPI_UP: second output (pre) or null
   float* outf;                    // EPI_WGRAD: [E,M,N]
   int accumulate;
+  int act;                        // EPI_UP / EPI_DGRAD_DOWN: ACT_GELU or ACT_RELU
+  // EPI_DOWN_COMBINE
+  const int32_t* token_of_row;       // [R], -1 = pad row
+  const float* gate_of_row;          // [R]
+  const int32_t* row_of_assignment;  // [T,k]: how many contributions a token receives
+  int topk;
+  float* yacc;                       // [T,N] fp32, zero before the launch
+  int32_t* arrive;                   // [T,N/32] zero before the launch, or null: the caller finishes y from yacc
+  __nv_bfloat16* yout;               // [T,N] bf16, written by the last contribution to a (token, 32-column chunk)
 };
+
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
 
 template <int BN, bool CTA2>
 struct SmemCfg {
@@ -229,6 +245,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int quarter = warp & 3;              // TMEM lane quarter this warp may read
     const int cgroup = (warp - 2) >> 2;        // which share of the tile's columns
     constexpr int kChunksPerWarp = (BN / 32) / (kEpiWarps / 4);
+    constexpr bool kCombine = (EPI == EPI_DOWN_COMBINE);
     unsigned char* stg = stage_out + (warp - 2) * kStgBytes;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -246,6 +263,16 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tma_store_wait_read0();
         mbar_arrive_expect_tx(&ld_bar[warp - 2], kStgBytes);
         tma_load_2d(stg, &tmC1, &ld_bar[warp - 2], n_tile * BN + cgroup * kChunksPerWarp * 32, row0);
+      }
+      // fused combine: this thread's row belongs to token `tok` (-1: pad row) with gate `gate`; the token receives
+      // `need` contributions (its kept assignments) to every column
+      int tok = -1, need = 0;
+      float gate = 0.f;
+      if (kCombine) {
+        tok = args.token_of_row[grow];
+        gate = args.gate_of_row[grow];
+        if (tok >= 0 && args.arrive)
+          for (int s = 0; s < args.topk; ++s) need += args.row_of_assignment[static_cast<size_t>(tok) * args.topk + s] >= 0;
       }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
@@ -265,7 +292,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           for (int j = 0; j < 4; ++j) pr[j] = *reinterpret_cast<const uint4*>(stg + lane * 64 + ((j ^ swz_l) << 4));
         }
         float4 bv[8];
-        if (EPI == EPI_UP || EPI == EPI_DOWN) {
+        if (EPI == EPI_UP || EPI == EPI_DOWN || kCombine) {
           const float* bp = args.bias + static_cast<size_t>(e) * args.N + col0;
 #pragma unroll
           for (int j = 0; j < 8; ++j) bv[j] = __ldg(reinterpret_cast<const float4*>(bp) + j);
@@ -293,7 +320,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           float f[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-          if (EPI == EPI_UP || EPI == EPI_DOWN) {
+          if (EPI == EPI_UP || EPI == EPI_DOWN || kCombine) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
               f[4 * j] += bv[j].x; f[4 * j + 1] += bv[j].y; f[4 * j + 2] += bv[j].z; f[4 * j + 3] += bv[j].w;
@@ -319,31 +346,81 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           }
           if (EPI == EPI_UP) {
+            if (args.act == ACT_RELU) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
-          }
-          if (EPI == EPI_DGRAD_DOWN) {
+              for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+            } else {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              float2 t;
-              t = bf16x2_to_float2(pr[j].x); f[8 * j] *= gelu_erf_grad(t.x); f[8 * j + 1] *= gelu_erf_grad(t.y);
-              t = bf16x2_to_float2(pr[j].y); f[8 * j + 2] *= gelu_erf_grad(t.x); f[8 * j + 3] *= gelu_erf_grad(t.y);
-              t = bf16x2_to_float2(pr[j].z); f[8 * j + 4] *= gelu_erf_grad(t.x); f[8 * j + 5] *= gelu_erf_grad(t.y);
-              t = bf16x2_to_float2(pr[j].w); f[8 * j + 6] *= gelu_erf_grad(t.x); f[8 * j + 7] *= gelu_erf_grad(t.y);
+              for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
             }
           }
+          if (EPI == EPI_DGRAD_DOWN) {
+            if (args.act == ACT_RELU) {      // d relu(v)/dv = [v > 0] (0 at v == 0, as torch)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                float2 t;
+                t = bf16x2_to_float2(pr[j].x); f[8 * j] = t.x > 0.f ? f[8 * j] : 0.f; f[8 * j + 1] = t.y > 0.f ? f[8 * j + 1] : 0.f;
+                t = bf16x2_to_float2(pr[j].y); f[8 * j + 2] = t.x > 0.f ? f[8 * j + 2] : 0.f; f[8 * j + 3] = t.y > 0.f ? f[8 * j + 3] : 0.f;
+                t = bf16x2_to_float2(pr[j].z); f[8 * j + 4] = t.x > 0.f ? f[8 * j + 4] : 0.f; f[8 * j + 5] = t.y > 0.f ? f[8 * j + 5] : 0.f;
+                t = bf16x2_to_float2(pr[j].w); f[8 * j + 6] = t.x > 0.f ? f[8 * j + 6] : 0.f; f[8 * j + 7] = t.y > 0.f ? f[8 * j + 7] : 0.f;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                float2 t;
+                t = bf16x2_to_float2(pr[j].x); f[8 * j] *= gelu_erf_grad(t.x); f[8 * j + 1] *= gelu_erf_grad(t.y);
+                t = bf16x2_to_float2(pr[j].y); f[8 * j + 2] *= gelu_erf_grad(t.x); f[8 * j + 3] *= gelu_erf_grad(t.y);
+                t = bf16x2_to_float2(pr[j].z); f[8 * j + 4] *= gelu_erf_grad(t.x); f[8 * j + 5] *= gelu_erf_grad(t.y);
+                t = bf16x2_to_float2(pr[j].w); f[8 * j + 6] *= gelu_erf_grad(t.x); f[8 * j + 7] *= gelu_erf_grad(t.y);
+              }
+            }
+          }
+          uint4 pk[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            pk[j].x = float2_to_bf16x2(f[8 * j], f[8 * j + 1]); pk[j].y = float2_to_bf16x2(f[8 * j + 2], f[8 * j + 3]);
+            pk[j].z = float2_to_bf16x2(f[8 * j + 4], f[8 * j + 5]); pk[j].w = float2_to_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+          }
+          if (kCombine && tok >= 0) {
+            // y[tok, col0 .. col0+31] += gate * yo[row]: the term is formed from the bf16-rounded expert output (the value
+            // the separate combine kernel would read back), added with fp32 reductions at L2.  Two terms commute, so
+            // for top_k <= 2 the result does not depend on which tile arrives first.
+            float* dst = args.yacc + static_cast<size_t>(tok) * args.N + col0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float v8[8];
+              unpack8(pk[j], v8);
+              red_add_v4(dst + 8 * j, combine_term(gate, v8[0]), combine_term(gate, v8[1]), combine_term(gate, v8[2]),
+                         combine_term(gate, v8[3]));
+              red_add_v4(dst + 8 * j + 4, combine_term(gate, v8[4]), combine_term(gate, v8[5]), combine_term(gate, v8[6]),
+                         combine_term(gate, v8[7]));
+            }
+            if (args.arrive) {
+              // the last of the token's `need` contributions to this 32-column chunk rounds it to the output dtype
+              __threadfence();
+              const int old = atomicAdd(args.arrive + static_cast<size_t>(tok) * (args.N >> 5) + (col0 >> 5), 1);
+              if (old == need - 1) {
+                __threadfence();
+                __nv_bfloat16* yo_ = args.yout + static_cast<size_t>(tok) * args.N + col0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float4 a = __ldcg(reinterpret_cast<const float4*>(dst + 8 * j));
+                  const float4 b = __ldcg(reinterpret_cast<const float4*>(dst + 8 * j) + 1);
+                  const float o8[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+                  stg128(yo_ + 8 * j, pack8(o8));
+                }
+              }
+            }
+          }
+          if (!kCombine || args.out0 != nullptr) {
           if (lane == 0) tma_store_wait_read0();
           __syncwarp();
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 pk;
-            pk.x = float2_to_bf16x2(f[8 * j], f[8 * j + 1]); pk.y = float2_to_bf16x2(f[8 * j + 2], f[8 * j + 3]);
-            pk.z = float2_to_bf16x2(f[8 * j + 4], f[8 * j + 5]); pk.w = float2_to_bf16x2(f[8 * j + 6], f[8 * j + 7]);
-            *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ swz) << 4)) = pk;
-          }
+          for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ swz) << 4)) = pk[j];
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) {
+          }
+          if (lane == 0 && (!kCombine || args.out0 != nullptr)) {
             tma_store_2d(&tmC0, stg, col0, row0);
             tma_store_commit();
             if (EPI == EPI_DGRAD_DOWN && cc + 1 < kChunksPerWarp) {   // next pre-activation box, once the store has read this one

@@ -89,6 +89,11 @@ struct PdlOffIf {
   ~PdlOffIf() { g_pdl = prev; }
 };
 
+// combine fused into the down-projection's epilogue: order-free fp32 accumulation is exact for at most two terms
+static inline bool fused_combine(const b200moe_layer_desc* q) {
+  return q->k <= 2 && !(q->flags & B200MOE_LAYER_SEPARATE_COMBINE);
+}
+
 static int check_desc(const b200moe_layer_desc* q, const char* what) {
   B200MOE_REQUIRE(q != nullptr, B200MOE_EINVAL, "%s: NULL descriptor", what);
   B200MOE_REQUIRE(q->T > 0, B200MOE_EINVAL, "%s: T=%d must be positive", what, q->T);
@@ -97,6 +102,9 @@ static int check_desc(const b200moe_layer_desc* q, const char* what) {
   B200MOE_REQUIRE(q->E >= 1 && q->E <= 64 && q->k >= 1 && q->k <= 8 && q->k <= q->E, B200MOE_EINVAL,
                   "%s: bad num_experts=%d / top_k=%d", what, q->E, q->k);
   B200MOE_REQUIRE(q->capacity >= 0, B200MOE_EINVAL, "%s: negative capacity", what);
+  B200MOE_REQUIRE(q->activation == B200MOE_ACT_GELU || q->activation == B200MOE_ACT_RELU, B200MOE_EINVAL,
+                  "%s: activation=%d must be B200MOE_ACT_GELU or B200MOE_ACT_RELU", what, q->activation);
+  B200MOE_REQUIRE((q->flags & ~B200MOE_LAYER_SEPARATE_COMBINE) == 0, B200MOE_EINVAL, "%s: unknown flags 0x%x", what, q->flags);
   B200MOE_REQUIRE(q->rows_cap > 0 && q->rows_cap % kRowPad == 0 &&
                       q->rows_cap >= b200moe_layer_rows_cap(q->T, q->k, q->E, q->capacity, q->d, q->F),
                   B200MOE_EINVAL, "%s: rows_cap=%d is below b200moe_layer_rows_cap(T,k,E,capacity,d,F)", what, q->rows_cap);
@@ -265,6 +273,8 @@ extern "C" int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* q, int64_t*
   bytes[B200MOE_WS_PRE] = R * F * 2;
   bytes[B200MOE_WS_H] = R * F * 2;
   bytes[B200MOE_WS_YO] = R * d * 2;
+  bytes[B200MOE_WS_Y_ACC] = fused_combine(q) ? T * d * 4 : 0;
+  bytes[B200MOE_WS_ARRIVE] = fused_combine(q) ? T * (d / 32) * 4 : 0;
   int64_t at = 0;
   for (int i = 0; i < B200MOE_WS_COUNT; ++i) { off[i] = at; at += align256(bytes[i]); }
   return at;
@@ -316,7 +326,16 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                     WS(int32_t, B200MOE_WS_KEPT_PER_EXPERT), WS(float, B200MOE_WS_LOSSES),
                     WS(int32_t, B200MOE_WS_SLOT_LIMIT), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
                     WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW), stream));
-  STEP("permute", b200moe_permute(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP), stream));
+  const bool fused = fused_combine(q);
+  if (fused) {
+    // the dispatch kernel also zeroes the fp32 accumulator / arrival counters of the fused combine (no memset launch);
+    // with the fused post-norm the LayerNorm kernel finishes from the accumulator, so no counters and no y rows
+    STEP("permute", b200moe_permute_init(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP),
+                                         WS(float, B200MOE_WS_Y_ACC), pn ? nullptr : WS(int32_t, B200MOE_WS_ARRIVE),
+                                         WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT), T, k, pn ? nullptr : y, stream));
+  } else {
+    STEP("permute", b200moe_permute(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP), stream));
+  }
   {
     // the bf16 expert weights may still be in preparation on another stream (the router, the plan and the permute do
     // not need them): join here, just before their first reader
@@ -324,13 +343,28 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
       cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), static_cast<cudaEvent_t>(weights_ready), 0);
     PdlOffIf np_(weights_ready != nullptr);
     STEP("ffn_up", b200moe_ffn_up(WS(void, B200MOE_WS_XP), w1, b1, meta, tile_expert, R, d, F, E,
-                                  save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H), pad, stream));
+                                  save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H),
+                                  q->activation, pad, stream));
+  }
+  if (fused) {
+    // yo is stored only for the backward (dgate = <dy, yo>); y leaves the epilogue itself
+    STEP("ffn_down", b200moe_ffn_down_combine(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert,
+                                              WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW),
+                                              WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT), T, k, R, d, F, E,
+                                              save_for_backward ? WS(void, B200MOE_WS_YO) : nullptr,
+                                              WS(float, B200MOE_WS_Y_ACC), pn ? nullptr : WS(int32_t, B200MOE_WS_ARRIVE),
+                                              pn ? nullptr : y, pad, stream));
+    if (pn) {
+      STEP("combine_ln", b200moe_combine_ln_fwd(nullptr, nullptr, nullptr, WS(float, B200MOE_WS_Y_ACC), pn->residual,
+                                                pn->gamma, pn->beta, pn->eps, T, k, d, y, pn->mean_rstd, stream));
+    }
+    return B200MOE_OK;
   }
   STEP("ffn_down", b200moe_ffn_down(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert, R, d, F, E,
                                     WS(void, B200MOE_WS_YO), pad, stream));
   if (pn) {
     STEP("combine_ln", b200moe_combine_ln_fwd(WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
-                                              WS(float, B200MOE_WS_TOPK_GATE), pn->residual, pn->gamma, pn->beta,
+                                              WS(float, B200MOE_WS_TOPK_GATE), nullptr, pn->residual, pn->gamma, pn->beta,
                                               pn->eps, T, k, d, y, pn->mean_rstd, stream));
   } else {
     STEP("combine", b200moe_combine(WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
@@ -364,7 +398,8 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
   PdlScope pdl_;
   if (pn) {
     STEP("combine_ln_bwd",
-         b200moe_combine_ln_bwd(dy, WS(void, B200MOE_WS_YO), roa, WS(float, B200MOE_WS_TOPK_GATE), pn->residual,
+         b200moe_combine_ln_bwd(dy, WS(void, B200MOE_WS_YO), roa, WS(float, B200MOE_WS_TOPK_GATE),
+                                fused_combine(q) ? WS(float, B200MOE_WS_Y_ACC) : nullptr, pn->residual,
                                 pn->gamma, pn->mean_rstd, T, k, d, pn->dv, pn->scratch, pn->dgamma, pn->dbeta, stream));
     dy = pn->dv;
   }
@@ -382,7 +417,8 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
     cudaStreamWaitEvent(fk->s2, fk->ev[0], 0);
   }
   STEP("ffn_dgrad_down",
-       b200moe_ffn_dgrad_down(dyp, w2, WS(void, B200MOE_WS_PRE), meta, tile_expert, R, d, F, E, dhpre, pad, stream));
+       b200moe_ffn_dgrad_down(dyp, w2, WS(void, B200MOE_WS_PRE), meta, tile_expert, R, d, F, E, dhpre, q->activation,
+                              pad, stream));
   if (fk) cudaEventRecord(fk->ev[1], main_s);
   {
     PdlOffIf np_(fk != nullptr);

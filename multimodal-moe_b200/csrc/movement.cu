@@ -10,10 +10,21 @@ namespace b200moe {
 constexpr int kMoveWarps = 8;
 constexpr int kMoveThreads = kMoveWarps * 32;
 
+// What the dispatch kernel prepares for the down-projection's fused combine epilogue (gemm.cu, EPI_DOWN_COMBINE), so that
+// no memset launch sits on the critical path: the fp32 accumulator and the arrival counters start at zero, and the
+// output rows of tokens that lost every assignment to the capacity limit (nothing will ever finalise them) are zero.
+struct CombineInit {
+  float* y_acc;                       // [T,d] fp32 or null
+  int32_t* arrive;                    // [T,d/32] or null
+  const int32_t* row_of_assignment;   // [T,k]
+  __nv_bfloat16* y;                   // [T,d] bf16 or null
+  int T, k;
+};
+
 // xp[r] = x[token_of_row[r]] or 0
 __global__ void __launch_bounds__(kMoveThreads)
 permute_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ token_of_row,
-               const int32_t* __restrict__ meta, int d, __nv_bfloat16* __restrict__ xp) {
+               const int32_t* __restrict__ meta, int d, __nv_bfloat16* __restrict__ xp, const CombineInit ci) {
   pdl_sync();
   const int R = meta[0];
   const int nchunk = d >> 3;
@@ -26,6 +37,24 @@ permute_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ 
       for (int c = lane; c < nchunk; c += 32) stg128(dst + c * 8, ldg128(src + c * 8));
     } else {
       for (int c = lane; c < nchunk; c += 32) stg128(dst + c * 8, make_uint4(0, 0, 0, 0));
+    }
+  }
+  if (ci.y_acc) {
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    const size_t gid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const size_t n_acc = static_cast<size_t>(ci.T) * d / 4;             // 16-byte pieces
+    for (size_t i = gid; i < n_acc; i += stride) stg128(ci.y_acc + 4 * i, make_uint4(0, 0, 0, 0));
+    if (ci.arrive) {
+      const size_t n_arr = static_cast<size_t>(ci.T) * (d >> 5) / 4;    // d % 128 == 0: a whole number of pieces
+      for (size_t i = gid; i < n_arr; i += stride) stg128(ci.arrive + 4 * i, make_uint4(0, 0, 0, 0));
+    }
+    if (ci.y) {
+      for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < ci.T; t += gridDim.x * kMoveWarps) {
+        bool any = false;
+        for (int s = 0; s < ci.k; ++s) any = any || ci.row_of_assignment[static_cast<size_t>(t) * ci.k + s] >= 0;
+        if (!any)
+          for (int c = lane; c < nchunk; c += 32) stg128(ci.y + static_cast<size_t>(t) * d + c * 8, make_uint4(0, 0, 0, 0));
+      }
     }
   }
 }
@@ -63,7 +92,7 @@ combine_kernel(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__
         float v[8];
         unpack8(ldg128(yo + static_cast<size_t>(r) * d + c * 8), v);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = fmaf(g, v[j], acc[j]);
+        for (int j = 0; j < 8; ++j) acc[j] = combine_add(acc[j], combine_term(g, v[j]));
       }
       stg128(y + static_cast<size_t>(t) * d + c * 8, pack8(acc));
     }
@@ -324,13 +353,27 @@ prepare_weights_kernel(const float* __restrict__ w1, __nv_bfloat16* __restrict__
 constexpr int kLnMaxI = 4;
 template <int NI>
 __device__ __forceinline__ void ln_gather_sum(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ roa,
-                                              const float* __restrict__ gate, const __nv_bfloat16* __restrict__ res,
+                                              const float* __restrict__ gate, const float* __restrict__ y_acc,
+                                              const __nv_bfloat16* __restrict__ res,
                                               int t, int k, int d, int lane, float (&v)[NI][8]) {
   const int nchunk = d >> 3;
 #pragma unroll
   for (int i = 0; i < NI; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+  if (y_acc) {            // the combine already happened in the down-projection's epilogue (fp32, same arithmetic)
+#pragma unroll
+    for (int i = 0; i < NI; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nchunk) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(y_acc + static_cast<size_t>(t) * d + c * 8));
+        const float4 b = __ldg(reinterpret_cast<const float4*>(y_acc + static_cast<size_t>(t) * d + c * 8) + 1);
+        v[i][0] = a.x; v[i][1] = a.y; v[i][2] = a.z; v[i][3] = a.w;
+        v[i][4] = b.x; v[i][5] = b.y; v[i][6] = b.z; v[i][7] = b.w;
+      }
+    }
+    k = 0;
+  }
   for (int s = 0; s < k; ++s) {
     const int r = roa[static_cast<size_t>(t) * k + s];
     if (r < 0) continue;
@@ -342,7 +385,7 @@ __device__ __forceinline__ void ln_gather_sum(const __nv_bfloat16* __restrict__ 
         float a[8];
         unpack8(ldg128(yo + static_cast<size_t>(r) * d + c * 8), a);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) v[i][j] = fmaf(g, a[j], v[i][j]);
+        for (int j = 0; j < 8; ++j) v[i][j] = combine_add(v[i][j], combine_term(g, a[j]));
       }
     }
   }
@@ -361,7 +404,8 @@ __device__ __forceinline__ void ln_gather_sum(const __nv_bfloat16* __restrict__ 
 template <int NI>
 __global__ void __launch_bounds__(kMoveThreads)
 combine_ln_fwd_kernel(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ roa,
-                      const float* __restrict__ gate, const __nv_bfloat16* __restrict__ res,
+                      const float* __restrict__ gate, const float* __restrict__ y_acc,
+                      const __nv_bfloat16* __restrict__ res,
                       const float* __restrict__ gamma, const float* __restrict__ beta, float eps, int T, int k, int d,
                       __nv_bfloat16* __restrict__ out, float* __restrict__ mean_rstd) {
   pdl_sync();
@@ -369,7 +413,7 @@ combine_ln_fwd_kernel(const __nv_bfloat16* __restrict__ yo, const int32_t* __res
   const float invd = 1.0f / static_cast<float>(d);
   for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps) {
     float v[NI][8];
-    ln_gather_sum<NI>(yo, roa, gate, res, t, k, d, lane, v);
+    ln_gather_sum<NI>(yo, roa, gate, y_acc, res, t, k, d, lane, v);
     float s = 0.f;
 #pragma unroll
     for (int i = 0; i < NI; ++i)
@@ -409,6 +453,7 @@ template <int NI>
 __global__ void __launch_bounds__(kMoveThreads)
 combine_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ yo,
                       const int32_t* __restrict__ roa, const float* __restrict__ gate,
+                      const float* __restrict__ y_acc,
                       const __nv_bfloat16* __restrict__ res, const float* __restrict__ gamma,
                       const float* __restrict__ mean_rstd, int T, int k, int d, __nv_bfloat16* __restrict__ dv,
                       float* __restrict__ scratch) {
@@ -423,7 +468,7 @@ combine_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat1
     for (int j = 0; j < 8; ++j) { dg[i][j] = 0.f; db[i][j] = 0.f; }
   for (int t = blockIdx.x * kMoveWarps + warp; t < T; t += gridDim.x * kMoveWarps) {
     float v[NI][8], dy[NI][8];
-    ln_gather_sum<NI>(yo, roa, gate, res, t, k, d, lane, v);
+    ln_gather_sum<NI>(yo, roa, gate, y_acc, res, t, k, d, lane, v);
     const float mean = mean_rstd[2 * static_cast<size_t>(t)], rstd = mean_rstd[2 * static_cast<size_t>(t) + 1];
     float m1 = 0.f, m2 = 0.f;
 #pragma unroll
@@ -496,13 +541,13 @@ ln_param_reduce_kernel(const float* __restrict__ scratch, int nblk, int d, float
 
 static inline int ln_bwd_blocks(int T) {
   int b = (T + kMoveWarps - 1) / kMoveWarps;
-  if (b > kNumSMs * 2) b = kNumSMs * 2;
+  if (b > num_sms() * 2) b = num_sms() * 2;
   return b < 1 ? 1 : b;
 }
 
 static inline int move_grid(long long rows) {
   long long b = (rows + kMoveWarps - 1) / kMoveWarps;
-  const long long cap = static_cast<long long>(kNumSMs) * 8;
+  const long long cap = static_cast<long long>(num_sms()) * 8;
   if (b > cap) b = cap;
   if (b < 1) b = 1;
   return static_cast<int>(b);
@@ -517,9 +562,19 @@ using namespace b200moe;
 
 extern "C" int b200moe_permute(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
                                void* xp, void* stream) {
+  return b200moe_permute_init(x, token_of_row, meta, rows_cap, d, xp, nullptr, nullptr, nullptr, 0, 0, nullptr, stream);
+}
+
+extern "C" int b200moe_permute_init(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap,
+                                    int d, void* xp, float* y_acc, int32_t* arrive,
+                                    const int32_t* row_of_assignment, int T, int k, void* y, void* stream) {
   B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "permute: d=%d must be a multiple of 8", d);
+  B200MOE_REQUIRE(y_acc == nullptr || (T > 0 && d % 128 == 0), B200MOE_EINVAL, "permute_init: bad T=%d / d=%d", T, d);
+  B200MOE_REQUIRE(y == nullptr || (y_acc != nullptr && row_of_assignment != nullptr && k >= 1), B200MOE_EINVAL,
+                  "permute_init: y without y_acc / row_of_assignment");
   if (int rc = b200moe_check_device()) return rc;
-  launch_k(permute_kernel, move_grid(rows_cap), kMoveThreads, 0, ST(stream), BF(x), token_of_row, meta, d, BFW(xp));
+  const CombineInit ci{y_acc, arrive, row_of_assignment, BFW(y), T, k};
+  launch_k(permute_kernel, move_grid(rows_cap), kMoveThreads, 0, ST(stream), BF(x), token_of_row, meta, d, BFW(xp), ci);
   return check_launch("permute");
 }
 
@@ -562,13 +617,14 @@ static int unpermute_bwd_impl(const void* dxp, const b200moe::PeerRows& pr, cons
   // 8 tokens per warp (each shared-memory read of wg feeds 64 FMAs) only where the router term is the limit: many
   // experts and enough tokens that 64-token blocks still cover the SMs; below that the kernel is latency-bound and
   // small blocks win (tools/unp_bench.py: 76 vs 86 us at E=16 / 65533 tokens, 88 vs 141 us at E=64 / 16384)
-  const bool big = T >= 64 * kNumSMs && E > 16;
+  const bool big = T >= 64 * num_sms() && E > 16;
   static const int tt_env = [] { const char* e = getenv("B200MOE_UNP_TT"); return e ? atoi(e) : 0; }();   // experiments
   const int tt = (tt_env == 2 || tt_env == 4 || tt_env == 8) ? tt_env : (big ? 8 : 2);
   const int tok = 8 * tt;
   const size_t smem = dlogits ? sizeof(float) * (static_cast<size_t>(E) * 256 + tok * E) : 0;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce unp_once;
+  const int dev = current_device();
+  if (!unp_once.done(dev)) {
     const int mx = static_cast<int>(sizeof(float) * (64 * 256 + 64 * 64));
     cudaError_t e1 = cudaFuncSetAttribute(unpermute_bwd_kernel<8, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
     cudaError_t e2 = cudaFuncSetAttribute(unpermute_bwd_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
@@ -578,7 +634,7 @@ static int unpermute_bwd_impl(const void* dxp, const b200moe::PeerRows& pr, cons
     cudaFuncSetAttribute(unpermute_bwd_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
     B200MOE_REQUIRE(e1 == cudaSuccess && e2 == cudaSuccess && e3 == cudaSuccess && e4 == cudaSuccess, B200MOE_ECUDA,
                     "unpermute_bwd: cudaFuncSetAttribute failed");
-    configured = true;
+    unp_once.set(dev);
   }
   dim3 grid((T + tok - 1) / tok, (d + 255) / 256);
   const bool p2p = pr.peers != nullptr;
@@ -616,7 +672,7 @@ extern "C" int b200moe_cast_f32_bf16(const float* src, void* dst, int64_t n, voi
   if (int rc = b200moe_check_device()) return rc;
   const int64_t n8 = n / 8;
   int64_t blocks = (n8 + 255) / 256;
-  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
   if (blocks < 1) blocks = 1;
   cast_f32_bf16_kernel<<<static_cast<int>(blocks), 256, 0, ST(stream)>>>(src, BFW(dst), n8, n);
   return check_launch("cast_f32_bf16");
@@ -648,24 +704,25 @@ extern "C" int b200moe_prepare_weights(const float* w1, void* w1_bf16, int64_t n
   const int64_t total = n1 / 8 + n2 / 8 + (wg ? (static_cast<int64_t>(2) * EP * d) / 8 : 0);
   if (total == 0) return B200MOE_OK;
   int64_t blocks = (total + 255) / 256;
-  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
   prepare_weights_kernel<<<static_cast<int>(blocks), 256, 0, ST(stream)>>>(
       w1, BFW(w1_bf16), n1 / 8, w2, BFW(w2_bf16), n2 / 8, wg, BFW(wg_split), E, EP, d);
   return check_launch("prepare_weights");
 }
 
 extern "C" int b200moe_combine_ln_fwd(const void* yo, const int32_t* row_of_assignment, const float* topk_gate,
-                                      const void* residual, const float* gamma, const float* beta, float eps, int T,
-                                      int k, int d, void* out, float* mean_rstd, void* stream) {
+                                      const float* y_acc, const void* residual, const float* gamma,
+                                      const float* beta, float eps, int T, int k, int d, void* out, float* mean_rstd,
+                                      void* stream) {
   B200MOE_REQUIRE(d > 0 && d % 8 == 0 && d <= 1024, B200MOE_EINVAL, "combine_ln_fwd: d=%d must be a multiple of 8, <= 1024", d);
-  B200MOE_REQUIRE(yo && row_of_assignment && topk_gate && residual && gamma && beta && out && mean_rstd, B200MOE_EINVAL,
-                  "combine_ln_fwd: NULL argument");
+  B200MOE_REQUIRE((y_acc || (yo && row_of_assignment && topk_gate)) && residual && gamma && beta && out && mean_rstd,
+                  B200MOE_EINVAL, "combine_ln_fwd: NULL argument");
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
   const int ni = (d / 8 + 31) / 32;
 #define LNF(NI)                                                                                                       \
   launch_k(combine_ln_fwd_kernel<NI>, move_grid(T), kMoveThreads, 0, ST(stream), BF(yo), row_of_assignment, topk_gate, \
-           BF(residual), gamma, beta, eps, T, k, d, BFW(out), mean_rstd)
+           y_acc, BF(residual), gamma, beta, eps, T, k, d, BFW(out), mean_rstd)
   if (ni == 1) LNF(1);
   else if (ni == 2) LNF(2);
   else LNF(4);
@@ -676,28 +733,29 @@ extern "C" int b200moe_combine_ln_fwd(const void* yo, const int32_t* row_of_assi
 extern "C" int64_t b200moe_ln_scratch_floats(int T, int d) { return static_cast<int64_t>(ln_bwd_blocks(T)) * 2 * d; }
 
 extern "C" int b200moe_combine_ln_bwd(const void* dout, const void* yo, const int32_t* row_of_assignment,
-                                      const float* topk_gate, const void* residual, const float* gamma,
+                                      const float* topk_gate, const float* y_acc, const void* residual, const float* gamma,
                                       const float* mean_rstd, int T, int k, int d, void* dv, float* scratch,
                                       float* dgamma, float* dbeta, void* stream) {
   B200MOE_REQUIRE(d > 0 && d % 8 == 0 && d <= 1024, B200MOE_EINVAL, "combine_ln_bwd: d=%d must be a multiple of 8, <= 1024", d);
-  B200MOE_REQUIRE(dout && yo && row_of_assignment && topk_gate && residual && gamma && mean_rstd && dv && scratch &&
-                      dgamma && dbeta, B200MOE_EINVAL, "combine_ln_bwd: NULL argument");
+  B200MOE_REQUIRE(dout && (y_acc || (yo && row_of_assignment && topk_gate)) && residual && gamma && mean_rstd && dv &&
+                      scratch && dgamma && dbeta, B200MOE_EINVAL, "combine_ln_bwd: NULL argument");
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
   const int ni = (d / 8 + 31) / 32, nblk = ln_bwd_blocks(T);
   const size_t smem = sizeof(float) * kMoveWarps * 2 * d;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce lnb_once;
+  const int dev = current_device();
+  if (!lnb_once.done(dev)) {
     const int mx = static_cast<int>(sizeof(float) * kMoveWarps * 2 * 1024);
     cudaError_t e1 = cudaFuncSetAttribute(combine_ln_bwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
     cudaError_t e2 = cudaFuncSetAttribute(combine_ln_bwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
     cudaError_t e3 = cudaFuncSetAttribute(combine_ln_bwd_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx);
     B200MOE_REQUIRE(e1 == cudaSuccess && e2 == cudaSuccess && e3 == cudaSuccess, B200MOE_ECUDA, "combine_ln_bwd: cudaFuncSetAttribute failed");
-    configured = true;
+    lnb_once.set(dev);
   }
 #define LNB(NI)                                                                                                     \
   launch_k(combine_ln_bwd_kernel<NI>, nblk, kMoveThreads, smem, ST(stream), BF(dout), BF(yo), row_of_assignment,      \
-           topk_gate, BF(residual), gamma, mean_rstd, T, k, d, BFW(dv), scratch)
+           topk_gate, y_acc, BF(residual), gamma, mean_rstd, T, k, d, BFW(dv), scratch)
   if (ni == 1) LNB(1);
   else if (ni == 2) LNB(2);
   else LNB(4);

@@ -413,10 +413,12 @@ extern "C" int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int
     return check_launch("plan_fused");
   }
   const size_t scan_smem = sizeof(int) * (kScanThreads / 32) * (static_cast<size_t>(k) * E + E + 1);
-  static bool scan_configured = false;
-  if (!scan_configured) {
-    cudaFuncSetAttribute(plan_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * (8 * 64 + 65) * 4);
-    scan_configured = true;
+  static DeviceOnce scan_once;
+  const int dev = current_device();
+  if (!scan_once.done(dev)) {
+    cudaError_t e = cudaFuncSetAttribute(plan_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * (8 * 64 + 65) * 4);
+    B200MOE_REQUIRE(e == cudaSuccess, B200MOE_ECUDA, "plan: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+    scan_once.set(dev);
   }
   launch_k(plan_scan_kernel, 1, kScanThreads, scan_smem, st, block_counts, block_stats, nblk, T, k, E, capacity, global_offset,
            expert_order, row_pad, rows_cap, aux_loss_weight, z_loss_weight, expert_offsets, meta, tile_expert,

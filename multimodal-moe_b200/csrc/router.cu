@@ -401,12 +401,13 @@ static int launch_router(const void* x, const void* wsplit, RouterArgs a, cudaSt
   if (int rc = make_tmap_bf16_2d(&tmX, x, a.d, a.T, 64, kRtTile)) return rc;
   if (int rc = make_tmap_bf16_2d(&tmW, wsplit, a.d, 2 * EP, 64, 2 * EP)) return rc;
   auto kern = router_fwd_kernel<EP, G>;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce once;
+  const int dev = current_device();
+  if (!once.done(dev)) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          kRtSmemBudget / Cfg::kCtasPerSm);
     B200MOE_REQUIRE(e == cudaSuccess, B200MOE_ECUDA, "router_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-    configured = true;
+    once.set(dev);
   }
   a.stages = Cfg::stages(a.k);
   static const int stage_cap = [] { const char* e = getenv("B200MOE_ROUTER_STAGES"); return e ? atoi(e) : 0; }();
@@ -414,7 +415,7 @@ static int launch_router(const void* x, const void* wsplit, RouterArgs a, cudaSt
   if (stage_cap >= 2 && stage_cap < a.stages) a.stages = stage_cap;
   B200MOE_REQUIRE(a.stages >= 2, B200MOE_EINVAL, "router_fwd: no shared memory left for the load ring (top_k=%d)", a.k);
   const int ntiles = (a.T + kRtTile - 1) / kRtTile;
-  const int max_ctas = cta_cap > 0 ? cta_cap : kNumSMs * Cfg::kCtasPerSm;
+  const int max_ctas = cta_cap > 0 ? cta_cap : num_sms() * Cfg::kCtasPerSm;
   const int grid = ntiles < max_ctas ? ntiles : max_ctas;
   launch_k(kern, grid, Cfg::kThreads, Cfg::total(a.k), st, tmX, tmW, a);
   return check_launch("router_fwd");
@@ -447,7 +448,7 @@ extern "C" int b200moe_router_fwd(const void* x, const float* ctx_bias, int toke
   if (wg != nullptr) {   // NULL: wg_split was already filled by b200moe_prepare_weights
     const int n = 2 * EP * d;
     int blocks = (n + 255) / 256;
-    if (blocks > 4 * kNumSMs) blocks = 4 * kNumSMs;
+    if (blocks > 4 * num_sms()) blocks = 4 * num_sms();
     router_split_wg_kernel<<<blocks, 256, 0, st>>>(wg, static_cast<__nv_bfloat16*>(wg_split), E, EP, d);
     if (int rc = check_launch("router_split_wg")) return rc;
   }

@@ -211,7 +211,7 @@ router_dwg_reduce_kernel(const float* __restrict__ scratch, int nchunks, int n, 
 
 static int dwg_chunks(int T, int d, int E) {
   const int slabs = (d + 255) / 256, groups = (E + kDwgEG - 1) / kDwgEG;
-  int chunks = (4 * kNumSMs + slabs * groups - 1) / (slabs * groups);
+  int chunks = (4 * num_sms() + slabs * groups - 1) / (slabs * groups);
   const int max_chunks = (T + 15) / 16;
   if (chunks > max_chunks) chunks = max_chunks;
   return chunks < 1 ? 1 : chunks;
@@ -261,11 +261,12 @@ extern "C" int b200moe_router_bwd_params(const float* dlogits, const void* x, in
     int tpc = (T + chunks - 1) / chunks;
     tpc = (tpc + 3) / 4 * 4;
     chunks = (T + tpc - 1) / tpc;
-    static bool configured = false;
-    if (!configured) {
+    static DeviceOnce once;
+    const int dev = current_device();
+    if (!once.done(dev)) {
       cudaError_t e = cudaFuncSetAttribute(router_dwg_partial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDwgRedBytes);
       B200MOE_REQUIRE(e == cudaSuccess, B200MOE_ECUDA, "router_bwd_params: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-      configured = true;
+      once.set(dev);
     }
     dim3 grid(chunks, (d + 255) / 256, (E + kDwgEG - 1) / kDwgEG);
     launch_k(router_dwg_partial_kernel, grid, 128, kDwgRedBytes, st, dlogits, static_cast<const __nv_bfloat16*>(x), T, d,

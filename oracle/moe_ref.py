@@ -139,8 +139,11 @@ class ContextMoERef(nn.Module):
                  context_dim: int = 32, activation: str = "gelu", aux_loss_weight: float = 1e-2,
                  z_loss_weight: float = 1e-3, normalize_topk: bool = True, ep_group=None):
         super().__init__()
-        if activation != "gelu":
-            raise ValueError("only exact-erf GELU is defined for this layer (utils.py:160-161)")
+        if activation not in ("gelu", "relu"):
+            # 'gelu' -> nn.GELU() exact erf (zoo/rtdetr/utils.py:160-161), the encoder FFN of hybrid_encoder.py:157;
+            # 'relu' -> nn.ReLU (utils.py:152-153), the decoder FFN of rtdetrv2_decoder.py:169,187,203
+            raise ValueError("activation must be 'gelu' or 'relu'")
+        self.activation = activation
         if top_k > num_experts:
             raise ValueError("top_k > num_experts")
         self.d_model, self.dim_feedforward = d_model, dim_feedforward
@@ -195,7 +198,8 @@ class ContextMoERef(nn.Module):
 
     def experts(self, xe: torch.Tensor, e: int) -> torch.Tensor:
         """A.6: W2_e . gelu_erf(W1_e . x + b1_e) + b2_e  (hybrid_encoder.py:157, dropout 0)."""
-        h = F.gelu(F.linear(xe, self.w1[e].float(), self.b1[e].float()))
+        pre = F.linear(xe, self.w1[e].float(), self.b1[e].float())
+        h = F.gelu(pre) if self.activation == "gelu" else F.relu(pre)
         return F.linear(h, self.w2[e].float(), self.b2[e].float())
 
     def forward(self, x: torch.Tensor, context: Optional[torch.Tensor] = None,

@@ -81,14 +81,35 @@ def main():
     }
     np.savez_compressed(os.path.join(HERE, "dense_ffn_d128_f256.npz"), **out2)
 
-    # the post-norm wrapper (:154-160): norm2(residual + ffn(src)) on the same src
+    # the post-norm wrapper (:154-160): norm2(residual + ffn(src)),
+    # at the smallest shape the CUDA path accepts (d, F multiples of 128), forward and backward, and the
+    # whole vendored encoder layer (:143-161: attention, both residuals, both norms) on the same weights: the in-situ
+    # known answer for b200moe.MoEEncoderLayer.from_dense (fused post-norm path) on the GPU
+    torch.manual_seed(20260222)
+    B3, HW3 = 3, 70
+    src3 = torch.randn(B3, HW3, d2, requires_grad=True)
+    go3 = torch.randn(B3, HW3, d2)
     with torch.no_grad():
-        src = torch.randn(B, HW, d)
-        wrapped = layer.norm2(src + layer.linear2(layer.activation(layer.linear1(src))))
-        full = layer(src)
-    np.savez_compressed(os.path.join(HERE, "postnorm_ffn_d64_f128.npz"), src=src.numpy(), out=wrapped.numpy(),
-                        full_layer_out=full.numpy(),
-                        **{k: v.numpy() for k, v in layer.state_dict().items()})
+        layer2.norm2.weight.uniform_(0.5, 1.5)
+        layer2.norm2.bias.uniform_(-0.2, 0.2)
+    for p_ in layer2.parameters():
+        p_.grad = None
+    wrapped3 = layer2.norm2(src3 + layer2.dropout2(layer2.linear2(layer2.dropout(layer2.activation(layer2.linear1(src3))))))
+    (wrapped3 * go3).sum().backward()
+    np.savez_compressed(os.path.join(HERE, "postnorm_ffn_d128_f256.npz"), src=src3.detach().numpy(), go=go3.numpy(),
+                        out=wrapped3.detach().numpy(), dsrc=src3.grad.numpy(),
+                        dnorm2_weight=layer2.norm2.weight.grad.numpy(), dnorm2_bias=layer2.norm2.bias.grad.numpy(),
+                        dw1=layer2.linear1.weight.grad.numpy(), dw2=layer2.linear2.weight.grad.numpy(),
+                        **{"sd." + k: v.numpy() for k, v in layer2.state_dict().items()})
+    for p_ in layer2.parameters():
+        p_.grad = None
+    pos3 = torch.randn(1, HW3, d2)
+    xin = src3.detach().clone().requires_grad_(True)
+    full3 = layer2(xin, pos_embed=pos3)
+    (full3 * go3).sum().backward()
+    np.savez_compressed(os.path.join(HERE, "encoder_layer_d128_f256.npz"), src=xin.detach().numpy(), pos=pos3.numpy(),
+                        go=go3.numpy(), out=full3.detach().numpy(), dsrc=xin.grad.numpy(),
+                        **{"sd." + k: v.numpy() for k, v in layer2.state_dict().items()})
     print("wrote", os.listdir(HERE))
 
 

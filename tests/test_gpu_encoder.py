@@ -2,7 +2,9 @@
 the vendored TransformerEncoderLayer (hybrid_encoder.py:116-161) is upcycled in place; with identical experts,
 renormalised gates and no capacity limit the swapped layer must reproduce the dense one (K1 anchor) and train."""
 import copy
+import os
 
+import numpy as np
 import pytest
 import torch
 import torch.nn as nn
@@ -144,3 +146,47 @@ def test_fused_post_norm_matches_unfused(B, HW, d, F, E, cf):
     # deterministic
     of2, dxf2, _, gf2 = run(True)
     assert torch.equal(of, of2) and torch.equal(dxf, dxf2) and torch.equal(gf["ln.weight"], gf2["ln.weight"])
+
+
+def _golden_layer(golden_dir, name):
+    g = {k: torch.from_numpy(v) for k, v in np.load(os.path.join(golden_dir, name)).items()}
+    sd = {k[3:]: v for k, v in g.items() if k.startswith("sd.")}
+    d, F = sd["linear1.weight"].shape[1], sd["linear1.weight"].shape[0]
+    dense = TransformerEncoderLayer(d, 8, F, False)
+    dense.load_state_dict(sd)                      # the vendored layer's own state_dict keys (hybrid_encoder.py:126-141)
+    return g, dense
+
+
+def test_fused_post_norm_matches_vendored_golden(golden_dir):
+    """Reference-derived known answer for §8(f)2: `norm2(src + linear2(gelu(linear1(src))))` computed by the UNMODIFIED
+    vendored layer (tests/golden/make_golden.py, hybrid_encoder.py:157-160) against ContextMoE.forward_post_norm with E
+    identical experts (renormalised gates, no drops), forward and backward."""
+    import b200moe
+    g, dense = _golden_layer(golden_dir, "postnorm_ffn_d128_f256.npz")
+    layer = b200moe.MoEEncoderLayer.from_dense(dense, num_experts=4, top_k=2, capacity_factor=None).cuda()
+    src = g["src"].cuda().requires_grad_(True)
+    out = layer.moe.forward_post_norm(src.to(torch.bfloat16), src.to(torch.bfloat16), layer.norm2)
+    (out.float() * g["go"].cuda()).sum().backward()
+
+    def rel(a, b):
+        return float((a.float().cpu() - b.float()).norm() / (b.float().norm() + 1e-12))
+    assert rel(out, g["out"]) <= 1e-2
+    assert rel(src.grad, g["dsrc"]) <= 1e-2
+    assert rel(layer.norm2.weight.grad, g["dnorm2_weight"]) <= 1e-2
+    assert rel(layer.norm2.bias.grad, g["dnorm2_bias"]) <= 1e-2
+    assert rel(layer.moe.w1.grad.sum(0), g["dw1"]) <= 1e-2
+    assert rel(layer.moe.w2.grad.sum(0), g["dw2"]) <= 1e-2
+
+
+def test_upcycled_layer_matches_vendored_encoder_layer_golden(golden_dir):
+    """The whole vendored TransformerEncoderLayer.forward (hybrid_encoder.py:143-161: attention with pos_embed, both
+    residuals, both LayerNorms) against MoEEncoderLayer.from_dense on the same weights, output and input gradient."""
+    import b200moe
+    g, dense = _golden_layer(golden_dir, "encoder_layer_d128_f256.npz")
+    layer = b200moe.MoEEncoderLayer.from_dense(dense.cuda(), num_experts=4, top_k=2, capacity_factor=None)
+    src = g["src"].cuda().requires_grad_(True)
+    out = layer(src, pos_embed=g["pos"].cuda())
+    (out.float() * g["go"].cuda()).sum().backward()
+    rel = float((out.float().cpu() - g["out"]).norm() / g["out"].norm())
+    reld = float((src.grad.float().cpu() - g["dsrc"]).norm() / g["dsrc"].norm())
+    assert rel <= 1e-2 and reld <= 1e-2, (rel, reld)

@@ -20,15 +20,17 @@ def _rel(a, b):
     return float((a.float().cpu() - b.float().cpu()).norm() / (b.float().cpu().norm() + 1e-12))
 
 
-def _pair(d, F, E, k, cf, ctx=False, seed=0, normalize=True):
+def _pair(d, F, E, k, cf, ctx=False, seed=0, normalize=True, activation="gelu"):
     import b200moe
     torch.manual_seed(seed)
     vs = R.CONTEXT_VOCAB_SIZES if ctx else ()
-    ref = R.ContextMoERef(d, F, E, k, cf, context_vocab_sizes=vs, context_dim=16, normalize_topk=normalize)
+    ref = R.ContextMoERef(d, F, E, k, cf, context_vocab_sizes=vs, context_dim=16, normalize_topk=normalize,
+                          activation=activation)
     with torch.no_grad():                                     # bf16-representable weights: isolates kernel error
         for p in (ref.w1, ref.w2):
             p.copy_(p.to(torch.bfloat16).float())
-    m = b200moe.ContextMoE(d, F, E, k, cf, context_vocab_sizes=vs, context_dim=16, normalize_topk=normalize)
+    m = b200moe.ContextMoE(d, F, E, k, cf, context_vocab_sizes=vs, context_dim=16, normalize_topk=normalize,
+                           activation=activation)
     m.load_state_dict(ref.state_dict())
     return ref, m.cuda()
 
@@ -42,12 +44,14 @@ def _run_both(ref, m, x, ctx, go):
     # oracle on the kernel's own logits => identical routing by construction of the comparison (A.11)
     xr = x.float().clone().requires_grad_(True)
     yr = ref(xr, ctx, logits_value=m.last_aux["logits"].cpu())
-    # routing parity on identical logits
+    # routing parity on identical logits: indices, gates, drops
     _, idx, gates = R.route(m.last_aux["logits"].cpu(), ref.top_k, ref.normalize_topk)
     assert torch.equal(m.last_aux["topk_idx"].cpu().long(), idx)
-    same_routing = torch.equal(ref.last_aux["topk_idx"], idx)
+    assert torch.equal(ref.last_aux["topk_idx"], idx)            # the oracle ran on the kernel's logits (logits_value)
+    assert torch.equal(m.last_aux["row_of_assignment"].cpu() >= 0, ref.last_aux["keep"])
+    assert torch.allclose(m.last_aux["gates"].cpu(), gates, rtol=1e-5, atol=1e-7)
     (yr * go).sum().add(ref.aux_loss).backward()
-    return xg, y, xr, yr, same_routing
+    return xg, y, xr, yr
 
 
 @pytest.mark.parametrize("B,HW,d,F,E,k,cf,ctx", [
@@ -56,28 +60,96 @@ def _run_both(ref, m, x, ctx, go):
     (4, 230, 512, 2048, 16, 2, 1.25, True),        # config C shape
     (2, 333, 128, 256, 4, 1, 0.5, False),          # top-1, heavy dropping, odd token count
     (1, 200, 1024, 4096, 64, 2, 2.0, False),       # config D shape on one GPU (many empty / tiny experts)
+    (8, 300, 256, 1024, 8, 2, 1.25, False),        # decoder FFN site: 8 x 300 queries (rtdetrv2_decoder.py:186-189)
+    (2, 257, 256, 512, 8, 3, 1.0, True),           # top-3: the separate combine kernel (fused epilogue is top_k <= 2)
 ])
-def test_layer_matches_oracle(B, HW, d, F, E, k, cf, ctx):
+@pytest.mark.parametrize("fused", [True, False])
+def test_layer_matches_oracle(B, HW, d, F, E, k, cf, ctx, fused):
+    """All gradients at the tolerance north_star states (rel-L2 <= 1e-2), the router's included.  Measured
+    (tools/grad_diag.py, round 2): gate.weight / ctx_proj / ctx_embed 2.3e-3 .. 3.4e-3 for top-2; 4.9e-3 .. 6.9e-3 for
+    top-1 with renormalised gates, where g = p / (p + 1e-9) == 1 in fp32 and the gate path of the gradient is exactly
+    zero in the kernel but rounding noise in the oracle's autograd."""
     ref, m = _pair(d, F, E, k, cf, ctx, seed=B * HW)
+    m.fused_combine = fused
     g = torch.Generator().manual_seed(1234)
     x = torch.randn(B, HW, d, generator=g).to(torch.bfloat16)
     go = torch.randn(B, HW, d, generator=g)
     c = torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1) if ctx else None
-    xg, y, xr, yr, same = _run_both(ref, m, x, c, go)
+    xg, y, xr, yr = _run_both(ref, m, x, c, go)
     assert y.dtype == torch.bfloat16 and y.shape == x.shape
     assert abs(float(m.aux_loss) - float(ref.aux_loss)) <= 1e-4
-    assert int(m.last_aux["dropped"]) == ref.last_aux["dropped"] or not same
-    if not same:
-        pytest.skip("fp32 logits of kernel and oracle differ in the last ulp at a top-k boundary for this seed")
+    assert int(m.last_aux["dropped"]) == ref.last_aux["dropped"]
     assert _rel(y, yr) <= REL
     assert _rel(xg.grad, xr.grad) <= REL
     for name in ("w1", "b1", "w2", "b2"):
         assert _rel(getattr(m, name).grad, getattr(ref, name).grad) <= REL, name
-    assert _rel(m.gate.weight.grad, ref.gate.weight.grad) <= 2e-2
+    assert _rel(m.gate.weight.grad, ref.gate.weight.grad) <= REL
     if ctx:
-        assert _rel(m.ctx_proj.weight.grad, ref.ctx_proj.weight.grad) <= 2e-2
+        assert _rel(m.ctx_proj.weight.grad, ref.ctx_proj.weight.grad) <= REL
         for a, b in zip(m.ctx_embed, ref.ctx_embed):
-            assert _rel(a.weight.grad, b.weight.grad) <= 2e-2
+            assert _rel(a.weight.grad, b.weight.grad) <= REL
+
+
+@pytest.mark.parametrize("B,HW,d,F,E,k,cf", [(8, 400, 256, 1024, 8, 2, 1.25), (3, 333, 512, 1024, 16, 2, 0.5),
+                                             (2, 333, 128, 256, 4, 1, 0.5), (1, 200, 1024, 2048, 64, 2, 2.0),
+                                             (40, 400, 256, 1024, 8, 2, 1.25)])
+def test_fused_combine_equals_separate_kernels(B, HW, d, F, E, k, cf):
+    """The down-projection's fused combine epilogue (b200moe_ffn_down_combine: fp32 reductions in tile order, the last
+    contribution rounds) against b200moe_ffn_down + b200moe_combine (slot order): bit-identical outputs and gradients,
+    with drops (tokens that lose every assignment must come out as exact zeros), in training and in inference."""
+    _, m = _pair(d, F, E, k, cf, ctx=True, seed=3 * B + HW)
+    g = torch.Generator().manual_seed(99)
+    x = torch.randn(B, HW, d, generator=g).to(torch.bfloat16).cuda()
+    go = torch.randn(B, HW, d, generator=g).cuda()
+    c = torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1).cuda()
+    outs = []
+    for fused in (True, False, True):
+        m.fused_combine = fused
+        m.zero_grad(set_to_none=True)
+        xg = x.clone().requires_grad_(True)
+        y = m(xg, c)
+        ((y.float() * go).sum() + m.aux_loss).backward()
+        with torch.no_grad():
+            yi = m(x, c)                                          # inference: the fused path stores no yo at all
+        torch.cuda.synchronize()
+        outs.append([y.detach().clone(), yi.clone(), xg.grad.clone()] +
+                    [p.grad.clone() for p in m.parameters() if p.grad is not None])
+    dropped_all = (m.last_aux["row_of_assignment"] < 0).all(dim=1)
+    if cf is not None and cf < 1.0:
+        assert int(dropped_all.sum()) > 0                         # the case exists in this test
+    assert float(outs[0][0].reshape(-1, d)[dropped_all].float().abs().sum()) == 0.0
+    for other in outs[1:]:
+        for a, b in zip(outs[0], other):
+            assert torch.equal(a, b)
+    assert torch.equal(outs[0][0], outs[0][1])
+
+
+@pytest.mark.parametrize("B,Q", [(8, 300), (8, 500)])
+def test_relu_experts_match_oracle(B, Q):
+    """Decoder FFN site (rtdetrv2_decoder.py:186-189,202-203: d=256, ffn=1024, activation='relu', 300-500 queries per
+    image): the ReLU epilogues of the up-projection and of dgrad_down against the oracle."""
+    d, F, E, k = 256, 1024, 8, 2
+    ref, m = _pair(d, F, E, k, 1.25, ctx=False, seed=Q, activation="relu")
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(B, Q, d, generator=g).to(torch.bfloat16)
+    go = torch.randn(B, Q, d, generator=g)
+    xg, y, xr, yr = _run_both(ref, m, x, None, go)
+    assert _rel(y, yr) <= REL and _rel(xg.grad, xr.grad) <= REL
+    for name in ("w1", "b1", "w2", "b2"):
+        assert _rel(getattr(m, name).grad, getattr(ref, name).grad) <= REL, name
+    assert _rel(m.gate.weight.grad, ref.gate.weight.grad) <= REL
+
+
+def test_plan_cache_follows_module_attributes():
+    """A later change of capacity_factor (or of any other field the C descriptor is built from) is not served a stale
+    cached plan."""
+    _, m = _pair(128, 256, 4, 2, None, seed=2)
+    x = torch.randn(2, 300, 128, device="cuda").to(torch.bfloat16)
+    m(x)
+    assert int(m.last_aux["dropped"]) == 0
+    m.capacity_factor = 0.25
+    m(x)
+    assert int(m.last_aux["dropped"]) > 0 and m.last_aux["capacity"] == 75
 
 
 def test_k1_identical_experts_equal_vendored_dense_ffn(golden_dir):

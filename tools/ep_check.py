@@ -90,10 +90,10 @@ def main():
         }
         dwg = m_ep.gate.weight.grad.clone()
         dist.all_reduce(dwg)
-        checks["dwg (sum over ranks)"] = rel(dwg, m_1.gate.weight.grad) < 2e-2
+        checks["dwg (sum over ranks)"] = rel(dwg, m_1.gate.weight.grad) < 1e-2
         dcp = m_ep.ctx_proj.weight.grad.clone()
         dist.all_reduce(dcp)
-        checks["dctx_proj (sum over ranks)"] = rel(dcp, m_1.ctx_proj.weight.grad) < 2e-2
+        checks["dctx_proj (sum over ranks)"] = rel(dcp, m_1.ctx_proj.weight.grad) < 1e-2
         bad = [n for n, v in checks.items() if not v]
         print(f"[rank {rank}] {path} B={B} HW={HW} d={d} F={F} E={E} k={k} cf={cf}: dropped(ep local)={int(a_ep['dropped'])} "
               f"dropped(1gpu)={int(a_1['dropped'])} rel_y={rel(y, y1[sl]):.2e} rel_dx={rel(x.grad, x1.grad[sl]):.2e} "
