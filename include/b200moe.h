@@ -76,6 +76,25 @@ int b200moe_prepare_weights(const float* w1, void* w1_bf16, int64_t n1, const fl
  *   block_counts [nblk,k,E] int32 (pre-drop assignments per router block, slot, expert)
  *   block_stats  [nblk,E+1] fp32 (sum_t p[t,e] per block; last column sum_t lse^2)                         */
 int64_t b200moe_router_scratch_bytes(int d, int E);   /* size of wg_split: bf16 hi/lo split of wg, [2*EP, d] */
+/* The context of a batch and the parameters of the A.2 context path, for the calls that evaluate the bias
+ * ctx_bias[b,e] = sum_i Embed_i[context[b,i],:] . Wc[e, i*cd:(i+1)*cd] themselves: the router computes the bias of the
+ * (at most four) images a 128-token tile touches while its first token tile is in flight, the whole-layer backward
+ * appends the parameter gradients to its router branch -- no separate launch either way.  A HOST struct of device
+ * pointers. */
+#define B200MOE_MAX_CTX_FIELDS 8
+typedef struct b200moe_ctx_desc {
+  const int64_t* context;                           /* [B, n_fields] ids, one per field per image */
+  const float* tables[B200MOE_MAX_CTX_FIELDS];      /* table i: [vocab[i], context_dim] fp32 */
+  int32_t vocab[B200MOE_MAX_CTX_FIELDS];
+  int32_t n_fields, context_dim, B;
+  const float* wc;                                  /* [E, n_fields*context_dim] fp32 */
+  float* dtables[B200MOE_MAX_CTX_FIELDS];           /* backward outputs, same shapes (unused by the forward) */
+  float* dwc;
+} b200moe_ctx_desc;
+/* ctx: NULL, or (with ctx_bias == NULL) the bias is evaluated inside the kernel; needs tokens_per_image >= 64. */
+int b200moe_router_fwd_ctx(const void* x, const b200moe_ctx_desc* ctx, int tokens_per_image, void* wg_split, int T,
+                           int d, int E, int k, int normalize_topk, float* logits, int32_t* topk_idx,
+                           float* topk_gate, int32_t* block_counts, float* block_stats, void* stream);
 int b200moe_router_fwd(const void* x, const float* ctx_bias, int tokens_per_image, const float* wg,
                        void* wg_split, int T, int d, int E, int k, int normalize_topk,
                        float* logits, int32_t* topk_idx, float* topk_gate,
@@ -103,11 +122,9 @@ int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int32_t* block
 int b200moe_permute(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
                     void* xp, void* stream);
 /* The same dispatch kernel, also preparing the fused combine of b200moe_ffn_down_combine (no memset launches on the
- * critical path): y_acc [T,d] fp32 := 0, arrive [T,d/32] int32 := 0 (may be NULL), and y[t,:] := 0 (bf16, may be NULL)
- * for every token that kept no assignment (nothing else writes those rows).  d % 128 == 0. */
+ * critical path): y_acc [T,d] fp32 := 0 and grid_sync (16 bytes, 16-byte aligned; may be NULL) := 0. */
 int b200moe_permute_init(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
-                         void* xp, float* y_acc, int32_t* arrive, const int32_t* row_of_assignment, int T, int k,
-                         void* y, void* stream);
+                         void* xp, float* y_acc, int32_t* grid_sync, int T, void* stream);
 
 /* A.7 combine: y[t,:] = sum_s gate[t,s] * yo[row_of_assignment[t,s],:] in slot order, fp32 accumulate. */
 int b200moe_combine(const void* yo, const int32_t* row_of_assignment, const float* topk_gate,
@@ -131,20 +148,50 @@ int b200moe_ffn_up(const void* xp, const void* w1, const float* b1, const int32_
 int b200moe_ffn_down(const void* h, const void* w2, const float* b2, const int32_t* meta,
                      const int32_t* tile_expert, int rows_cap, int d, int F, int E,
                      void* yo, int row_pad, void* stream);
+/* Optional fused post-norm of the encoder layer (hybrid_encoder.py:158-160): with a non-NULL b200moe_postnorm the last
+ * kernel of the forward computes out = LayerNorm(residual + combine(yo)) instead of y = combine(yo) (the [T,d]
+ * intermediates y and y + residual are never written), and the backward starts from d(out).                   */
+typedef struct b200moe_postnorm {
+  const void* residual;     /* [T,d] bf16, or fp32 with residual_f32 (the encoder's residual stream under autocast) */
+  const float* gamma;       /* [d] LayerNorm weight */
+  const float* beta;        /* [d] LayerNorm bias */
+  float eps;
+  float* mean_rstd;         /* [T,2] fp32, written by the forward, read by the backward */
+  int32_t residual_f32;     /* dtype of residual: 0 = bf16, 1 = fp32 */
+  int32_t out_f32;          /* dtype of the layer output y: 0 = bf16, 1 = fp32 */
+} b200moe_postnorm;
+typedef struct b200moe_postnorm_bwd {
+  const void* residual;     /* as in the forward */
+  const float* gamma;
+  const float* mean_rstd;   /* from the forward */
+  void* dv;                 /* [T,d] bf16 out: gradient of the pre-norm sum = d(MoE output) (and d(residual) when that is bf16) */
+  float* scratch;           /* b200moe_ln_scratch_floats(T, d) floats */
+  float* dgamma;            /* [d] out */
+  float* dbeta;             /* [d] out */
+  int32_t residual_f32;
+  int32_t dout_f32;         /* dtype of dy = d(out): 0 = bf16, 1 = fp32 */
+  float* dres_f32;          /* [T,d] fp32 out or NULL: the same gradient unrounded, for an fp32 residual */
+} b200moe_postnorm_bwd;
 /* Down-projection with the gate-weighted combine of A.7 FUSED INTO ITS EPILOGUE (the `linear2` half of
  * hybrid_encoder.py:157 and the weighted sum over the selected experts in one kernel): for every live row r
  *   y_acc[token_of_row[r], :] += gate_of_row[r] * bf16(h[r] @ w2[e]^T + b2[e])          (fp32 reductions at L2)
  * straight from the accumulator registers.  top_k <= 2 only: two fp32 terms commute, so the result does not depend on
  * the order in which tiles finish and is bit-identical to b200moe_ffn_down + b200moe_combine.
- *   yo     : [R,d] bf16 expert outputs, stored as b200moe_ffn_down does, or NULL (inference: the backward is its only reader)
- *   y_acc  : [T,d] fp32, zero on entry (b200moe_permute_init)
- *   arrive : [T,d/32] int32, zero on entry, or NULL.  With it the thread that delivers the LAST contribution to a
- *            (token, 32-column chunk) reads the chunk back from L2 and writes y [T,d] bf16: no combine / convert
- *            launch follows.  Without it the caller finishes from y_acc (b200moe_combine_ln_fwd). */
+ *   yo        : [R,d] bf16 expert outputs, stored as b200moe_ffn_down does, or NULL (inference: the backward is its
+ *               only reader)
+ *   y_acc     : [T,d] fp32, zero on entry (b200moe_permute_init)
+ *   grid_sync : one int32 counter, zero on entry (b200moe_permute_init), with y [T,d] bf16; or both NULL.  With them the
+ *               kernel ends with a grid-wide rendezvous (the grid is persistent: never more CTAs than are resident at
+ *               once) after which its CTAs convert y_acc to y: no combine / convert launch follows, and tokens that
+ *               kept no assignment come out as zeros.  Without them the caller finishes from y_acc
+ *               (b200moe_combine_ln_fwd).
+ *   postnorm  : NULL, or (with grid_sync, d <= 1024) the tail writes y = LayerNorm(residual + combine) instead --
+ *               hybrid_encoder.py:157-160 in ONE kernel: down-projection, combine, residual add, norm2. */
 int b200moe_ffn_down_combine(const void* h, const void* w2, const float* b2, const int32_t* meta,
                              const int32_t* tile_expert, const int32_t* token_of_row, const float* gate_of_row,
-                             const int32_t* row_of_assignment, int T, int k, int rows_cap, int d, int F, int E,
-                             void* yo, float* y_acc, int32_t* arrive, void* y, int row_pad, void* stream);
+                             int T, int k, int rows_cap, int d, int F, int E,
+                             void* yo, float* y_acc, int32_t* grid_sync, void* y,
+                             const b200moe_postnorm* postnorm, int row_pad, void* stream);
 
 /* Expert FFN, backward.
  *   dgrad_down: dhpre = (dyp @ w2[e]) * act'(pre)             [R,F]
@@ -252,7 +299,6 @@ int b200moe_ep_p2p_unpermute_bwd(const void* const* peers, int64_t buf_offset_by
  * context [B,n_fields] int64 (device); tables: HOST array of n_fields device pointers, table i is [vocab[i], cd]
  * fp32; vocab: HOST array; wc [E, n_fields*cd] fp32.  Ids outside [0, vocab[i]) contribute nothing.
  * Backward writes every element of dtables[i] and dwc (fixed summation order over the images).                 */
-#define B200MOE_MAX_CTX_FIELDS 8
 int b200moe_ctx_bias_fwd(const int64_t* context, const float* const* tables, const int32_t* vocab, int n_fields,
                          int context_dim, const float* wc, int B, int E, float* ctx_bias, void* stream);
 int b200moe_ctx_bias_bwd(const int64_t* context, const float* dctx_bias, const float* const* tables,
@@ -283,42 +329,24 @@ enum {
   B200MOE_WS_EXPERT_OFFSETS, B200MOE_WS_META, B200MOE_WS_TILE_EXPERT, B200MOE_WS_TOKENS_PER_EXPERT,
   B200MOE_WS_KEPT_PER_EXPERT, B200MOE_WS_LOSSES, B200MOE_WS_SLOT_LIMIT, B200MOE_WS_ROW_OF_ASSIGNMENT,
   B200MOE_WS_TOKEN_OF_ROW, B200MOE_WS_GATE_OF_ROW, B200MOE_WS_XP, B200MOE_WS_PRE, B200MOE_WS_H, B200MOE_WS_YO,
-  B200MOE_WS_Y_ACC /* [T,d] fp32 */, B200MOE_WS_ARRIVE /* [T,d/32] int32 */,
+  B200MOE_WS_Y_ACC /* [T,d] fp32 */, B200MOE_WS_GRID_SYNC /* 4 x int32 */, B200MOE_WS_CTX_BIAS /* [B,E] fp32 */,
   B200MOE_WS_COUNT
 };
 enum {
   B200MOE_BWS_DYP = 0, B200MOE_BWS_DGATE_ROW, B200MOE_BWS_DHPRE, B200MOE_BWS_DXP, B200MOE_BWS_DLOGITS,
-  B200MOE_BWS_DWG_SCRATCH, B200MOE_BWS_COUNT
+  B200MOE_BWS_DWG_SCRATCH, B200MOE_BWS_DCTX /* [B,E] fp32 */, B200MOE_BWS_COUNT
 };
-/* Optional fused post-norm of the encoder layer (hybrid_encoder.py:158-160): with a non-NULL b200moe_postnorm the last
- * kernel of the forward computes out = LayerNorm(residual + combine(yo)) instead of y = combine(yo) (the [T,d]
- * intermediates y and y + residual are never written), and the backward starts from d(out).                   */
-typedef struct b200moe_postnorm {
-  const void* residual;     /* [T,d] bf16 */
-  const float* gamma;       /* [d] LayerNorm weight */
-  const float* beta;        /* [d] LayerNorm bias */
-  float eps;
-  float* mean_rstd;         /* [T,2] fp32, written by the forward, read by the backward */
-} b200moe_postnorm;
-typedef struct b200moe_postnorm_bwd {
-  const void* residual;     /* [T,d] bf16 */
-  const float* gamma;
-  const float* mean_rstd;   /* from the forward */
-  void* dv;                 /* [T,d] bf16 out: gradient of the pre-norm sum = d(residual) = d(MoE output) */
-  float* scratch;           /* b200moe_ln_scratch_floats(T, d) floats */
-  float* dgamma;            /* [d] out */
-  float* dbeta;             /* [d] out */
-} b200moe_postnorm_bwd;
 /* y_acc != NULL: the combine already happened in the down-projection's epilogue; the pre-norm sum is y_acc + residual
  * (yo / row_of_assignment / topk_gate are then unused and may be NULL). */
 int b200moe_combine_ln_fwd(const void* yo, const int32_t* row_of_assignment, const float* topk_gate,
-                           const float* y_acc, const void* residual, const float* gamma, const float* beta, float eps,
-                           int T, int k, int d, void* out, float* mean_rstd, void* stream);
+                           const float* y_acc, const void* residual, int residual_f32, const float* gamma,
+                           const float* beta, float eps, int T, int k, int d, void* out, int out_f32,
+                           float* mean_rstd, void* stream);
 int64_t b200moe_ln_scratch_floats(int T, int d);
-int b200moe_combine_ln_bwd(const void* dout, const void* yo, const int32_t* row_of_assignment,
-                           const float* topk_gate, const float* y_acc, const void* residual, const float* gamma,
-                           const float* mean_rstd, int T, int k, int d, void* dv, float* scratch, float* dgamma,
-                           float* dbeta, void* stream);
+int b200moe_combine_ln_bwd(const void* dout, int dout_f32, const void* yo, const int32_t* row_of_assignment,
+                           const float* topk_gate, const float* y_acc, const void* residual, int residual_f32,
+                           const float* gamma, const float* mean_rstd, int T, int k, int d, void* dv, float* dres_f32,
+                           float* scratch, float* dgamma, float* dbeta, void* stream);
 
 int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* desc, int64_t* offsets /* [B200MOE_WS_COUNT] */);
 int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* desc, int64_t* offsets /* [B200MOE_BWS_COUNT] */);
@@ -326,7 +354,10 @@ int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* desc, int64_t* off
  * B200MOE_LAYER_SEPARATE_COMBINE: down -> combine).  x [T,d] bf16; ctx_bias [B,E] fp32 or NULL; wg_split
  * from b200moe_prepare_weights; w1 [E,F,d], w2 [E,d,F] bf16; b1 [E,F], b2 [E,d] fp32; y [T,d] bf16.
  * save_for_backward == 0 skips the pre-activation store. */
-int b200moe_layer_fwd(const b200moe_layer_desc* desc, const void* x, const float* ctx_bias, const void* wg_split,
+/* The context enters either as ctx_bias [B,E] (computed by the caller: b200moe_ctx_bias_fwd) or as ctx (evaluated
+ * inside the router kernel; both NULL: no context). */
+int b200moe_layer_fwd(const b200moe_layer_desc* desc, const void* x, const float* ctx_bias,
+                      const b200moe_ctx_desc* ctx, const void* wg_split,
                       const void* w1, const float* b1, const void* w2, const float* b2, void* ws, void* y,
                       int save_for_backward, const b200moe_postnorm* postnorm /* or NULL */,
                       void* weights_ready /* cudaEvent_t recorded after w1 / w2 were prepared on another stream, or NULL:
@@ -338,8 +369,9 @@ int b200moe_layer_fwd(const b200moe_layer_desc* desc, const void* x, const float
 int b200moe_layer_bwd(const b200moe_layer_desc* desc, const void* x, const float* wg, const void* w1,
                       const void* w2, const void* ws, void* bws, const void* dy, const float* d_aux, void* dx,
                       float* dctx_bias, float* dwg, float* dw1, float* db1, float* dw2, float* db2,
-                      int has_ctx_bias, const b200moe_postnorm_bwd* postnorm /* or NULL: dy is then d(out) */,
-                      void* stream);
+                      int has_ctx_bias, const b200moe_ctx_desc* ctx /* or NULL; with it the gradients ctx->dtables and
+                      ctx->dwc are written on the router branch (dctx_bias may then be NULL) */,
+                      const b200moe_postnorm_bwd* postnorm /* or NULL: dy is then d(out) */, void* stream);
 /* Per-step CUDA-event timing of the two calls above (measurement aid): enable, run, synchronize the stream, then read
  * entries 0,1,... until the call returns B200MOE_EINVAL.  b200moe_layer_profile(x) also clears earlier entries. */
 int b200moe_layer_profile(int enable);

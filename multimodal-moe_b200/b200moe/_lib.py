@@ -26,14 +26,15 @@ SIGNATURES = {
     "b200moe_cast_f32_bf16": [_P, _P, _L, _P],
     "b200moe_router_scratch_bytes": [_I, _I],
     "b200moe_router_fwd": [_P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],
+    "b200moe_router_fwd_ctx": [_P, _P, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _P],
     "b200moe_plan": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _I, _F, _F, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "b200moe_permute": [_P, _P, _P, _I, _I, _P, _P],
-    "b200moe_permute_init": [_P, _P, _P, _I, _I, _P, _P, _P, _P, _I, _I, _P, _P],
+    "b200moe_permute_init": [_P, _P, _P, _I, _I, _P, _P, _P, _I, _P],
     "b200moe_combine": [_P, _P, _P, _I, _I, _I, _P, _P],
     "b200moe_combine_bwd": [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P],
     "b200moe_ffn_up": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _I, _P],
     "b200moe_ffn_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
-    "b200moe_ffn_down_combine": [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _I, _P],
+    "b200moe_ffn_down_combine": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _I, _P],
     "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _I, _P],
     "b200moe_ffn_dgrad_up": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
     "b200moe_ffn_wgrad": [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
@@ -54,11 +55,11 @@ SIGNATURES = {
     "b200moe_layer_profile_read": [_I, _P, _P],
     "b200moe_layer_ws_layout": [_P, _P],
     "b200moe_layer_bwd_ws_layout": [_P, _P],
-    "b200moe_layer_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P],
-    "b200moe_layer_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P],
-    "b200moe_combine_ln_fwd": [_P, _P, _P, _P, _P, _P, _P, _F, _I, _I, _I, _P, _P, _P],
+    "b200moe_layer_fwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P],
+    "b200moe_layer_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _P, _P, _P],
+    "b200moe_combine_ln_fwd": [_P, _P, _P, _P, _P, _I, _P, _P, _F, _I, _I, _I, _P, _I, _P, _P],
     "b200moe_ln_scratch_floats": [_I, _I],
-    "b200moe_combine_ln_bwd": [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P],
+    "b200moe_combine_ln_bwd": [_P, _I, _P, _P, _P, _P, _P, _I, _P, _P, _I, _I, _I, _P, _P, _P, _P, _P, _P],
     "b200moe_router_bwd_dlogits": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _P, _P],
     "b200moe_dwg_scratch_floats": [_I, _I, _I],
     "b200moe_router_bwd_dwg": [_P, _P, _I, _I, _I, _P, _P, _P],
@@ -78,13 +79,24 @@ _RESTYPE = {"b200moe_last_error": C.c_char_p, "b200moe_launch_count": C.c_int64,
 class PostNorm(C.Structure):
     """b200moe_postnorm of include/b200moe.h."""
     _fields_ = [("residual", C.c_void_p), ("gamma", C.c_void_p), ("beta", C.c_void_p), ("eps", C.c_float),
-                ("mean_rstd", C.c_void_p)]
+                ("mean_rstd", C.c_void_p), ("residual_f32", C.c_int32), ("out_f32", C.c_int32)]
 
 
 class PostNormBwd(C.Structure):
     """b200moe_postnorm_bwd of include/b200moe.h."""
     _fields_ = [("residual", C.c_void_p), ("gamma", C.c_void_p), ("mean_rstd", C.c_void_p), ("dv", C.c_void_p),
-                ("scratch", C.c_void_p), ("dgamma", C.c_void_p), ("dbeta", C.c_void_p)]
+                ("scratch", C.c_void_p), ("dgamma", C.c_void_p), ("dbeta", C.c_void_p), ("residual_f32", C.c_int32),
+                ("dout_f32", C.c_int32), ("dres_f32", C.c_void_p)]
+
+
+MAX_CTX_FIELDS = 8
+
+
+class CtxDesc(C.Structure):
+    """b200moe_ctx_desc of include/b200moe.h."""
+    _fields_ = [("context", C.c_void_p), ("tables", C.c_void_p * MAX_CTX_FIELDS), ("vocab", C.c_int32 * MAX_CTX_FIELDS),
+                ("n_fields", C.c_int32), ("context_dim", C.c_int32), ("B", C.c_int32), ("wc", C.c_void_p),
+                ("dtables", C.c_void_p * MAX_CTX_FIELDS), ("dwc", C.c_void_p)]
 
 
 class LayerDesc(C.Structure):
@@ -102,8 +114,8 @@ LAYER_SEPARATE_COMBINE = 1                # B200MOE_LAYER_SEPARATE_COMBINE
 
 WS_NAMES = ("logits", "topk_idx", "topk_gate", "block_counts", "block_stats", "expert_offsets", "meta", "tile_expert",
             "tokens_per_expert", "kept_per_expert", "losses", "slot_limit", "row_of_assignment", "token_of_row",
-            "gate_of_row", "xp", "pre", "h", "yo", "y_acc", "arrive")
-BWS_NAMES = ("dyp", "dgate_row", "dhpre", "dxp", "dlogits", "dwg_scratch")
+            "gate_of_row", "xp", "pre", "h", "yo", "y_acc", "grid_sync", "ctx_bias")
+BWS_NAMES = ("dyp", "dgate_row", "dhpre", "dxp", "dlogits", "dwg_scratch", "dctx")
 
 _lib: Optional[C.CDLL] = None
 
@@ -142,7 +154,7 @@ def stream_ptr() -> int:
 # kernels launched by each entry point (memset nodes not counted); used for bench.py's gpu_launches
 KERNELS_PER_CALL = {
     "b200moe_cast_f32_bf16": 1, "b200moe_prepare_weights": 1, "b200moe_ctx_bias_fwd": 1, "b200moe_ctx_bias_bwd": 1,
-    "b200moe_layer_fwd": 7, "b200moe_layer_bwd": 11, "b200moe_combine_ln_fwd": 1, "b200moe_combine_ln_bwd": 2, "b200moe_router_bwd_params": 2, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
+    "b200moe_layer_fwd": 6, "b200moe_layer_bwd": 12, "b200moe_router_fwd_ctx": 1, "b200moe_combine_ln_fwd": 1, "b200moe_combine_ln_bwd": 2, "b200moe_router_bwd_params": 2, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
     "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
     "b200moe_permute_init": 1, "b200moe_ffn_down_combine": 1,

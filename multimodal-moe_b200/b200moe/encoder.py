@@ -10,7 +10,7 @@ computes what the dense one did (the K1 anchor of SURVEY.md §8(c)) and training
 """
 from __future__ import annotations
 
-from typing import Optional
+from typing import Optional, Sequence
 
 import torch
 import torch.nn as nn
@@ -19,12 +19,24 @@ from .layer import ContextMoE
 
 
 class MoEEncoderLayer(nn.Module):
-    def __init__(self, d_model: int, nhead: int, dim_feedforward: int = 2048, dropout: float = 0.1,
-                 activation: str = "gelu", normalize_before: bool = False, **moe_kwargs):
+    # every argument is named: the vendored registry records the constructor's argspec (workspace.py:63-87), a
+    # **kwargs would be dropped by `create()`
+    def __init__(self, d_model: int, nhead: int, dim_feedforward: int = 2048, dropout: float = 0.0,
+                 activation: str = "gelu", normalize_before: bool = False, num_experts: int = 8, top_k: int = 2,
+                 capacity_factor: Optional[float] = 1.25, context_vocab_sizes: Sequence[int] = (),
+                 context_dim: int = 32, aux_loss_weight: float = 1e-2, z_loss_weight: float = 1e-3,
+                 normalize_topk: bool = True, ep_group=None):
         super().__init__()
+        if dropout > 0.0:
+            # hybrid_encoder.py:157 applies self.dropout between the activation and linear2; the expert FFNs have no
+            # inner dropout (A.6: dropout 0, as rtdetrv2_r50vd.yml:38 configures the encoder)
+            raise ValueError("MoEEncoderLayer supports dropout=0.0 only (the vendored encoder default)")
         self.normalize_before = normalize_before
         self.self_attn = nn.MultiheadAttention(d_model, nhead, dropout, batch_first=True)
-        self.moe = ContextMoE(d_model, dim_feedforward, activation=activation, **moe_kwargs)
+        self.moe = ContextMoE(d_model, dim_feedforward, num_experts, top_k=top_k, capacity_factor=capacity_factor,
+                              context_vocab_sizes=context_vocab_sizes, context_dim=context_dim, activation=activation,
+                              aux_loss_weight=aux_loss_weight, z_loss_weight=z_loss_weight,
+                              normalize_topk=normalize_topk, ep_group=ep_group)
         self.norm1 = nn.LayerNorm(d_model)
         self.norm2 = nn.LayerNorm(d_model)
         self.dropout1 = nn.Dropout(dropout)
@@ -69,6 +81,18 @@ class MoEEncoderLayer(nn.Module):
         """Build from a constructed dense layer (anything with self_attn, linear1, linear2, norm1, norm2, dropout1,
         dropout2, normalize_before): shares its attention / norm modules, copies the dense FFN into every expert."""
         d_model, dff = dense.linear1.in_features, dense.linear1.out_features
+        inner = getattr(dense, "dropout", None)
+        if isinstance(inner, nn.Dropout) and inner.p > 0.0:
+            raise ValueError("the dense layer applies dropout inside its FFN (hybrid_encoder.py:157); the expert FFNs "
+                             "have none (A.6) -- build the encoder with dropout=0.0 (rtdetrv2_r50vd.yml:38)")
+        if moe_kwargs.get("activation") is None:
+            act = getattr(dense, "activation", None)          # zoo/rtdetr/utils.py:137-172 builds these modules
+            if act is None or isinstance(act, nn.GELU) or act is torch.nn.functional.gelu:
+                moe_kwargs["activation"] = "gelu"
+            elif isinstance(act, nn.ReLU) or act is torch.nn.functional.relu:
+                moe_kwargs["activation"] = "relu"
+            else:
+                raise ValueError(f"unsupported FFN activation {act!r}: the expert epilogues implement gelu and relu")
         new = cls.__new__(cls)
         nn.Module.__init__(new)
         new.normalize_before = bool(getattr(dense, "normalize_before", False))

@@ -305,9 +305,14 @@ class _EPFunction(torch.autograd.Function):
             dx = ops.unpermute_bwd(dxs, p.row_of_assignment, dlogits, wgf, T, k, d)
         t_w1, t_b1, t_w2, t_b2, t_wg = ctx.dtypes
 
-        def cast(g, dt):
+        scale = float(getattr(mod, "expert_grad_scale", 1.0))
+
+        def cast(g, dt, expert=False):
+            if g is not None and expert and scale != 1.0:
+                g = g.mul_(scale)                 # DDP's mean-over-ranks convention (b200moe/checkpoint.py)
             return g if g is None or g.dtype == dt else g.to(dt)
-        return (dx, dctx, cast(dwg, t_wg), cast(dw1, t_w1), cast(db1, t_b1), cast(dw2, t_w2), cast(db2, t_b2),
+        return (dx, dctx, cast(dwg, t_wg), cast(dw1, t_w1, True), cast(db1, t_b1, True), cast(dw2, t_w2, True),
+                cast(db2, t_b2, True),
                 None, None)
 
 

@@ -5,8 +5,10 @@ and remains the fallback).
 
 Per module one symmetric arena (torch.distributed._symmetric_memory: cuMem allocations mapped into every rank of the
 group, plus signal pads for a device-side barrier) holds xp | yo | dyp | dxp, each [rows_cap, d] bf16 with
-rows_cap = E_local * pad128(capacity for T_cap tokens per rank).  T_cap is agreed once (max over the ranks at the
-first call); a later call with more tokens on some rank raises on that rank.
+rows_cap = E_local * pad(capacity for T_cap tokens per rank).  T_cap is agreed once: the constructor's `ep_max_tokens`
+(declare it for multiscale training) or else the first batch, max over the ranks.  What has to fit is the GLOBAL row
+count, so single ranks may exceed T_cap; if the rows of a pass do not fit, the device-side flag of ep_p2p_tables (the
+same on every rank) makes the next backward / forward raise on ALL ranks.
 
 Forward : router -> histogram all-gather -> ep_route_tables -> plan (send layout) -> ep_p2p_tables ->
           ep_p2p_dispatch (gather x rows, store them into the expert ranks' xp) -> barrier -> up -> down (into yo)
@@ -55,15 +57,31 @@ class P2PUnavailable(RuntimeError):
     pass
 
 
+def _agree(ok: bool, group, dev) -> bool:
+    """True iff `ok` on every rank (every rank calls this at the same point, whatever happened to it locally)."""
+    t = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    return int(t.item()) == 1
+
+
 class _Arena:
-    def __init__(self, mod, group, T_cap: int, dev):
+    """Symmetric row buffers of one module.  Set-up is a fixed sequence of collectives that every rank executes in the
+    same order whether or not a local step failed, so a failure on one rank turns into P2PUnavailable on all of them
+    instead of a hang in mismatched collectives."""
+
+    def __init__(self, mod, group, T_local: int, dev):
+        err, symm = None, None
         try:
-            import torch.distributed._symmetric_memory as symm
+            import torch.distributed._symmetric_memory as symm      # private torch API: probed, never assumed
         except Exception as e:  # noqa: BLE001
-            raise P2PUnavailable(f"torch symmetric memory is not importable: {e!r}") from e
+            err = e
+        if not _agree(err is None, group, dev):
+            raise P2PUnavailable(f"torch symmetric memory is not importable on every rank: {err!r}")
         W = dist.get_world_size(group)
         E, k, d = mod.num_experts, mod.top_k, mod.d_model
-        t = torch.tensor([T_cap], dtype=torch.int64, device=dev)
+        # tokens per rank the arena is sized for: the declared maximum (multiscale training varies the token count per
+        # step and per rank, configs/rtdetrv2/include/dataloader.yml:22) or else the first batch, max over the ranks
+        t = torch.tensor([max(int(T_local), int(mod.ep_max_tokens or 0))], dtype=torch.int64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
         self.T_cap = int(t.item())
         cap = ops.capacity_of(mod.capacity_factor, self.T_cap * W, k, E)
@@ -72,35 +90,56 @@ class _Arena:
                                                              mod.dim_feedforward))
         self.rows_cap = mod.num_local_experts * ((cap + self.row_pad - 1) // self.row_pad * self.row_pad)
         self.buf_bytes = self.rows_cap * d * 2
-        self.mem = symm.empty(4 * self.buf_bytes, dtype=torch.uint8, device=dev)
-        self.hdl = symm.rendezvous(self.mem, group)
-        self.peers = torch.tensor(list(self.hdl.buffer_ptrs), dtype=torch.int64, device=dev)
+        try:
+            self.mem = symm.empty(4 * self.buf_bytes, dtype=torch.uint8, device=dev)
+        except Exception as e:  # noqa: BLE001
+            err = e
+        if not _agree(err is None, group, dev):
+            raise P2PUnavailable(f"symmetric allocation of {4 * self.buf_bytes} bytes failed on some rank: {err!r}")
+        try:
+            self.hdl = symm.rendezvous(self.mem, group)               # collective: reached by every rank or by none
+            self.peers = torch.tensor(list(self.hdl.buffer_ptrs), dtype=torch.int64, device=dev)
+        except Exception as e:  # noqa: BLE001
+            err = e
+        if not _agree(err is None, group, dev):
+            raise P2PUnavailable(f"symmetric-memory rendezvous failed on some rank: {err!r}")
         bf = self.mem.view(torch.bfloat16).view(4, self.rows_cap, d)
         self.xp, self.yo, self.dyp, self.dxp = bf[0], bf[1], bf[2], bf[3]
         self.off = [i * self.buf_bytes for i in range(4)]
         self.pending = False           # a forward whose backward has not run yet owns the arena
+        # overflow evidence: meta[5] of b200moe_ep_p2p_tables (identical on every rank, it is computed from the gathered
+        # histogram) lands here asynchronously and is looked at by the next backward / forward
+        self.flag_host = torch.zeros(8, dtype=torch.int32).pin_memory()
+        self.flag_event = None
 
     def barrier(self, channel: int):
         self.hdl.barrier(channel=channel)
+
+    def note_meta(self, meta: torch.Tensor):
+        self.flag_host.copy_(meta, non_blocking=True)
+        self.flag_event = torch.cuda.Event()
+        self.flag_event.record()
+
+    def check_overflow(self):
+        """Raises on EVERY rank (the flag is the same everywhere) when the rows of the last pass did not fit the arena."""
+        if self.flag_event is None:
+            return
+        self.flag_event.synchronize()
+        self.flag_event = None
+        if int(self.flag_host[5]) != 0:
+            raise RuntimeError(
+                f"expert-parallel peer-memory arena overflow: it was sized for {self.T_cap} tokens per rank "
+                f"({self.rows_cap} rows), the last batch needed more.  Construct the layer with ep_max_tokens=<largest "
+                f"tokens per rank> (multiscale training: the largest scale), or with ep_p2p=False for the NCCL path")
 
 
 def arena_for(mod, T: int, dev) -> _Arena:
     a = mod.__dict__.get("_p2p_arena")
     if a is None:
-        # every rank must take the same transport: agree on the outcome of the (collective) set-up
-        err = None
-        try:
-            a = _Arena(mod, mod.ep_group, T, dev)
-        except Exception as e:  # noqa: BLE001
-            err = e
-        ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=dev)
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=mod.ep_group)
-        if int(ok.item()) == 0:
-            raise P2PUnavailable(f"peer-memory arena could not be set up on every rank: {err!r}")
-        mod.__dict__["_p2p_arena"] = a
-    if T > a.T_cap:
-        raise RuntimeError(f"expert-parallel peer-memory arena was sized for {a.T_cap} tokens per rank, got {T}; "
-                           f"construct the layer with ep_p2p=False or call with the largest batch first")
+        a = mod.__dict__["_p2p_arena"] = _Arena(mod, mod.ep_group, T, dev)    # raises P2PUnavailable on every rank or none
+    # no per-rank check of T against T_cap here: a rank-local raise would leave the other ranks waiting in the
+    # histogram all-gather.  What must fit is the GLOBAL row count; the device-side flag says so on all ranks alike.
+    a.check_overflow()
     return a
 
 
@@ -136,6 +175,7 @@ class _P2PFunction(torch.autograd.Function):
         send_cap = ops.rows_upper_bound(T, k, E, -1)
         p = ops.plan(r, T, k, E, _BIG, mod.aux_loss_weight, mod.z_loss_weight, global_offset=goff_shift,
                      expert_order=None, row_pad=1, rows_cap=send_cap)
+        p.capacity = kept[W * E]          # the global capacity (device scalar; the plan call above only saw the shifted offsets)
         R = ar.rows_cap
         dest_off = torch.empty((E,), dtype=i32, device=dev)
         offs = torch.empty((EL + 1,), dtype=i32, device=dev)
@@ -143,6 +183,7 @@ class _P2PFunction(torch.autograd.Function):
         tile_e = torch.empty((R // 128,), dtype=i32, device=dev)
         _lib.call("b200moe_ep_p2p_tables", kept.data_ptr(), W, E, rank, R, ar.row_pad, dest_off.data_ptr(), offs.data_ptr(),
                   meta.data_ptr(), tile_e.data_ptr(), st)
+        ar.note_meta(meta)
         _lib.call("b200moe_ep_p2p_zero_pads", kept.data_ptr(), offs.data_ptr(), W, E, rank, d, ar.xp.data_ptr(),
                   ar.dyp.data_ptr() if need_grad else None, st)
         dest_of_row = torch.empty((send_cap,), dtype=i32, device=dev)
@@ -187,6 +228,7 @@ class _P2PFunction(torch.autograd.Function):
         d_aux_t = d_aux.float().contiguous() if d_aux is not None else None
         f32 = torch.float32
 
+        ar.check_overflow()               # before any gradient of an overflowed pass reaches the optimizer
         dgate_row = torch.empty((send_cap,), dtype=f32, device=dev)
         _lib.call("b200moe_ep_p2p_combine_bwd", dy.data_ptr(), ar.peers.data_ptr(), ar.off[1], ar.off[2], R,
                   dest_of_row.data_ptr(), p.token_of_row.data_ptr(), p.gate_of_row.data_ptr(), p.meta.data_ptr(),
@@ -233,9 +275,14 @@ class _P2PFunction(torch.autograd.Function):
         ar.pending = False
         t_w1, t_b1, t_w2, t_b2, t_wg = ctx.dtypes
 
-        def cast(g, dt):
+        scale = float(getattr(mod, "expert_grad_scale", 1.0))
+
+        def cast(g, dt, expert=False):
+            if g is not None and expert and scale != 1.0:
+                g = g.mul_(scale)                 # DDP's mean-over-ranks convention (b200moe/checkpoint.py)
             return g if g is None or g.dtype == dt else g.to(dt)
-        return (dx, dctx, cast(dwg, t_wg), cast(dw1, t_w1), cast(db1, t_b1), cast(dw2, t_w2), cast(db2, t_b2),
+        return (dx, dctx, cast(dwg, t_wg), cast(dw1, t_w1, True), cast(db1, t_b1, True), cast(dw2, t_w2, True),
+                cast(db2, t_b2, True),
                 None, None, None)
 
 

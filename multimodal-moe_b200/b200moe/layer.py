@@ -28,7 +28,7 @@ _WS_DTYPES = {"logits": torch.float32, "topk_idx": torch.int32, "topk_gate": tor
               "kept_per_expert": torch.int32, "losses": torch.float32, "slot_limit": torch.int32,
               "row_of_assignment": torch.int32, "token_of_row": torch.int32, "gate_of_row": torch.float32,
               "xp": torch.bfloat16, "pre": torch.bfloat16, "h": torch.bfloat16, "yo": torch.bfloat16,
-              "y_acc": torch.float32, "arrive": torch.int32}
+              "y_acc": torch.float32, "grid_sync": torch.int32, "ctx_bias": torch.float32}
 
 
 def _f32c(t: torch.Tensor) -> torch.Tensor:
@@ -68,7 +68,8 @@ class _LayerPlan:
                       "tile_expert": (R // 128,), "tokens_per_expert": (E,), "kept_per_expert": (E,), "losses": (3,),
                       "slot_limit": (2 * k * E,), "row_of_assignment": (T, k), "token_of_row": (R,),
                       "gate_of_row": (R,), "xp": (R, d), "pre": (R, F), "h": (R, F), "yo": (R, d),
-                      "y_acc": (T, d) if self.fused else (0, d), "arrive": (T, d // 32) if self.fused else (0, d // 32)}
+                      "y_acc": (T, d) if self.fused else (0, d), "grid_sync": (4,) if self.fused else (0,),
+                      "ctx_bias": ((T + tpi - 1) // tpi, E)}
         self.capacity, self.rows_cap = cap, rows_cap
 
     def view(self, ws: torch.Tensor, name: str) -> torch.Tensor:
@@ -161,30 +162,33 @@ class _MoEFunction(torch.autograd.Function):
         w1b, w2b, wsplit, wgf, ready = mod._prepared(w1, w2, wg, overlap=not _lib.PROFILING)
         b1f, b2f = _f32c(b1), _f32c(b2)
         st = _lib.stream_ptr()
-        cb = None
+        cx_ptr = None
         if context is not None and wc is not None:
-            B = context.shape[0]
-            cb = torch.empty((B, E), dtype=torch.float32, device=dev)
+            # A.2: the bias is evaluated inside the router kernel (per 128-token tile, while its tokens are in flight)
             tabs = [_f32c(t) for t in tables]
             wcf = _f32c(wc)
-            tp, vp = mod._ctx_arrays(tabs)
-            _lib.call("b200moe_ctx_bias_fwd", context.data_ptr(), tp, vp, len(tabs), mod.context_dim, wcf.data_ptr(),
-                      B, E, cb.data_ptr(), st)
+            cx = mod._ctx_desc(context, tabs, wcf)
+            cx_ptr = C.addressof(cx)
             ctx.ctx_saved = (context, tabs, wcf)
         ws = torch.empty((pl.ws_bytes,), dtype=torch.uint8, device=dev)
-        y = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
         pn_ptr = None
         ctx.ln = None
+        out_f32 = False
         if residual is not None:                     # fused post-norm: y = LayerNorm(residual + MoE(x))
+            # the residual stream keeps its dtype (fp32 under the reference's autocast: LayerNorm outputs fp32) and the
+            # normalised output has it too, as with the vendored `norm2(residual + ffn)` (hybrid_encoder.py:158-160)
+            out_f32 = residual.dtype == torch.float32
             gam, bet = _f32c(ln_w), _f32c(ln_b)
             mean_rstd = torch.empty((T, 2), dtype=torch.float32, device=dev)
-            pn = _lib.PostNorm(residual.data_ptr(), gam.data_ptr(), bet.data_ptr(), float(ln_eps), mean_rstd.data_ptr())
+            pn = _lib.PostNorm(residual.data_ptr(), gam.data_ptr(), bet.data_ptr(), float(ln_eps), mean_rstd.data_ptr(),
+                               int(out_f32), int(out_f32))
             pn_ptr = C.addressof(pn)
             ctx.ln = (residual, gam, mean_rstd, ln_w.dtype, ln_b.dtype)
-        _lib.call("b200moe_layer_fwd", pl.desc_ptr, x2.data_ptr(), cb.data_ptr() if cb is not None else None,
+        y = torch.empty((T, d), dtype=torch.float32 if out_f32 else torch.bfloat16, device=dev)
+        _lib.call("b200moe_layer_fwd", pl.desc_ptr, x2.data_ptr(), None, cx_ptr,
                   wsplit.data_ptr(), w1b.data_ptr(), b1f.data_ptr(), w2b.data_ptr(), b2f.data_ptr(), ws.data_ptr(),
                   y.data_ptr(), int(need_grad), pn_ptr, ready.cuda_event if ready is not None else None, st)
-        ctx.mod, ctx.pl, ctx.has_ctx = mod, pl, cb is not None
+        ctx.mod, ctx.pl, ctx.has_ctx = mod, pl, cx_ptr is not None
         ctx.dtypes = (wg.dtype, w1.dtype, b1.dtype, w2.dtype, b2.dtype)
         ctx.save_for_backward(x2, wgf, w1b, w2b, ws)
         losses = pl.view(ws, "losses")
@@ -202,9 +206,10 @@ class _MoEFunction(torch.autograd.Function):
         E, F = mod.num_experts, mod.dim_feedforward
         dev = x2.device
         need = ctx.needs_input_grad      # x2, context, wg, wc, w1, b1, w2, b2, mod, tpi, residual, ln_w, ln_b, eps, *tables
+        res_f32 = ctx.ln is not None and ctx.ln[0].dtype == torch.float32
         if dy is None:
             dy = torch.zeros_like(x2)
-        dy = dy.contiguous().to(torch.bfloat16)
+        dy = dy.contiguous().to(torch.float32 if res_f32 else torch.bfloat16)
         d_aux_t = _f32c(d_aux) if d_aux is not None else None
         f32 = torch.float32
         dx = torch.empty((T, d), dtype=torch.bfloat16, device=dev) if need[0] else None
@@ -214,29 +219,9 @@ class _MoEFunction(torch.autograd.Function):
         dw2 = torch.empty((E, d, F), dtype=f32, device=dev) if need[6] else None
         db2 = torch.empty((E, d), dtype=f32, device=dev) if need[7] else None
         want_ctx = ctx.has_ctx and (need[3] or any(need[14:]))
-        dcb = None
+        dwc, dtabs, cx_ptr = None, (), None
         if want_ctx:
-            B = ctx.ctx_saved[0].shape[0]
-            dcb = torch.empty((B, E), dtype=f32, device=dev)
-        bws = torch.empty((pl.bws_bytes,), dtype=torch.uint8, device=dev)
-        p = lambda t: t.data_ptr() if t is not None else None  # noqa: E731
-        st = _lib.stream_ptr()
-        pn_ptr, dres, dgam, dbet = None, None, None, None
-        if ctx.ln is not None:
-            residual, gam, mean_rstd, t_lw, t_lb = ctx.ln
-            dres = torch.empty((T, d), dtype=torch.bfloat16, device=dev)
-            dgam, dbet = torch.empty((d,), dtype=f32, device=dev), torch.empty((d,), dtype=f32, device=dev)
-            scr = torch.empty((_lib.load().b200moe_ln_scratch_floats(T, d),), dtype=f32, device=dev)
-            pn = _lib.PostNormBwd(residual.data_ptr(), gam.data_ptr(), mean_rstd.data_ptr(), dres.data_ptr(),
-                                  scr.data_ptr(), dgam.data_ptr(), dbet.data_ptr())
-            pn_ptr = C.addressof(pn)
-        _lib.call("b200moe_layer_bwd", pl.desc_ptr, x2.data_ptr(), wgf.data_ptr(), w1b.data_ptr(), w2b.data_ptr(),
-                  ws.data_ptr(), bws.data_ptr(), dy.data_ptr(), p(d_aux_t), p(dx), p(dcb), p(dwg), p(dw1), p(db1),
-                  p(dw2), p(db2), int(ctx.has_ctx), pn_ptr, st)
-        if ctx.ln is not None:
-            dgam, dbet = (dgam if dgam.dtype == t_lw else dgam.to(t_lw)), (dbet if dbet.dtype == t_lb else dbet.to(t_lb))
-        dwc, dtabs = None, ()
-        if want_ctx:
+            # d(ctx_proj), d(ctx_embed) are written by the same C call, on its router branch
             context, tabs, wcf = ctx.ctx_saved
             dwc = torch.empty_like(wcf)
             flat = torch.empty((sum(t.numel() for t in tabs),), dtype=f32, device=dev)
@@ -244,11 +229,28 @@ class _MoEFunction(torch.autograd.Function):
             for t in tabs:
                 dtabs.append(flat[o:o + t.numel()].view(t.shape))
                 o += t.numel()
-            tp, vp = mod._ctx_arrays(tabs)
-            dp = (C.c_void_p * len(tabs))(*[t.data_ptr() for t in dtabs])
-            _lib.call("b200moe_ctx_bias_bwd", context.data_ptr(), dcb.data_ptr(), tp, vp, len(tabs), mod.context_dim,
-                      wcf.data_ptr(), context.shape[0], E, C.addressof(dp), dwc.data_ptr(), st)
+            cx = mod._ctx_desc(context, tabs, wcf, dtabs, dwc)
+            cx_ptr = C.addressof(cx)
             dtabs = tuple(dtabs)
+        bws = torch.empty((pl.bws_bytes,), dtype=torch.uint8, device=dev)
+        p = lambda t: t.data_ptr() if t is not None else None  # noqa: E731
+        st = _lib.stream_ptr()
+        pn_ptr, dres, dgam, dbet = None, None, None, None
+        if ctx.ln is not None:
+            residual, gam, mean_rstd, t_lw, t_lb = ctx.ln
+            dv = torch.empty((T, d), dtype=torch.bfloat16, device=dev)        # d(MoE output): feeds the expert backward
+            dres = torch.empty((T, d), dtype=f32, device=dev) if res_f32 else dv
+            dgam, dbet = torch.empty((d,), dtype=f32, device=dev), torch.empty((d,), dtype=f32, device=dev)
+            scr = torch.empty((_lib.load().b200moe_ln_scratch_floats(T, d),), dtype=f32, device=dev)
+            pn = _lib.PostNormBwd(residual.data_ptr(), gam.data_ptr(), mean_rstd.data_ptr(), dv.data_ptr(),
+                                  scr.data_ptr(), dgam.data_ptr(), dbet.data_ptr(), int(res_f32), int(res_f32),
+                                  dres.data_ptr() if res_f32 else None)
+            pn_ptr = C.addressof(pn)
+        _lib.call("b200moe_layer_bwd", pl.desc_ptr, x2.data_ptr(), wgf.data_ptr(), w1b.data_ptr(), w2b.data_ptr(),
+                  ws.data_ptr(), bws.data_ptr(), dy.data_ptr(), p(d_aux_t), p(dx), None, p(dwg), p(dw1), p(db1),
+                  p(dw2), p(db2), int(ctx.has_ctx), cx_ptr, pn_ptr, st)
+        if ctx.ln is not None:
+            dgam, dbet = (dgam if dgam.dtype == t_lw else dgam.to(t_lw)), (dbet if dbet.dtype == t_lb else dbet.to(t_lb))
         t_wg, t_w1, t_b1, t_w2, t_b2 = ctx.dtypes
 
         def cast(g, dt):
@@ -269,7 +271,7 @@ class ContextMoE(nn.Module):
                  capacity_factor: Optional[float] = 1.25, context_vocab_sizes: Sequence[int] = (),
                  context_dim: int = 32, activation: str = "gelu", aux_loss_weight: float = 1e-2,
                  z_loss_weight: float = 1e-3, normalize_topk: bool = True, ep_group=None,
-                 ep_p2p: Optional[bool] = None):
+                 ep_p2p: Optional[bool] = None, ep_max_tokens: Optional[int] = None):
         super().__init__()
         if activation not in _lib.ACTIVATIONS:
             # encoder FFN: exact-erf GELU (zoo/rtdetr/utils.py:160-161); decoder FFN: ReLU (rtdetrv2_decoder.py:169)
@@ -293,6 +295,10 @@ class ContextMoE(nn.Module):
         self.fused_combine = True
         self.ep_group = ep_group
         self.ep_p2p = ep_p2p          # None: peer-memory dispatch when available; False: NCCL all-to-all; True: required
+        self.ep_max_tokens = ep_max_tokens   # tokens per rank the peer-memory arena is sized for (None: the first batch)
+        # debugging aid (one host sync per forward): raise on context ids outside [0, vocab); by default such ids behave
+        # like "missing" without its embedding (they contribute nothing to the bias)
+        self.validate_context = False
         self.ep_chunks = 1            # groups of local experts whose all-to-all overlaps the other groups' GEMMs
         # (measured at 2 GPUs, workload D: 1 group 3.72 ms, 2 groups 4.00 ms, 4 groups 4.91 ms per step)
         self.ep_size, self.ep_rank = 1, 0
@@ -302,6 +308,9 @@ class ContextMoE(nn.Module):
         if num_experts % self.ep_size:
             raise ValueError("num_experts must be divisible by the expert-parallel world size")
         self.num_local_experts = num_experts // self.ep_size   # experts [ep_rank*EL, (ep_rank+1)*EL) live here
+        # expert-parallel backward multiplies the gradients of w1, b1, w2, b2 by this: 1 / ep_size puts them on DDP's
+        # mean-over-ranks scale (b200moe.checkpoint.ddp_ignore_experts sets it; 1.0 = plain sum over all ranks' losses)
+        self.expert_grad_scale = 1.0
 
         E, Fh, d = self.num_local_experts, dim_feedforward, d_model
         self.gate = nn.Linear(d, num_experts, bias=False)
@@ -431,13 +440,29 @@ class ContextMoE(nn.Module):
             from . import ep_p2p
             try:
                 ar = ep_p2p.arena_for(self, xb.shape[0], xb.device)
-            except ep_p2p.P2PUnavailable:
+            except ep_p2p.P2PUnavailable:      # raised on every rank or on none (the set-up agrees collectively)
                 if self.ep_p2p:
                     raise
                 self.ep_p2p, ar = False, None
             if ar is not None and not ar.pending:
                 return ep_p2p.p2p_forward(self, xb, cb, tpi, ar)
         return ep_forward(self, xb, cb, tpi)
+
+    def _ctx_desc(self, context, tabs, wcf, dtabs=None, dwc=None):
+        """b200moe_ctx_desc (a HOST struct of device pointers) for the whole-layer calls; the caller keeps it alive for
+        the duration of the call."""
+        n = len(tabs)
+        cx = _lib.CtxDesc()
+        cx.context = context.data_ptr()
+        for i, t in enumerate(tabs):
+            cx.tables[i] = t.data_ptr()
+            cx.vocab[i] = t.shape[0]
+            if dtabs is not None:
+                cx.dtables[i] = dtabs[i].data_ptr()
+        cx.n_fields, cx.context_dim, cx.B = n, self.context_dim, context.shape[0]
+        cx.wc = wcf.data_ptr()
+        cx.dwc = dwc.data_ptr() if dwc is not None else None
+        return cx
 
     def _ctx_arrays(self, tabs):
         """HOST arrays (device pointers of the embedding tables, their vocabulary sizes) for the ctx_bias calls."""
@@ -460,6 +485,10 @@ class ContextMoE(nn.Module):
             raise RuntimeError("b200moe.ContextMoE runs on a B200 (sm_100a) only; there is no CPU fallback")
         if x.shape[-1] != self.d_model:
             raise ValueError(f"last dim {x.shape[-1]} != d_model {self.d_model}")
+        if x.device.index != torch.cuda.current_device():
+            # the C calls launch on the CURRENT device's stream: make x's device current for the duration of the call
+            with torch.cuda.device(x.device):
+                return self.forward(x, context, _post)
         shape = x.shape
         x2 = x.reshape(-1, self.d_model)
         T = x2.shape[0]
@@ -472,6 +501,10 @@ class ContextMoE(nn.Module):
         B = shape[0] if x.dim() == 3 else 1
         if context is not None and context.shape[0] != B:
             raise ValueError("context must have one row per image")
+        if context is not None and self.validate_context and self.ctx_proj is not None:
+            vs = torch.tensor(self.context_vocab_sizes, device=context.device)
+            if context.shape[1] != len(self.context_vocab_sizes) or bool(((context < 0) | (context >= vs)).any()):
+                raise ValueError(f"context ids outside the vocabulary {self.context_vocab_sizes}: {context.tolist()}")
         tpi = T // B
         xb = x2 if x2.dtype == torch.bfloat16 else x2.to(torch.bfloat16)
         if not xb.is_contiguous():
@@ -501,7 +534,8 @@ class ContextMoE(nn.Module):
             if res.shape != x.shape:
                 raise ValueError("residual must have the shape of x")
             res_b = res.reshape(-1, self.d_model)
-            res_b = res_b if res_b.dtype == torch.bfloat16 else res_b.to(torch.bfloat16)
+            if res_b.dtype not in (torch.bfloat16, torch.float32):
+                res_b = res_b.float()
             res_b = res_b if res_b.is_contiguous() else res_b.contiguous()
             ln_w, ln_b, ln_eps = norm.weight, norm.bias, norm.eps
         y, aux, _stats = _MoEFunction.apply(xb, ctx_ids, self.gate.weight,

@@ -149,31 +149,28 @@ def ffn_up(xp, w1, b1, meta, tile_expert, save_pre: bool = True, row_pad: int = 
     return pre, h
 
 
-def permute_init(x: torch.Tensor, token_of_row: torch.Tensor, meta: torch.Tensor, rows_cap: int,
-                 row_of_assignment: torch.Tensor, finalize: bool = True):
-    """Dispatch + the zero state of the fused combine: (xp, y_acc [T,d] fp32, arrive [T,d/32] | None, y [T,d] | None)."""
+def permute_init(x: torch.Tensor, token_of_row: torch.Tensor, meta: torch.Tensor, rows_cap: int, finalize: bool = True):
+    """Dispatch + the zero state of the fused combine: (xp, y_acc [T,d] fp32, grid_sync [4] int32 | None)."""
     T, d = x.shape
-    k = row_of_assignment.shape[1]
     xp = _empty((rows_cap, d), torch.bfloat16, x.device)
     y_acc = _empty((T, d), torch.float32, x.device)
-    arrive = _empty((T, d // 32), torch.int32, x.device) if finalize else None
-    y = _empty((T, d), torch.bfloat16, x.device) if finalize else None
-    call("b200moe_permute_init", ptr(x), ptr(token_of_row), ptr(meta), rows_cap, d, ptr(xp), ptr(y_acc), ptr(arrive),
-         ptr(row_of_assignment), T, k, ptr(y), stream_ptr())
-    return xp, y_acc, arrive, y
+    sync = _empty((4,), torch.int32, x.device) if finalize else None
+    call("b200moe_permute_init", ptr(x), ptr(token_of_row), ptr(meta), rows_cap, d, ptr(xp), ptr(y_acc), ptr(sync), T,
+         stream_ptr())
+    return xp, y_acc, sync
 
 
-def ffn_down_combine(h, w2, b2, meta, tile_expert, token_of_row, gate_of_row, row_of_assignment, y_acc, arrive, y,
+def ffn_down_combine(h, w2, b2, meta, tile_expert, token_of_row, gate_of_row, T: int, k: int, y_acc, grid_sync,
                      row_pad: int = ROW_PAD, save_yo: bool = True):
-    """Down-projection with the combine fused into its epilogue (top_k <= 2).  Returns yo (or None)."""
+    """Down-projection with the combine fused into its epilogue (top_k <= 2).  Returns (yo | None, y | None)."""
     rows_cap, F = h.shape
     E, d, _ = w2.shape
-    T, k = row_of_assignment.shape
     yo = _empty((rows_cap, d), torch.bfloat16, h.device) if save_yo else None
+    y = _empty((T, d), torch.bfloat16, h.device) if grid_sync is not None else None
     call("b200moe_ffn_down_combine", ptr(h), ptr(w2), ptr(b2), ptr(meta), ptr(tile_expert), ptr(token_of_row),
-         ptr(gate_of_row), ptr(row_of_assignment), T, k, rows_cap, d, F, E, ptr(yo), ptr(y_acc), ptr(arrive), ptr(y),
-         row_pad, stream_ptr())
-    return yo
+         ptr(gate_of_row), T, k, rows_cap, d, F, E, ptr(yo), ptr(y_acc), ptr(grid_sync), ptr(y), None, row_pad,
+         stream_ptr())
+    return yo, y
 
 
 def ffn_down(h, w2, b2, meta, tile_expert, row_pad: int = ROW_PAD, out: Optional[torch.Tensor] = None):

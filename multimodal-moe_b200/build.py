@@ -25,10 +25,8 @@ FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std
 
 
 def _deps(src: str) -> list[str]:
-    deps = [os.path.join(CSRC, src), os.path.join(CSRC, "common.cuh"),
-            os.path.join(HERE, "..", "include", "b200moe.h")]
-    if src == "gemm.cu":
-        deps.append(os.path.join(CSRC, "gemm_host.inc"))
+    deps = [os.path.join(CSRC, src), os.path.join(HERE, "..", "include", "b200moe.h")]
+    deps += [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".inc"))]
     return deps
 
 

@@ -131,6 +131,37 @@ __device__ __forceinline__ uint4 pack8(const float (&v)[8]) {
   return r;
 }
 
+// Context path of A.2 as the kernels see it (device pointers by value): ctx_bias[b,e] = sum_i emb_b[i] * wc[e, i] with
+// emb_b the concatenation of the rows Embed_f[context[b,f]].  ctx_bias_dot is THE arithmetic of that dot product -- the
+// stand-alone kernel (layer.cu) and the router's in-kernel evaluation both call it, so they produce the same bits.
+struct CtxTables {
+  const float* table[B200MOE_MAX_CTX_FIELDS];
+  float* dtable[B200MOE_MAX_CTX_FIELDS];
+  int vocab[B200MOE_MAX_CTX_FIELDS];
+};
+struct CtxArgs {
+  const int64_t* context;   // [B,n] or null
+  CtxTables tb;
+  const float* wc;          // [E, n*cd]
+  int n, cd;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ float ctx_emb_value(const CtxArgs& c, int b, int i) {
+  const int f = i / c.cd, j = i - f * c.cd;
+  const long long id = c.context[static_cast<size_t>(b) * c.n + f];
+  return (id >= 0 && id < c.tb.vocab[f]) ? c.tb.table[f][static_cast<size_t>(id) * c.cd + j] : 0.f;
+}
+// one warp: lanes stride the n*cd products in order, then the xor-shuffle tree (fixed order: deterministic)
+template <typename EmbFn>
+__device__ __forceinline__ float ctx_bias_dot(EmbFn emb, const float* __restrict__ wc_row, int ncd, int lane) {
+  float s = 0.f;
+  for (int i = lane; i < ncd; i += 32) s = fmaf(emb(i), wc_row[i], s);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  return s;
+}
+#endif
+
 // The A.7 combine y[t] = sum_s g_s * yo_s, fp32, slot order: product and sum are rounded separately (no FMA contraction)
 // and flush subnormals, which is exactly what an fp32 reduction at L2 (red.global.add.f32) does with a pre-multiplied
 // term.  A sum of k <= 2 such terms does not depend on their order, so the down-projection's fused epilogue (terms

@@ -17,6 +17,7 @@
 //   MN-major tile [64 k-rows][64 bf16] per 64-wide chunk of M/N, chunks 8192 B apart (LBO), 8-k-row groups
 //            1024 B apart (SBO); one k-step (16 k-rows) = +2048 B
 #include "common.cuh"
+#include "postnorm.cuh"
 
 namespace b200moe {
 
@@ -52,11 +53,16 @@ struct GemmArgs {
   // EPI_DOWN_COMBINE
   const int32_t* token_of_row;       // [R], -1 = pad row
   const float* gate_of_row;          // [R]
-  const int32_t* row_of_assignment;  // [T,k]: how many contributions a token receives
-  int topk;
   float* yacc;                       // [T,N] fp32, zero before the launch
-  int32_t* arrive;                   // [T,N/32] zero before the launch, or null: the caller finishes y from yacc
-  __nv_bfloat16* yout;               // [T,N] bf16, written by the last contribution to a (token, 32-column chunk)
+  int32_t* grid_sync;                // one counter, zero before the launch, or null: the caller finishes y from yacc
+  void* yout;                        // [T,N]: written from yacc by the kernel's tail once every CTA has delivered --
+  int T;                             //        bf16 y, or with ln_gamma the fused post-norm LayerNorm(residual + y)
+  const void* ln_res;                // [T,N] residual (bf16 / fp32), with ln_gamma
+  const float* ln_gamma;             // [N] or null: plain conversion
+  const float* ln_beta;
+  float* ln_mean_rstd;               // [T,2]
+  float ln_eps;
+  int ln_res_f32, ln_out_f32;
 };
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
@@ -264,15 +270,22 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         mbar_arrive_expect_tx(&ld_bar[warp - 2], kStgBytes);
         tma_load_2d(stg, &tmC1, &ld_bar[warp - 2], n_tile * BN + cgroup * kChunksPerWarp * 32, row0);
       }
-      // fused combine: this thread's row belongs to token `tok` (-1: pad row) with gate `gate`; the token receives
-      // `need` contributions (its kept assignments) to every column
-      int tok = -1, need = 0;
+      // bias of this warp's chunks, one column per lane (a 128-byte line per chunk), requested before the wait for the
+      // accumulator and broadcast by shuffles below: the per-chunk broadcast loads (8 x LDG.128 behind the TMEM load)
+      // put an L2 round trip into every chunk's latency chain
+      float bias_lane[kChunksPerWarp];
+      if (EPI == EPI_UP || EPI == EPI_DOWN || kCombine) {
+#pragma unroll
+        for (int cc = 0; cc < kChunksPerWarp; ++cc)
+          bias_lane[cc] = __ldg(args.bias + static_cast<size_t>(e) * args.N + n_tile * BN +
+                                (cgroup * kChunksPerWarp + cc) * 32 + lane);
+      }
+      // fused combine: this thread's row belongs to token `tok` (-1: pad row) and carries the gate `gate`
+      int tok = -1;
       float gate = 0.f;
       if (kCombine) {
         tok = args.token_of_row[grow];
         gate = args.gate_of_row[grow];
-        if (tok >= 0 && args.arrive)
-          for (int s = 0; s < args.topk; ++s) need += args.row_of_assignment[static_cast<size_t>(tok) * args.topk + s] >= 0;
       }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
@@ -290,12 +303,6 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const uint32_t swz_l = (lane >> 1) & 3;
 #pragma unroll
           for (int j = 0; j < 4; ++j) pr[j] = *reinterpret_cast<const uint4*>(stg + lane * 64 + ((j ^ swz_l) << 4));
-        }
-        float4 bv[8];
-        if (EPI == EPI_UP || EPI == EPI_DOWN || kCombine) {
-          const float* bp = args.bias + static_cast<size_t>(e) * args.N + col0;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) bv[j] = __ldg(reinterpret_cast<const float4*>(bp) + j);
         }
         tmem_ld_wait();
         if (EPI == EPI_WGRAD) {
@@ -321,10 +328,11 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
           if (EPI == EPI_UP || EPI == EPI_DOWN || kCombine) {
+            float bl = bias_lane[0];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              f[4 * j] += bv[j].x; f[4 * j + 1] += bv[j].y; f[4 * j + 2] += bv[j].z; f[4 * j + 3] += bv[j].w;
-            }
+            for (int q = 1; q < kChunksPerWarp; ++q) bl = (cc == q) ? bias_lane[q] : bl;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] += __shfl_sync(0xffffffffu, bl, j);
           }
           // bf16 box [32 rows][32 cols] = 2 KB, 64-byte swizzle: 16-byte chunk j of row r sits at j ^ ((r >> 1) & 3)
           const uint32_t swz = (lane >> 1) & 3;
@@ -395,22 +403,6 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               red_add_v4(dst + 8 * j + 4, combine_term(gate, v8[4]), combine_term(gate, v8[5]), combine_term(gate, v8[6]),
                          combine_term(gate, v8[7]));
             }
-            if (args.arrive) {
-              // the last of the token's `need` contributions to this 32-column chunk rounds it to the output dtype
-              __threadfence();
-              const int old = atomicAdd(args.arrive + static_cast<size_t>(tok) * (args.N >> 5) + (col0 >> 5), 1);
-              if (old == need - 1) {
-                __threadfence();
-                __nv_bfloat16* yo_ = args.yout + static_cast<size_t>(tok) * args.N + col0;
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  const float4 a = __ldcg(reinterpret_cast<const float4*>(dst + 8 * j));
-                  const float4 b = __ldcg(reinterpret_cast<const float4*>(dst + 8 * j) + 1);
-                  const float o8[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-                  stg128(yo_ + 8 * j, pack8(o8));
-                }
-              }
-            }
           }
           if (!kCombine || args.out0 != nullptr) {
           if (lane == 0) tma_store_wait_read0();
@@ -441,6 +433,41 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   tc_fence_before();
   __syncthreads();
+  if (EPI == EPI_DOWN_COMBINE && args.grid_sync != nullptr) {
+    // Tail of the fused combine: once EVERY CTA of the grid has issued its reductions (one counter; the grid is never
+    // larger than what is resident at once, and dependents of a programmatic launch are scheduled only after all CTAs of
+    // this grid run), the accumulator is complete in L2 and the CTAs share its conversion to bf16.  No combine / convert
+    // launch follows, and tokens without a kept assignment come out as the zeros the accumulator started with.
+    if (threadIdx.x == 0) {
+      __threadfence();                                         // cumulative over the CTA's reductions (bar.sync above)
+      atomicAdd(args.grid_sync, 1);
+      int seen;
+      do {
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(args.grid_sync) : "memory");
+        if (seen < static_cast<int>(gridDim.x)) __nanosleep(100);
+      } while (seen < static_cast<int>(gridDim.x));
+      __threadfence();
+    }
+    __syncthreads();
+    if (args.ln_gamma != nullptr) {
+      // fused post-norm (hybrid_encoder.py:158-160): a warp per token, N <= 1024
+      const int nwarps = static_cast<int>(blockDim.x >> 5);
+      for (int t = blockIdx.x * nwarps + warp; t < args.T; t += gridDim.x * nwarps)
+        ln_forward_token<kLnMaxI>(nullptr, nullptr, nullptr, args.yacc, true, args.ln_res, args.ln_res_f32 != 0,
+                                  args.ln_gamma, args.ln_beta, args.ln_eps, t, 0, args.N, lane, args.yout,
+                                  args.ln_out_f32 != 0, args.ln_mean_rstd);
+    } else {
+      const size_t n8 = static_cast<size_t>(args.T) * args.N / 8;
+      const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+      __nv_bfloat16* yb = static_cast<__nv_bfloat16*>(args.yout);
+      for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += stride) {
+        const float4 a = __ldcg(reinterpret_cast<const float4*>(args.yacc) + 2 * i);
+        const float4 b = __ldcg(reinterpret_cast<const float4*>(args.yacc) + 2 * i + 1);
+        const float o8[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        stg128(yb + 8 * i, pack8(o8));
+      }
+    }
+  }
   if (CTA2) cluster_sync_all();                 // neither CTA leaves while the other may still touch its smem / TMEM
   if (warp == 1) {
     tc_fence_after();

@@ -64,8 +64,8 @@ struct PdlScope {
 // (plain event fork/join, so the pattern is captured into a CUDA graph as parallel branches).
 struct ForkState {
   bool ok = false;
-  cudaStream_t s1 = nullptr, s2 = nullptr;
-  cudaEvent_t ev[5] = {};
+  cudaStream_t s1 = nullptr, s2 = nullptr, s3 = nullptr;
+  cudaEvent_t ev[6] = {};
 };
 static ForkState g_fork[16];
 static int g_fork_mode = 1;   // 0 never, 1 always (measured faster at every size of the sweep: 3200 .. 65600 tokens)
@@ -76,6 +76,7 @@ static ForkState* fork_state() {
   if (!f.ok) {
     if (cudaStreamCreateWithFlags(&f.s1, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     if (cudaStreamCreateWithFlags(&f.s2, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaStreamCreateWithFlags(&f.s3, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     for (auto& e : f.ev)
       if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
     f.ok = true;
@@ -112,12 +113,6 @@ static int check_desc(const b200moe_layer_desc* q, const char* what) {
 }
 
 // ---- context bias ---------------------------------------------------------------------------------------------
-struct CtxTables {
-  const float* table[B200MOE_MAX_CTX_FIELDS];
-  float* dtable[B200MOE_MAX_CTX_FIELDS];
-  int vocab[B200MOE_MAX_CTX_FIELDS];
-};
-
 // one block per image, thread per expert-strided output; the n*cd-long embedding row sits in shared memory
 __global__ void __launch_bounds__(512)
 ctx_bias_fwd_kernel(const int64_t* __restrict__ context, const CtxTables tb, int n, int cd,
@@ -132,9 +127,7 @@ ctx_bias_fwd_kernel(const int64_t* __restrict__ context, const CtxTables tb, int
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int e = warp; e < E; e += (blockDim.x >> 5)) {
-    float s = 0.f;
-    for (int i = lane; i < n * cd; i += 32) s = fmaf(emb_s[i], wc[static_cast<size_t>(e) * n * cd + i], s);
-    s = warp_sum(s);
+    const float s = ctx_bias_dot([&](int i) { return emb_s[i]; }, wc + static_cast<size_t>(e) * n * cd, n * cd, lane);
     if (lane == 0) out[static_cast<size_t>(b) * E + e] = s;
   }
 }
@@ -274,7 +267,8 @@ extern "C" int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* q, int64_t*
   bytes[B200MOE_WS_H] = R * F * 2;
   bytes[B200MOE_WS_YO] = R * d * 2;
   bytes[B200MOE_WS_Y_ACC] = fused_combine(q) ? T * d * 4 : 0;
-  bytes[B200MOE_WS_ARRIVE] = fused_combine(q) ? T * (d / 32) * 4 : 0;
+  bytes[B200MOE_WS_GRID_SYNC] = fused_combine(q) ? 16 : 0;
+  bytes[B200MOE_WS_CTX_BIAS] = ((T + q->tokens_per_image - 1) / (q->tokens_per_image > 0 ? q->tokens_per_image : T)) * E * 4;
   int64_t at = 0;
   for (int i = 0; i < B200MOE_WS_COUNT; ++i) { off[i] = at; at += align256(bytes[i]); }
   return at;
@@ -290,6 +284,7 @@ extern "C" int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* q, int6
   bytes[B200MOE_BWS_DXP] = R * d * 2;
   bytes[B200MOE_BWS_DLOGITS] = T * E * 4;
   bytes[B200MOE_BWS_DWG_SCRATCH] = b200moe_dwg_scratch_floats(q->T, q->d, q->E) * 4;
+  bytes[B200MOE_BWS_DCTX] = ((T + q->tokens_per_image - 1) / (q->tokens_per_image > 0 ? q->tokens_per_image : T)) * E * 4;
   int64_t at = 0;
   for (int i = 0; i < B200MOE_BWS_COUNT; ++i) { off[i] = at; at += align256(bytes[i]); }
   return at;
@@ -298,7 +293,7 @@ extern "C" int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* q, int6
 #define WS(T_, i) reinterpret_cast<T_*>(base + off[i])
 
 extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, const float* ctx_bias,
-                                 const void* wg_split, const void* w1, const float* b1, const void* w2,
+                                 const b200moe_ctx_desc* cx, const void* wg_split, const void* w1, const float* b1, const void* w2,
                                  const float* b2, void* ws, void* y, int save_for_backward,
                                  const b200moe_postnorm* pn, void* weights_ready, void* stream) {
   if (int rc = check_desc(q, "layer_fwd")) return rc;
@@ -312,11 +307,28 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
   const int pad = b200moe_layer_row_pad(T, k, E, q->capacity, d, F);
   int rc;
   PdlScope pdl_;
-  STEP("router_fwd",
-       b200moe_router_fwd(x, ctx_bias, q->tokens_per_image, nullptr, const_cast<void*>(wg_split), T, d, E, k,
-                          q->normalize_topk, WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX),
-                          WS(float, B200MOE_WS_TOPK_GATE), WS(int32_t, B200MOE_WS_BLOCK_COUNTS),
-                          WS(float, B200MOE_WS_BLOCK_STATS), stream));
+  B200MOE_REQUIRE(!(ctx_bias && cx), B200MOE_EINVAL, "layer_fwd: pass ctx_bias or ctx, not both");
+  if (cx && (q->tokens_per_image < 64 || cx->n_fields * cx->context_dim > 256)) {
+    // few tokens per image (a 128-token tile would touch many images) or a wide context embedding: the stand-alone
+    // kernel fills the workspace slot
+    STEP("ctx_bias_fwd", b200moe_ctx_bias_fwd(cx->context, cx->tables, cx->vocab, cx->n_fields, cx->context_dim, cx->wc,
+                                              cx->B, E, WS(float, B200MOE_WS_CTX_BIAS), stream));
+    ctx_bias = WS(float, B200MOE_WS_CTX_BIAS);
+    cx = nullptr;
+  }
+  if (cx) {
+    STEP("router_fwd",
+         b200moe_router_fwd_ctx(x, cx, q->tokens_per_image, const_cast<void*>(wg_split), T, d, E, k, q->normalize_topk,
+                                WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX),
+                                WS(float, B200MOE_WS_TOPK_GATE), WS(int32_t, B200MOE_WS_BLOCK_COUNTS),
+                                WS(float, B200MOE_WS_BLOCK_STATS), stream));
+  } else {
+    STEP("router_fwd",
+         b200moe_router_fwd(x, ctx_bias, q->tokens_per_image, nullptr, const_cast<void*>(wg_split), T, d, E, k,
+                            q->normalize_topk, WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX),
+                            WS(float, B200MOE_WS_TOPK_GATE), WS(int32_t, B200MOE_WS_BLOCK_COUNTS),
+                            WS(float, B200MOE_WS_BLOCK_STATS), stream));
+  }
   STEP("plan",
        b200moe_plan(WS(int32_t, B200MOE_WS_TOPK_IDX), WS(float, B200MOE_WS_TOPK_GATE),
                     WS(int32_t, B200MOE_WS_BLOCK_COUNTS), WS(float, B200MOE_WS_BLOCK_STATS), T, k, E, q->capacity,
@@ -328,11 +340,9 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                     WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW), stream));
   const bool fused = fused_combine(q);
   if (fused) {
-    // the dispatch kernel also zeroes the fp32 accumulator / arrival counters of the fused combine (no memset launch);
-    // with the fused post-norm the LayerNorm kernel finishes from the accumulator, so no counters and no y rows
+    // the dispatch kernel also zeroes the fp32 accumulator / rendezvous counter of the fused combine (no memset launch)
     STEP("permute", b200moe_permute_init(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP),
-                                         WS(float, B200MOE_WS_Y_ACC), pn ? nullptr : WS(int32_t, B200MOE_WS_ARRIVE),
-                                         WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT), T, k, pn ? nullptr : y, stream));
+                                         WS(float, B200MOE_WS_Y_ACC), WS(int32_t, B200MOE_WS_GRID_SYNC), T, stream));
   } else {
     STEP("permute", b200moe_permute(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP), stream));
   }
@@ -347,25 +357,22 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                                   q->activation, pad, stream));
   }
   if (fused) {
-    // yo is stored only for the backward (dgate = <dy, yo>); y leaves the epilogue itself
+    // yo is stored only for the backward (dgate = <dy, yo>); y -- or, with the fused post-norm,
+    // LayerNorm(residual + y) -- leaves the kernel's own tail: the forward ends here
     STEP("ffn_down", b200moe_ffn_down_combine(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert,
                                               WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW),
-                                              WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT), T, k, R, d, F, E,
-                                              save_for_backward ? WS(void, B200MOE_WS_YO) : nullptr,
-                                              WS(float, B200MOE_WS_Y_ACC), pn ? nullptr : WS(int32_t, B200MOE_WS_ARRIVE),
-                                              pn ? nullptr : y, pad, stream));
-    if (pn) {
-      STEP("combine_ln", b200moe_combine_ln_fwd(nullptr, nullptr, nullptr, WS(float, B200MOE_WS_Y_ACC), pn->residual,
-                                                pn->gamma, pn->beta, pn->eps, T, k, d, y, pn->mean_rstd, stream));
-    }
+                                              T, k, R, d, F, E, save_for_backward ? WS(void, B200MOE_WS_YO) : nullptr,
+                                              WS(float, B200MOE_WS_Y_ACC), WS(int32_t, B200MOE_WS_GRID_SYNC), y, pn, pad,
+                                              stream));
     return B200MOE_OK;
   }
   STEP("ffn_down", b200moe_ffn_down(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert, R, d, F, E,
                                     WS(void, B200MOE_WS_YO), pad, stream));
   if (pn) {
     STEP("combine_ln", b200moe_combine_ln_fwd(WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
-                                              WS(float, B200MOE_WS_TOPK_GATE), nullptr, pn->residual, pn->gamma, pn->beta,
-                                              pn->eps, T, k, d, y, pn->mean_rstd, stream));
+                                              WS(float, B200MOE_WS_TOPK_GATE), nullptr, pn->residual, pn->residual_f32,
+                                              pn->gamma, pn->beta, pn->eps, T, k, d, y, pn->out_f32, pn->mean_rstd,
+                                              stream));
   } else {
     STEP("combine", b200moe_combine(WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
                                     WS(float, B200MOE_WS_TOPK_GATE), T, k, d, y, stream));
@@ -376,7 +383,8 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
 extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, const float* wg, const void* w1,
                                  const void* w2, const void* ws, void* bws, const void* dy, const float* d_aux,
                                  void* dx, float* dctx_bias, float* dwg, float* dw1, float* db1, float* dw2,
-                                 float* db2, int has_ctx_bias, const b200moe_postnorm_bwd* pn, void* stream) {
+                                 float* db2, int has_ctx_bias, const b200moe_ctx_desc* cx,
+                                 const b200moe_postnorm_bwd* pn, void* stream) {
   if (int rc = check_desc(q, "layer_bwd")) return rc;
   B200MOE_REQUIRE(x && wg && w1 && w2 && ws && bws && dy, B200MOE_EINVAL, "layer_bwd: NULL argument");
   int64_t off[B200MOE_WS_COUNT], boff[B200MOE_BWS_COUNT];
@@ -398,16 +406,22 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
   PdlScope pdl_;
   if (pn) {
     STEP("combine_ln_bwd",
-         b200moe_combine_ln_bwd(dy, WS(void, B200MOE_WS_YO), roa, WS(float, B200MOE_WS_TOPK_GATE),
+         b200moe_combine_ln_bwd(dy, pn->dout_f32, WS(void, B200MOE_WS_YO), roa, WS(float, B200MOE_WS_TOPK_GATE),
                                 fused_combine(q) ? WS(float, B200MOE_WS_Y_ACC) : nullptr, pn->residual,
-                                pn->gamma, pn->mean_rstd, T, k, d, pn->dv, pn->scratch, pn->dgamma, pn->dbeta, stream));
+                                pn->residual_f32, pn->gamma, pn->mean_rstd, T, k, d, pn->dv, pn->dres_f32, pn->scratch,
+                                pn->dgamma, pn->dbeta, stream));
     dy = pn->dv;
   }
   ForkState* fk = (!g_prof_on && g_fork_mode) ? fork_state() : nullptr;
   cudaStream_t main_s = static_cast<cudaStream_t>(stream);
-  void* s1 = fk ? static_cast<void*>(fk->s1) : stream;   // router gradients
-  void* s2 = fk ? static_cast<void*>(fk->s2) : stream;   // weight gradients, bias sums
+  void* s1 = fk ? static_cast<void*>(fk->s1) : stream;   // router gradients (+ context-path gradients)
+  void* s2 = fk ? static_cast<void*>(fk->s2) : stream;   // weight gradients
+  void* s3 = fk ? static_cast<void*>(fk->s3) : stream;   // bias column sums
   float* dctx = (dctx_bias && has_ctx_bias) ? dctx_bias : nullptr;
+  if (cx != nullptr) {                               // parameter gradients of the context path wanted: dctx is scratch
+    B200MOE_REQUIRE(cx->dwc != nullptr && cx->context != nullptr, B200MOE_EINVAL, "layer_bwd: bad context descriptor");
+    if (dctx == nullptr) dctx = BWS(float, B200MOE_BWS_DCTX);
+  }
   STEP("combine_bwd",
        b200moe_combine_bwd(dy, WS(void, B200MOE_WS_YO), WS(int32_t, B200MOE_WS_TOKEN_OF_ROW),
                            WS(float, B200MOE_WS_GATE_OF_ROW), meta, R, d, dyp, BWS(float, B200MOE_BWS_DGATE_ROW), stream));
@@ -432,17 +446,23 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
     STEP("router_bwd_params", b200moe_router_bwd_params(dlogits, x, T, d, E, q->tokens_per_image,
                                                         BWS(float, B200MOE_BWS_DWG_SCRATCH), dwg, dctx, s1));
   }
-  // bias column sums ride on the router stream (short: dlogits -> dWg / dctx) rather than behind the two weight-gradient
-  // GEMMs, which are the longest branch at small rows-per-expert (workload D: 0.66 ms against 0.65 ms for the dgrad chain)
-  if (fk && (db1 || db2)) cudaStreamWaitEvent(fk->s1, fk->ev[1], 0);
+  if (cx != nullptr) {
+    // d(ctx_embed), d(ctx_proj) from dctx, on the router branch (off the dx chain)
+    STEP("ctx_bias_bwd", b200moe_ctx_bias_bwd(cx->context, dctx, cx->tables, cx->vocab, cx->n_fields, cx->context_dim,
+                                              cx->wc, cx->B, E, cx->dtables, cx->dwc, s1));
+  }
+  // bias column sums on a branch of their own, as soon as dgrad_down has written dhpre: behind the router gradients
+  // (round 1) they were the tail of the whole pass at 3200 tokens (graph timeline: dx done at 96 us, colsum at 107 us),
+  // behind the two weight-gradient GEMMs they would be at large rows-per-expert
+  if (fk) cudaStreamWaitEvent(fk->s3, fk->ev[1], 0);      // unconditional: the join below needs s3 inside the capture
   {
     PdlOffIf np_(fk != nullptr);
     if (db2 && db1) {
-      STEP("colsum", b200moe_colsum(dyp, d, db2, dhpre, F, db1, offs, E, 0, s1));
+      STEP("colsum", b200moe_colsum(dyp, d, db2, dhpre, F, db1, offs, E, 0, s3));
     } else if (db2) {
-      STEP("colsum", b200moe_colsum(dyp, d, db2, nullptr, 0, nullptr, offs, E, 0, s1));
+      STEP("colsum", b200moe_colsum(dyp, d, db2, nullptr, 0, nullptr, offs, E, 0, s3));
     } else if (db1) {
-      STEP("colsum", b200moe_colsum(dhpre, F, db1, nullptr, 0, nullptr, offs, E, 0, s1));
+      STEP("colsum", b200moe_colsum(dhpre, F, db1, nullptr, 0, nullptr, offs, E, 0, s3));
     }
   }
   if (dw2) {
@@ -464,8 +484,10 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
   if (fk) {
     cudaEventRecord(fk->ev[3], fk->s1);
     cudaEventRecord(fk->ev[4], fk->s2);
+    cudaEventRecord(fk->ev[5], fk->s3);
     cudaStreamWaitEvent(main_s, fk->ev[3], 0);
     cudaStreamWaitEvent(main_s, fk->ev[4], 0);
+    cudaStreamWaitEvent(main_s, fk->ev[5], 0);
   }
   return B200MOE_OK;
 #undef BWS

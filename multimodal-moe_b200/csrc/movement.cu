@@ -4,6 +4,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "postnorm.cuh"
 
 namespace b200moe {
 
@@ -11,14 +12,11 @@ constexpr int kMoveWarps = 8;
 constexpr int kMoveThreads = kMoveWarps * 32;
 
 // What the dispatch kernel prepares for the down-projection's fused combine epilogue (gemm.cu, EPI_DOWN_COMBINE), so that
-// no memset launch sits on the critical path: the fp32 accumulator and the arrival counters start at zero, and the
-// output rows of tokens that lost every assignment to the capacity limit (nothing will ever finalise them) are zero.
+// no memset launch sits on the critical path: the fp32 accumulator and the grid rendezvous counter start at zero.
 struct CombineInit {
-  float* y_acc;                       // [T,d] fp32 or null
-  int32_t* arrive;                    // [T,d/32] or null
-  const int32_t* row_of_assignment;   // [T,k]
-  __nv_bfloat16* y;                   // [T,d] bf16 or null
-  int T, k;
+  float* y_acc;        // [T,d] fp32 or null
+  int32_t* grid_sync;  // 4 ints (16 bytes) or null
+  int T;
 };
 
 // xp[r] = x[token_of_row[r]] or 0
@@ -44,18 +42,7 @@ permute_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ 
     const size_t gid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     const size_t n_acc = static_cast<size_t>(ci.T) * d / 4;             // 16-byte pieces
     for (size_t i = gid; i < n_acc; i += stride) stg128(ci.y_acc + 4 * i, make_uint4(0, 0, 0, 0));
-    if (ci.arrive) {
-      const size_t n_arr = static_cast<size_t>(ci.T) * (d >> 5) / 4;    // d % 128 == 0: a whole number of pieces
-      for (size_t i = gid; i < n_arr; i += stride) stg128(ci.arrive + 4 * i, make_uint4(0, 0, 0, 0));
-    }
-    if (ci.y) {
-      for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < ci.T; t += gridDim.x * kMoveWarps) {
-        bool any = false;
-        for (int s = 0; s < ci.k; ++s) any = any || ci.row_of_assignment[static_cast<size_t>(t) * ci.k + s] >= 0;
-        if (!any)
-          for (int c = lane; c < nchunk; c += 32) stg128(ci.y + static_cast<size_t>(t) * d + c * 8, make_uint4(0, 0, 0, 0));
-      }
-    }
+    if (ci.grid_sync && gid == 0) stg128(ci.grid_sync, make_uint4(0, 0, 0, 0));
   }
 }
 
@@ -350,99 +337,18 @@ prepare_weights_kernel(const float* __restrict__ w1, __nv_bfloat16* __restrict__
 // One warp per token; a lane owns the 16-byte chunks lane, lane+32, ... of the row (d <= 1024: at most four), so the
 // gate-weighted sum, the residual add, both LayerNorm moments and the affine output never leave registers and the
 // token's [T,d] intermediate (y, y + residual) is never written.  mean / rstd are kept for the backward pass.
-constexpr int kLnMaxI = 4;
-template <int NI>
-__device__ __forceinline__ void ln_gather_sum(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ roa,
-                                              const float* __restrict__ gate, const float* __restrict__ y_acc,
-                                              const __nv_bfloat16* __restrict__ res,
-                                              int t, int k, int d, int lane, float (&v)[NI][8]) {
-  const int nchunk = d >> 3;
-#pragma unroll
-  for (int i = 0; i < NI; ++i)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
-  if (y_acc) {            // the combine already happened in the down-projection's epilogue (fp32, same arithmetic)
-#pragma unroll
-    for (int i = 0; i < NI; ++i) {
-      const int c = lane + 32 * i;
-      if (c < nchunk) {
-        const float4 a = __ldg(reinterpret_cast<const float4*>(y_acc + static_cast<size_t>(t) * d + c * 8));
-        const float4 b = __ldg(reinterpret_cast<const float4*>(y_acc + static_cast<size_t>(t) * d + c * 8) + 1);
-        v[i][0] = a.x; v[i][1] = a.y; v[i][2] = a.z; v[i][3] = a.w;
-        v[i][4] = b.x; v[i][5] = b.y; v[i][6] = b.z; v[i][7] = b.w;
-      }
-    }
-    k = 0;
-  }
-  for (int s = 0; s < k; ++s) {
-    const int r = roa[static_cast<size_t>(t) * k + s];
-    if (r < 0) continue;
-    const float g = gate[static_cast<size_t>(t) * k + s];
-#pragma unroll
-    for (int i = 0; i < NI; ++i) {
-      const int c = lane + 32 * i;
-      if (c < nchunk) {
-        float a[8];
-        unpack8(ldg128(yo + static_cast<size_t>(r) * d + c * 8), a);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[i][j] = combine_add(v[i][j], combine_term(g, a[j]));
-      }
-    }
-  }
-#pragma unroll
-  for (int i = 0; i < NI; ++i) {
-    const int c = lane + 32 * i;
-    if (c < nchunk) {
-      float a[8];
-      unpack8(ldg128(res + static_cast<size_t>(t) * d + c * 8), a);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) v[i][j] += a[j];
-    }
-  }
-}
-
 template <int NI>
 __global__ void __launch_bounds__(kMoveThreads)
 combine_ln_fwd_kernel(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ roa,
                       const float* __restrict__ gate, const float* __restrict__ y_acc,
-                      const __nv_bfloat16* __restrict__ res,
+                      const void* __restrict__ res, int res_f32,
                       const float* __restrict__ gamma, const float* __restrict__ beta, float eps, int T, int k, int d,
-                      __nv_bfloat16* __restrict__ out, float* __restrict__ mean_rstd) {
+                      void* __restrict__ out, int out_f32, float* __restrict__ mean_rstd) {
   pdl_sync();
-  const int lane = threadIdx.x & 31, nchunk = d >> 3;
-  const float invd = 1.0f / static_cast<float>(d);
-  for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps) {
-    float v[NI][8];
-    ln_gather_sum<NI>(yo, roa, gate, y_acc, res, t, k, d, lane, v);
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < NI; ++i)
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s += v[i][j];          // missing chunks are zero
-    const float mean = warp_sum(s) * invd;
-    float q = 0.f;
-#pragma unroll
-    for (int i = 0; i < NI; ++i)
-      if (lane + 32 * i < nchunk)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { const float c_ = v[i][j] - mean; q = fmaf(c_, c_, q); }
-    const float rstd = rsqrtf(warp_sum(q) * invd + eps);
-#pragma unroll
-    for (int i = 0; i < NI; ++i) {
-      const int c = lane + 32 * i;
-      if (c < nchunk) {
-        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c * 8)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c * 8) + 1);
-        const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c * 8)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c * 8) + 1);
-        const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-        const float bt[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-        float o[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = fmaf((v[i][j] - mean) * rstd, gm[j], bt[j]);
-        stg128(out + static_cast<size_t>(t) * d + c * 8, pack8(o));
-      }
-    }
-    if (lane == 0) { mean_rstd[2 * static_cast<size_t>(t)] = mean; mean_rstd[2 * static_cast<size_t>(t) + 1] = rstd; }
-  }
+  const int lane = threadIdx.x & 31;
+  for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps)
+    ln_forward_token<NI>(yo, roa, gate, y_acc, false, res, res_f32 != 0, gamma, beta, eps, t, k, d, lane, out,
+                         out_f32 != 0, mean_rstd);
 }
 
 // Backward: recomputes the pre-norm sum v and xhat from the same inputs, dv = rstd (dxhat - mean(dxhat) - xhat
@@ -451,12 +357,12 @@ combine_ln_fwd_kernel(const __nv_bfloat16* __restrict__ yo, const int32_t* __res
 // per block; a second launch sums the blocks in order (deterministic).
 template <int NI>
 __global__ void __launch_bounds__(kMoveThreads)
-combine_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ yo,
+combine_ln_bwd_kernel(const void* __restrict__ dout, int dout_f32, const __nv_bfloat16* __restrict__ yo,
                       const int32_t* __restrict__ roa, const float* __restrict__ gate,
                       const float* __restrict__ y_acc,
-                      const __nv_bfloat16* __restrict__ res, const float* __restrict__ gamma,
+                      const void* __restrict__ res, int res_f32, const float* __restrict__ gamma,
                       const float* __restrict__ mean_rstd, int T, int k, int d, __nv_bfloat16* __restrict__ dv,
-                      float* __restrict__ scratch) {
+                      float* __restrict__ dres_f32, float* __restrict__ scratch) {
   extern __shared__ __align__(16) float lnb_s[];       // [8 warps][2][d]
   pdl_sync();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nchunk = d >> 3;
@@ -468,7 +374,7 @@ combine_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat1
     for (int j = 0; j < 8; ++j) { dg[i][j] = 0.f; db[i][j] = 0.f; }
   for (int t = blockIdx.x * kMoveWarps + warp; t < T; t += gridDim.x * kMoveWarps) {
     float v[NI][8], dy[NI][8];
-    ln_gather_sum<NI>(yo, roa, gate, y_acc, res, t, k, d, lane, v);
+    ln_gather_sum<NI>(yo, roa, gate, y_acc, false, res, res_f32 != 0, t, k, d, lane, v);
     const float mean = mean_rstd[2 * static_cast<size_t>(t)], rstd = mean_rstd[2 * static_cast<size_t>(t) + 1];
     float m1 = 0.f, m2 = 0.f;
 #pragma unroll
@@ -476,7 +382,7 @@ combine_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat1
       const int c = lane + 32 * i;
       if (c < nchunk) {
         float a[8];
-        unpack8(ldg128(dout + static_cast<size_t>(t) * d + c * 8), a);
+        load8_any(dout, dout_f32 != 0, static_cast<size_t>(t) * d + c * 8, a);
         const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c * 8)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c * 8) + 1);
         const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
 #pragma unroll
@@ -504,6 +410,7 @@ combine_ln_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat1
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = rstd * (dy[i][j] - m1 - v[i][j] * m2);
         stg128(dv + static_cast<size_t>(t) * d + c * 8, pack8(o));
+        if (dres_f32) store8_any(dres_f32, true, static_cast<size_t>(t) * d + c * 8, o);
       }
     }
   }
@@ -562,18 +469,17 @@ using namespace b200moe;
 
 extern "C" int b200moe_permute(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
                                void* xp, void* stream) {
-  return b200moe_permute_init(x, token_of_row, meta, rows_cap, d, xp, nullptr, nullptr, nullptr, 0, 0, nullptr, stream);
+  return b200moe_permute_init(x, token_of_row, meta, rows_cap, d, xp, nullptr, nullptr, 0, stream);
 }
 
 extern "C" int b200moe_permute_init(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap,
-                                    int d, void* xp, float* y_acc, int32_t* arrive,
-                                    const int32_t* row_of_assignment, int T, int k, void* y, void* stream) {
+                                    int d, void* xp, float* y_acc, int32_t* grid_sync, int T, void* stream) {
   B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "permute: d=%d must be a multiple of 8", d);
-  B200MOE_REQUIRE(y_acc == nullptr || (T > 0 && d % 128 == 0), B200MOE_EINVAL, "permute_init: bad T=%d / d=%d", T, d);
-  B200MOE_REQUIRE(y == nullptr || (y_acc != nullptr && row_of_assignment != nullptr && k >= 1), B200MOE_EINVAL,
-                  "permute_init: y without y_acc / row_of_assignment");
+  B200MOE_REQUIRE(y_acc == nullptr || (T > 0 && d % 4 == 0), B200MOE_EINVAL, "permute_init: bad T=%d / d=%d", T, d);
+  B200MOE_REQUIRE(grid_sync == nullptr || (y_acc != nullptr && (reinterpret_cast<uintptr_t>(grid_sync) & 15) == 0),
+                  B200MOE_EINVAL, "permute_init: grid_sync needs y_acc and 16-byte alignment");
   if (int rc = b200moe_check_device()) return rc;
-  const CombineInit ci{y_acc, arrive, row_of_assignment, BFW(y), T, k};
+  const CombineInit ci{y_acc, grid_sync, T};
   launch_k(permute_kernel, move_grid(rows_cap), kMoveThreads, 0, ST(stream), BF(x), token_of_row, meta, d, BFW(xp), ci);
   return check_launch("permute");
 }
@@ -711,9 +617,9 @@ extern "C" int b200moe_prepare_weights(const float* w1, void* w1_bf16, int64_t n
 }
 
 extern "C" int b200moe_combine_ln_fwd(const void* yo, const int32_t* row_of_assignment, const float* topk_gate,
-                                      const float* y_acc, const void* residual, const float* gamma,
-                                      const float* beta, float eps, int T, int k, int d, void* out, float* mean_rstd,
-                                      void* stream) {
+                                      const float* y_acc, const void* residual, int residual_f32, const float* gamma,
+                                      const float* beta, float eps, int T, int k, int d, void* out, int out_f32,
+                                      float* mean_rstd, void* stream) {
   B200MOE_REQUIRE(d > 0 && d % 8 == 0 && d <= 1024, B200MOE_EINVAL, "combine_ln_fwd: d=%d must be a multiple of 8, <= 1024", d);
   B200MOE_REQUIRE((y_acc || (yo && row_of_assignment && topk_gate)) && residual && gamma && beta && out && mean_rstd,
                   B200MOE_EINVAL, "combine_ln_fwd: NULL argument");
@@ -722,7 +628,7 @@ extern "C" int b200moe_combine_ln_fwd(const void* yo, const int32_t* row_of_assi
   const int ni = (d / 8 + 31) / 32;
 #define LNF(NI)                                                                                                       \
   launch_k(combine_ln_fwd_kernel<NI>, move_grid(T), kMoveThreads, 0, ST(stream), BF(yo), row_of_assignment, topk_gate, \
-           y_acc, BF(residual), gamma, beta, eps, T, k, d, BFW(out), mean_rstd)
+           y_acc, residual, residual_f32, gamma, beta, eps, T, k, d, out, out_f32, mean_rstd)
   if (ni == 1) LNF(1);
   else if (ni == 2) LNF(2);
   else LNF(4);
@@ -732,10 +638,11 @@ extern "C" int b200moe_combine_ln_fwd(const void* yo, const int32_t* row_of_assi
 
 extern "C" int64_t b200moe_ln_scratch_floats(int T, int d) { return static_cast<int64_t>(ln_bwd_blocks(T)) * 2 * d; }
 
-extern "C" int b200moe_combine_ln_bwd(const void* dout, const void* yo, const int32_t* row_of_assignment,
-                                      const float* topk_gate, const float* y_acc, const void* residual, const float* gamma,
-                                      const float* mean_rstd, int T, int k, int d, void* dv, float* scratch,
-                                      float* dgamma, float* dbeta, void* stream) {
+extern "C" int b200moe_combine_ln_bwd(const void* dout, int dout_f32, const void* yo, const int32_t* row_of_assignment,
+                                      const float* topk_gate, const float* y_acc, const void* residual,
+                                      int residual_f32, const float* gamma, const float* mean_rstd, int T, int k, int d,
+                                      void* dv, float* dres_f32, float* scratch, float* dgamma, float* dbeta,
+                                      void* stream) {
   B200MOE_REQUIRE(d > 0 && d % 8 == 0 && d <= 1024, B200MOE_EINVAL, "combine_ln_bwd: d=%d must be a multiple of 8, <= 1024", d);
   B200MOE_REQUIRE(dout && (y_acc || (yo && row_of_assignment && topk_gate)) && residual && gamma && mean_rstd && dv &&
                       scratch && dgamma && dbeta, B200MOE_EINVAL, "combine_ln_bwd: NULL argument");
@@ -754,8 +661,8 @@ extern "C" int b200moe_combine_ln_bwd(const void* dout, const void* yo, const in
     lnb_once.set(dev);
   }
 #define LNB(NI)                                                                                                     \
-  launch_k(combine_ln_bwd_kernel<NI>, nblk, kMoveThreads, smem, ST(stream), BF(dout), BF(yo), row_of_assignment,      \
-           topk_gate, y_acc, BF(residual), gamma, mean_rstd, T, k, d, BFW(dv), scratch)
+  launch_k(combine_ln_bwd_kernel<NI>, nblk, kMoveThreads, smem, ST(stream), dout, dout_f32, BF(yo), row_of_assignment, \
+           topk_gate, y_acc, residual, residual_f32, gamma, mean_rstd, T, k, d, BFW(dv), dres_f32, scratch)
   if (ni == 1) LNB(1);
   else if (ni == 2) LNB(2);
   else LNB(4);

@@ -26,6 +26,9 @@ namespace b200moe {
 constexpr int kRtTile = kRouterTokPerBlock;  // 128 tokens = one MMA M tile = one router block of the plan
 constexpr int kRtXBytes = kRtTile * 64 * 2;  // one k-block of the token tile: [128][64] bf16, 128-byte swizzle
 constexpr int kRtSmemBudget = 224 * 1024;
+constexpr int kRtMaxImg = 3;                 // images a 128-token tile may touch when the router evaluates the context bias
+constexpr int kRtMinTokPerImg = 64;          //   itself: tokens_per_image >= 64 -> at most 3
+constexpr int kRtMaxNcd = 256;               //   and n_fields * context_dim <= 256 (embedding rows staged in shared memory)
 
 // G = column groups of the epilogue: a token's EP logits are split over G threads (EP / G columns each), so that the
 // epilogue -- the part that bounds this kernel -- runs on 4*G warps per CTA with 1/G of the straight-line code.
@@ -36,7 +39,8 @@ struct RouterCfg {
   static constexpr int kStageBytes = kRtXBytes + kWBytes;
   static constexpr int kMaxStages = 6;
   static constexpr int kCtasPerSm = (EP == 64) ? 1 : 2;
-  static constexpr int kFixedTail = 2 * 4 * (EP + 1) * 4 /*stat_s*/ + 2 * 8 * 64 * 4 /*cnt_s*/ + 256 /*barriers*/;
+  static constexpr int kFixedTail = 2 * 4 * (EP + 1) * 4 /*stat_s*/ + 2 * 8 * 64 * 4 /*cnt_s*/ + 256 /*barriers*/ +
+                                    kRtMaxImg * 64 * 4 /*cb_s*/ + kRtMaxImg * kRtMaxNcd * 4 /*emb_s*/;
   static constexpr uint32_t kTmemCols = 2 * EP < 32 ? 32 : 2 * EP;
   // exchange area between the column groups: per token and group the local max, local sum and k candidates (key, index)
   static int xch_bytes(int k) { return G * (2 + 2 * k) * kRtTile * 4; }
@@ -95,6 +99,7 @@ __device__ __forceinline__ int col_of_lane(int lane) {   // N = 16: lane bits 4.
 }
 
 struct RouterArgs {
+  CtxArgs ctx;                 // context != null: the bias is evaluated per tile inside the kernel (A.2)
   const float* ctx_bias;
   int tokens_per_image;
   int T, d, E, k, normalize;
@@ -127,6 +132,8 @@ router_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
   uint64_t* tfull_bar = empty_bar + Cfg::kMaxStages;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  float* cb_s = reinterpret_cast<float*>(tail + Cfg::kFixedTail - kRtMaxImg * (64 + kRtMaxNcd) * 4);   // [kRtMaxImg][64]
+  float* emb_s = cb_s + kRtMaxImg * 64;                                                                // [kRtMaxImg][ncd]
   float* xch = reinterpret_cast<float*>(tail + Cfg::kFixedTail);             // [G][2 + 2k][128]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -212,10 +219,36 @@ router_fwd_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
       const int t = tile * kRtTile + tok;
       const bool live = t < T;
-      const float* cb = (a.ctx_bias && live) ? a.ctx_bias + static_cast<size_t>(t / a.tokens_per_image) * E + c0 : nullptr;
       float cbv[CPT];                             // context bias fetched ahead of the accumulator wait
+      if (a.ctx.context != nullptr) {
+        // A.2 evaluated here: the (at most kRtMaxImg) images this tile touches x E experts, one warp per dot product,
+        // while the tile's tokens are still in flight; same arithmetic as the stand-alone kernel (ctx_bias_dot)
+        const int b0 = (tile * kRtTile) / a.tokens_per_image;
+        const int t_last = min(T, (tile + 1) * kRtTile) - 1;
+        const int nimg = t_last / a.tokens_per_image - b0 + 1;
+        const int ncd = a.ctx.n * a.ctx.cd;
+        // embedding rows of the tile's images first (id -> table value: two dependent loads, every thread in parallel;
+        // a dot product that walked them itself serialised five such chains: +6 us at 3200 tokens)
+        for (int q = et; q < nimg * ncd; q += kEpi) {
+          const int img = q / ncd;
+          emb_s[img * kRtMaxNcd + (q - img * ncd)] = ctx_emb_value(a.ctx, b0 + img, q - img * ncd);
+        }
+        epi_bar_sync<kEpi>();
+        for (int p = warp - 2; p < nimg * E; p += kEpi / 32) {
+          const int img = p / E, e = p - img * E;
+          const float* em = emb_s + img * kRtMaxNcd;
+          const float s = ctx_bias_dot([&](int i) { return em[i]; }, a.ctx.wc + static_cast<size_t>(e) * ncd, ncd, lane);
+          if (lane == 0) cb_s[img * 64 + e] = s;
+        }
+        epi_bar_sync<kEpi>();
+        const float* row = cb_s + (live ? t / a.tokens_per_image - b0 : 0) * 64 + c0;
 #pragma unroll
-      for (int c = 0; c < CPT; ++c) cbv[c] = (cb && c0 + c < E) ? __ldg(cb + c) : 0.f;
+        for (int c = 0; c < CPT; ++c) cbv[c] = (live && c0 + c < E) ? row[c] : 0.f;
+      } else {
+        const float* cb = (a.ctx_bias && live) ? a.ctx_bias + static_cast<size_t>(t / a.tokens_per_image) * E + c0 : nullptr;
+#pragma unroll
+        for (int c = 0; c < CPT; ++c) cbv[c] = (cb && c0 + c < E) ? __ldg(cb + c) : 0.f;
+      }
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * EP + c0;
@@ -430,16 +463,35 @@ extern "C" int64_t b200moe_router_scratch_bytes(int d, int E) {
   return static_cast<int64_t>(2) * b200moe::router_ep(E) * d * 2;
 }
 
-extern "C" int b200moe_router_fwd(const void* x, const float* ctx_bias, int tokens_per_image, const float* wg,
-                                  void* wg_split, int T, int d, int E, int k, int normalize_topk, float* logits,
-                                  int32_t* topk_idx, float* topk_gate, int32_t* block_counts, float* block_stats,
-                                  void* stream) {
+static int router_fwd_impl(const void* x, const float* ctx_bias, const b200moe_ctx_desc* ctx, int tokens_per_image,
+                           const float* wg, void* wg_split, int T, int d, int E, int k, int normalize_topk,
+                           float* logits, int32_t* topk_idx, float* topk_gate, int32_t* block_counts,
+                           float* block_stats, void* stream) {
   using namespace b200moe;
   B200MOE_REQUIRE(T >= 0 && d > 0 && d % 64 == 0, B200MOE_EINVAL, "router_fwd: d=%d must be a positive multiple of 64", d);
   B200MOE_REQUIRE(E >= 1 && E <= 64, B200MOE_EINVAL, "router_fwd: num_experts=%d outside [1,64]", E);
   B200MOE_REQUIRE(k >= 1 && k <= E && k <= 8, B200MOE_EINVAL, "router_fwd: top_k=%d must be in [1,min(E,8)]", k);
-  B200MOE_REQUIRE(ctx_bias == nullptr || tokens_per_image > 0, B200MOE_EINVAL, "router_fwd: tokens_per_image <= 0");
+  B200MOE_REQUIRE((ctx_bias == nullptr && ctx == nullptr) || tokens_per_image > 0, B200MOE_EINVAL,
+                  "router_fwd: tokens_per_image <= 0");
   B200MOE_REQUIRE(wg_split != nullptr, B200MOE_EINVAL, "router_fwd: wg_split scratch is NULL (b200moe_router_scratch_bytes)");
+  CtxArgs ca{};
+  if (ctx != nullptr) {
+    B200MOE_REQUIRE(ctx_bias == nullptr, B200MOE_EINVAL, "router_fwd: pass ctx_bias or ctx, not both");
+    B200MOE_REQUIRE(tokens_per_image >= kRtMinTokPerImg, B200MOE_EINVAL,
+                    "router_fwd: in-kernel context bias needs tokens_per_image >= %d (got %d): use b200moe_ctx_bias_fwd",
+                    kRtMinTokPerImg, tokens_per_image);
+    B200MOE_REQUIRE(ctx->context && ctx->wc && ctx->n_fields >= 1 && ctx->n_fields <= B200MOE_MAX_CTX_FIELDS &&
+                        ctx->context_dim > 0 && ctx->n_fields * ctx->context_dim <= kRtMaxNcd, B200MOE_EINVAL,
+                    "router_fwd: bad context descriptor (n_fields * context_dim must be <= %d for the in-kernel bias)", kRtMaxNcd);
+    ca.context = ctx->context; ca.wc = ctx->wc; ca.n = ctx->n_fields; ca.cd = ctx->context_dim;
+    for (int i = 0; i < B200MOE_MAX_CTX_FIELDS; ++i) {
+      ca.tb.table[i] = i < ctx->n_fields ? ctx->tables[i] : nullptr;
+      ca.tb.dtable[i] = nullptr;
+      ca.tb.vocab[i] = i < ctx->n_fields ? ctx->vocab[i] : 0;
+      B200MOE_REQUIRE(i >= ctx->n_fields || (ctx->tables[i] != nullptr && ctx->vocab[i] > 0), B200MOE_EINVAL,
+                      "router_fwd: bad context table %d", i);
+    }
+  }
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
@@ -452,9 +504,24 @@ extern "C" int b200moe_router_fwd(const void* x, const float* ctx_bias, int toke
     router_split_wg_kernel<<<blocks, 256, 0, st>>>(wg, static_cast<__nv_bfloat16*>(wg_split), E, EP, d);
     if (int rc = check_launch("router_split_wg")) return rc;
   }
-  RouterArgs a{ctx_bias, tokens_per_image, T, d, E, k, normalize_topk, logits, topk_idx, topk_gate, block_counts,
+  RouterArgs a{ca, ctx_bias, tokens_per_image, T, d, E, k, normalize_topk, logits, topk_idx, topk_gate, block_counts,
                block_stats, 0};
   if (EP == 16) return E <= 8 ? launch_router<16, 1>(x, wg_split, a, st) : launch_router<16, 2>(x, wg_split, a, st);
   if (EP == 32) return launch_router<32, 2>(x, wg_split, a, st);
   return launch_router<64, 4>(x, wg_split, a, st);
+}
+
+extern "C" int b200moe_router_fwd(const void* x, const float* ctx_bias, int tokens_per_image, const float* wg,
+                                  void* wg_split, int T, int d, int E, int k, int normalize_topk, float* logits,
+                                  int32_t* topk_idx, float* topk_gate, int32_t* block_counts, float* block_stats,
+                                  void* stream) {
+  return router_fwd_impl(x, ctx_bias, nullptr, tokens_per_image, wg, wg_split, T, d, E, k, normalize_topk, logits,
+                         topk_idx, topk_gate, block_counts, block_stats, stream);
+}
+
+extern "C" int b200moe_router_fwd_ctx(const void* x, const b200moe_ctx_desc* ctx, int tokens_per_image, void* wg_split,
+                                      int T, int d, int E, int k, int normalize_topk, float* logits, int32_t* topk_idx,
+                                      float* topk_gate, int32_t* block_counts, float* block_stats, void* stream) {
+  return router_fwd_impl(x, nullptr, ctx, tokens_per_image, nullptr, wg_split, T, d, E, k, normalize_topk, logits,
+                         topk_idx, topk_gate, block_counts, block_stats, stream);
 }

@@ -157,15 +157,22 @@ def _golden_layer(golden_dir, name):
     return g, dense
 
 
-def test_fused_post_norm_matches_vendored_golden(golden_dir):
+@pytest.mark.parametrize("fp32_stream", [False, True])
+def test_fused_post_norm_matches_vendored_golden(golden_dir, fp32_stream):
     """Reference-derived known answer for §8(f)2: `norm2(src + linear2(gelu(linear1(src))))` computed by the UNMODIFIED
     vendored layer (tests/golden/make_golden.py, hybrid_encoder.py:157-160) against ContextMoE.forward_post_norm with E
-    identical experts (renormalised gates, no drops), forward and backward."""
+    identical experts (renormalised gates, no drops), forward and backward.  fp32_stream: residual and output stay
+    fp32, as the encoder's residual stream is under the reference's autocast (LayerNorm outputs fp32)."""
     import b200moe
     g, dense = _golden_layer(golden_dir, "postnorm_ffn_d128_f256.npz")
     layer = b200moe.MoEEncoderLayer.from_dense(dense, num_experts=4, top_k=2, capacity_factor=None).cuda()
     src = g["src"].cuda().requires_grad_(True)
-    out = layer.moe.forward_post_norm(src.to(torch.bfloat16), src.to(torch.bfloat16), layer.norm2)
+    if fp32_stream:
+        out = layer.moe.forward_post_norm(src, src, layer.norm2)
+        assert out.dtype == torch.float32
+    else:
+        out = layer.moe.forward_post_norm(src.to(torch.bfloat16), src.to(torch.bfloat16), layer.norm2)
+        assert out.dtype == torch.bfloat16
     (out.float() * g["go"].cuda()).sum().backward()
 
     def rel(a, b):

@@ -315,3 +315,91 @@ def test_empty_batch_and_eval_mode():
     with torch.no_grad():
         y1, y2 = m(x), m(x)
     assert torch.equal(y1, y2) and y1.shape == x.shape and torch.isfinite(y1.float()).all()
+
+
+def test_training_step_contract_fp16_autocast_gradscaler_clip():
+    """the step exactly as the vendored engine runs it (src/solver/det_engine.py:44-59) --
+    `torch.autocast(device_type)` with the DEFAULT dtype (fp16 on CUDA), fp32 loss outside autocast, GradScaler,
+    unscale_, clip_grad_norm_(0.1), step, update, zero_grad -- over a multiscale sequence of token counts
+    (dataloader.yml:22: HW in 225 .. 625).  Every step: finite loss and gradients, the scaler never skips, and the
+    unscaled gradients match the fp32 oracle run on the same weights (rel-L2 <= 1e-2)."""
+    B, d, F, E, k = 4, 256, 1024, 8, 2
+    ref, m = _pair(d, F, E, k, 1.25, ctx=True, seed=17)
+    head = torch.nn.Linear(d, 4).cuda()
+    params = list(m.parameters()) + list(head.parameters())
+    opt = torch.optim.AdamW(params, lr=1e-4)
+    scaler = torch.amp.GradScaler("cuda")
+    g = torch.Generator().manual_seed(3)
+    report = []
+    for step, HW in enumerate((225, 400, 625, 400, 225)):
+        x = torch.randn(B, HW, d, generator=g)
+        c = torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1)
+        tgt = torch.randn(B, HW, 4, generator=g)
+        ref.load_state_dict(m.state_dict())                     # the oracle follows the optimizer's weights
+        ref.zero_grad(set_to_none=True)
+        xg = x.cuda().requires_grad_(True)
+        with torch.autocast(device_type="cuda", cache_enabled=True):       # default dtype: float16
+            y = m(xg, c.cuda())
+            out = head(y)
+            assert out.dtype == torch.float16
+        with torch.autocast(device_type="cuda", enabled=False):
+            loss = (out.float() - tgt.cuda()).pow(2).mean() + m.aux_loss
+        scaler.scale(loss).backward()
+        scaler.unscale_(opt)
+        assert torch.isfinite(loss) and all(torch.isfinite(p.grad).all() for p in params)
+        # the oracle on the same weights, the kernel's logits and the same upstream gradient
+        xr = x.clone().requires_grad_(True)
+        yr = ref(xr, c, logits_value=m.last_aux["logits"].cpu())
+        hw_, hb_ = head.weight.detach().cpu().float(), head.bias.detach().cpu().float()
+        outr = torch.nn.functional.linear(yr, hw_, hb_)
+        ((outr - tgt).pow(2).mean() + ref.aux_loss).backward()
+        rels = {"dx": _rel(xg.grad / scaler.get_scale(), xr.grad),          # unscale_ touches the parameters only
+                "dwg": _rel(m.gate.weight.grad, ref.gate.weight.grad)}
+        for name in ("w1", "w2", "b1", "b2"):
+            rels[name] = _rel(getattr(m, name).grad, getattr(ref, name).grad)
+        report.append((step, HW, {k_: round(v, 5) for k_, v in rels.items()}))
+        torch.nn.utils.clip_grad_norm_(params, 0.1)
+        scale_before = scaler.get_scale()
+        scaler.step(opt)
+        scaler.update()
+        opt.zero_grad()
+        assert scaler.get_scale() >= scale_before              # no inf / nan: the step was not skipped
+    # the fp16 head (autocast) sits between the loss and the layer: dy reaches the layer fp16-rounded and rank-4
+    worst = {k_: max(r[2][k_] for r in report) for k_ in report[0][2]}
+    print("a4 report:", report)
+    assert all(v <= 2e-2 for k_, v in worst.items() if k_ != "dwg") and worst["dwg"] <= 3e-2, report
+
+
+def test_graphed_step_matches_eager():
+    """GraphedStep (forward + the caller's loss + backward in ONE CUDA graph, host inputs copied straight into the captured
+    buffers) against the eager module: bit-exact loss, dx and parameter gradients over several steps with an optimizer
+    updating the weights in place and zero_grad(set_to_none=True) in between (det_engine.py:59)."""
+    import b200moe
+    B, HW, d, F, E, k = 4, 200, 256, 512, 8, 2
+    _, m = _pair(d, F, E, k, 1.25, ctx=True, seed=23)
+    ref = copy.deepcopy(m)
+    g = torch.Generator().manual_seed(6)
+    xs = [torch.randn(B, HW, d, generator=g).to(torch.bfloat16).pin_memory() for _ in range(3)]
+    cs = [torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1).pin_memory()
+          for _ in range(3)]
+    go = torch.randn(B, HW, d, generator=g).cuda()
+
+    def loss_fn(y, w):
+        return (y.float() * w).sum()
+
+    step = b200moe.GraphedStep(m, loss_fn, xs[0], cs[0], go)
+    opt_m, opt_r = torch.optim.SGD(m.parameters(), lr=1e-3), torch.optim.SGD(ref.parameters(), lr=1e-3)
+    for i in range(3):
+        loss = step(xs[i], cs[i], go)
+        xr = xs[i].cuda().requires_grad_(True)
+        lr_ = loss_fn(ref(xr, cs[i].cuda()), go) + ref.aux_loss
+        lr_.backward()
+        assert torch.equal(loss, lr_.detach()) and torch.equal(step.dx, xr.grad)
+        grads_m = {n: p.grad for n, p in m.named_parameters() if p.grad is not None}
+        grads_r = {n: p.grad for n, p in ref.named_parameters() if p.grad is not None}
+        assert grads_m.keys() == grads_r.keys() and len(grads_m) >= 7
+        for n in grads_r:
+            assert torch.equal(grads_m[n], grads_r[n]), n
+        assert torch.equal(m.last_aux["topk_idx"], ref.last_aux["topk_idx"])
+        opt_m.step(); opt_r.step()
+        opt_m.zero_grad(set_to_none=True); opt_r.zero_grad(set_to_none=True)

@@ -122,3 +122,73 @@ def test_ep_state_dict_round_trip_world2():
         p.join(120)
     assert all(p.exitcode == 0 for p in procs)
     assert out.get(timeout=5) == "ok"
+
+
+def _clip_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import b200moe
+        from b200moe import checkpoint as ck
+        torch.manual_seed(3)
+        moe = b200moe.ContextMoE(128, 128, 4, 2, ep_group=dist.group.WORLD)
+        model = nn.Sequential(nn.Linear(8, 8), moe)
+        assert moe.expert_grad_scale == 1.0
+        ck.ddp_ignore_experts(model)
+        assert moe.expert_grad_scale == 0.5                       # DDP's mean-over-ranks convention (2 ranks)
+        g = torch.Generator().manual_seed(11)                     # the same "global" gradient on both ranks ...
+        sharded_names = set(ck.expert_param_names(model))
+        rep = {n: torch.randn(p.shape, generator=g) for n, p in model.named_parameters() if n not in sharded_names}
+        full = {p: torch.randn((4,) + tuple(getattr(moe, p).shape[1:]), generator=g) for p in ck.EXPERT_PARAMS}
+        for n, p in model.named_parameters():
+            if n in sharded_names:
+                p.grad = full[n.split(".")[-1]][rank * 2:(rank + 1) * 2].clone()   # ... each rank holds its expert shard
+            else:
+                p.grad = rep[n].clone()
+        ref_sq = sum(float(v.pow(2).sum()) for v in rep.values()) + sum(float(v.pow(2).sum()) for v in full.values())
+        norm = ck.clip_grad_norm_(model, 0.1)
+        assert abs(float(norm) - ref_sq ** 0.5) < 1e-3 * ref_sq ** 0.5
+        coef = 0.1 / (ref_sq ** 0.5 + 1e-6)
+        assert torch.allclose(model[0].weight.grad, rep["0.weight"] * coef, rtol=1e-5, atol=1e-8)
+        assert torch.allclose(moe.w1.grad, full["w1"][rank * 2:(rank + 1) * 2] * coef, rtol=1e-5, atol=1e-8)
+        # replicated gradients stay bit-identical across the ranks after the clip
+        gathered = [torch.empty_like(moe.gate.weight.grad) for _ in range(world)]
+        dist.all_gather(gathered, moe.gate.weight.grad)
+        assert torch.equal(gathered[0], gathered[1])
+        # torch's own clip would have used a rank-local norm: different coefficients on the two ranks
+        local_sq = sum(float(p.grad.pow(2).sum()) for p in model.parameters())
+        both = [None, None]
+        dist.all_gather_object(both, local_sq)
+        assert abs(both[0] - both[1]) > 1e-12
+
+        # EPGradScaler: an overflow in ONE rank's shard is seen by every rank
+        opt = torch.optim.SGD(model.parameters(), lr=0.1)
+        scaler = ck.EPGradScaler(ep_group=dist.group.WORLD, device="cpu", init_scale=4.0)
+        before = model[0].weight.detach().clone()
+        for p in model.parameters():
+            p.grad = torch.ones_like(p)
+        scaler.scale(torch.zeros((), requires_grad=True))          # initialises the scale tensor lazily
+        if rank == 1:
+            moe.w2.grad[0, 0, 0] = float("inf")
+        scaler.unscale_(opt)
+        scaler.step(opt)
+        scaler.update()
+        assert torch.equal(model[0].weight.detach(), before)       # skipped on BOTH ranks
+        assert scaler.get_scale() == 2.0                           # and the scale backed off on both
+        if rank == 0:
+            out.put("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ep_clip_and_scaler_world2():
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_clip_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(180)
+    assert all(p.exitcode == 0 for p in procs)
+    assert out.get(timeout=5) == "ok"
