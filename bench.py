@@ -175,8 +175,8 @@ def hbm_kernels(w, T, kept, per_call_ms, peak_gbs):
     A = kept
     algo = {
         "router_fwd": T * d * 2 + T * E * 4 + T * k * 8,            # read x; write logits, top-k indices and gates
-        "permute": 4 * A * d + 4 * T * d,                           # gather read + write; zero the fp32 combine accumulator
-        "combine": 2 * A * d + 2 * T * d,                           # (separate-combine path) read kept rows, write y
+        "permute": 4 * A * d,                                       # gather read + write
+        "combine": 2 * A * d + 2 * T * d,                           # (separate kernels only; else inside ffn_down's tail)
         "combine_bwd": 6 * A * d,                                   # read dy (gathered) and yo, write dyp
         "unpermute_bwd": 2 * A * d + 2 * T * d,                     # read dxp, write dx
         "colsum": 2 * A * (d + F),                                  # read dyp and dhpre

@@ -122,7 +122,8 @@ int b200moe_plan(const int32_t* topk_idx, const float* topk_gate, int32_t* block
 int b200moe_permute(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
                     void* xp, void* stream);
 /* The same dispatch kernel, also preparing the fused combine of b200moe_ffn_down_combine (no memset launches on the
- * critical path): y_acc [T,d] fp32 := 0 and grid_sync (16 bytes, 16-byte aligned; may be NULL) := 0. */
+ * critical path): grid_sync (16 bytes, 16-byte aligned) := 0 and, for the reduction mode, y_acc [T,d] fp32 := 0
+ * (either may be NULL). */
 int b200moe_permute_init(const void* x, const int32_t* token_of_row, const int32_t* meta, int rows_cap, int d,
                          void* xp, float* y_acc, int32_t* grid_sync, int T, void* stream);
 
@@ -172,23 +173,25 @@ typedef struct b200moe_postnorm_bwd {
   int32_t dout_f32;         /* dtype of dy = d(out): 0 = bf16, 1 = fp32 */
   float* dres_f32;          /* [T,d] fp32 out or NULL: the same gradient unrounded, for an fp32 residual */
 } b200moe_postnorm_bwd;
-/* Down-projection with the gate-weighted combine of A.7 FUSED INTO ITS EPILOGUE (the `linear2` half of
- * hybrid_encoder.py:157 and the weighted sum over the selected experts in one kernel): for every live row r
- *   y_acc[token_of_row[r], :] += gate_of_row[r] * bf16(h[r] @ w2[e]^T + b2[e])          (fp32 reductions at L2)
- * straight from the accumulator registers.  top_k <= 2 only: two fp32 terms commute, so the result does not depend on
- * the order in which tiles finish and is bit-identical to b200moe_ffn_down + b200moe_combine.
- *   yo        : [R,d] bf16 expert outputs, stored as b200moe_ffn_down does, or NULL (inference: the backward is its
- *               only reader)
- *   y_acc     : [T,d] fp32, zero on entry (b200moe_permute_init)
- *   grid_sync : one int32 counter, zero on entry (b200moe_permute_init), with y [T,d] bf16; or both NULL.  With them the
- *               kernel ends with a grid-wide rendezvous (the grid is persistent: never more CTAs than are resident at
- *               once) after which its CTAs convert y_acc to y: no combine / convert launch follows, and tokens that
- *               kept no assignment come out as zeros.  Without them the caller finishes from y_acc
- *               (b200moe_combine_ln_fwd).
- *   postnorm  : NULL, or (with grid_sync, d <= 1024) the tail writes y = LayerNorm(residual + combine) instead --
- *               hybrid_encoder.py:157-160 in ONE kernel: down-projection, combine, residual add, norm2. */
+/* Down-projection and the gate-weighted combine of A.7 in ONE kernel (the `linear2` half of hybrid_encoder.py:157 and
+ * the weighted sum over the selected experts; with `postnorm` also :158-160).  Two modes:
+ *   gather mode (y_acc == NULL; any top_k): the epilogues store the expert outputs yo [R,d] as b200moe_ffn_down does;
+ *     the kernel ends with a grid-wide rendezvous (the grid is persistent: never more CTAs than are resident at once),
+ *     after which its CTAs compute y[t,:] = sum_s topk_gate[t,s] * yo[row_of_assignment[t,s],:] (slot order, fp32) from
+ *     the rows just written -- bit-identical to b200moe_ffn_down + b200moe_combine, no second launch.
+ *   reduction mode (y_acc != NULL; top_k <= 2): the combine happens IN THE EPILOGUE, straight from the accumulator
+ *     registers: y_acc[token_of_row[r], :] += gate_of_row[r] * bf16(h[r] @ w2[e]^T + b2[e]) as fp32 reductions at L2.
+ *     Two fp32 terms commute, so the result does not depend on the order in which tiles finish and is bit-identical to
+ *     the other paths.  yo may be NULL (inference: the backward is its only reader).  y_acc [T,d] fp32 must be zero
+ *     on entry (b200moe_permute_init).  With grid_sync + y the tail converts y_acc to y after the rendezvous; with
+ *     both NULL the caller finishes from y_acc (b200moe_combine_ln_fwd).  Measured (round 2): the 2 x A x d fp32
+ *     reductions cost more than the separate combine kernel from ~10^4 tokens on (L2 atomic throughput), so the
+ *     whole-layer call uses gather mode unless B200MOE_LAYER_COMBINE_REDUCE is set.
+ *   grid_sync : one int32 counter, zero on entry (b200moe_permute_init)
+ *   postnorm  : NULL, or (d <= 1024) the tail writes y = LayerNorm(residual + combine) instead of the combine. */
 int b200moe_ffn_down_combine(const void* h, const void* w2, const float* b2, const int32_t* meta,
                              const int32_t* tile_expert, const int32_t* token_of_row, const float* gate_of_row,
+                             const int32_t* row_of_assignment, const float* topk_gate,
                              int T, int k, int rows_cap, int d, int F, int E,
                              void* yo, float* y_acc, int32_t* grid_sync, void* y,
                              const b200moe_postnorm* postnorm, int row_pad, void* stream);
@@ -319,10 +322,11 @@ typedef struct b200moe_layer_desc {
   int32_t activation;         /* B200MOE_ACT_GELU | B200MOE_ACT_RELU */
   int32_t flags;              /* B200MOE_LAYER_* */
 } b200moe_layer_desc;
-/* flags: the fused combine (b200moe_ffn_down_combine) is the default for top_k <= 2; this bit selects the separate
- * b200moe_ffn_down + b200moe_combine kernels instead (the tested reference of the fused epilogue; top_k > 2 always
- * takes them). */
+/* flags: by default the down-projection kernel combines in its tail (b200moe_ffn_down_combine, gather mode).
+ *   B200MOE_LAYER_SEPARATE_COMBINE: the separate b200moe_ffn_down + b200moe_combine kernels (the tested reference);
+ *   B200MOE_LAYER_COMBINE_REDUCE  : the combine in the epilogue itself by fp32 reductions (top_k <= 2; gather mode else). */
 #define B200MOE_LAYER_SEPARATE_COMBINE 1
+#define B200MOE_LAYER_COMBINE_REDUCE 2
 
 enum {
   B200MOE_WS_LOGITS = 0, B200MOE_WS_TOPK_IDX, B200MOE_WS_TOPK_GATE, B200MOE_WS_BLOCK_COUNTS, B200MOE_WS_BLOCK_STATS,

@@ -34,7 +34,7 @@ SIGNATURES = {
     "b200moe_combine_bwd": [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P],
     "b200moe_ffn_up": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _I, _P],
     "b200moe_ffn_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
-    "b200moe_ffn_down_combine": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _I, _P],
+    "b200moe_ffn_down_combine": [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P, _P, _P, _I, _P],
     "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _I, _P],
     "b200moe_ffn_dgrad_up": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
     "b200moe_ffn_wgrad": [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
@@ -110,6 +110,8 @@ class LayerDesc(C.Structure):
 ACT_GELU, ACT_RELU = 0, 1                 # B200MOE_ACT_*
 ACTIVATIONS = {"gelu": ACT_GELU, "relu": ACT_RELU}
 LAYER_SEPARATE_COMBINE = 1                # B200MOE_LAYER_SEPARATE_COMBINE
+LAYER_COMBINE_REDUCE = 2                  # B200MOE_LAYER_COMBINE_REDUCE
+COMBINE_FLAGS = {"tail": 0, "epilogue": LAYER_COMBINE_REDUCE, "separate": LAYER_SEPARATE_COMBINE}
 
 
 WS_NAMES = ("logits", "topk_idx", "topk_gate", "block_counts", "block_stats", "expert_offsets", "meta", "tile_expert",

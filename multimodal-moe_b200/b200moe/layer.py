@@ -49,10 +49,11 @@ class _LayerPlan:
         rows_cap = lib.b200moe_layer_rows_cap(T, k, E, cap, d, F)
         if rows_cap <= 0:
             raise RuntimeError(f"b200moe: bad layer shape T={T} k={k} E={E}")
-        self.fused = bool(mod.fused_combine) and k <= 2
+        self.fused = mod.combine != "separate"
+        self.reduce = mod.combine == "epilogue" and k <= 2
         self.desc = _lib.LayerDesc(T, d, F, E, k, tpi, cap, rows_cap, int(mod.normalize_topk),
                                    mod.aux_loss_weight, mod.z_loss_weight, _lib.ACTIVATIONS[mod.activation],
-                                   0 if mod.fused_combine else _lib.LAYER_SEPARATE_COMBINE)
+                                   _lib.COMBINE_FLAGS[mod.combine])
         self.desc_ptr = C.addressof(self.desc)
         off = (C.c_int64 * len(_lib.WS_NAMES))()
         self.ws_bytes = lib.b200moe_layer_ws_layout(self.desc_ptr, C.addressof(off))
@@ -68,7 +69,7 @@ class _LayerPlan:
                       "tile_expert": (R // 128,), "tokens_per_expert": (E,), "kept_per_expert": (E,), "losses": (3,),
                       "slot_limit": (2 * k * E,), "row_of_assignment": (T, k), "token_of_row": (R,),
                       "gate_of_row": (R,), "xp": (R, d), "pre": (R, F), "h": (R, F), "yo": (R, d),
-                      "y_acc": (T, d) if self.fused else (0, d), "grid_sync": (4,) if self.fused else (0,),
+                      "y_acc": (T, d) if self.reduce else (0, d), "grid_sync": (4,) if self.fused else (0,),
                       "ctx_bias": ((T + tpi - 1) // tpi, E)}
         self.capacity, self.rows_cap = cap, rows_cap
 
@@ -290,9 +291,11 @@ class ContextMoE(nn.Module):
         self.context_vocab_sizes = tuple(context_vocab_sizes)
         self.context_dim = context_dim
         self.activation = activation
-        # combine fused into the down-projection's epilogue (top_k <= 2); False selects the separate down + combine
-        # kernels, the tested reference of the fused epilogue
-        self.fused_combine = True
+        # where the A.7 combine runs: "tail" (default) inside the down-projection kernel, after a grid-wide rendezvous,
+        # from the expert outputs it just stored; "epilogue": in the down-projection's epilogue itself by fp32 reductions
+        # (top_k <= 2; measured slower from ~10^4 tokens on: L2 atomic throughput); "separate": down + combine kernels,
+        # the tested reference of both
+        self.combine = "tail"
         self.ep_group = ep_group
         self.ep_p2p = ep_p2p          # None: peer-memory dispatch when available; False: NCCL all-to-all; True: required
         self.ep_max_tokens = ep_max_tokens   # tokens per rank the peer-memory arena is sized for (None: the first batch)
@@ -381,7 +384,7 @@ class ContextMoE(nn.Module):
         # everything the descriptor is built from: a later change of capacity_factor, the loss weights, ... must not
         # be served a stale plan
         key = (T, tpi, self.capacity_factor, self.normalize_topk, self.aux_loss_weight, self.z_loss_weight,
-               self.activation, self.fused_combine)
+               self.activation, self.combine)
         pl = self._plans.get(key)
         if pl is None:
             if len(self._plans) > 64:       # multiscale training varies T per step (dataloader.yml:22)

@@ -149,27 +149,30 @@ def ffn_up(xp, w1, b1, meta, tile_expert, save_pre: bool = True, row_pad: int = 
     return pre, h
 
 
-def permute_init(x: torch.Tensor, token_of_row: torch.Tensor, meta: torch.Tensor, rows_cap: int, finalize: bool = True):
-    """Dispatch + the zero state of the fused combine: (xp, y_acc [T,d] fp32, grid_sync [4] int32 | None)."""
+def permute_init(x: torch.Tensor, token_of_row: torch.Tensor, meta: torch.Tensor, rows_cap: int, finalize: bool = True,
+                 reduce: bool = True):
+    """Dispatch + the zero state of the fused combine: (xp, y_acc [T,d] fp32 | None, grid_sync [4] int32 | None)."""
     T, d = x.shape
     xp = _empty((rows_cap, d), torch.bfloat16, x.device)
-    y_acc = _empty((T, d), torch.float32, x.device)
+    y_acc = _empty((T, d), torch.float32, x.device) if reduce else None
     sync = _empty((4,), torch.int32, x.device) if finalize else None
     call("b200moe_permute_init", ptr(x), ptr(token_of_row), ptr(meta), rows_cap, d, ptr(xp), ptr(y_acc), ptr(sync), T,
          stream_ptr())
     return xp, y_acc, sync
 
 
-def ffn_down_combine(h, w2, b2, meta, tile_expert, token_of_row, gate_of_row, T: int, k: int, y_acc, grid_sync,
-                     row_pad: int = ROW_PAD, save_yo: bool = True):
-    """Down-projection with the combine fused into its epilogue (top_k <= 2).  Returns (yo | None, y | None)."""
+def ffn_down_combine(h, w2, b2, meta, tile_expert, token_of_row, gate_of_row, row_of_assignment, topk_gate,
+                     y_acc, grid_sync, row_pad: int = ROW_PAD, save_yo: bool = True):
+    """Down-projection + combine in one kernel.  y_acc None: gather mode (the tail combines from yo); else reduction mode
+    (top_k <= 2, the epilogue adds into y_acc).  Returns (yo | None, y | None)."""
     rows_cap, F = h.shape
     E, d, _ = w2.shape
-    yo = _empty((rows_cap, d), torch.bfloat16, h.device) if save_yo else None
+    T, k = row_of_assignment.shape
+    yo = _empty((rows_cap, d), torch.bfloat16, h.device) if (save_yo or y_acc is None) else None
     y = _empty((T, d), torch.bfloat16, h.device) if grid_sync is not None else None
     call("b200moe_ffn_down_combine", ptr(h), ptr(w2), ptr(b2), ptr(meta), ptr(tile_expert), ptr(token_of_row),
-         ptr(gate_of_row), T, k, rows_cap, d, F, E, ptr(yo), ptr(y_acc), ptr(grid_sync), ptr(y), None, row_pad,
-         stream_ptr())
+         ptr(gate_of_row), ptr(row_of_assignment), ptr(topk_gate), T, k, rows_cap, d, F, E, ptr(yo), ptr(y_acc),
+         ptr(grid_sync), ptr(y), None, row_pad, stream_ptr())
     return yo, y
 
 

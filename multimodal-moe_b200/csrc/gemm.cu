@@ -34,6 +34,10 @@ constexpr int BK = 64;
 // copy: 8 warps with 4 KB boxes.
 __host__ __device__ constexpr int epi_warps(int epi) { return epi == 4 /*EPI_WGRAD*/ ? 8 : 16; }
 __host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
+// (Tried in round 2 and dropped: a two-stage, 8-epilogue-warp configuration with TWO CTAs per SM for the latency-bound
+// problem sizes.  At 3200 tokens every GEMM got slower -- up 11.9 -> 14.4 us, dgrad_down 12.1 -> 18.4 us: two k-blocks in
+// flight do not cover the TMA latency -- and the co-residency of independent branches did not make up for it: 104 -> 107
+// us per step, gpurun_out timelines of round 2.)
 
 struct GemmArgs {
   const int32_t* meta;            // row mode: meta[1] = number of 128-row tiles in use
@@ -53,7 +57,10 @@ struct GemmArgs {
   // EPI_DOWN_COMBINE
   const int32_t* token_of_row;       // [R], -1 = pad row
   const float* gate_of_row;          // [R]
-  float* yacc;                       // [T,N] fp32, zero before the launch
+  float* yacc;                       // [T,N] fp32, zero before the launch (reduction mode), or null (gather mode)
+  const int32_t* row_of_assignment;  // [T,k]  gather mode: the tail combines from the stored yo rows
+  const float* topk_gate;            // [T,k]
+  int topk;
   int32_t* grid_sync;                // one counter, zero before the launch, or null: the caller finishes y from yacc
   void* yout;                        // [T,N]: written from yacc by the kernel's tail once every CTA has delivered --
   int T;                             //        bf16 y, or with ln_gamma the fused post-norm LayerNorm(residual + y)
@@ -97,7 +104,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int kTileM = CTA2 ? 2 * BM : BM;                               // rows of one scheduled tile
   constexpr int kEpiWarps = epi_warps(EPI);
   constexpr int kEpiThreads = kEpiWarps * 32;
-  constexpr int kStgBytes = Cfg::kOutBytes / kEpiWarps;                    // 4 KB (wgrad) or 2 KB
+  constexpr int kStgBytes = Cfg::kOutBytes / kEpiWarps;                    // staging per warp: 4 KB, or 2 KB with 16 warps
+  constexpr int kBoxBytes = kWgrad ? 4096 : 2048;                          // one [32 x 32] box: fp32 or bf16
   constexpr uint32_t kTmemCols = 2 * BN;  // 256 or 512: power of two
   constexpr uint32_t kIdesc = make_idesc_bf16(kTileM, BN, A_MN, B_MN);
 
@@ -267,7 +275,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // requested before the wait for the accumulator.
       if (EPI == EPI_DGRAD_DOWN && lane == 0) {
         tma_store_wait_read0();
-        mbar_arrive_expect_tx(&ld_bar[warp - 2], kStgBytes);
+        mbar_arrive_expect_tx(&ld_bar[warp - 2], kBoxBytes);
         tma_load_2d(stg, &tmC1, &ld_bar[warp - 2], n_tile * BN + cgroup * kChunksPerWarp * 32, row0);
       }
       // bias of this warp's chunks, one column per lane (a 128-byte line per chunk), requested before the wait for the
@@ -283,7 +291,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // fused combine: this thread's row belongs to token `tok` (-1: pad row) and carries the gate `gate`
       int tok = -1;
       float gate = 0.f;
-      if (kCombine) {
+      if (kCombine && args.yacc != nullptr) {
         tok = args.token_of_row[grow];
         gate = args.gate_of_row[grow];
       }
@@ -389,7 +397,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             pk[j].x = float2_to_bf16x2(f[8 * j], f[8 * j + 1]); pk[j].y = float2_to_bf16x2(f[8 * j + 2], f[8 * j + 3]);
             pk[j].z = float2_to_bf16x2(f[8 * j + 4], f[8 * j + 5]); pk[j].w = float2_to_bf16x2(f[8 * j + 6], f[8 * j + 7]);
           }
-          if (kCombine && tok >= 0) {
+          if (kCombine && tok >= 0 && args.yacc != nullptr) {
             // y[tok, col0 .. col0+31] += gate * yo[row]: the term is formed from the bf16-rounded expert output (the value
             // the separate combine kernel would read back), added with fp32 reductions at L2.  Two terms commute, so
             // for top_k <= 2 the result does not depend on which tile arrives first.
@@ -417,7 +425,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             tma_store_commit();
             if (EPI == EPI_DGRAD_DOWN && cc + 1 < kChunksPerWarp) {   // next pre-activation box, once the store has read this one
               tma_store_wait_read0();
-              mbar_arrive_expect_tx(&ld_bar[warp - 2], kStgBytes);
+              mbar_arrive_expect_tx(&ld_bar[warp - 2], kBoxBytes);
               tma_load_2d(stg, &tmC1, &ld_bar[warp - 2], col0 + 32, row0);
             }
           }
@@ -433,11 +441,18 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   tc_fence_before();
   __syncthreads();
+  if (CTA2) cluster_sync_all();                 // neither CTA leaves while the other may still touch its smem / TMEM
+  if (warp == 1) {                              // TMEM goes back before the rendezvous below: a CTA of this grid that is
+    tc_fence_after();                           // still waiting for columns must never wait for CTAs that wait for it
+    if (CTA2) tmem_dealloc2<kTmemCols>(tmem_base);
+    else tmem_dealloc<kTmemCols>(tmem_base);
+  }
   if (EPI == EPI_DOWN_COMBINE && args.grid_sync != nullptr) {
-    // Tail of the fused combine: once EVERY CTA of the grid has issued its reductions (one counter; the grid is never
-    // larger than what is resident at once, and dependents of a programmatic launch are scheduled only after all CTAs of
-    // this grid run), the accumulator is complete in L2 and the CTAs share its conversion to bf16.  No combine / convert
-    // launch follows, and tokens without a kept assignment come out as the zeros the accumulator started with.
+    // Tail of the fused combine: once EVERY CTA of the grid has delivered its rows (one counter; the grid is never larger
+    // than what is resident at once, and dependents of a programmatic launch are scheduled only after all CTAs of this
+    // grid run), the CTAs share the combine itself -- gather mode: y[t] = sum_s gate * yo[row] from the rows just stored
+    // (any top_k, slot order); reduction mode: the fp32 accumulator the epilogues added to is complete in L2 and is
+    // converted.  No combine launch follows; tokens without a kept assignment come out as zeros either way.
     if (threadIdx.x == 0) {
       __threadfence();                                         // cumulative over the CTA's reductions (bar.sync above)
       atomicAdd(args.grid_sync, 1);
@@ -449,13 +464,18 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       __threadfence();
     }
     __syncthreads();
+    const int nwarps = static_cast<int>(blockDim.x >> 5);
+    const __nv_bfloat16* yo_rows = args.yacc ? nullptr : args.out0;       // gather mode: the rows every CTA just stored
     if (args.ln_gamma != nullptr) {
       // fused post-norm (hybrid_encoder.py:158-160): a warp per token, N <= 1024
-      const int nwarps = static_cast<int>(blockDim.x >> 5);
       for (int t = blockIdx.x * nwarps + warp; t < args.T; t += gridDim.x * nwarps)
-        ln_forward_token<kLnMaxI>(nullptr, nullptr, nullptr, args.yacc, true, args.ln_res, args.ln_res_f32 != 0,
-                                  args.ln_gamma, args.ln_beta, args.ln_eps, t, 0, args.N, lane, args.yout,
-                                  args.ln_out_f32 != 0, args.ln_mean_rstd);
+        ln_forward_token<kLnMaxI>(yo_rows, args.row_of_assignment, args.topk_gate, args.yacc, true, args.ln_res,
+                                  args.ln_res_f32 != 0, args.ln_gamma, args.ln_beta, args.ln_eps, t, args.topk, args.N,
+                                  lane, args.yout, args.ln_out_f32 != 0, args.ln_mean_rstd);
+    } else if (args.yacc == nullptr) {
+      for (int t = blockIdx.x * nwarps + warp; t < args.T; t += gridDim.x * nwarps)
+        combine_token(yo_rows, args.row_of_assignment, args.topk_gate, true, t, args.topk, args.N, lane,
+                      static_cast<__nv_bfloat16*>(args.yout));
     } else {
       const size_t n8 = static_cast<size_t>(args.T) * args.N / 8;
       const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
@@ -467,12 +487,6 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         stg128(yb + 8 * i, pack8(o8));
       }
     }
-  }
-  if (CTA2) cluster_sync_all();                 // neither CTA leaves while the other may still touch its smem / TMEM
-  if (warp == 1) {
-    tc_fence_after();
-    if (CTA2) tmem_dealloc2<kTmemCols>(tmem_base);
-    else tmem_dealloc<kTmemCols>(tmem_base);
   }
 }
 

@@ -90,9 +90,11 @@ struct PdlOffIf {
   ~PdlOffIf() { g_pdl = prev; }
 };
 
-// combine fused into the down-projection's epilogue: order-free fp32 accumulation is exact for at most two terms
-static inline bool fused_combine(const b200moe_layer_desc* q) {
-  return q->k <= 2 && !(q->flags & B200MOE_LAYER_SEPARATE_COMBINE);
+// combine inside the down-projection kernel (its tail, or -- reduction mode -- its epilogue: order-free fp32 accumulation
+// is exact for at most two terms)
+static inline bool fused_combine(const b200moe_layer_desc* q) { return !(q->flags & B200MOE_LAYER_SEPARATE_COMBINE); }
+static inline bool reduce_combine(const b200moe_layer_desc* q) {
+  return fused_combine(q) && (q->flags & B200MOE_LAYER_COMBINE_REDUCE) && q->k <= 2;
 }
 
 static int check_desc(const b200moe_layer_desc* q, const char* what) {
@@ -105,7 +107,8 @@ static int check_desc(const b200moe_layer_desc* q, const char* what) {
   B200MOE_REQUIRE(q->capacity >= 0, B200MOE_EINVAL, "%s: negative capacity", what);
   B200MOE_REQUIRE(q->activation == B200MOE_ACT_GELU || q->activation == B200MOE_ACT_RELU, B200MOE_EINVAL,
                   "%s: activation=%d must be B200MOE_ACT_GELU or B200MOE_ACT_RELU", what, q->activation);
-  B200MOE_REQUIRE((q->flags & ~B200MOE_LAYER_SEPARATE_COMBINE) == 0, B200MOE_EINVAL, "%s: unknown flags 0x%x", what, q->flags);
+  B200MOE_REQUIRE((q->flags & ~(B200MOE_LAYER_SEPARATE_COMBINE | B200MOE_LAYER_COMBINE_REDUCE)) == 0, B200MOE_EINVAL,
+                  "%s: unknown flags 0x%x", what, q->flags);
   B200MOE_REQUIRE(q->rows_cap > 0 && q->rows_cap % kRowPad == 0 &&
                       q->rows_cap >= b200moe_layer_rows_cap(q->T, q->k, q->E, q->capacity, q->d, q->F),
                   B200MOE_EINVAL, "%s: rows_cap=%d is below b200moe_layer_rows_cap(T,k,E,capacity,d,F)", what, q->rows_cap);
@@ -266,7 +269,7 @@ extern "C" int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* q, int64_t*
   bytes[B200MOE_WS_PRE] = R * F * 2;
   bytes[B200MOE_WS_H] = R * F * 2;
   bytes[B200MOE_WS_YO] = R * d * 2;
-  bytes[B200MOE_WS_Y_ACC] = fused_combine(q) ? T * d * 4 : 0;
+  bytes[B200MOE_WS_Y_ACC] = reduce_combine(q) ? T * d * 4 : 0;
   bytes[B200MOE_WS_GRID_SYNC] = fused_combine(q) ? 16 : 0;
   bytes[B200MOE_WS_CTX_BIAS] = ((T + q->tokens_per_image - 1) / (q->tokens_per_image > 0 ? q->tokens_per_image : T)) * E * 4;
   int64_t at = 0;
@@ -340,9 +343,11 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                     WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW), stream));
   const bool fused = fused_combine(q);
   if (fused) {
-    // the dispatch kernel also zeroes the fp32 accumulator / rendezvous counter of the fused combine (no memset launch)
+    // the dispatch kernel also zeroes the rendezvous counter (and the fp32 accumulator of the reduction mode) of the
+    // fused combine: no memset launch
     STEP("permute", b200moe_permute_init(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP),
-                                         WS(float, B200MOE_WS_Y_ACC), WS(int32_t, B200MOE_WS_GRID_SYNC), T, stream));
+                                         reduce_combine(q) ? WS(float, B200MOE_WS_Y_ACC) : nullptr,
+                                         WS(int32_t, B200MOE_WS_GRID_SYNC), T, stream));
   } else {
     STEP("permute", b200moe_permute(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP), stream));
   }
@@ -357,13 +362,16 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                                   q->activation, pad, stream));
   }
   if (fused) {
-    // yo is stored only for the backward (dgate = <dy, yo>); y -- or, with the fused post-norm,
-    // LayerNorm(residual + y) -- leaves the kernel's own tail: the forward ends here
+    // y -- or, with the fused post-norm, LayerNorm(residual + y) -- leaves the kernel's own tail: the forward ends here.
+    // Reduction mode stores yo only for the backward (dgate = <dy, yo>).
+    const bool red = reduce_combine(q);
     STEP("ffn_down", b200moe_ffn_down_combine(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert,
                                               WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW),
-                                              T, k, R, d, F, E, save_for_backward ? WS(void, B200MOE_WS_YO) : nullptr,
-                                              WS(float, B200MOE_WS_Y_ACC), WS(int32_t, B200MOE_WS_GRID_SYNC), y, pn, pad,
-                                              stream));
+                                              WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT), WS(float, B200MOE_WS_TOPK_GATE),
+                                              T, k, R, d, F, E,
+                                              (!red || save_for_backward) ? WS(void, B200MOE_WS_YO) : nullptr,
+                                              red ? WS(float, B200MOE_WS_Y_ACC) : nullptr,
+                                              WS(int32_t, B200MOE_WS_GRID_SYNC), y, pn, pad, stream));
     return B200MOE_OK;
   }
   STEP("ffn_down", b200moe_ffn_down(WS(void, B200MOE_WS_H), w2, b2, meta, tile_expert, R, d, F, E,
@@ -407,7 +415,7 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
   if (pn) {
     STEP("combine_ln_bwd",
          b200moe_combine_ln_bwd(dy, pn->dout_f32, WS(void, B200MOE_WS_YO), roa, WS(float, B200MOE_WS_TOPK_GATE),
-                                fused_combine(q) ? WS(float, B200MOE_WS_Y_ACC) : nullptr, pn->residual,
+                                reduce_combine(q) ? WS(float, B200MOE_WS_Y_ACC) : nullptr, pn->residual,
                                 pn->residual_f32, pn->gamma, pn->mean_rstd, T, k, d, pn->dv, pn->dres_f32, pn->scratch,
                                 pn->dgamma, pn->dbeta, stream));
     dy = pn->dv;
@@ -435,6 +443,9 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
                               pad, stream));
   if (fk) cudaEventRecord(fk->ev[1], main_s);
   {
+    // (tried in round 2 and dropped: finishing dlogits inside combine_bwd by per-token arrival counters -- it removes this
+    // launch and the cross-stream edge into unpermute_bwd, but the fence / atomic / dependent-load chain made combine_bwd,
+    // which IS on the dx chain, 3.9 -> 12.7 us at 3200 tokens: 104 -> 111 us per step)
     PdlOffIf np_(fk != nullptr);
     STEP("router_bwd_dlogits",
          b200moe_router_bwd_dlogits(WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX), roa,

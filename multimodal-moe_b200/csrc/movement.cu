@@ -37,12 +37,12 @@ permute_kernel(const __nv_bfloat16* __restrict__ x, const int32_t* __restrict__ 
       for (int c = lane; c < nchunk; c += 32) stg128(dst + c * 8, make_uint4(0, 0, 0, 0));
     }
   }
+  const size_t gid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (ci.grid_sync && gid == 0) stg128(ci.grid_sync, make_uint4(0, 0, 0, 0));
   if (ci.y_acc) {
     const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
-    const size_t gid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     const size_t n_acc = static_cast<size_t>(ci.T) * d / 4;             // 16-byte pieces
     for (size_t i = gid; i < n_acc; i += stride) stg128(ci.y_acc + 4 * i, make_uint4(0, 0, 0, 0));
-    if (ci.grid_sync && gid == 0) stg128(ci.grid_sync, make_uint4(0, 0, 0, 0));
   }
 }
 
@@ -67,23 +67,9 @@ __global__ void __launch_bounds__(kMoveThreads)
 combine_kernel(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ row_of_assignment,
                const float* __restrict__ topk_gate, int T, int k, int d, __nv_bfloat16* __restrict__ y) {
   pdl_sync();
-  const int nchunk = d >> 3;
   const int lane = threadIdx.x & 31;
-  for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps) {
-    for (int c = lane; c < nchunk; c += 32) {
-      float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      for (int s = 0; s < k; ++s) {
-        const int r = row_of_assignment[static_cast<size_t>(t) * k + s];
-        if (r < 0) continue;
-        const float g = topk_gate[static_cast<size_t>(t) * k + s];
-        float v[8];
-        unpack8(ldg128(yo + static_cast<size_t>(r) * d + c * 8), v);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] = combine_add(acc[j], combine_term(g, v[j]));
-      }
-      stg128(y + static_cast<size_t>(t) * d + c * 8, pack8(acc));
-    }
-  }
+  for (int t = blockIdx.x * kMoveWarps + (threadIdx.x >> 5); t < T; t += gridDim.x * kMoveWarps)
+    combine_token(yo, row_of_assignment, topk_gate, false, t, k, d, lane, y);
 }
 
 // dyp[r] = gate_of_row[r] * dy[token_of_row[r]];  dgate_row[r] = <dy[token], yo[r]>
@@ -476,8 +462,8 @@ extern "C" int b200moe_permute_init(const void* x, const int32_t* token_of_row, 
                                     int d, void* xp, float* y_acc, int32_t* grid_sync, int T, void* stream) {
   B200MOE_REQUIRE(d > 0 && d % 8 == 0, B200MOE_EINVAL, "permute: d=%d must be a multiple of 8", d);
   B200MOE_REQUIRE(y_acc == nullptr || (T > 0 && d % 4 == 0), B200MOE_EINVAL, "permute_init: bad T=%d / d=%d", T, d);
-  B200MOE_REQUIRE(grid_sync == nullptr || (y_acc != nullptr && (reinterpret_cast<uintptr_t>(grid_sync) & 15) == 0),
-                  B200MOE_EINVAL, "permute_init: grid_sync needs y_acc and 16-byte alignment");
+  B200MOE_REQUIRE(grid_sync == nullptr || (reinterpret_cast<uintptr_t>(grid_sync) & 15) == 0, B200MOE_EINVAL,
+                  "permute_init: grid_sync needs 16-byte alignment");
   if (int rc = b200moe_check_device()) return rc;
   const CombineInit ci{y_acc, grid_sync, T};
   launch_k(permute_kernel, move_grid(rows_cap), kMoveThreads, 0, ST(stream), BF(x), token_of_row, meta, d, BFW(xp), ci);

@@ -252,15 +252,21 @@ plan_fused_kernel(const int32_t* __restrict__ topk_idx, const float* __restrict_
   const bool lead = blockIdx.x == 0;
   pdl_sync();
 
-  for (int q = threadIdx.x; q < kE; q += blockDim.x) {
-    int tot = 0, base = 0;
-    for (int b = 0; b < nblk; ++b) {
-      const int c = block_counts[static_cast<size_t>(b) * kE + q];
-      base += (b < static_cast<int>(blockIdx.x)) ? c : 0;
-      tot += c;
+  // totals and this block's exclusive base of every (slot, expert) column: a warp per column, the lanes over the (at most
+  // kFusedMaxBlocks = 64) router blocks, so every load of the scan is in flight at once (a thread per column walked the
+  // blocks one dependent load after the other: the longest latency chain of the kernel at 3200 tokens)
+  for (int q = warp; q < kE; q += nwarps) {
+    const int c0 = lane < nblk ? block_counts[static_cast<size_t>(lane) * kE + q] : 0;
+    const int c1 = lane + 32 < nblk ? block_counts[static_cast<size_t>(lane + 32) * kE + q] : 0;
+    const int me = static_cast<int>(blockIdx.x);
+    int tot = c0 + c1;
+    int base = (lane < me ? c0 : 0) + (lane + 32 < me ? c1 : 0);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      tot += __shfl_xor_sync(0xffffffffu, tot, o);
+      base += __shfl_xor_sync(0xffffffffu, base, o);
     }
-    total_s[q] = tot;
-    base_s[q] = base;
+    if (lane == 0) { total_s[q] = tot; base_s[q] = base; }
   }
   if (lead) {   // loss statistics: one warp per column, lanes stride the blocks, fixed order
     for (int e = warp; e <= E; e += nwarps) {

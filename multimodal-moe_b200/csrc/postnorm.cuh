@@ -60,7 +60,8 @@ __device__ __forceinline__ void ln_gather_sum(const __nv_bfloat16* __restrict__ 
       const int c = lane + 32 * i;
       if (c < nchunk) {
         float a[8];
-        unpack8(ldg128(yo + static_cast<size_t>(r) * d + c * 8), a);
+        const __nv_bfloat16* src = yo + static_cast<size_t>(r) * d + c * 8;
+        unpack8(acc_cg ? ldcg128(src) : ldg128(src), a);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[i][j] = combine_add(v[i][j], combine_term(g, a[j]));
       }
@@ -75,6 +76,28 @@ __device__ __forceinline__ void ln_gather_sum(const __nv_bfloat16* __restrict__ 
 #pragma unroll
       for (int j = 0; j < 8; ++j) v[i][j] += a[j];
     }
+  }
+}
+
+// A.7 for one token, one warp: y[t] = sum_s gate[t,s] * yo[row[t,s]] in slot order, fp32 (combine_term / combine_add).
+// `cg`: yo was written earlier in the SAME kernel by other CTAs (read it coherently at L2).
+__device__ __forceinline__ void combine_token(const __nv_bfloat16* __restrict__ yo, const int32_t* __restrict__ roa,
+                                              const float* __restrict__ gate, bool cg, int t, int k, int d, int lane,
+                                              __nv_bfloat16* __restrict__ y) {
+  const int nchunk = d >> 3;
+  for (int c = lane; c < nchunk; c += 32) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int s = 0; s < k; ++s) {
+      const int r = roa[static_cast<size_t>(t) * k + s];
+      if (r < 0) continue;
+      const float g = gate[static_cast<size_t>(t) * k + s];
+      const __nv_bfloat16* src = yo + static_cast<size_t>(r) * d + c * 8;
+      float v[8];
+      unpack8(cg ? ldcg128(src) : ldg128(src), v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[j] = combine_add(acc[j], combine_term(g, v[j]));
+    }
+    stg128(y + static_cast<size_t>(t) * d + c * 8, pack8(acc));
   }
 }
 

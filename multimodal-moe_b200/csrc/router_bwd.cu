@@ -9,78 +9,22 @@
 #include <math.h>
 
 #include "common.cuh"
+#include "router_grad.cuh"
 
 namespace b200moe {
 
-template <int EP>
-__global__ void __launch_bounds__(128)
+// one warp per token (router_grad.cuh)
+__global__ void __launch_bounds__(256)
 router_dlogits_kernel(const float* __restrict__ logits, const int32_t* __restrict__ topk_idx,
                       const int32_t* __restrict__ row_of_assignment, const float* __restrict__ dgate_row,
                       const int32_t* __restrict__ tokens_per_expert, const float* __restrict__ d_aux, int T, int E,
                       int k, int normalize, float aux_w, float z_w, float* __restrict__ dlogits) {
-  __shared__ float f_s[64];
   pdl_sync();
-  if (threadIdx.x < E)
-    f_s[threadIdx.x] = static_cast<float>(tokens_per_expert[threadIdx.x]) / static_cast<float>(static_cast<long long>(T) * k);
-  __syncthreads();
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= T) return;
   const float da = d_aux ? *d_aux : 0.f;
-  const float d_lb = da * aux_w, d_z = da * z_w;
-  const float invT = 1.0f / static_cast<float>(T);
-
-  float l[EP], p[EP], dp[EP];
-  float mx = -INFINITY;
-#pragma unroll
-  for (int e = 0; e < EP; ++e) {
-    l[e] = (e < E) ? logits[static_cast<size_t>(t) * E + e] : -INFINITY;
-    mx = fmaxf(mx, l[e]);
-  }
-  float ssum = 0.f;
-#pragma unroll
-  for (int e = 0; e < EP; ++e) {
-    p[e] = (e < E) ? expf(l[e] - mx) : 0.f;
-    ssum += p[e];
-  }
-  const float inv = 1.0f / ssum;
-  const float lse = mx + logf(ssum);
-#pragma unroll
-  for (int e = 0; e < EP; ++e) {
-    p[e] *= inv;
-    dp[e] = (e < E) ? d_lb * static_cast<float>(E) * f_s[e] * invT : 0.f;
-  }
-  // gate path
-  if (dgate_row) {
-    int idx[8];
-    float dg[8], ps[8];
-    float S = 0.f;
-    for (int s = 0; s < k; ++s) {
-      idx[s] = topk_idx[static_cast<size_t>(t) * k + s];
-      const int r = row_of_assignment[static_cast<size_t>(t) * k + s];
-      dg[s] = r >= 0 ? dgate_row[r] : 0.f;
-      float pv = 0.f;
-#pragma unroll
-      for (int e = 0; e < EP; ++e) pv = (e == idx[s]) ? p[e] : pv;
-      ps[s] = pv;
-      S += pv;
-    }
-    float corr = 0.f;
-    const float den = S + 1e-9f;
-    if (normalize)
-      for (int s = 0; s < k; ++s) corr += dg[s] * (ps[s] / den);
-    for (int s = 0; s < k; ++s) {
-      const float g = normalize ? (dg[s] - corr) / den : dg[s];
-#pragma unroll
-      for (int e = 0; e < EP; ++e) dp[e] += (e == idx[s]) ? g : 0.f;
-    }
-  }
-  float dot = 0.f;
-#pragma unroll
-  for (int e = 0; e < EP; ++e) dot = fmaf(p[e], dp[e], dot);
-  const float zc = d_z * 2.0f * lse * invT;
-#pragma unroll
-  for (int e = 0; e < EP; ++e)
-    if (e < E) dlogits[static_cast<size_t>(t) * E + e] = p[e] * (dp[e] - dot) + zc * p[e];
+  const int lane = threadIdx.x & 31;
+  for (int t = blockIdx.x * 8 + (threadIdx.x >> 5); t < T; t += gridDim.x * 8)
+    dlogits_token_warp(logits, topk_idx, row_of_assignment, dgate_row, false, tokens_per_expert, da * aux_w, da * z_w, t, T,
+                       E, k, normalize, lane, dlogits);
 }
 
 // dWg = dlogits^T x in two fixed-order stages (deterministic, no atomics).
@@ -230,15 +174,10 @@ extern "C" int b200moe_router_bwd_dlogits(const float* logits, const int32_t* to
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  const int grid = (T + 127) / 128;
-#define CASE(EP)                                                                                                  \
-  launch_k(router_dlogits_kernel<EP>, grid, 128, 0, st, logits, topk_idx, row_of_assignment, dgate_row,            \
-           tokens_per_expert, d_aux, T, E, k, normalize_topk, aux_loss_weight, z_loss_weight, dlogits)
-  if (E <= 8) CASE(8);
-  else if (E <= 16) CASE(16);
-  else if (E <= 32) CASE(32);
-  else CASE(64);
-#undef CASE
+  int grid = (T + 7) / 8;
+  if (grid > 16 * num_sms()) grid = 16 * num_sms();
+  launch_k(router_dlogits_kernel, grid, 256, 0, st, logits, topk_idx, row_of_assignment, dgate_row, tokens_per_expert,
+           d_aux, T, E, k, normalize_topk, aux_loss_weight, z_loss_weight, dlogits);
   return check_launch("router_dlogits");
 }
 

@@ -109,13 +109,15 @@ def test_decoder_ffn_site_shape():
 
 @pytest.mark.parametrize("B,HW,d,F,E,cf", [(8, 400, 256, 1024, 8, 1.25), (3, 231, 512, 1024, 16, 0.5), (2, 100, 128, 256, 4, None),
                                            (2, 77, 1024, 1024, 8, 1.0)])
-def test_fused_post_norm_matches_unfused(B, HW, d, F, E, cf):
+@pytest.mark.parametrize("combine", ["tail", "epilogue", "separate"])
+def test_fused_post_norm_matches_unfused(B, HW, d, F, E, cf, combine):
     """LayerNorm(residual + MoE(x)) through the fused combine kernel (forward and backward) against the same module
     with torch's add + LayerNorm around the plain forward.  Both run the same expert kernels on the same routing, so
     the only differences are the bf16 rounding of y that the fused path skips and summation order."""
     import b200moe
     torch.manual_seed(B * HW)
     m = b200moe.ContextMoE(d, F, E, 2, cf, context_vocab_sizes=(6, 10, 4, 6, 4)).cuda()
+    m.combine = combine          # LayerNorm in the down-projection's tail (both fused modes) or in its own kernel
     norm = nn.LayerNorm(d).cuda()
     with torch.no_grad():
         norm.weight.uniform_(0.5, 1.5)

@@ -63,14 +63,14 @@ def _run_both(ref, m, x, ctx, go):
     (8, 300, 256, 1024, 8, 2, 1.25, False),        # decoder FFN site: 8 x 300 queries (rtdetrv2_decoder.py:186-189)
     (2, 257, 256, 512, 8, 3, 1.0, True),           # top-3: the separate combine kernel (fused epilogue is top_k <= 2)
 ])
-@pytest.mark.parametrize("fused", [True, False])
-def test_layer_matches_oracle(B, HW, d, F, E, k, cf, ctx, fused):
+@pytest.mark.parametrize("combine", ["tail", "epilogue", "separate"])
+def test_layer_matches_oracle(B, HW, d, F, E, k, cf, ctx, combine):
     """All gradients at the tolerance north_star states (rel-L2 <= 1e-2), the router's included.  Measured
     (tools/grad_diag.py, round 2): gate.weight / ctx_proj / ctx_embed 2.3e-3 .. 3.4e-3 for top-2; 4.9e-3 .. 6.9e-3 for
     top-1 with renormalised gates, where g = p / (p + 1e-9) == 1 in fp32 and the gate path of the gradient is exactly
     zero in the kernel but rounding noise in the oracle's autograd."""
     ref, m = _pair(d, F, E, k, cf, ctx, seed=B * HW)
-    m.fused_combine = fused
+    m.combine = combine
     g = torch.Generator().manual_seed(1234)
     x = torch.randn(B, HW, d, generator=g).to(torch.bfloat16)
     go = torch.randn(B, HW, d, generator=g)
@@ -94,17 +94,18 @@ def test_layer_matches_oracle(B, HW, d, F, E, k, cf, ctx, fused):
                                              (2, 333, 128, 256, 4, 1, 0.5), (1, 200, 1024, 2048, 64, 2, 2.0),
                                              (40, 400, 256, 1024, 8, 2, 1.25)])
 def test_fused_combine_equals_separate_kernels(B, HW, d, F, E, k, cf):
-    """The down-projection's fused combine epilogue (b200moe_ffn_down_combine: fp32 reductions in tile order, the last
-    contribution rounds) against b200moe_ffn_down + b200moe_combine (slot order): bit-identical outputs and gradients,
-    with drops (tokens that lose every assignment must come out as exact zeros), in training and in inference."""
+    """The combine inside the down-projection kernel -- its tail after the grid-wide rendezvous ("tail", gather from the
+    rows just stored) and its epilogue ("epilogue": fp32 reductions in tile order) -- against b200moe_ffn_down +
+    b200moe_combine (slot order): bit-identical outputs and gradients, with drops (tokens that lose every assignment
+    must come out as exact zeros), in training and in inference."""
     _, m = _pair(d, F, E, k, cf, ctx=True, seed=3 * B + HW)
     g = torch.Generator().manual_seed(99)
     x = torch.randn(B, HW, d, generator=g).to(torch.bfloat16).cuda()
     go = torch.randn(B, HW, d, generator=g).cuda()
     c = torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1).cuda()
     outs = []
-    for fused in (True, False, True):
-        m.fused_combine = fused
+    for mode in ("tail", "separate", "epilogue", "tail"):
+        m.combine = mode
         m.zero_grad(set_to_none=True)
         xg = x.clone().requires_grad_(True)
         y = m(xg, c)
@@ -364,10 +365,16 @@ def test_training_step_contract_fp16_autocast_gradscaler_clip():
         scaler.update()
         opt.zero_grad()
         assert scaler.get_scale() >= scale_before              # no inf / nan: the step was not skipped
-    # the fp16 head (autocast) sits between the loss and the layer: dy reaches the layer fp16-rounded and rank-4
+        with torch.no_grad():
+            # keep the expert masters bf16-representable, as _pair made them: an Adam step moves every weight by ~lr =
+            # 1e-4, below half a bf16 ulp of most of them, so the kernel's bf16 operand copies would round back to the OLD
+            # weights while the fp32 oracle uses the new ones -- a systematic (not a kernel) difference of 1.4e-2 .. 5.6e-2
+            # in the following step (tools/a4_diag.py: 4e-3 with masters that are not bf16-exact to begin with)
+            for p in (m.w1, m.w2):
+                p.copy_(p.to(torch.bfloat16).float())
     worst = {k_: max(r[2][k_] for r in report) for k_ in report[0][2]}
     print("a4 report:", report)
-    assert all(v <= 2e-2 for k_, v in worst.items() if k_ != "dwg") and worst["dwg"] <= 3e-2, report
+    assert all(v <= REL for v in worst.values()), report
 
 
 def test_graphed_step_matches_eager():
