@@ -322,11 +322,16 @@ typedef struct b200moe_layer_desc {
   int32_t activation;         /* B200MOE_ACT_GELU | B200MOE_ACT_RELU */
   int32_t flags;              /* B200MOE_LAYER_* */
 } b200moe_layer_desc;
-/* flags: by default the down-projection kernel combines in its tail (b200moe_ffn_down_combine, gather mode).
- *   B200MOE_LAYER_SEPARATE_COMBINE: the separate b200moe_ffn_down + b200moe_combine kernels (the tested reference);
- *   B200MOE_LAYER_COMBINE_REDUCE  : the combine in the epilogue itself by fp32 reductions (top_k <= 2; gather mode else). */
+/* flags: where the A.7 combine runs.  Default (no bit): inside the down-projection kernel's tail
+ * (b200moe_ffn_down_combine, gather mode) while the expert outputs yo [R,d] stay L2-resident (R*d*2 <= 48 MB), the
+ * separate kernels beyond that -- measured, round 2: tail 18.5 vs 22.6 us at 3200 tokens, 0.076 vs 0.083 ms at
+ * C/14720, but 0.272 vs 0.235 ms at C/65533, where the rendezvous idles the early CTAs longer than a launch costs.
+ *   B200MOE_LAYER_SEPARATE_COMBINE: always b200moe_ffn_down + b200moe_combine (the tested reference);
+ *   B200MOE_LAYER_COMBINE_TAIL    : always the tail of the down-projection kernel;
+ *   B200MOE_LAYER_COMBINE_REDUCE  : in the epilogue itself by fp32 reductions (top_k <= 2; tail else). */
 #define B200MOE_LAYER_SEPARATE_COMBINE 1
 #define B200MOE_LAYER_COMBINE_REDUCE 2
+#define B200MOE_LAYER_COMBINE_TAIL 4
 
 enum {
   B200MOE_WS_LOGITS = 0, B200MOE_WS_TOPK_IDX, B200MOE_WS_TOPK_GATE, B200MOE_WS_BLOCK_COUNTS, B200MOE_WS_BLOCK_STATS,

@@ -111,7 +111,9 @@ ACT_GELU, ACT_RELU = 0, 1                 # B200MOE_ACT_*
 ACTIVATIONS = {"gelu": ACT_GELU, "relu": ACT_RELU}
 LAYER_SEPARATE_COMBINE = 1                # B200MOE_LAYER_SEPARATE_COMBINE
 LAYER_COMBINE_REDUCE = 2                  # B200MOE_LAYER_COMBINE_REDUCE
-COMBINE_FLAGS = {"tail": 0, "epilogue": LAYER_COMBINE_REDUCE, "separate": LAYER_SEPARATE_COMBINE}
+LAYER_COMBINE_TAIL = 4                    # B200MOE_LAYER_COMBINE_TAIL
+COMBINE_FLAGS = {"auto": 0, "tail": LAYER_COMBINE_TAIL, "epilogue": LAYER_COMBINE_REDUCE,
+                 "separate": LAYER_SEPARATE_COMBINE}
 
 
 WS_NAMES = ("logits", "topk_idx", "topk_gate", "block_counts", "block_stats", "expert_offsets", "meta", "tile_expert",

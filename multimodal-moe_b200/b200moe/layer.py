@@ -49,7 +49,8 @@ class _LayerPlan:
         rows_cap = lib.b200moe_layer_rows_cap(T, k, E, cap, d, F)
         if rows_cap <= 0:
             raise RuntimeError(f"b200moe: bad layer shape T={T} k={k} E={E}")
-        self.fused = mod.combine != "separate"
+        # mirrors fused_combine() / reduce_combine() of csrc/layer.cu (the workspace layout depends on them)
+        self.fused = mod.combine in ("tail", "epilogue") or (mod.combine == "auto" and rows_cap * d * 2 <= (48 << 20))
         self.reduce = mod.combine == "epilogue" and k <= 2
         self.desc = _lib.LayerDesc(T, d, F, E, k, tpi, cap, rows_cap, int(mod.normalize_topk),
                                    mod.aux_loss_weight, mod.z_loss_weight, _lib.ACTIVATIONS[mod.activation],
@@ -291,11 +292,11 @@ class ContextMoE(nn.Module):
         self.context_vocab_sizes = tuple(context_vocab_sizes)
         self.context_dim = context_dim
         self.activation = activation
-        # where the A.7 combine runs: "tail" (default) inside the down-projection kernel, after a grid-wide rendezvous,
-        # from the expert outputs it just stored; "epilogue": in the down-projection's epilogue itself by fp32 reductions
-        # (top_k <= 2; measured slower from ~10^4 tokens on: L2 atomic throughput); "separate": down + combine kernels,
-        # the tested reference of both
-        self.combine = "tail"
+        # where the A.7 combine runs: "tail": inside the down-projection kernel, after a grid-wide rendezvous, from the expert
+        # outputs it just stored; "epilogue": in the down-projection's epilogue itself by fp32 reductions (top_k <= 2;
+        # measured slower from ~10^4 tokens on: L2 atomic throughput); "separate": down + combine kernels, the tested
+        # reference of both; "auto" (default): tail while yo fits L2, separate beyond (include/b200moe.h has the numbers)
+        self.combine = "auto"
         self.ep_group = ep_group
         self.ep_p2p = ep_p2p          # None: peer-memory dispatch when available; False: NCCL all-to-all; True: required
         self.ep_max_tokens = ep_max_tokens   # tokens per rank the peer-memory arena is sized for (None: the first batch)
@@ -415,17 +416,19 @@ class ContextMoE(nn.Module):
         ready = None
         if overlap and (a1[2] or a2[2]):
             cur = torch.cuda.current_stream(dev)
-            _lib.call("b200moe_prepare_weights", None, w1b.data_ptr(), 0, None, w2b.data_ptr(), 0, wgf.data_ptr(),
-                      wsplit.data_ptr(), self.d_model, self.num_experts, _lib.stream_ptr())
             side = self.__dict__.get("_prep_stream")
             if side is None or side.device != dev:
                 side = self.__dict__["_prep_stream"] = torch.cuda.Stream(device=dev)
+            # the side stream forks BEFORE the gate split is launched: in a captured graph the two preparations are then
+            # independent roots (as children of the gate-split node the router started ~6 us late at 3200 tokens)
             side.wait_stream(cur)
             with torch.cuda.stream(side):
                 _lib.call("b200moe_prepare_weights", *a1, *a2, None, None, self.d_model, self.num_experts,
                           _lib.stream_ptr())
                 ready = torch.cuda.Event()
                 ready.record(side)
+            _lib.call("b200moe_prepare_weights", None, w1b.data_ptr(), 0, None, w2b.data_ptr(), 0, wgf.data_ptr(),
+                      wsplit.data_ptr(), self.d_model, self.num_experts, _lib.stream_ptr())
             self.__dict__["_prep_keep"] = (w1f, w2f)      # read on the side stream: keep them until the next call
         else:
             _lib.call("b200moe_prepare_weights", *a1, *a2, wgf.data_ptr(), wsplit.data_ptr(), self.d_model,

@@ -92,7 +92,11 @@ struct PdlOffIf {
 
 // combine inside the down-projection kernel (its tail, or -- reduction mode -- its epilogue: order-free fp32 accumulation
 // is exact for at most two terms)
-static inline bool fused_combine(const b200moe_layer_desc* q) { return !(q->flags & B200MOE_LAYER_SEPARATE_COMBINE); }
+static inline bool fused_combine(const b200moe_layer_desc* q) {
+  if (q->flags & B200MOE_LAYER_SEPARATE_COMBINE) return false;
+  if (q->flags & (B200MOE_LAYER_COMBINE_TAIL | B200MOE_LAYER_COMBINE_REDUCE)) return true;
+  return static_cast<int64_t>(q->rows_cap) * q->d * 2 <= (48ll << 20);     // yo still L2-resident when the tail reads it
+}
 static inline bool reduce_combine(const b200moe_layer_desc* q) {
   return fused_combine(q) && (q->flags & B200MOE_LAYER_COMBINE_REDUCE) && q->k <= 2;
 }
@@ -107,7 +111,8 @@ static int check_desc(const b200moe_layer_desc* q, const char* what) {
   B200MOE_REQUIRE(q->capacity >= 0, B200MOE_EINVAL, "%s: negative capacity", what);
   B200MOE_REQUIRE(q->activation == B200MOE_ACT_GELU || q->activation == B200MOE_ACT_RELU, B200MOE_EINVAL,
                   "%s: activation=%d must be B200MOE_ACT_GELU or B200MOE_ACT_RELU", what, q->activation);
-  B200MOE_REQUIRE((q->flags & ~(B200MOE_LAYER_SEPARATE_COMBINE | B200MOE_LAYER_COMBINE_REDUCE)) == 0, B200MOE_EINVAL,
+  B200MOE_REQUIRE((q->flags & ~(B200MOE_LAYER_SEPARATE_COMBINE | B200MOE_LAYER_COMBINE_REDUCE | B200MOE_LAYER_COMBINE_TAIL)) == 0,
+                  B200MOE_EINVAL,
                   "%s: unknown flags 0x%x", what, q->flags);
   B200MOE_REQUIRE(q->rows_cap > 0 && q->rows_cap % kRowPad == 0 &&
                       q->rows_cap >= b200moe_layer_rows_cap(q->T, q->k, q->E, q->capacity, q->d, q->F),

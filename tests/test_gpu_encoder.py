@@ -109,7 +109,7 @@ def test_decoder_ffn_site_shape():
 
 @pytest.mark.parametrize("B,HW,d,F,E,cf", [(8, 400, 256, 1024, 8, 1.25), (3, 231, 512, 1024, 16, 0.5), (2, 100, 128, 256, 4, None),
                                            (2, 77, 1024, 1024, 8, 1.0)])
-@pytest.mark.parametrize("combine", ["tail", "epilogue", "separate"])
+@pytest.mark.parametrize("combine", ["auto", "tail", "epilogue", "separate"])
 def test_fused_post_norm_matches_unfused(B, HW, d, F, E, cf, combine):
     """LayerNorm(residual + MoE(x)) through the fused combine kernel (forward and backward) against the same module
     with torch's add + LayerNorm around the plain forward.  Both run the same expert kernels on the same routing, so

@@ -63,7 +63,7 @@ def _run_both(ref, m, x, ctx, go):
     (8, 300, 256, 1024, 8, 2, 1.25, False),        # decoder FFN site: 8 x 300 queries (rtdetrv2_decoder.py:186-189)
     (2, 257, 256, 512, 8, 3, 1.0, True),           # top-3: the separate combine kernel (fused epilogue is top_k <= 2)
 ])
-@pytest.mark.parametrize("combine", ["tail", "epilogue", "separate"])
+@pytest.mark.parametrize("combine", ["auto", "tail", "epilogue", "separate"])
 def test_layer_matches_oracle(B, HW, d, F, E, k, cf, ctx, combine):
     """All gradients at the tolerance north_star states (rel-L2 <= 1e-2), the router's included.  Measured
     (tools/grad_diag.py, round 2): gate.weight / ctx_proj / ctx_embed 2.3e-3 .. 3.4e-3 for top-2; 4.9e-3 .. 6.9e-3 for
