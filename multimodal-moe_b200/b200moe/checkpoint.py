@@ -60,7 +60,9 @@ def ddp_ignore_experts(model: nn.Module) -> List[str]:
     mean-over-ranks convention (see the module docstring)."""
     names = expert_param_names(model)
     prev = list(getattr(model, "_ddp_params_and_buffers_to_ignore", []))
-    model._ddp_params_and_buffers_to_ignore = prev + [n for n in names if n not in prev]
+    # DDP matches f"{module_name}.{param_name}": for parameters of the ROOT module that is ".w1", not "w1"
+    spelled = names + ["." + n for n in names if "." not in n]
+    model._ddp_params_and_buffers_to_ignore = prev + [n for n in spelled if n not in prev]
     for _, m in _ep_modules(model):
         if m.ep_size > 1:
             m.expert_grad_scale = 1.0 / m.ep_size

@@ -136,8 +136,10 @@ class _EPFunction(torch.autograd.Function):
         W, rank = dist.get_world_size(group), dist.get_rank(group)
         T, d = x2.shape
         E, k, EL = mod.num_experts, mod.top_k, mod.num_local_experts
-        need_grad = any(ctx.needs_input_grad)
-        w1b, w2b, wsplit, wgf, _ = mod._prepared(w1, w2, wg)          # one launch: bf16 operands + gate hi/lo split
+        # needs_input_grad is True for parameters even under torch.no_grad(): the caller's grad mode decides
+        need_grad = any(ctx.needs_input_grad) and mod.__dict__.get("_grad_mode", True)
+        # bf16 operands + gate hi/lo split; the two slab casts run on a side stream under the router and the dispatch
+        w1b, w2b, wsplit, wgf, w_ready = mod._prepared(w1, w2, wg, overlap=not _lib.PROFILING)
         b1f, b2f = b1.float().contiguous(), b2.float().contiguous()
         cb = ctx_bias.float().contiguous() if ctx_bias is not None else None
         dev = x2.device
@@ -195,6 +197,8 @@ class _EPFunction(torch.autograd.Function):
                 arrived.append(ev)
         # grouped GEMMs per group as its rows arrive; results go home on the communication stream
         ys = torch.empty((max(n_send, 1), d), dtype=torch.bfloat16, device=dev)
+        if w_ready is not None:
+            comp.wait_event(w_ready)
         for c, ch in enumerate(chunks):
             comp.wait_event(arrived[c])
             xr = ch.xp

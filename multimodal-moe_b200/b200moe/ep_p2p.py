@@ -150,8 +150,11 @@ class _P2PFunction(torch.autograd.Function):
         W, rank = dist.get_world_size(group), dist.get_rank(group)
         T, d = x2.shape
         E, k, EL = mod.num_experts, mod.top_k, mod.num_local_experts
-        need_grad = any(ctx.needs_input_grad)
-        w1b, w2b, wsplit, wgf, _ = mod._prepared(w1, w2, wg)
+        # needs_input_grad is True for parameters even under torch.no_grad(): the caller's grad mode decides
+        need_grad = any(ctx.needs_input_grad) and mod.__dict__.get("_grad_mode", True)
+        # the bf16 casts of this rank's expert slabs run on a side stream under the router, the histogram exchange and
+        # the dispatch; the up-projection is the first kernel that needs them
+        w1b, w2b, wsplit, wgf, ready = mod._prepared(w1, w2, wg, overlap=not _lib.PROFILING)
         b1f, b2f = b1.float().contiguous(), b2.float().contiguous()
         cb = ctx_bias.float().contiguous() if ctx_bias is not None else None
         dev = x2.device
@@ -191,6 +194,8 @@ class _P2PFunction(torch.autograd.Function):
                   p.meta.data_ptr(), dest_off.data_ptr(), ar.peers.data_ptr(), ar.off[0], R, send_cap, E, EL, d,
                   dest_of_row.data_ptr(), st)
         ar.barrier(0)                                   # every rank's rows have landed in xp
+        if ready is not None:
+            torch.cuda.current_stream(dev).wait_event(ready)
         pre, h = ops.ffn_up(ar.xp, w1b, b1f, meta, tile_e, save_pre=need_grad, row_pad=ar.row_pad,
                             activation=_lib.ACTIVATIONS[mod.activation])
         ops.ffn_down(h, w2b, b2f, meta, tile_e, row_pad=ar.row_pad, out=ar.yo)
@@ -262,15 +267,22 @@ class _P2PFunction(torch.autograd.Function):
             ops.ffn_wgrad(ar.dyp, h, offs, EL, out=dw2)
         if need[3]:
             ops.ffn_wgrad(dhpre, ar.xp, offs, EL, out=dw1)
-        if need[6] and need[4]:
-            ops.colsum(ar.dyp, offs, EL, out=db2, a1=dhpre, out1=db1)
-        elif need[6]:
-            ops.colsum(ar.dyp, offs, EL, out=db2)
-        elif need[4]:
-            ops.colsum(dhpre, offs, EL, out=db1)
+        if need[4] or need[6]:
+            # bias gradients: a bandwidth-bound column sum, on the side stream next to the tensor-bound weight gradients
+            side = _side_stream(mod, dev)
+            if dxs is None:
+                side.wait_stream(comp)
+            with torch.cuda.stream(side):
+                if need[6] and need[4]:
+                    ops.colsum(ar.dyp, offs, EL, out=db2, a1=dhpre, out1=db1)
+                elif need[6]:
+                    ops.colsum(ar.dyp, offs, EL, out=db2)
+                else:
+                    ops.colsum(dhpre, offs, EL, out=db1)
         dx = None
-        if need[0]:
+        if need[0] or need[4] or need[6]:
             comp.wait_stream(side)
+        if need[0]:
             dx = ops.unpermute_bwd(dxs, p.row_of_assignment, dlogits, wgf, T, k, d)
         ar.pending = False
         t_w1, t_b1, t_w2, t_b2, t_wg = ctx.dtypes

@@ -157,7 +157,9 @@ class _MoEFunction(torch.autograd.Function):
         T, d = x2.shape
         dev = x2.device
         E = mod.num_experts
-        need_grad = any(ctx.needs_input_grad)   # forward runs under no_grad: ask autograd, not the grad mode
+        # Function.forward itself always runs with grad mode off, and needs_input_grad is True for parameters even under
+        # the caller's torch.no_grad(): the caller's grad mode (noted by ContextMoE.forward) decides what is saved
+        need_grad = any(ctx.needs_input_grad) and mod.__dict__.get("_grad_mode", True)
         pl = mod._layer_plan(T, tpi)
         # (while bench.py's per-kernel timing records, the casts stay on the current stream: a cast running next to the
         # router / plan / permute would steal their HBM bandwidth and the numbers would not be those of isolated kernels)
@@ -498,6 +500,7 @@ class ContextMoE(nn.Module):
         shape = x.shape
         x2 = x.reshape(-1, self.d_model)
         T = x2.shape[0]
+        self.__dict__["_grad_mode"] = torch.is_grad_enabled()
         if T == 0:
             self.aux_loss = x.new_zeros((), dtype=torch.float32)
             return x.clone() if _post is None else _post[1](_post[0] + x)

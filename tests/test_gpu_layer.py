@@ -106,6 +106,10 @@ def test_fused_combine_equals_separate_kernels(B, HW, d, F, E, k, cf):
     outs = []
     for mode in ("tail", "separate", "epilogue", "tail"):
         m.combine = mode
+        # poison the allocator's free blocks: the workspaces of this pass reuse them, so a kernel that read a row before
+        # its producer wrote it (the rendezvous of the fused modes) would see NaN, not the previous mode's identical values
+        junk = torch.full((96 << 20,), float("nan"), device="cuda")
+        del junk
         m.zero_grad(set_to_none=True)
         xg = x.clone().requires_grad_(True)
         y = m(xg, c)

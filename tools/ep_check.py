@@ -59,10 +59,17 @@ def varying_tokens_and_overflow(rank, world, dev):
             small(torch.randn(1, 128, d, device=dev).to(torch.bfloat16))        # arena sized for 128 tokens per rank
         xb = torch.randn(4, 512, d, device=dev).to(torch.bfloat16).requires_grad_(True)
         try:
-            small(xb).float().sum().backward()
+            ys = small(xb)
+            ar = small.__dict__.get("_p2p_arena")
+            torch.cuda.synchronize()
+            print(f"[rank {rank}] overflow case: arena rows_cap={ar.rows_cap} T_cap={ar.T_cap} pending={ar.pending} "
+                  f"flag={ar.flag_host.tolist()} event={ar.flag_event is not None}", flush=True)
+            ys.float().sum().backward()
             raised = False
         except RuntimeError as e:
             raised = "arena overflow" in str(e)
+            if not raised:
+                print(f"[rank {rank}] unexpected error: {e}", flush=True)
         ok = ok and bool(raised)
     print(f"[rank {rank}] varying tokens per step and rank over {path}: {'OK' if ok else 'FAILED'}"
           f" (overflow raised on this rank: {raised})", flush=True)
