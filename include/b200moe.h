@@ -146,6 +146,14 @@ int b200moe_combine_bwd(const void* dy, const void* yo, const int32_t* token_of_
 int b200moe_ffn_up(const void* xp, const void* w1, const float* b1, const int32_t* meta,
                    const int32_t* tile_expert, int rows_cap, int d, int F, int E,
                    void* pre, void* h, int activation, int row_pad, void* stream);
+/* The up-projection with the dispatch gather of A.5 fused into its A-operand load: row r of the permuted buffer is
+ * x[token_of_row[r], :] fetched by the kernel's own TMA loads (tile::gather4; pad rows, token_of_row < 0, arrive as
+ * zeros), so xp [R,d] is never written and b200moe_permute is not launched.  x [T,d] bf16.  `clear`: NULL, or one int32
+ * the kernel sets to zero (the grid_sync counter of the b200moe_ffn_down_combine that follows).  Bit-identical to
+ * b200moe_permute + b200moe_ffn_up; slower (see B200MOE_LAYER_GATHER_DISPATCH).                                    */
+int b200moe_ffn_up_gather(const void* x, const int32_t* token_of_row, int T, const void* w1, const float* b1,
+                          const int32_t* meta, const int32_t* tile_expert, int rows_cap, int d, int F, int E,
+                          void* pre, void* h, int activation, int row_pad, int32_t* clear, void* stream);
 int b200moe_ffn_down(const void* h, const void* w2, const float* b2, const int32_t* meta,
                      const int32_t* tile_expert, int rows_cap, int d, int F, int E,
                      void* yo, int row_pad, void* stream);
@@ -210,6 +218,18 @@ int b200moe_ffn_dgrad_up(const void* dhpre, const void* w1, const int32_t* meta,
                          void* dxp, int row_pad, void* stream);
 int b200moe_ffn_wgrad(const void* a, const void* b, const int32_t* expert_offsets, int rows_cap,
                       int M, int N, int E, float* dw, int accumulate, void* stream);
+/* Both weight gradients of the FFN in one launch: dw_a[e] = a0^T b0 [E,M0,N0] and dw_b[e] = a1^T b1 [E,M1,N1]
+ * (dw2 = dyp^T h: M0 = d, N0 = F; dw1 = dhpre^T xp: M1 = F, N1 = d), bit-identical to two b200moe_ffn_wgrad calls.  The
+ * tiles of both problems share one persistent grid (no partly filled last wave per problem, no queueing of the second
+ * launch behind the first). */
+int b200moe_ffn_wgrad2(const void* a0, const void* b0, int M0, int N0, float* dw_a,
+                       const void* a1, const void* b1, int M1, int N1, float* dw_b,
+                       const int32_t* expert_offsets, int rows_cap, int E, int accumulate, void* stream);
+/* wgrad with b = x[token_of_row[rows of e], :] gathered by the TMA loads of the B operand (dw1 = dhpre^T xp without
+ * the permuted copy; x [T,N] bf16). */
+int b200moe_ffn_wgrad_gather(const void* a, const void* x, const int32_t* token_of_row, int T,
+                             const int32_t* expert_offsets, int rows_cap, int M, int N, int E, float* dw,
+                             int accumulate, void* stream);
 /* Bias gradients of both projections in ONE launch (a1 may be NULL): db0[e,:] = column sums of a0 over the rows of
  * expert e, same for (a1, db1).  Fixed summation order, no scratch.  ncols multiples of 64. */
 int b200moe_colsum(const void* a0, int ncols0, float* db0, const void* a1, int ncols1, float* db1,
@@ -332,6 +352,14 @@ typedef struct b200moe_layer_desc {
 #define B200MOE_LAYER_SEPARATE_COMBINE 1
 #define B200MOE_LAYER_COMBINE_REDUCE 2
 #define B200MOE_LAYER_COMBINE_TAIL 4
+/* Dispatch.  Default: b200moe_permute writes the permuted tokens xp [R,d] and the GEMMs read them with tiled TMA loads.
+ *   B200MOE_LAYER_GATHER_DISPATCH: the permuted copy is never made -- b200moe_ffn_up_gather in the forward and
+ *   b200moe_ffn_wgrad_gather in the backward fetch x[token_of_row[r]] through tile::gather4 TMA loads (no
+ *   b200moe_permute launch, workspace slot XP empty).  Bit-identical; measured SLOWER on B200 (round 2: a gather4 moves
+ *   4 x 128 B and an SM's TMA unit retires one per ~95 cycles, ~5 B/clk against >100 B/clk for tiled boxes: up-projection
+ *   0.235 -> 0.79 ms at E=64 d=1024, the w1 weight gradient 0.22 -> 0.78 ms at C/65533), so it is an option, not the
+ *   default.  Ignored with COMBINE_REDUCE (whose accumulator the permute kernel clears). */
+#define B200MOE_LAYER_GATHER_DISPATCH 8
 
 enum {
   B200MOE_WS_LOGITS = 0, B200MOE_WS_TOPK_IDX, B200MOE_WS_TOPK_GATE, B200MOE_WS_BLOCK_COUNTS, B200MOE_WS_BLOCK_STATS,

@@ -38,6 +38,9 @@ SIGNATURES = {
     "b200moe_ffn_dgrad_down": [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _I, _P],
     "b200moe_ffn_dgrad_up": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
     "b200moe_ffn_wgrad": [_P, _P, _P, _I, _I, _I, _I, _P, _I, _P],
+    "b200moe_ffn_wgrad2": [_P, _P, _I, _I, _P, _P, _P, _I, _I, _P, _P, _I, _I, _I, _P],
+    "b200moe_ffn_up_gather": [_P, _P, _I, _P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _I, _I, _P, _P],
+    "b200moe_ffn_wgrad_gather": [_P, _P, _P, _I, _P, _I, _I, _I, _I, _P, _I, _P],
     "b200moe_colsum": [_P, _I, _P, _P, _I, _P, _P, _I, _I, _P],
     "b200moe_prepare_weights": [_P, _P, _L, _P, _P, _L, _P, _P, _I, _I, _P],
     "b200moe_ctx_bias_fwd": [_P, _P, _P, _I, _I, _P, _I, _I, _P, _P],
@@ -112,6 +115,8 @@ ACTIVATIONS = {"gelu": ACT_GELU, "relu": ACT_RELU}
 LAYER_SEPARATE_COMBINE = 1                # B200MOE_LAYER_SEPARATE_COMBINE
 LAYER_COMBINE_REDUCE = 2                  # B200MOE_LAYER_COMBINE_REDUCE
 LAYER_COMBINE_TAIL = 4                    # B200MOE_LAYER_COMBINE_TAIL
+LAYER_GATHER_DISPATCH = 8                 # B200MOE_LAYER_GATHER_DISPATCH
+DISPATCH_FLAGS = {"permute": 0, "gather": LAYER_GATHER_DISPATCH}
 COMBINE_FLAGS = {"auto": 0, "tail": LAYER_COMBINE_TAIL, "epilogue": LAYER_COMBINE_REDUCE,
                  "separate": LAYER_SEPARATE_COMBINE}
 
@@ -158,10 +163,10 @@ def stream_ptr() -> int:
 # kernels launched by each entry point (memset nodes not counted); used for bench.py's gpu_launches
 KERNELS_PER_CALL = {
     "b200moe_cast_f32_bf16": 1, "b200moe_prepare_weights": 1, "b200moe_ctx_bias_fwd": 1, "b200moe_ctx_bias_bwd": 1,
-    "b200moe_layer_fwd": 6, "b200moe_layer_bwd": 12, "b200moe_router_fwd_ctx": 1, "b200moe_combine_ln_fwd": 1, "b200moe_combine_ln_bwd": 2, "b200moe_router_bwd_params": 2, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
+    "b200moe_layer_fwd": 6, "b200moe_layer_bwd": 11, "b200moe_router_fwd_ctx": 1, "b200moe_combine_ln_fwd": 1, "b200moe_combine_ln_bwd": 2, "b200moe_router_bwd_params": 2, "b200moe_router_fwd": 2, "b200moe_plan": 2, "b200moe_permute": 1,
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
     "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
-    "b200moe_permute_init": 1, "b200moe_ffn_down_combine": 1,
+    "b200moe_permute_init": 1, "b200moe_ffn_down_combine": 1, "b200moe_ffn_up_gather": 1, "b200moe_ffn_wgrad2": 1, "b200moe_ffn_wgrad_gather": 1,
     "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,
     "b200moe_unpermute_bwd": 1, "b200moe_ep_recv_plan": 1, "b200moe_ep_hist": 1, "b200moe_ep_route_tables": 1, "b200moe_scatter_rows": 1,
 }

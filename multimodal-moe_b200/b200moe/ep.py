@@ -291,9 +291,11 @@ class _EPFunction(torch.autograd.Function):
                     dxr.record_stream(comm)
                     _a2a_into(dxs[send_off[c]:send_off[c + 1]], dxr[:ch.n_recv], recv_splits[c], send_splits[c],
                               group)
-            if need[5]:
+            if need[5] and need[3]:
+                ops.ffn_wgrad2(dyp, ch.h, dhpre, ch.xp, ch.offs, n, out0=dw2[ch.lo:ch.hi], out1=dw1[ch.lo:ch.hi])
+            elif need[5]:
                 ops.ffn_wgrad(dyp, ch.h, ch.offs, n, out=dw2[ch.lo:ch.hi])
-            if need[3]:
+            elif need[3]:
                 ops.ffn_wgrad(dhpre, ch.xp, ch.offs, n, out=dw1[ch.lo:ch.hi])
             if need[6] and need[4]:
                 ops.colsum(dyp, ch.offs, n, out=db2[ch.lo:ch.hi], a1=dhpre, out1=db1[ch.lo:ch.hi])

@@ -263,9 +263,11 @@ class _P2PFunction(torch.autograd.Function):
         db1 = torch.empty((EL, F), dtype=f32, device=dev) if need[4] else None
         dw2 = torch.empty((EL, d, F), dtype=f32, device=dev) if need[5] else None
         db2 = torch.empty((EL, d), dtype=f32, device=dev) if need[6] else None
-        if need[5]:
+        if need[5] and need[3]:
+            ops.ffn_wgrad2(ar.dyp, h, dhpre, ar.xp, offs, EL, out0=dw2, out1=dw1)     # one persistent grid for both
+        elif need[5]:
             ops.ffn_wgrad(ar.dyp, h, offs, EL, out=dw2)
-        if need[3]:
+        elif need[3]:
             ops.ffn_wgrad(dhpre, ar.xp, offs, EL, out=dw1)
         if need[4] or need[6]:
             # bias gradients: a bandwidth-bound column sum, on the side stream next to the tensor-bound weight gradients

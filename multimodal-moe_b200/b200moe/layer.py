@@ -51,10 +51,11 @@ class _LayerPlan:
             raise RuntimeError(f"b200moe: bad layer shape T={T} k={k} E={E}")
         # mirrors fused_combine() / reduce_combine() of csrc/layer.cu (the workspace layout depends on them)
         self.fused = mod.combine in ("tail", "epilogue") or (mod.combine == "auto" and rows_cap * d * 2 <= (48 << 20))
-        self.reduce = mod.combine == "epilogue" and k <= 2
+        self.reduce = self.fused and mod.combine == "epilogue" and k <= 2
+        self.gather = mod.dispatch == "gather" and not self.reduce      # gather_dispatch() of csrc/layer.cu
         self.desc = _lib.LayerDesc(T, d, F, E, k, tpi, cap, rows_cap, int(mod.normalize_topk),
                                    mod.aux_loss_weight, mod.z_loss_weight, _lib.ACTIVATIONS[mod.activation],
-                                   _lib.COMBINE_FLAGS[mod.combine])
+                                   _lib.COMBINE_FLAGS[mod.combine] | _lib.DISPATCH_FLAGS[mod.dispatch])
         self.desc_ptr = C.addressof(self.desc)
         off = (C.c_int64 * len(_lib.WS_NAMES))()
         self.ws_bytes = lib.b200moe_layer_ws_layout(self.desc_ptr, C.addressof(off))
@@ -69,7 +70,7 @@ class _LayerPlan:
                       "block_stats": (nblk, E + 1), "expert_offsets": (E + 1,), "meta": (8,),
                       "tile_expert": (R // 128,), "tokens_per_expert": (E,), "kept_per_expert": (E,), "losses": (3,),
                       "slot_limit": (2 * k * E,), "row_of_assignment": (T, k), "token_of_row": (R,),
-                      "gate_of_row": (R,), "xp": (R, d), "pre": (R, F), "h": (R, F), "yo": (R, d),
+                      "gate_of_row": (R,), "xp": (0 if self.gather else R, d), "pre": (R, F), "h": (R, F), "yo": (R, d),
                       "y_acc": (T, d) if self.reduce else (0, d), "grid_sync": (4,) if self.fused else (0,),
                       "ctx_bias": ((T + tpi - 1) // tpi, E)}
         self.capacity, self.rows_cap = cap, rows_cap
@@ -299,6 +300,11 @@ class ContextMoE(nn.Module):
         # measured slower from ~10^4 tokens on: L2 atomic throughput); "separate": down + combine kernels, the tested
         # reference of both; "auto" (default): tail while yo fits L2, separate beyond (include/b200moe.h has the numbers)
         self.combine = "auto"
+        # how the tokens reach the experts: "permute" (default): b200moe_permute writes xp [R,d], the GEMMs read it with
+        # tiled TMA loads; "gather": the up-projection's (and, backward, the w1 weight-gradient's) TMA loads fetch
+        # x[token_of_row[r]] themselves (tile::gather4), no permuted copy exists -- bit-identical, measured slower on
+        # B200 (include/b200moe.h, B200MOE_LAYER_GATHER_DISPATCH)
+        self.dispatch = "permute"
         self.ep_group = ep_group
         self.ep_p2p = ep_p2p          # None: peer-memory dispatch when available; False: NCCL all-to-all; True: required
         self.ep_max_tokens = ep_max_tokens   # tokens per rank the peer-memory arena is sized for (None: the first batch)
@@ -387,7 +393,7 @@ class ContextMoE(nn.Module):
         # everything the descriptor is built from: a later change of capacity_factor, the loss weights, ... must not
         # be served a stale plan
         key = (T, tpi, self.capacity_factor, self.normalize_topk, self.aux_loss_weight, self.z_loss_weight,
-               self.activation, self.combine)
+               self.activation, self.combine, self.dispatch)
         pl = self._plans.get(key)
         if pl is None:
             if len(self._plans) > 64:       # multiscale training varies T per step (dataloader.yml:22)

@@ -149,6 +149,18 @@ def ffn_up(xp, w1, b1, meta, tile_expert, save_pre: bool = True, row_pad: int = 
     return pre, h
 
 
+def ffn_up_gather(x, token_of_row, w1, b1, meta, tile_expert, rows_cap: int, save_pre: bool = True,
+                  row_pad: int = ROW_PAD, activation: int = _lib.ACT_GELU, clear: Optional[torch.Tensor] = None):
+    """ffn_up on rows x[token_of_row[r]] gathered by the kernel's TMA loads (no permuted copy)."""
+    T, d = x.shape
+    E, F, _ = w1.shape
+    pre = _empty((rows_cap, F), torch.bfloat16, x.device) if save_pre else None
+    h = _empty((rows_cap, F), torch.bfloat16, x.device)
+    call("b200moe_ffn_up_gather", ptr(x), ptr(token_of_row), T, ptr(w1), ptr(b1), ptr(meta), ptr(tile_expert), rows_cap,
+         d, F, E, ptr(pre), ptr(h), activation, row_pad, ptr(clear), stream_ptr())
+    return pre, h
+
+
 def permute_init(x: torch.Tensor, token_of_row: torch.Tensor, meta: torch.Tensor, rows_cap: int, finalize: bool = True,
                  reduce: bool = True):
     """Dispatch + the zero state of the fused combine: (xp, y_acc [T,d] fp32 | None, grid_sync [4] int32 | None)."""
@@ -211,6 +223,33 @@ def ffn_wgrad(a, b, expert_offsets, E: int, out: Optional[torch.Tensor] = None, 
         accumulate = False
     call("b200moe_ffn_wgrad", ptr(a), ptr(b), ptr(expert_offsets), rows_cap, M, N, E, ptr(out), int(accumulate),
          stream_ptr())
+    return out
+
+
+def ffn_wgrad2(a0, b0, a1, b1, expert_offsets, E: int, out0: Optional[torch.Tensor] = None,
+               out1: Optional[torch.Tensor] = None, accumulate: bool = False):
+    """Both weight gradients in one launch: (a0^T b0 [E,M0,N0], a1^T b1 [E,M1,N1]) per expert."""
+    rows_cap, M0 = a0.shape
+    N0, M1, N1 = b0.shape[1], a1.shape[1], b1.shape[1]
+    if out0 is None or out1 is None:
+        out0 = _empty((E, M0, N0), torch.float32, a0.device)
+        out1 = _empty((E, M1, N1), torch.float32, a0.device)
+        accumulate = False
+    call("b200moe_ffn_wgrad2", ptr(a0), ptr(b0), M0, N0, ptr(out0), ptr(a1), ptr(b1), M1, N1, ptr(out1),
+         ptr(expert_offsets), rows_cap, E, int(accumulate), stream_ptr())
+    return out0, out1
+
+
+def ffn_wgrad_gather(a, x, token_of_row, expert_offsets, E: int, out: Optional[torch.Tensor] = None,
+                     accumulate: bool = False):
+    """ffn_wgrad with b = x[token_of_row[r]] gathered by the kernel's TMA loads."""
+    rows_cap, M = a.shape
+    T, N = x.shape
+    if out is None:
+        out = _empty((E, M, N), torch.float32, a.device)
+        accumulate = False
+    call("b200moe_ffn_wgrad_gather", ptr(a), ptr(x), ptr(token_of_row), T, ptr(expert_offsets), rows_cap, M, N, E,
+         ptr(out), int(accumulate), stream_ptr())
     return out
 
 

@@ -332,6 +332,27 @@ __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorM
       :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
       : "memory");
 }
+// Four rows of a 2-D tensor (map with a [1 x box] box) picked by index, laid down as four consecutive 128-byte-swizzled
+// rows: the shared-memory image is that of rows r .. r+3 of a tiled box when dst = box + 128 r (the swizzle is a
+// function of the address), negative or past-the-end rows arrive as zeros and still count towards complete_tx
+// (tools/gather4_probe.cu, measured on sm_100a).
+__device__ __forceinline__ void tma_gather4(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, const int4& rows) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6, "
+      "%7}], [%2];"
+      :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(rows.x),
+         "r"(rows.y), "r"(rows.z), "r"(rows.w)
+      : "memory");
+}
+__device__ __forceinline__ void tma_gather4_pair(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0,
+                                                 const int4& rows) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile::gather4.mbarrier::complete_tx::bytes [%0], [%1, "
+      "{%3, %4, %5, %6, %7}], [%2];"
+      :: "r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0),
+         "r"(rows.x), "r"(rows.y), "r"(rows.z), "r"(rows.w)
+      : "memory");
+}
 // D[tmem of both CTAs] (+)= A[256 rows: 128 per CTA] * B[N: N/2 per CTA]; issued by ONE thread of CTA 0.
 __device__ __forceinline__ void umma_bf16_ss_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
                                                   uint32_t accumulate) {

@@ -70,6 +70,19 @@ struct GemmArgs {
   float* ln_mean_rstd;               // [T,2]
   float ln_eps;
   int ln_res_f32, ln_out_f32;
+  // A-stationary schedule (template ARES): the A tile of a unit (= `nrun` consecutive N tiles of one M tile) is loaded
+  // once and stays in shared memory, only B streams through the ring
+  int nrun;                          // N tiles per unit (divides N / BN); ignored without ARES
+  int nstages;                       // ring depth with ARES (<= K / BK and <= 8)
+  // operand rows fetched through a row map by TMA (tile::gather4) instead of read from a permuted copy:
+  // row mode: row r of A is row gather_idx[r] of the tensor behind tmA; wgrad mode: the same for the k-rows of B.
+  // Negative indices deliver zeros (pad rows).
+  const int32_t* gather_idx;
+  // wgrad mode, second problem of the same launch (both weight gradients of the FFN: their tiles share one persistent
+  // grid, so neither ends on a partly filled wave and the second does not queue behind the first): operands behind
+  // tmA2 / tmB2, output [E,M2,N2] behind tmC1; M2 == 0: one problem
+  int M2, N2;
+  int32_t* zero_i32;                 // one int the kernel clears (the rendezvous counter of the fused combine that follows)
 };
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
@@ -82,6 +95,8 @@ struct SmemCfg {
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = kBLoad * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
+  // (tried in round 2: 4 stages for the BN = 128 tiles, so that their 160 KB footprint leaves room for the kernels of the
+  // other branches beside the persistent CTA -- isolated GEMMs at 3200 tokens 16.7 -> 18.9 us, step time unchanged)
   static constexpr int kStages = (kStageBytes > 32768) ? 4 : 6;
   static constexpr int kOutBytes = 8 * 4096;                               // epilogue staging: 8 x 4 KB or 16 x 2 KB
   static constexpr int kBarBytes = 512;
@@ -92,14 +107,22 @@ struct SmemCfg {
 // HALF of the B tile, CTA 0 issues one M=256 MMA that reads both halves, and each CTA's TMEM receives its own 128
 // output rows: per FLOP the pair pulls 2/3 of the operand bytes through L2 that two independent CTAs would -- the
 // 128 x 256 tiles are L2-bandwidth-bound (ncu: ~14 TB/s of L2->SM traffic at 58-72 % tensor-pipe activity).
-template <int BN, bool A_MN, bool B_MN, int EPI, bool CTA2>
+// ARES (row mode, K = d_model <= 512): A-stationary.  The 128 x 256 tiles of the up-projection and of dgrad-down stream
+// 48 KB per k-block through L2 for 512 tensor-pipe cycles -- 14 KB per clock over the chip against the ~6.3 KB per clock
+// the L2 slices deliver (ncu round 2: 11-12 TB/s of TMA loads at 44 % tensor-pipe activity).  With the A tile resident
+// ([K/64] boxes of 16 KB) and CTA pairs splitting B, a k-block costs 16 KB per CTA: a third of the traffic.
+template <int BN, bool A_MN, bool B_MN, int EPI, bool CTA2, bool ARES = false>
 __global__ void __launch_bounds__(gemm_threads(EPI), 1)
 grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC0, const __grid_constant__ CUtensorMap tmC1,
+                    const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
                     const GemmArgs args) {
   using Cfg = SmemCfg<BN, CTA2>;
   constexpr int kStages = Cfg::kStages;
+  constexpr int kMaxStages = ARES ? 8 : kStages;
+  constexpr int kRingStage = ARES ? Cfg::kBBytes : Cfg::kStageBytes;      // bytes of one ring slot
   constexpr bool kWgrad = (EPI == EPI_WGRAD);
+  static_assert(!ARES || (!kWgrad && !A_MN), "the A-stationary schedule is a row-mode schedule");
   constexpr int kBLoad = Cfg::kBLoad;
   constexpr int kTileM = CTA2 ? 2 * BM : BM;                               // rows of one scheduled tile
   constexpr int kEpiWarps = epi_warps(EPI);
@@ -111,10 +134,13 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  unsigned char* stage_out = smem + kStages * Cfg::kStageBytes;            // per-warp epilogue staging boxes
+  const int nstages = ARES ? args.nstages : kStages;
+  unsigned char* a_res = smem;                                             // ARES: [K / BK] resident A boxes
+  unsigned char* ring = ARES ? smem + (args.K / BK) * Cfg::kABytes : smem;
+  unsigned char* stage_out = ring + nstages * kRingStage;                  // per-warp epilogue staging boxes
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + Cfg::kOutBytes);
-  uint64_t* empty_bar = full_bar + kStages;
-  uint64_t* tfull_bar = empty_bar + kStages;
+  uint64_t* empty_bar = full_bar + kMaxStages;
+  uint64_t* tfull_bar = empty_bar + kMaxStages;
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
   uint64_t* ld_bar = reinterpret_cast<uint64_t*>(tmem_slot + 2);           // EPI_DGRAD_DOWN: one per epilogue warp
@@ -128,9 +154,10 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmC0);
     if (EPI == EPI_UP || EPI == EPI_DGRAD_DOWN) tma_prefetch_desc(&tmC1);
+    if (kWgrad && args.M2 != 0) { tma_prefetch_desc(&tmA2); tma_prefetch_desc(&tmB2); tma_prefetch_desc(&tmC1); }
     if (EPI == EPI_DGRAD_DOWN)
       for (int w = 0; w < kEpiWarps; ++w) mbar_init(&ld_bar[w], 1);
-    for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    for (int s = 0; s < nstages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tfull_bar[a], 1); mbar_init(&tempty_bar[a], (CTA2 ? 2 : 1) * kEpiThreads); }
     fence_mbar_init();
   }
@@ -148,17 +175,31 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // ---- tile schedule (identical in every role) -------------------------------------------------------------
   const int tiles_n = args.N / BN;
   const int tiles_m = kWgrad ? args.M / kTileM : 0;
-  const int total_tiles = kWgrad ? args.E * tiles_m * tiles_n : (args.meta[1] / (kTileM / BM)) * tiles_n;
+  const int tiles_n2 = kWgrad ? args.N2 / BN : 0;                          // second weight gradient of the launch (or 0)
+  const int tiles_m2 = kWgrad ? args.M2 / kTileM : 0;
+  const int total_tiles = kWgrad ? args.E * (tiles_m * tiles_n + tiles_m2 * tiles_n2)
+                                 : (args.meta[1] / (kTileM / BM)) * tiles_n;
   const int worker = CTA2 ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
   const int nworkers = CTA2 ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
+  // a worker takes whole units: `nrun` consecutive tiles (one M tile, a run of N tiles); nrun == 1 without ARES
+  const int nrun = ARES ? args.nrun : 1;
+  const int total_units = total_tiles / nrun;
+#define FOR_EACH_TILE(tile)                                              \
+  for (int unit_ = worker; unit_ < total_units; unit_ += nworkers)        \
+    for (int j_ = 0, tile = unit_ * nrun; j_ < nrun; ++j_, ++tile)
+  if (args.zero_i32 != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *args.zero_i32 = 0;
 
+  int prob = 0;                                     // wgrad mode: which of the launch's two problems the tile belongs to
   auto decode = [&](int tile, int& e, int& m_tile, int& n_tile, int& krow0, int& kblocks) {
     if (kWgrad) {
-      const int per_e = tiles_m * tiles_n;
+      prob = (tiles_m2 != 0 && tile >= args.E * tiles_m * tiles_n) ? 1 : 0;
+      if (prob) tile -= args.E * tiles_m * tiles_n;
+      const int tn = prob ? tiles_n2 : tiles_n;
+      const int per_e = (prob ? tiles_m2 : tiles_m) * tn;
       e = tile / per_e;
       const int r = tile - e * per_e;
-      m_tile = r / tiles_n;
-      n_tile = r - m_tile * tiles_n;
+      m_tile = r / tn;
+      n_tile = r - m_tile * tn;
       if (CTA2) m_tile = 2 * m_tile + static_cast<int>(cta_rank);         // this CTA's 128 rows of the 256-row tile
       const int r0 = args.expert_offsets[e], r1 = args.expert_offsets[e + 1];
       krow0 = r0;
@@ -175,37 +216,79 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   if (warp == 0) {
     // ======================= TMA producer =======================
-    if (lane == 0) {
+    // One elected lane issues the tiled loads.  With a row map (args.gather_idx) the whole warp takes part: a
+    // tile::gather4 load moves four rows, lane l fetches rows 4l .. 4l+3 of a 128-row K-major box, or (wgrad, B read
+    // MN-major) lanes 0-15 / 16-31 fetch the 64 k-rows of alternate 64-column chunks.
+    const bool gather = args.gather_idx != nullptr;
+    if (lane == 0 || gather) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = worker; tile < total_tiles; tile += nworkers) {
-        int e, m_tile, n_tile, krow0, kblocks;
-        decode(tile, e, m_tile, n_tile, krow0, kblocks);
-        for (int kb = 0; kb < kblocks; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
-          unsigned char* sa = smem + stage * Cfg::kStageBytes;
-          unsigned char* sb = sa + Cfg::kABytes;
-          // the bytes of BOTH CTAs land on CTA 0's barrier, armed by CTA 0 alone
-          if (leader) mbar_arrive_expect_tx(&full_bar[stage], (CTA2 ? 2 : 1) * Cfg::kStageBytes);
-          auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
-            if (CTA2) tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
-            else tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
-          };
-          if (A_MN) {
+      auto a_row0 = [&](int unit) {                       // first A row this CTA loads for a unit (row mode)
+        const int m = (unit * nrun) / tiles_n;
+        return (CTA2 ? 2 * m + static_cast<int>(cta_rank) : m) * BM;
+      };
+      int4 gi_next = make_int4(-1, -1, -1, -1);           // row map of the next unit, fetched one unit ahead
+      if (gather && !kWgrad && worker < total_units)
+        gi_next = *reinterpret_cast<const int4*>(args.gather_idx + a_row0(worker) + 4 * lane);
+      for (int unit_ = worker; unit_ < total_units; unit_ += nworkers) {
+        const int4 gi = gi_next;
+        if (gather && !kWgrad && unit_ + nworkers < total_units)
+          gi_next = *reinterpret_cast<const int4*>(args.gather_idx + a_row0(unit_ + nworkers) + 4 * lane);
+        for (int j_ = 0, tile = unit_ * nrun; j_ < nrun; ++j_, ++tile) {
+          int e, m_tile, n_tile, krow0, kblocks;
+          decode(tile, e, m_tile, n_tile, krow0, kblocks);
+          const bool load_a = !ARES || j_ == 0;           // A-stationary: the unit's first tile brings A in
+          int4 bi = make_int4(-1, -1, -1, -1);            // wgrad: row map of the k-block, fetched one k-block ahead
+          if (gather && kWgrad && kblocks > 0)
+            bi = *reinterpret_cast<const int4*>(args.gather_idx + krow0 + 4 * (lane & 15));
+          for (int kb = 0; kb < kblocks; ++kb) {
+            const int4 bi_cur = bi;
+            if (gather && kWgrad && kb + 1 < kblocks)
+              bi = *reinterpret_cast<const int4*>(args.gather_idx + krow0 + (kb + 1) * BK + 4 * (lane & 15));
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            unsigned char* sa = ARES ? a_res + kb * Cfg::kABytes : ring + stage * kRingStage;
+            unsigned char* sb = ARES ? ring + stage * kRingStage : sa + Cfg::kABytes;
+            // the bytes of BOTH CTAs land on CTA 0's barrier, armed by CTA 0 alone
+            if (lane == 0 && leader)
+              mbar_arrive_expect_tx(&full_bar[stage], (CTA2 ? 2 : 1) * ((load_a ? Cfg::kABytes : 0) + Cfg::kBBytes));
+            if (gather) __syncwarp();
+            auto load = [&](void* dst, const CUtensorMap* tm, int c0, int c1) {
+              if (CTA2) tma_load_2d_pair(dst, tm, &full_bar[stage], c0, c1);
+              else tma_load_2d(dst, tm, &full_bar[stage], c0, c1);
+            };
+            auto load4 = [&](void* dst, const CUtensorMap* tm, int c0, const int4& rows) {
+              if (CTA2) tma_gather4_pair(dst, tm, &full_bar[stage], c0, rows);
+              else tma_gather4(dst, tm, &full_bar[stage], c0, rows);
+            };
+            if (load_a) {
+              if (A_MN) {
+                if (lane == 0) {
+                  const CUtensorMap* pA = (kWgrad && prob) ? &tmA2 : &tmA;
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j) load(sa + j * 8192, &tmA, m_tile * BM + j * 64, krow0 + kb * BK);
-          } else {
-            load(sa, &tmA, kb * BK, m_tile * BM);
-          }
-          const int n0 = n_tile * BN + static_cast<int>(cta_rank) * kBLoad;      // this CTA's share of the B tile
-          if (B_MN) {
-            const int krow = kWgrad ? krow0 + kb * BK : e * args.K + kb * BK;
+                  for (int j = 0; j < BM / 64; ++j) load(sa + j * 8192, pA, m_tile * BM + j * 64, krow0 + kb * BK);
+                }
+              } else if (gather) {
+                load4(sa + lane * 512, &tmA, kb * BK, gi);          // rows 4l .. 4l+3 of the box, 128 B each
+              } else if (lane == 0) {
+                load(sa, &tmA, kb * BK, m_tile * BM);
+              }
+            }
+            const int n0 = n_tile * BN + static_cast<int>(cta_rank) * kBLoad;      // this CTA's share of the B tile
+            if (B_MN) {
+              const int krow = kWgrad ? krow0 + kb * BK : e * args.K + kb * BK;
+              if (kWgrad && gather) {
+                for (int j = lane >> 4; j < kBLoad / 64; j += 2)
+                  load4(sb + j * 8192 + (lane & 15) * 512, &tmB, n0 + j * 64, bi_cur);
+              } else if (lane == 0) {
+                const CUtensorMap* pB = (kWgrad && prob) ? &tmB2 : &tmB;
 #pragma unroll
-            for (int j = 0; j < kBLoad / 64; ++j) load(sb + j * 8192, &tmB, n0 + j * 64, krow);
-          } else {
-            load(sb, &tmB, kb * BK, e * args.N + n0);
+                for (int j = 0; j < kBLoad / 64; ++j) load(sb + j * 8192, pB, n0 + j * 64, krow);
+              }
+            } else if (lane == 0) {
+              load(sb, &tmB, kb * BK, e * args.N + n0);
+            }
+            if (++stage == nstages) { stage = 0; phase ^= 1; }
           }
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
@@ -216,7 +299,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = worker; tile < total_tiles; tile += nworkers) {
+      FOR_EACH_TILE(tile) {
         int e, m_tile, n_tile, krow0, kblocks;
         decode(tile, e, m_tile, n_tile, krow0, kblocks);
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
@@ -225,8 +308,8 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-          const uint32_t sb = sa + Cfg::kABytes;
+          const uint32_t sa = smem_u32(ARES ? a_res + kb * Cfg::kABytes : ring + stage * kRingStage);
+          const uint32_t sb = ARES ? smem_u32(ring + stage * kRingStage) : sa + Cfg::kABytes;
           const uint64_t da = A_MN ? make_smem_desc(sa, 8192, 1024) : make_smem_desc(sa, 16, 1024);
           const uint64_t db = B_MN ? make_smem_desc(sb, 8192, 1024) : make_smem_desc(sb, 16, 1024);
 #pragma unroll
@@ -239,7 +322,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           // frees the smem slot (of both CTAs) once these MMAs have read it
           if (CTA2) umma_commit_pair(&empty_bar[stage]);
           else umma_commit(&empty_bar[stage]);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          if (++stage == nstages) { stage = 0; phase ^= 1; }
         }
         if (kblocks > 0) {                               // accumulator complete (in both CTAs' TMEM)
           if (CTA2) umma_commit_pair(&tfull_bar[acc]);
@@ -264,7 +347,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int acc = 0;
     uint32_t acc_phase = 0;
     uint32_t ld_phase = 0;
-    for (int tile = worker; tile < total_tiles; tile += nworkers) {
+    FOR_EACH_TILE(tile) {
       int e, m_tile, n_tile, krow0, kblocks;
       decode(tile, e, m_tile, n_tile, krow0, kblocks);
       const int row0 = m_tile * BM + quarter * 32;                 // first of this warp's 32 output rows
@@ -326,9 +409,10 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0) {
-            const int grow0 = e * args.M + row0;
-            if (args.accumulate) tma_reduce_add_2d(&tmC0, stg, col0, grow0);
-            else tma_store_2d(&tmC0, stg, col0, grow0);
+            const int grow0 = e * (prob ? args.M2 : args.M) + row0;
+            const CUtensorMap* pC = prob ? &tmC1 : &tmC0;
+            if (args.accumulate) tma_reduce_add_2d(pC, stg, col0, grow0);
+            else tma_store_2d(pC, stg, col0, grow0);
             tma_store_commit();
           }
         } else {
@@ -412,16 +496,17 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                          combine_term(gate, v8[7]));
             }
           }
+          unsigned char* stg0 = stg;
           if (!kCombine || args.out0 != nullptr) {
           if (lane == 0) tma_store_wait_read0();
           __syncwarp();
 #pragma unroll
-          for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(stg + lane * 64 + ((j ^ swz) << 4)) = pk[j];
+          for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(stg0 + lane * 64 + ((j ^ swz) << 4)) = pk[j];
           fence_proxy_async_smem();
           __syncwarp();
           }
           if (lane == 0 && (!kCombine || args.out0 != nullptr)) {
-            tma_store_2d(&tmC0, stg, col0, row0);
+            tma_store_2d(&tmC0, stg0, col0, row0);
             tma_store_commit();
             if (EPI == EPI_DGRAD_DOWN && cc + 1 < kChunksPerWarp) {   // next pre-activation box, once the store has read this one
               tma_store_wait_read0();
@@ -490,6 +575,7 @@ grouped_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 }
 
+#undef FOR_EACH_TILE
 }  // namespace b200moe
 
 #include "gemm_host.inc"

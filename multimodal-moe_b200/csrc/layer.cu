@@ -74,7 +74,11 @@ static ForkState* fork_state() {
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
   ForkState& f = g_fork[dev];
   if (!f.ok) {
-    if (cudaStreamCreateWithFlags(&f.s1, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    // the router branch ends the pass at the small problem sizes (three short dependent kernels): its blocks go first
+    // whenever an SM frees up
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    if (cudaStreamCreateWithPriority(&f.s1, cudaStreamNonBlocking, hi) != cudaSuccess) return nullptr;
     if (cudaStreamCreateWithFlags(&f.s2, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     if (cudaStreamCreateWithFlags(&f.s3, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     for (auto& e : f.ev)
@@ -100,6 +104,10 @@ static inline bool fused_combine(const b200moe_layer_desc* q) {
 static inline bool reduce_combine(const b200moe_layer_desc* q) {
   return fused_combine(q) && (q->flags & B200MOE_LAYER_COMBINE_REDUCE) && q->k <= 2;
 }
+// dispatch gather inside the GEMM operand loads (no permuted copy of x): opt-in, measured slower (include/b200moe.h)
+static inline bool gather_dispatch(const b200moe_layer_desc* q) {
+  return (q->flags & B200MOE_LAYER_GATHER_DISPATCH) && !reduce_combine(q);
+}
 
 static int check_desc(const b200moe_layer_desc* q, const char* what) {
   B200MOE_REQUIRE(q != nullptr, B200MOE_EINVAL, "%s: NULL descriptor", what);
@@ -111,7 +119,8 @@ static int check_desc(const b200moe_layer_desc* q, const char* what) {
   B200MOE_REQUIRE(q->capacity >= 0, B200MOE_EINVAL, "%s: negative capacity", what);
   B200MOE_REQUIRE(q->activation == B200MOE_ACT_GELU || q->activation == B200MOE_ACT_RELU, B200MOE_EINVAL,
                   "%s: activation=%d must be B200MOE_ACT_GELU or B200MOE_ACT_RELU", what, q->activation);
-  B200MOE_REQUIRE((q->flags & ~(B200MOE_LAYER_SEPARATE_COMBINE | B200MOE_LAYER_COMBINE_REDUCE | B200MOE_LAYER_COMBINE_TAIL)) == 0,
+  B200MOE_REQUIRE((q->flags & ~(B200MOE_LAYER_SEPARATE_COMBINE | B200MOE_LAYER_COMBINE_REDUCE | B200MOE_LAYER_COMBINE_TAIL |
+                                 B200MOE_LAYER_GATHER_DISPATCH)) == 0,
                   B200MOE_EINVAL,
                   "%s: unknown flags 0x%x", what, q->flags);
   B200MOE_REQUIRE(q->rows_cap > 0 && q->rows_cap % kRowPad == 0 &&
@@ -270,7 +279,7 @@ extern "C" int64_t b200moe_layer_ws_layout(const b200moe_layer_desc* q, int64_t*
   bytes[B200MOE_WS_ROW_OF_ASSIGNMENT] = T * k * 4;
   bytes[B200MOE_WS_TOKEN_OF_ROW] = R * 4;
   bytes[B200MOE_WS_GATE_OF_ROW] = R * 4;
-  bytes[B200MOE_WS_XP] = R * d * 2;
+  bytes[B200MOE_WS_XP] = gather_dispatch(q) ? 0 : R * d * 2;
   bytes[B200MOE_WS_PRE] = R * F * 2;
   bytes[B200MOE_WS_H] = R * F * 2;
   bytes[B200MOE_WS_YO] = R * d * 2;
@@ -347,7 +356,11 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                     WS(int32_t, B200MOE_WS_SLOT_LIMIT), WS(int32_t, B200MOE_WS_ROW_OF_ASSIGNMENT),
                     WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), WS(float, B200MOE_WS_GATE_OF_ROW), stream));
   const bool fused = fused_combine(q);
-  if (fused) {
+  const bool gather = gather_dispatch(q);
+  if (gather) {
+    // no dispatch kernel: the up-projection gathers its A rows through token_of_row by TMA (and clears the rendezvous
+    // counter of the fused combine on its way)
+  } else if (fused) {
     // the dispatch kernel also zeroes the rendezvous counter (and the fp32 accumulator of the reduction mode) of the
     // fused combine: no memset launch
     STEP("permute", b200moe_permute_init(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), meta, R, d, WS(void, B200MOE_WS_XP),
@@ -362,9 +375,16 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
     if (weights_ready)
       cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), static_cast<cudaEvent_t>(weights_ready), 0);
     PdlOffIf np_(weights_ready != nullptr);
-    STEP("ffn_up", b200moe_ffn_up(WS(void, B200MOE_WS_XP), w1, b1, meta, tile_expert, R, d, F, E,
-                                  save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H),
-                                  q->activation, pad, stream));
+    if (gather) {
+      STEP("ffn_up", b200moe_ffn_up_gather(x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), T, w1, b1, meta, tile_expert, R, d,
+                                           F, E, save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr,
+                                           WS(void, B200MOE_WS_H), q->activation, pad,
+                                           fused ? WS(int32_t, B200MOE_WS_GRID_SYNC) : nullptr, stream));
+    } else {
+      STEP("ffn_up", b200moe_ffn_up(WS(void, B200MOE_WS_XP), w1, b1, meta, tile_expert, R, d, F, E,
+                                    save_for_backward ? WS(void, B200MOE_WS_PRE) : nullptr, WS(void, B200MOE_WS_H),
+                                    q->activation, pad, stream));
+    }
   }
   if (fused) {
     // y -- or, with the fused post-norm, LayerNorm(residual + y) -- leaves the kernel's own tail: the forward ends here.
@@ -481,14 +501,27 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
       STEP("colsum", b200moe_colsum(dhpre, F, db1, nullptr, 0, nullptr, offs, E, 0, s3));
     }
   }
-  if (dw2) {
+  if (dw2 && dw1 && !gather_dispatch(q)) {
+    // both weight gradients in one persistent grid, once dgrad_down has written dhpre
+    if (fk) cudaStreamWaitEvent(fk->s2, fk->ev[1], 0);
     PdlOffIf np_(fk != nullptr);
-    STEP("ffn_wgrad", b200moe_ffn_wgrad(dyp, WS(void, B200MOE_WS_H), offs, R, d, F, E, dw2, 0, s2));
-  }
-  if (fk) cudaStreamWaitEvent(fk->s2, fk->ev[1], 0);
-  if (dw1) {
-    PdlOffIf np_(fk != nullptr);
-    STEP("ffn_wgrad", b200moe_ffn_wgrad(dhpre, WS(void, B200MOE_WS_XP), offs, R, F, d, E, dw1, 0, s2));
+    STEP("ffn_wgrad", b200moe_ffn_wgrad2(dyp, WS(void, B200MOE_WS_H), d, F, dw2, dhpre, WS(void, B200MOE_WS_XP), F, d, dw1,
+                                         offs, R, E, 0, s2));
+  } else {
+    if (dw2) {
+      PdlOffIf np_(fk != nullptr);
+      STEP("ffn_wgrad", b200moe_ffn_wgrad(dyp, WS(void, B200MOE_WS_H), offs, R, d, F, E, dw2, 0, s2));
+    }
+    if (fk) cudaStreamWaitEvent(fk->s2, fk->ev[1], 0);
+    if (dw1) {
+      PdlOffIf np_(fk != nullptr);
+      if (gather_dispatch(q)) {
+        STEP("ffn_wgrad", b200moe_ffn_wgrad_gather(dhpre, x, WS(int32_t, B200MOE_WS_TOKEN_OF_ROW), T, offs, R, F, d, E,
+                                                   dw1, 0, s2));
+      } else {
+        STEP("ffn_wgrad", b200moe_ffn_wgrad(dhpre, WS(void, B200MOE_WS_XP), offs, R, F, d, E, dw1, 0, s2));
+      }
+    }
   }
   if (dx) {
     void* dxp = BWS(void, B200MOE_BWS_DXP);

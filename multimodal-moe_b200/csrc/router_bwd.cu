@@ -13,8 +13,11 @@
 
 namespace b200moe {
 
-// one warp per token (router_grad.cuh)
-__global__ void __launch_bounds__(256)
+// one warp per token (router_grad.cuh).  128-thread blocks and no shared memory: at the small problem sizes this kernel
+// runs on a side stream next to dgrad_down, whose persistent CTAs (576 threads x 96 registers, ~all of the shared memory)
+// leave ~9 K registers per SM -- a 128-thread block fits beside them, a 256-thread block waited for an SM (round 2
+// timeline at 3200 tokens: launched at 61 us, started at 71 us).
+__global__ void __launch_bounds__(128)
 router_dlogits_kernel(const float* __restrict__ logits, const int32_t* __restrict__ topk_idx,
                       const int32_t* __restrict__ row_of_assignment, const float* __restrict__ dgate_row,
                       const int32_t* __restrict__ tokens_per_expert, const float* __restrict__ d_aux, int T, int E,
@@ -22,7 +25,7 @@ router_dlogits_kernel(const float* __restrict__ logits, const int32_t* __restric
   pdl_sync();
   const float da = d_aux ? *d_aux : 0.f;
   const int lane = threadIdx.x & 31;
-  for (int t = blockIdx.x * 8 + (threadIdx.x >> 5); t < T; t += gridDim.x * 8)
+  for (int t = blockIdx.x * 4 + (threadIdx.x >> 5); t < T; t += gridDim.x * 4)
     dlogits_token_warp(logits, topk_idx, row_of_assignment, dgate_row, false, tokens_per_expert, da * aux_w, da * z_w, t, T,
                        E, k, normalize, lane, dlogits);
 }
@@ -174,9 +177,9 @@ extern "C" int b200moe_router_bwd_dlogits(const float* logits, const int32_t* to
   if (T == 0) return B200MOE_OK;
   if (int rc = b200moe_check_device()) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  int grid = (T + 7) / 8;
-  if (grid > 16 * num_sms()) grid = 16 * num_sms();
-  launch_k(router_dlogits_kernel, grid, 256, 0, st, logits, topk_idx, row_of_assignment, dgate_row, tokens_per_expert,
+  int grid = (T + 3) / 4;
+  if (grid > 32 * num_sms()) grid = 32 * num_sms();
+  launch_k(router_dlogits_kernel, grid, 128, 0, st, logits, topk_idx, row_of_assignment, dgate_row, tokens_per_expert,
            d_aux, T, E, k, normalize_topk, aux_loss_weight, z_loss_weight, dlogits);
   return check_launch("router_dlogits");
 }

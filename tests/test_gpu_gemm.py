@@ -48,6 +48,8 @@ CASES = [
     (4, 512, 1024, [6000, 5000, 0, 8100], 256),                    # CTA-pair layout: every GEMM on cta_group::2 tiles
     (2, 1024, 4096, [3000, 2500], 256),                            # CTA pairs for up / dgrad_down only
     (8, 1024, 2048, [300, 200, 0, 129, 520, 64, 1, 700], 128),     # weight-gradient GEMMs on CTA pairs (ragged K, empty expert)
+    (8, 256, 1024, [3000, 2900, 0, 3100, 2500, 1, 3300, 2800], 256),  # A-stationary pairs at d_model = 256 (4 k-blocks resident)
+    (16, 512, 2048, [1500] * 15 + [700], 256),                     # A-stationary pairs at d_model = 512, run of 2 N tiles
 ]
 
 
@@ -98,6 +100,8 @@ def test_ffn_backward_stages(ops, E, d, F, rows, pad):
     dxp = ops.ffn_dgrad_up(dhpre, w1.to(dev), md, ted, row_pad=pad)
     dw2 = ops.ffn_wgrad(dyp.to(dev), h.to(dev), od, E)
     dw1 = ops.ffn_wgrad(dhpre, xp.to(dev), od, E)
+    dw2m, dw1m = ops.ffn_wgrad2(dyp.to(dev), h.to(dev), dhpre, xp.to(dev), od, E)    # both in one launch: bit-identical
+    assert torch.equal(dw2m, dw2) and torch.equal(dw1m, dw1)
     db2 = ops.colsum(dyp.to(dev), od, E)
     db1 = ops.colsum(dhpre, od, E)
     torch.cuda.synchronize()
@@ -119,6 +123,39 @@ def test_ffn_backward_stages(ops, E, d, F, rows, pad):
         assert _rel(dw1[e].cpu(), dw1_ref) < 1e-4, f"dw1 expert {e}"
         assert torch.allclose(db2[e].cpu(), dyp[sl].float().sum(0), atol=1e-2, rtol=1e-3)
         assert torch.allclose(db1[e].cpu(), dhpre_c[sl].float().sum(0), atol=1e-2, rtol=1e-3)
+
+
+@pytest.mark.parametrize("E,d,F,rows,pad", CASES)
+def test_gathered_operands_equal_permuted_copy(ops, E, d, F, rows, pad):
+    """The dispatch gather fused into the TMA operand loads (tile::gather4 through token_of_row; pads = -1 -> zeros):
+    the up-projection and the weight gradient of w1 must be bit-identical to the same GEMMs on the permuted copy."""
+    g = torch.Generator().manual_seed(E * 77 + d)
+    offs, meta, te, valid, rexp, R, rows_cap = _layout(E, rows, pad)
+    dev = "cuda"
+    T = max(int(valid.sum()) // 2, 8)                                # every token is used about twice (top-2)
+    x = torch.randn(T, d, generator=g).to(torch.bfloat16)
+    tok = torch.full((rows_cap,), -1, dtype=torch.int32)
+    tok[valid] = torch.randint(0, T, (int(valid.sum()),), generator=g, dtype=torch.int32)
+    xp = torch.zeros(rows_cap, d, dtype=torch.bfloat16)
+    xp[valid] = x[tok[valid].long()]
+    w1 = (torch.randn(E, F, d, generator=g) * d ** -0.5).to(torch.bfloat16).to(dev)
+    b1 = (torch.randn(E, F, generator=g) * 0.1).to(dev)
+    md, ted, od = meta.to(dev), te.to(dev), offs.to(dev)
+    # NaN poison in the freed blocks the outputs will reuse: rows the kernel must not leave unwritten show up
+    junk = torch.full((rows_cap * F,), float("nan"), dtype=torch.bfloat16, device=dev)
+    del junk
+    pre0, h0 = ops.ffn_up(xp.to(dev), w1, b1, md, ted, row_pad=pad)
+    clear = torch.full((4,), 7, dtype=torch.int32, device=dev)
+    pre1, h1 = ops.ffn_up_gather(x.to(dev), tok.to(dev), w1, b1, md, ted, rows_cap, row_pad=pad, clear=clear)
+    torch.cuda.synchronize()
+    assert torch.equal(pre0[:R], pre1[:R]) and torch.equal(h0[:R], h1[:R])
+    assert clear.tolist() == [0, 7, 7, 7]
+    dh = torch.randn(rows_cap, F, generator=g).to(torch.bfloat16)
+    dh[~valid] = 0
+    dw_ref = ops.ffn_wgrad(dh.to(dev), xp.to(dev), od, E)
+    dw = ops.ffn_wgrad_gather(dh.to(dev), x.to(dev), tok.to(dev), od, E)
+    torch.cuda.synchronize()
+    assert torch.equal(dw, dw_ref)
 
 
 def test_wgrad_accumulate(ops):

@@ -92,20 +92,23 @@ def test_layer_matches_oracle(B, HW, d, F, E, k, cf, ctx, combine):
 
 @pytest.mark.parametrize("B,HW,d,F,E,k,cf", [(8, 400, 256, 1024, 8, 2, 1.25), (3, 333, 512, 1024, 16, 2, 0.5),
                                              (2, 333, 128, 256, 4, 1, 0.5), (1, 200, 1024, 2048, 64, 2, 2.0),
-                                             (40, 400, 256, 1024, 8, 2, 1.25)])
+                                             (40, 400, 256, 1024, 8, 2, 1.25),
+                                             (72, 900, 256, 1024, 8, 2, 1.25)])   # 256-row segments: A-stationary pairs
 def test_fused_combine_equals_separate_kernels(B, HW, d, F, E, k, cf):
     """The combine inside the down-projection kernel -- its tail after the grid-wide rendezvous ("tail", gather from the
     rows just stored) and its epilogue ("epilogue": fp32 reductions in tile order) -- against b200moe_ffn_down +
     b200moe_combine (slot order): bit-identical outputs and gradients, with drops (tokens that lose every assignment
-    must come out as exact zeros), in training and in inference."""
+    must come out as exact zeros), in training and in inference.  The same for the dispatch: rows gathered by the GEMMs'
+    own TMA loads ("gather": no permuted copy) against b200moe_permute + the plain GEMMs ("permute")."""
     _, m = _pair(d, F, E, k, cf, ctx=True, seed=3 * B + HW)
     g = torch.Generator().manual_seed(99)
     x = torch.randn(B, HW, d, generator=g).to(torch.bfloat16).cuda()
     go = torch.randn(B, HW, d, generator=g).cuda()
     c = torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1).cuda()
     outs = []
-    for mode in ("tail", "separate", "epilogue", "tail"):
-        m.combine = mode
+    for mode, dispatch in (("tail", "gather"), ("separate", "permute"), ("epilogue", "gather"), ("tail", "permute"),
+                           ("separate", "gather")):
+        m.combine, m.dispatch = mode, dispatch
         # poison the allocator's free blocks: the workspaces of this pass reuse them, so a kernel that read a row before
         # its producer wrote it (the rendezvous of the fused modes) would see NaN, not the previous mode's identical values
         junk = torch.full((96 << 20,), float("nan"), device="cuda")

@@ -20,6 +20,8 @@ b1 = torch.zeros(E, F, device="cuda")
 b2 = torch.zeros(E, d, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 pad = 256 if n % 256 == 0 else 128
+ACT = int(os.environ.get("GEMM_BENCH_ACT", "0"))           # 0 gelu, 1 relu (cheap epilogue: tells feed-bound from epilogue-bound)
+print("env:", {k: v for k, v in os.environ.items() if k.startswith(("B200MOE_GEMM", "GEMM_BENCH"))}, flush=True)
 
 
 def timed(name, fn, flops, nbytes):
@@ -37,10 +39,10 @@ def timed(name, fn, flops, nbytes):
 
 
 fl = 2.0 * R * d * F
-pre, h = ops.ffn_up(xp, w1, b1, meta, te, save_pre=True, row_pad=pad)
-timed("up (pre + h)", lambda: ops.ffn_up(xp, w1, b1, meta, te, save_pre=True, row_pad=pad), fl, R * d * 2 + 2 * R * F * 2)
-timed("up (h only)", lambda: ops.ffn_up(xp, w1, b1, meta, te, save_pre=False, row_pad=pad), fl, R * d * 2 + R * F * 2)
+pre, h = ops.ffn_up(xp, w1, b1, meta, te, save_pre=True, row_pad=pad, activation=ACT)
+timed("up (pre + h)", lambda: ops.ffn_up(xp, w1, b1, meta, te, save_pre=True, row_pad=pad, activation=ACT), fl, R * d * 2 + 2 * R * F * 2)
+timed("up (h only)", lambda: ops.ffn_up(xp, w1, b1, meta, te, save_pre=False, row_pad=pad, activation=ACT), fl, R * d * 2 + R * F * 2)
 timed("down", lambda: ops.ffn_down(h, w2, b2, meta, te, row_pad=pad), fl, R * F * 2 + R * d * 2)
 dyp = xp
-timed("dgrad_down", lambda: ops.ffn_dgrad_down(dyp, w2, pre, meta, te, row_pad=pad), fl, R * d * 2 + 2 * R * F * 2)
+timed("dgrad_down", lambda: ops.ffn_dgrad_down(dyp, w2, pre, meta, te, row_pad=pad, activation=ACT), fl, R * d * 2 + 2 * R * F * 2)
 timed("dgrad_up", lambda: ops.ffn_dgrad_up(h, w1, meta, te, row_pad=pad), fl, R * F * 2 + R * d * 2)
