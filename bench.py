@@ -263,7 +263,8 @@ def run_dense_anchor(steps, warmup, w):
 # ---------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------
-GEMM_CALLS = ("ffn_up", "ffn_down", "ffn_dgrad_down", "ffn_dgrad_up", "ffn_wgrad")
+GEMM_CALLS = ("ffn_up", "ffn_up_gather", "ffn_down", "ffn_dgrad_down", "ffn_dgrad_up", "ffn_wgrad", "ffn_wgrad2",
+              "ffn_wgrad_gather")
 NVLINK_CALLS = ("ep_p2p_dispatch", "ep_p2p_combine", "ep_p2p_combine_bwd", "ep_p2p_pull_rows")
 
 
@@ -773,7 +774,7 @@ def main():
         peak = pk["tf_burst"] if ms_per_step < 1.0 else pk["tf_sust"]
         key = f"{wl_name}{res['T']}" + (f"_ep{world}" if dist_on else "")
         tr = ncu_traffic(key)
-        line["roofline"] = {"bound": "tensor", "kernel": "grouped_gemm_kernel (6 launches: up, down, 2 dgrad, 2 wgrad)",
+        line["roofline"] = {"bound": "tensor", "kernel": "grouped_gemm_kernel (up, down, dgrad_down, dgrad_up, both weight gradients in one launch)",
                             "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                             "peak_source": pk["src"] + (" burst" if ms_per_step < 1.0 else " sustained"),
                             "flops_per_step": fl, "gemm_ms_per_step": res["gemm_ms"],

@@ -393,12 +393,23 @@ int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* desc, int64_t* off
  * save_for_backward == 0 skips the pre-activation store. */
 /* The context enters either as ctx_bias [B,E] (computed by the caller: b200moe_ctx_bias_fwd) or as ctx (evaluated
  * inside the router kernel; both NULL: no context). */
+/* Preparation of the bf16 expert operands overlapped with the first kernels of the pass (which need only the gate
+ * split): the fp32 -> bf16 casts of b200moe_prepare_weights, launched by b200moe_layer_fwd itself on `side_stream`
+ * AFTER its router kernel -- a cast launched first fills every thread slot of every SM and the router then waits for
+ * the cast's last wave (round 2: 204 us at 32 experts of d=1024, F=4096) -- and joined just before the up-projection.
+ * w1_f32 / w2_f32 may be NULL individually (that operand is already bf16).  Alternatively `ready` alone: a cudaEvent_t
+ * the caller recorded after preparing w1 / w2 on a stream of its own. */
+typedef struct b200moe_weight_prep {
+  const float* w1_f32; int64_t n1;   /* element counts, multiples of 8; results go to the w1 / w2 passed to the call */
+  const float* w2_f32; int64_t n2;
+  void* side_stream;                 /* cudaStream_t, not the call's stream */
+  void* ready;                       /* cudaEvent_t or NULL */
+} b200moe_weight_prep;
 int b200moe_layer_fwd(const b200moe_layer_desc* desc, const void* x, const float* ctx_bias,
                       const b200moe_ctx_desc* ctx, const void* wg_split,
                       const void* w1, const float* b1, const void* w2, const float* b2, void* ws, void* y,
                       int save_for_backward, const b200moe_postnorm* postnorm /* or NULL */,
-                      void* weights_ready /* cudaEvent_t recorded after w1 / w2 were prepared on another stream, or NULL:
-                                             waited for just before the up-projection */,
+                      const b200moe_weight_prep* prep /* or NULL: w1 / w2 are ready */,
                       void* stream);
 /* Mirror of the forward incl. the A.12 router gradient.  dy [T,d] bf16; d_aux: device scalar (gradient of the
  * weighted auxiliary loss) or NULL.  Any of the gradient outputs may be NULL (not computed):

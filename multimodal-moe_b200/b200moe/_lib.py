@@ -110,6 +110,12 @@ class LayerDesc(C.Structure):
                 ("activation", C.c_int32), ("flags", C.c_int32)]
 
 
+class WeightPrep(C.Structure):
+    """b200moe_weight_prep (include/b200moe.h)."""
+    _fields_ = [("w1_f32", C.c_void_p), ("n1", C.c_int64), ("w2_f32", C.c_void_p), ("n2", C.c_int64),
+                ("side_stream", C.c_void_p), ("ready", C.c_void_p)]
+
+
 ACT_GELU, ACT_RELU = 0, 1                 # B200MOE_ACT_*
 ACTIVATIONS = {"gelu": ACT_GELU, "relu": ACT_RELU}
 LAYER_SEPARATE_COMBINE = 1                # B200MOE_LAYER_SEPARATE_COMBINE

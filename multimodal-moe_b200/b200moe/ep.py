@@ -147,7 +147,11 @@ class _EPFunction(torch.autograd.Function):
         st = _lib.stream_ptr()
         i32 = torch.int32
 
+        if w_ready is not None:
+            w_ready.fork()
         r = ops.router_fwd(x2, None, cb, tokens_per_image, k, mod.normalize_topk, wg_split=wsplit, E=E)
+        if w_ready is not None:
+            w_ready.launch()    # after the router: a cast launched first would hold every SM's thread slots
         # histograms of every rank (+ token counts): one kernel, one small all-gather, one kernel for the global
         # routing tables; only the kept counts travel to the host (the one sync of the pass: all-to-all split sizes)
         C, ELc, order_dev, seg_dev = _ep_static(mod, dev, E, W)
@@ -198,7 +202,7 @@ class _EPFunction(torch.autograd.Function):
         # grouped GEMMs per group as its rows arrive; results go home on the communication stream
         ys = torch.empty((max(n_send, 1), d), dtype=torch.bfloat16, device=dev)
         if w_ready is not None:
-            comp.wait_event(w_ready)
+            w_ready.join()
         for c, ch in enumerate(chunks):
             comp.wait_event(arrived[c])
             xr = ch.xp

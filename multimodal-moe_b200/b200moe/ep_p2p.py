@@ -30,10 +30,11 @@ from . import _lib, ops
 _BIG = 1 << 30
 
 
-def _side_stream(mod, dev) -> torch.cuda.Stream:
-    s = mod.__dict__.get("_p2p_side")
+def _side_stream(mod, dev, which: int = 0) -> torch.cuda.Stream:
+    key = "_p2p_side" if which == 0 else f"_p2p_side{which}"
+    s = mod.__dict__.get(key)
     if s is None or s.device != dev:
-        s = mod.__dict__["_p2p_side"] = torch.cuda.Stream(device=dev)
+        s = mod.__dict__[key] = torch.cuda.Stream(device=dev)
     return s
 
 
@@ -161,7 +162,11 @@ class _P2PFunction(torch.autograd.Function):
         st = _lib.stream_ptr()
         i32 = torch.int32
 
+        if ready is not None:
+            ready.fork()
         r = ops.router_fwd(x2, None, cb, tokens_per_image, k, mod.normalize_topk, wg_split=wsplit, E=E)
+        if ready is not None:
+            ready.launch()      # after the router: a cast launched first would hold every SM's thread slots
         mine = torch.empty((k * E + 1,), dtype=i32, device=dev)
         _lib.call("b200moe_ep_hist", r.block_counts.data_ptr(), r.block_counts.shape[0], k, E, T, mine.data_ptr(), st)
         allh = torch.empty((W, k * E + 1), dtype=i32, device=dev)
@@ -195,7 +200,7 @@ class _P2PFunction(torch.autograd.Function):
                   dest_of_row.data_ptr(), st)
         ar.barrier(0)                                   # every rank's rows have landed in xp
         if ready is not None:
-            torch.cuda.current_stream(dev).wait_event(ready)
+            ready.join()
         pre, h = ops.ffn_up(ar.xp, w1b, b1f, meta, tile_e, save_pre=need_grad, row_pad=ar.row_pad,
                             activation=_lib.ACTIVATIONS[mod.activation])
         ops.ffn_down(h, w2b, b2f, meta, tile_e, row_pad=ar.row_pad, out=ar.yo)
@@ -238,27 +243,33 @@ class _P2PFunction(torch.autograd.Function):
         _lib.call("b200moe_ep_p2p_combine_bwd", dy.data_ptr(), ar.peers.data_ptr(), ar.off[1], ar.off[2], R,
                   dest_of_row.data_ptr(), p.token_of_row.data_ptr(), p.gate_of_row.data_ptr(), p.meta.data_ptr(),
                   send_cap, d, dgate_row.data_ptr(), st)
-        # the router gradients need nothing from the other ranks: they run while the slowest rank's rows arrive
+        # dlogits feeds unpermute_bwd at the end of the dx chain; the parameter gradients of the router (the gate's weight
+        # gradient is 2 T E d fp32 FMAs on CUDA cores: 106 us at workload D) wait for the tail of the pass, where they run
+        # next to the bandwidth-bound bias sums and unpermute_bwd instead of in front of the barrier (round-2 timeline)
         dlogits = ops.router_bwd_dlogits(r.logits, r.topk_idx, p.row_of_assignment, dgate_row, p.tokens_per_expert,
                                          d_aux_t, mod.normalize_topk, mod.aux_loss_weight, mod.z_loss_weight)
-        dwg, dctx = ops.router_bwd_params(dlogits, x2, ctx.tpi, want_dwg=need[2],
-                                          want_dctx=bool(ctx.has_ctx and need[1]))
         ar.barrier(2)                                   # every rank's dyp rows have landed
         dhpre = ops.ffn_dgrad_down(ar.dyp, w2b, pre, meta, tile_e, row_pad=ar.row_pad,
                                    activation=_lib.ACTIVATIONS[mod.activation])
         comp = torch.cuda.current_stream()
+        overlap = not _lib.PROFILING                    # per-kernel timing wants kernels running alone
+        side = _side_stream(mod, dev) if overlap else comp          # rows home, then the bias sums
+        side2 = _side_stream(mod, dev, 1) if overlap else comp      # router parameter gradients
         dxs = None
         if need[0]:
             ops.ffn_dgrad_up(dhpre, w1b, meta, tile_e, row_pad=ar.row_pad, out=ar.dxp)
             ar.barrier(3)                               # every rank's dxp is complete
+        side.wait_stream(comp)
+        pulled = None
+        if need[0]:
             # the rows come home on a side stream (a plain copy kernel: no shared memory, so it runs on the SMs next to
             # the persistent weight-gradient CTAs) while the tensor-bound kernels below keep the main stream busy
-            side = _side_stream(mod, dev)
-            side.wait_stream(comp)
             dxs = torch.empty((send_cap, d), dtype=torch.bfloat16, device=dev)
             with torch.cuda.stream(side):
                 _lib.call("b200moe_ep_p2p_pull_rows", ar.peers.data_ptr(), ar.off[3], R, dest_of_row.data_ptr(),
                           p.meta.data_ptr(), send_cap, d, dxs.data_ptr(), side.cuda_stream)
+                pulled = torch.cuda.Event()
+                pulled.record(side)
         dw1 = torch.empty((EL, F, d), dtype=f32, device=dev) if need[3] else None
         db1 = torch.empty((EL, F), dtype=f32, device=dev) if need[4] else None
         dw2 = torch.empty((EL, d, F), dtype=f32, device=dev) if need[5] else None
@@ -270,10 +281,7 @@ class _P2PFunction(torch.autograd.Function):
         elif need[3]:
             ops.ffn_wgrad(dhpre, ar.xp, offs, EL, out=dw1)
         if need[4] or need[6]:
-            # bias gradients: a bandwidth-bound column sum, on the side stream next to the tensor-bound weight gradients
-            side = _side_stream(mod, dev)
-            if dxs is None:
-                side.wait_stream(comp)
+            # bias gradients: a bandwidth-bound column sum behind the returning rows on the side stream
             with torch.cuda.stream(side):
                 if need[6] and need[4]:
                     ops.colsum(ar.dyp, offs, EL, out=db2, a1=dhpre, out1=db1)
@@ -281,11 +289,20 @@ class _P2PFunction(torch.autograd.Function):
                     ops.colsum(ar.dyp, offs, EL, out=db2)
                 else:
                     ops.colsum(dhpre, offs, EL, out=db1)
+        dwg = dctx = None
+        if need[2] or (ctx.has_ctx and need[1]):
+            side2.wait_stream(comp)                     # behind the weight gradients: the tail of the pass
+            with torch.cuda.stream(side2):
+                dwg, dctx = ops.router_bwd_params(dlogits, x2, ctx.tpi, want_dwg=need[2],
+                                                  want_dctx=bool(ctx.has_ctx and need[1]))
         dx = None
-        if need[0] or need[4] or need[6]:
-            comp.wait_stream(side)
         if need[0]:
+            if pulled is not None and overlap:
+                comp.wait_event(pulled)                 # only the rows: the bias sums keep running beside unpermute_bwd
             dx = ops.unpermute_bwd(dxs, p.row_of_assignment, dlogits, wgf, T, k, d)
+        if overlap:
+            comp.wait_stream(side)
+            comp.wait_stream(side2)
         ar.pending = False
         t_w1, t_b1, t_w2, t_b2, t_wg = ctx.dtypes
 

@@ -39,6 +39,34 @@ def _f32c(t: torch.Tensor) -> torch.Tensor:
     return t if t.is_contiguous() else t.contiguous()
 
 
+class _CastJob:
+    """The fp32 -> bf16 casts of the expert slabs, deferred so that they can be launched after the router kernel:
+    `struct()` for b200moe_layer_fwd (which launches them itself), `fork()` / `launch()` / `join()` for the
+    expert-parallel passes that drive the kernels from Python."""
+
+    def __init__(self, mod, a1, a2, side, keep):
+        self.mod, self.a1, self.a2, self.side, self.keep = mod, a1, a2, side, keep
+        mod.__dict__["_prep_keep"] = keep            # fp32 sources are read on the side stream: alive until the next call
+        self._c = None
+
+    def struct(self):
+        self._c = _lib.WeightPrep(self.a1[0], self.a1[2], self.a2[0], self.a2[2], self.side.cuda_stream, None)
+        return C.addressof(self._c)
+
+    def fork(self):
+        self.side.wait_stream(torch.cuda.current_stream(self.side.device))
+
+    def launch(self):
+        with torch.cuda.stream(self.side):
+            _lib.call("b200moe_prepare_weights", *self.a1, *self.a2, None, None, self.mod.d_model, self.mod.num_experts,
+                      _lib.stream_ptr())
+            self.ev = torch.cuda.Event()
+            self.ev.record(self.side)
+
+    def join(self):
+        torch.cuda.current_stream(self.side.device).wait_event(self.ev)
+
+
 class _LayerPlan:
     """Host-side description of one (T, tokens_per_image) problem: the C descriptor and both workspace layouts."""
 
@@ -192,7 +220,7 @@ class _MoEFunction(torch.autograd.Function):
         y = torch.empty((T, d), dtype=torch.float32 if out_f32 else torch.bfloat16, device=dev)
         _lib.call("b200moe_layer_fwd", pl.desc_ptr, x2.data_ptr(), None, cx_ptr,
                   wsplit.data_ptr(), w1b.data_ptr(), b1f.data_ptr(), w2b.data_ptr(), b2f.data_ptr(), ws.data_ptr(),
-                  y.data_ptr(), int(need_grad), pn_ptr, ready.cuda_event if ready is not None else None, st)
+                  y.data_ptr(), int(need_grad), pn_ptr, ready.struct() if ready is not None else None, st)
         ctx.mod, ctx.pl, ctx.has_ctx = mod, pl, cx_ptr is not None
         ctx.dtypes = (wg.dtype, w1.dtype, b1.dtype, w2.dtype, b2.dtype)
         ctx.save_for_backward(x2, wgf, w1b, w2b, ws)
@@ -345,7 +373,7 @@ class ContextMoE(nn.Module):
         new = self.__class__.__new__(self.__class__)
         memo[id(self)] = new
         for k_, v in self.__dict__.items():
-            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side", "_prep_stream",
+            if k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side", "_p2p_side1", "_prep_stream",
                       "_prep_keep"):
                 continue
             if k_ in ("_wcache", "last_aux", "_plans"):
@@ -361,7 +389,7 @@ class ContextMoE(nn.Module):
     def __getstate__(self):
         s = dict(self.__dict__)
         s["_wcache"], s["last_aux"], s["aux_loss"], s["ep_group"], s["_plans"] = {}, {}, torch.zeros(()), None, {}
-        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side", "_prep_stream",
+        for k_ in ("_ep_comm_stream", "_last_ws", "_last", "_ctx_keep", "_ep_static", "_ep_pinned", "_p2p_arena", "_p2p_side", "_p2p_side1", "_prep_stream",
                       "_prep_keep"):
             s.pop(k_, None)
         return s
@@ -403,9 +431,9 @@ class ContextMoE(nn.Module):
 
     def _prepared(self, w1, w2, wg, overlap: bool = False):
         """bf16 operand copies of w1 / w2 and the bf16 hi/lo split of the gate, redone only when a parameter changed
-        (version counters).  Returns (w1_bf16, w2_bf16, wg_split, wg_fp32, ready): with `overlap` the two big casts run
-        on a side stream next to the router / plan / permute, and `ready` is the CUDA event b200moe_layer_fwd waits for
-        just before the up-projection (None when nothing is in flight); without it, one launch on the current stream."""
+        (version counters).  Returns (w1_bf16, w2_bf16, wg_split, wg_fp32, job): with `overlap` the two big casts are NOT
+        launched here but returned as a `_CastJob` (None when nothing is to do) that the forward runs on a side stream
+        next to the router / plan / permute; without it, one launch on the current stream."""
         key = (w1.data_ptr(), w1._version, w2.data_ptr(), w2._version, wg.data_ptr(), wg._version, str(w1.device))
         hit = self._wcache.get("prep")
         if hit is not None and hit[0] == key:
@@ -423,21 +451,15 @@ class ContextMoE(nn.Module):
         a2 = (w2f.data_ptr(), w2b.data_ptr(), w2f.numel()) if w2b is not w2d else (None, w2b.data_ptr(), 0)
         ready = None
         if overlap and (a1[2] or a2[2]):
-            cur = torch.cuda.current_stream(dev)
             side = self.__dict__.get("_prep_stream")
             if side is None or side.device != dev:
                 side = self.__dict__["_prep_stream"] = torch.cuda.Stream(device=dev)
-            # the side stream forks BEFORE the gate split is launched: in a captured graph the two preparations are then
-            # independent roots (as children of the gate-split node the router started ~6 us late at 3200 tokens)
-            side.wait_stream(cur)
-            with torch.cuda.stream(side):
-                _lib.call("b200moe_prepare_weights", *a1, *a2, None, None, self.d_model, self.num_experts,
-                          _lib.stream_ptr())
-                ready = torch.cuda.Event()
-                ready.record(side)
+            # only the gate split is launched here; the casts of the expert slabs are handed back as a job that the
+            # forward launches on the side stream AFTER its router kernel (b200moe_weight_prep in include/b200moe.h has
+            # the reason) and joins before the up-projection
             _lib.call("b200moe_prepare_weights", None, w1b.data_ptr(), 0, None, w2b.data_ptr(), 0, wgf.data_ptr(),
                       wsplit.data_ptr(), self.d_model, self.num_experts, _lib.stream_ptr())
-            self.__dict__["_prep_keep"] = (w1f, w2f)      # read on the side stream: keep them until the next call
+            ready = _CastJob(self, a1, a2, side, (w1f, w2f))
         else:
             _lib.call("b200moe_prepare_weights", *a1, *a2, wgf.data_ptr(), wsplit.data_ptr(), self.d_model,
                       self.num_experts, _lib.stream_ptr())

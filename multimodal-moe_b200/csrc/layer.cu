@@ -74,11 +74,9 @@ static ForkState* fork_state() {
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
   ForkState& f = g_fork[dev];
   if (!f.ok) {
-    // the router branch ends the pass at the small problem sizes (three short dependent kernels): its blocks go first
-    // whenever an SM frees up
-    int lo = 0, hi = 0;
-    cudaDeviceGetStreamPriorityRange(&lo, &hi);
-    if (cudaStreamCreateWithPriority(&f.s1, cudaStreamNonBlocking, hi) != cudaSuccess) return nullptr;
+    // (tried in round 2: the router branch at the highest stream priority -- its blocks then take the SMs the next GEMM
+    // of the dx chain is waiting for: dgrad_up started 83 us late at C/65533)
+    if (cudaStreamCreateWithFlags(&f.s1, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     if (cudaStreamCreateWithFlags(&f.s2, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     if (cudaStreamCreateWithFlags(&f.s3, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     for (auto& e : f.ev)
@@ -312,7 +310,7 @@ extern "C" int64_t b200moe_layer_bwd_ws_layout(const b200moe_layer_desc* q, int6
 extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, const float* ctx_bias,
                                  const b200moe_ctx_desc* cx, const void* wg_split, const void* w1, const float* b1, const void* w2,
                                  const float* b2, void* ws, void* y, int save_for_backward,
-                                 const b200moe_postnorm* pn, void* weights_ready, void* stream) {
+                                 const b200moe_postnorm* pn, const b200moe_weight_prep* prep, void* stream) {
   if (int rc = check_desc(q, "layer_fwd")) return rc;
   B200MOE_REQUIRE(x && wg_split && w1 && b1 && w2 && b2 && ws && y, B200MOE_EINVAL, "layer_fwd: NULL argument");
   int64_t off[B200MOE_WS_COUNT];
@@ -325,6 +323,31 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
   int rc;
   PdlScope pdl_;
   B200MOE_REQUIRE(!(ctx_bias && cx), B200MOE_EINVAL, "layer_fwd: pass ctx_bias or ctx, not both");
+  // weight casts on the caller's side stream: forked here (no dependency on the router), LAUNCHED after the router
+  cudaEvent_t weights_ready = prep ? static_cast<cudaEvent_t>(prep->ready) : nullptr;
+  const bool cast_here = prep && (prep->w1_f32 || prep->w2_f32);
+  ForkState* pf = nullptr;
+  if (cast_here) {
+    B200MOE_REQUIRE(prep->side_stream != nullptr && prep->side_stream != stream, B200MOE_EINVAL,
+                    "layer_fwd: the weight preparation needs a side stream");
+    pf = fork_state();
+    B200MOE_REQUIRE(pf != nullptr, B200MOE_ECUDA, "layer_fwd: cannot create the fork events");
+    cudaEventRecord(pf->ev[0], static_cast<cudaStream_t>(stream));
+    cudaStreamWaitEvent(static_cast<cudaStream_t>(prep->side_stream), pf->ev[0], 0);
+  }
+  auto launch_cast = [&]() -> int {
+    if (!cast_here) return B200MOE_OK;
+    const bool pdl_was = g_pdl;
+    g_pdl = false;
+    int rc_ = b200moe_prepare_weights(prep->w1_f32, const_cast<void*>(w1), prep->w1_f32 ? prep->n1 : 0, prep->w2_f32,
+                                      const_cast<void*>(w2), prep->w2_f32 ? prep->n2 : 0, nullptr, nullptr, q->d, q->E,
+                                      prep->side_stream);
+    g_pdl = pdl_was;
+    if (rc_) return rc_;
+    cudaEventRecord(pf->ev[1], static_cast<cudaStream_t>(prep->side_stream));
+    weights_ready = pf->ev[1];
+    return B200MOE_OK;
+  };
   if (cx && (q->tokens_per_image < 64 || cx->n_fields * cx->context_dim > 256)) {
     // few tokens per image (a 128-token tile would touch many images) or a wide context embedding: the stand-alone
     // kernel fills the workspace slot
@@ -346,6 +369,7 @@ extern "C" int b200moe_layer_fwd(const b200moe_layer_desc* q, const void* x, con
                             WS(float, B200MOE_WS_TOPK_GATE), WS(int32_t, B200MOE_WS_BLOCK_COUNTS),
                             WS(float, B200MOE_WS_BLOCK_STATS), stream));
   }
+  if (int rc_ = launch_cast()) return rc_;
   STEP("plan",
        b200moe_plan(WS(int32_t, B200MOE_WS_TOPK_IDX), WS(float, B200MOE_WS_TOPK_GATE),
                     WS(int32_t, B200MOE_WS_BLOCK_COUNTS), WS(float, B200MOE_WS_BLOCK_STATS), T, k, E, q->capacity,

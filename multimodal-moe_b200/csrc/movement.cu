@@ -290,8 +290,24 @@ prepare_weights_kernel(const float* __restrict__ w1, __nv_bfloat16* __restrict__
   const int64_t ns_8 = wg ? (static_cast<int64_t>(2) * EP * d) >> 3 : 0;
   const int64_t total = n1_8 + n2_8 + ns_8;
   const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
-    if (i < n1_8 + n2_8) {
+  const int64_t nw_8 = n1_8 + n2_8;
+  // expert slabs: two 32-byte reads per thread in flight (the grid leaves half of every SM's thread slots to the
+  // kernels this cast runs beside: with 2048 resident threads per SM the router waited for the cast's last wave --
+  // 204 us at 32 local experts of workload D, round-2 timeline)
+  int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  for (; i + stride < nw_8; i += 2 * stride) {
+    const int64_t i1 = i + stride;
+    const bool f0 = i < n1_8, f1 = i1 < n1_8;
+    const float4* s0 = reinterpret_cast<const float4*>(f0 ? w1 : w2) + 2 * (f0 ? i : i - n1_8);
+    const float4* s1 = reinterpret_cast<const float4*>(f1 ? w1 : w2) + 2 * (f1 ? i1 : i1 - n1_8);
+    const float4 a0 = __ldg(s0), b0 = __ldg(s0 + 1), a1 = __ldg(s1), b1 = __ldg(s1 + 1);
+    const float v0[8] = {a0.x, a0.y, a0.z, a0.w, b0.x, b0.y, b0.z, b0.w};
+    const float v1[8] = {a1.x, a1.y, a1.z, a1.w, b1.x, b1.y, b1.z, b1.w};
+    stg128((f0 ? w1b : w2b) + 8 * (f0 ? i : i - n1_8), pack8(v0));
+    stg128((f1 ? w1b : w2b) + 8 * (f1 ? i1 : i1 - n1_8), pack8(v1));
+  }
+  for (; i < total; i += stride) {
+    if (i < nw_8) {
       const bool first = i < n1_8;
       const float* src = first ? w1 : w2;
       __nv_bfloat16* dst = first ? w1b : w2b;
@@ -301,7 +317,7 @@ prepare_weights_kernel(const float* __restrict__ w1, __nv_bfloat16* __restrict__
       const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
       stg128(dst + 8 * c, pack8(v));
     } else {
-      const int64_t c = i - n1_8 - n2_8;
+      const int64_t c = i - nw_8;
       const int64_t el = c * 8;
       const int row = static_cast<int>(el / d), col = static_cast<int>(el - static_cast<int64_t>(row) * d);
       const int e = row < EP ? row : row - EP;
@@ -596,7 +612,7 @@ extern "C" int b200moe_prepare_weights(const float* w1, void* w1_bf16, int64_t n
   const int64_t total = n1 / 8 + n2 / 8 + (wg ? (static_cast<int64_t>(2) * EP * d) / 8 : 0);
   if (total == 0) return B200MOE_OK;
   int64_t blocks = (total + 255) / 256;
-  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
+  if (blocks > num_sms() * 4) blocks = num_sms() * 4;      // half of the thread slots: see the kernel
   prepare_weights_kernel<<<static_cast<int>(blocks), 256, 0, ST(stream)>>>(
       w1, BFW(w1_bf16), n1 / 8, w2, BFW(w2_bf16), n2 / 8, wg, BFW(wg_split), E, EP, d);
   return check_launch("prepare_weights");

@@ -106,9 +106,12 @@ router_dwg_partial_kernel(const float* __restrict__ dlogits, const __nv_bfloat16
 }
 
 // blocks [0, nred): dwg[i] = sum over chunks of scratch[c][i];  blocks [nred, nred + B): dctx[b,:] for image b
+// tensor-pipe partials (lo_off != 0): chunk c holds [128][d] = hi rows 0..63, lo rows 64..127 -> element i of dwg is
+// scratch[c*cstride + i] + scratch[c*cstride + lo_off + i]
 __global__ void __launch_bounds__(256)
 router_dwg_reduce_kernel(const float* __restrict__ scratch, int nchunks, int n, float* __restrict__ dwg, int nred,
-                         const float* __restrict__ dlogits, int T, int E, int tpi, float* __restrict__ dctx) {
+                         const float* __restrict__ dlogits, int T, int E, int tpi, float* __restrict__ dctx,
+                         int64_t cstride, int lo_off) {
   pdl_sync();
   if (static_cast<int>(blockIdx.x) < nred) {
     // 32 outputs x 8 phases per block: phase p sums chunks p, p+8, ... (eight loads in flight), then the phases are
@@ -122,11 +125,17 @@ router_dwg_reduce_kernel(const float* __restrict__ scratch, int nchunks, int n, 
       for (; c + 56 < nchunks; c += 64) {
         float a[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) a[u] = scratch[static_cast<size_t>(c + 8 * u) * n + i];
+        for (int u = 0; u < 8; ++u) {
+          const float* q = scratch + static_cast<size_t>(c + 8 * u) * cstride + i;
+          a[u] = lo_off ? q[0] + q[lo_off] : q[0];
+        }
 #pragma unroll
         for (int u = 0; u < 8; ++u) s += a[u];
       }
-      for (; c < nchunks; c += 8) s += scratch[static_cast<size_t>(c) * n + i];
+      for (; c < nchunks; c += 8) {
+        const float* q = scratch + static_cast<size_t>(c) * cstride + i;
+        s += lo_off ? q[0] + q[lo_off] : q[0];
+      }
     }
     ph_s[p][o] = s;
     __syncthreads();
@@ -156,6 +165,53 @@ router_dwg_reduce_kernel(const float* __restrict__ scratch, int nchunks, int n, 
   }
 }
 
+// ---- the same contraction on the tensor pipe (T >= kDwgTensorMinT) --------------------------------------------------
+// dWg = dlogits^T x is a [E x T] x [T x d] product: 2 T E d FMAs, 84 us on CUDA cores at E = 64, d = 1024, T = 16384.  The
+// weight-gradient mode of the grouped GEMM (gemm.cu) computes it with fake experts = chunks of rows: A = the bf16
+// (hi | lo) split of dlogits ([T,128]: hi in columns 0..E-1, lo = bf16(v - hi) in columns 64..64+E-1 -- 16 mantissa bits,
+// x is bf16 already), B = x, partial[c] [128,d] fp32, then the fixed-order reduction above adds chunks and hi + lo.
+constexpr int kDwgTensorMinT = 8192;
+struct DwgPlan { int t64, chunk_rows, nchunks; };
+static DwgPlan dwg_tensor_plan(int T, int d) {
+  DwgPlan p;
+  p.t64 = (T + 63) / 64 * 64;
+  const int want = (2 * num_sms() + d / 128 - 1) / (d / 128);           // ~two tiles per SM
+  p.chunk_rows = ((p.t64 + want - 1) / want + 63) / 64 * 64;
+  p.nchunks = (p.t64 + p.chunk_rows - 1) / p.chunk_rows;
+  return p;
+}
+// scratch layout (floats): partial [nchunks][128][d] | dl_split [t64][128] bf16 | chunk_offsets [nchunks + 1] int32
+static int64_t dwg_tensor_floats(int T, int d) {
+  const DwgPlan p = dwg_tensor_plan(T, d);
+  return static_cast<int64_t>(p.nchunks) * 128 * d + static_cast<int64_t>(p.t64) * 64 + (p.nchunks + 1 + 63) / 64 * 64;
+}
+
+__global__ void __launch_bounds__(256)
+router_dl_split_kernel(const float* __restrict__ dlogits, int T, int E, int t64, int chunk_rows, int nchunks,
+                       __nv_bfloat16* __restrict__ split, int32_t* __restrict__ chunk_offsets) {
+  pdl_sync();
+  if (blockIdx.x == 0)
+    for (int c = threadIdx.x; c <= nchunks; c += blockDim.x) chunk_offsets[c] = min(c * chunk_rows, t64);
+  // a thread writes 8 of the 128 columns of a row (16 bytes)
+  const int64_t n = static_cast<int64_t>(t64) * 16;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < n;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int t = static_cast<int>(i >> 4), c8 = static_cast<int>(i & 15) * 8;
+    const bool lo = c8 >= 64;
+    const int e0 = lo ? c8 - 64 : c8;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float x = (t < T && e0 + j < E) ? dlogits[static_cast<size_t>(t) * E + e0 + j] : 0.f;
+      v[j] = lo ? x - __bfloat162float(__float2bfloat16_rn(x)) : x;
+    }
+    stg128(split + static_cast<size_t>(t) * 128 + c8, pack8(v));
+  }
+}
+
+int launch_dwg_gemm(const void* dl_split, const void* x, int T, int N, const int32_t* chunk_offsets, int nchunks,
+                    float* partial, cudaStream_t st);       // gemm_host.inc
+
 static int dwg_chunks(int T, int d, int E) {
   const int slabs = (d + 255) / 256, groups = (E + kDwgEG - 1) / kDwgEG;
   int chunks = (4 * num_sms() + slabs * groups - 1) / (slabs * groups);
@@ -178,14 +234,17 @@ extern "C" int b200moe_router_bwd_dlogits(const float* logits, const int32_t* to
   if (int rc = b200moe_check_device()) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int grid = (T + 3) / 4;
-  if (grid > 32 * num_sms()) grid = 32 * num_sms();
+  if (grid > 128 * num_sms()) grid = 128 * num_sms();   // one token per warp up to 75 k tokens: every gather in flight at once
   launch_k(router_dlogits_kernel, grid, 128, 0, st, logits, topk_idx, row_of_assignment, dgate_row, tokens_per_expert,
            d_aux, T, E, k, normalize_topk, aux_loss_weight, z_loss_weight, dlogits);
   return check_launch("router_dlogits");
 }
 
 extern "C" int64_t b200moe_dwg_scratch_floats(int T, int d, int E) {
-  return static_cast<int64_t>(dwg_chunks(T, d, E)) * E * d;
+  const int64_t simt = static_cast<int64_t>(dwg_chunks(T, d, E)) * E * d;
+  if (T < kDwgTensorMinT || d % 128 != 0) return simt;
+  const int64_t tens = dwg_tensor_floats(T, d);
+  return tens > simt ? tens : simt;
 }
 
 extern "C" int b200moe_router_bwd_params(const float* dlogits, const void* x, int T, int d, int E,
@@ -198,7 +257,24 @@ extern "C" int b200moe_router_bwd_params(const float* dlogits, const void* x, in
   if (int rc = b200moe_check_device()) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int chunks = 0;
-  if (dwg) {
+  int64_t cstride = static_cast<int64_t>(E) * d;
+  int lo_off = 0;
+  if (dwg && T >= kDwgTensorMinT) {
+    // tensor pipe: split -> grouped GEMM in weight-gradient mode over row chunks -> reduction (below)
+    const DwgPlan p = dwg_tensor_plan(T, d);
+    float* partial = scratch;
+    __nv_bfloat16* split = reinterpret_cast<__nv_bfloat16*>(scratch + static_cast<int64_t>(p.nchunks) * 128 * d);
+    int32_t* offs = reinterpret_cast<int32_t*>(scratch + static_cast<int64_t>(p.nchunks) * 128 * d +
+                                               static_cast<int64_t>(p.t64) * 64);
+    int blocks = static_cast<int>((static_cast<int64_t>(p.t64) * 16 + 255) / 256);
+    if (blocks > 8 * num_sms()) blocks = 8 * num_sms();
+    launch_k(router_dl_split_kernel, blocks, 256, 0, st, dlogits, T, E, p.t64, p.chunk_rows, p.nchunks, split, offs);
+    if (int rc = check_launch("router_dl_split")) return rc;
+    if (int rc = launch_dwg_gemm(split, x, T, d, offs, p.nchunks, partial, st)) return rc;
+    chunks = p.nchunks;
+    cstride = static_cast<int64_t>(128) * d;
+    lo_off = 64 * d;
+  } else if (dwg) {
     chunks = dwg_chunks(T, d, E);
     int tpc = (T + chunks - 1) / chunks;
     tpc = (tpc + 3) / 4 * 4;
@@ -219,7 +295,7 @@ extern "C" int b200moe_router_bwd_params(const float* dlogits, const void* x, in
   const int nred = dwg ? (n + 31) / 32 : 0;
   const int B = dctx_bias ? (T + tokens_per_image - 1) / tokens_per_image : 0;
   launch_k(router_dwg_reduce_kernel, nred + B, 256, 0, st, scratch, chunks, n, dwg, nred, dlogits, T, E,
-           tokens_per_image > 0 ? tokens_per_image : T, dctx_bias);
+           tokens_per_image > 0 ? tokens_per_image : T, dctx_bias, cstride, lo_off);
   return check_launch("router_dwg_reduce");
 }
 
