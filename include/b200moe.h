@@ -246,6 +246,16 @@ int b200moe_router_bwd_dlogits(const float* logits, const int32_t* topk_idx, con
 int64_t b200moe_dwg_scratch_floats(int T, int d, int E);
 int b200moe_router_bwd_dwg(const float* dlogits, const void* x, int T, int d, int E, float* scratch,
                            float* dwg, void* stream);
+/* The same gradient for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The scratch
+ * is a device array built into the library, B200MOE_DWG_STATIC_MAX_FLOATS floats = 16 MB, held by every GPU that loads
+ * the library until the process exits; the call allocates nothing (no cudaMalloc / cudaFree, no allocating library
+ * routine) and fails with B200MOE_EINVAL when b200moe_dwg_scratch_floats(T, d, E) exceeds the array (e.g. d = 1024 at
+ * 16384 tokens; 3200 x 256 x 8 needs 0.4 M floats).  All calls on a device share the array: calls that overlap on the
+ * GPU (different streams) race -- serialise them.  Results are bit-identical to b200moe_router_bwd_dwg. */
+#define B200MOE_DWG_STATIC_MAX_FLOATS (4 * 1024 * 1024)
+int b200moe_router_bwd_dwg_noalloc(const float* dlogits, const void* x, int T, int d, int E, float* dwg,
+                                   void* stream);
 /* Both parameter gradients of the router in two launches (either output may be NULL): dwg as above and
  * dctx_bias [B,E] = segment sums of dlogits over the tokens of each image, reduced inside the second launch. */
 int b200moe_router_bwd_params(const float* dlogits, const void* x, int T, int d, int E, int tokens_per_image,

@@ -66,6 +66,7 @@ SIGNATURES = {
     "b200moe_router_bwd_dlogits": [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _P, _P],
     "b200moe_dwg_scratch_floats": [_I, _I, _I],
     "b200moe_router_bwd_dwg": [_P, _P, _I, _I, _I, _P, _P, _P],
+    "b200moe_router_bwd_dwg_noalloc": [_P, _P, _I, _I, _I, _P, _P],
     "b200moe_router_bwd_dctx": [_P, _I, _I, _I, _P, _P],
     "b200moe_router_bwd_params": [_P, _P, _I, _I, _I, _I, _P, _P, _P, _P],
     "b200moe_unpermute_bwd": [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P],
@@ -173,7 +174,7 @@ KERNELS_PER_CALL = {
     "b200moe_combine": 1, "b200moe_combine_bwd": 1, "b200moe_ffn_up": 1, "b200moe_ffn_down": 1,
     "b200moe_ffn_dgrad_down": 1, "b200moe_ffn_dgrad_up": 1, "b200moe_ffn_wgrad": 1, "b200moe_colsum": 1,
     "b200moe_permute_init": 1, "b200moe_ffn_down_combine": 1, "b200moe_ffn_up_gather": 1, "b200moe_ffn_wgrad2": 1, "b200moe_ffn_wgrad_gather": 1,
-    "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dctx": 1,
+    "b200moe_router_bwd_dlogits": 1, "b200moe_router_bwd_dwg": 2, "b200moe_router_bwd_dwg_noalloc": 2, "b200moe_router_bwd_dctx": 1,
     "b200moe_unpermute_bwd": 1, "b200moe_ep_recv_plan": 1, "b200moe_ep_hist": 1, "b200moe_ep_route_tables": 1, "b200moe_scatter_rows": 1,
 }
 

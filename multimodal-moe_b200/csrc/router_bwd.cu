@@ -310,3 +310,41 @@ extern "C" int b200moe_router_bwd_dctx(const float* dlogits, int T, int E, int t
   B200MOE_REQUIRE(tokens_per_image > 0 && dctx_bias != nullptr, B200MOE_EINVAL, "router_bwd_dctx: bad arguments");
   return b200moe_router_bwd_params(dlogits, nullptr, T, 128, E, tokens_per_image, nullptr, nullptr, dctx_bias, stream);
 }
+
+// ---- b200moe_router_bwd_dwg without caller scratch -------------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot allocate (code
+// under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The two-stage reduction's scratch
+// lives in a file-scope device array of B200MOE_DWG_STATIC_MAX_FLOATS floats (16 MB; every GPU that loads the library
+// holds it until exit).  In host code the array's NAME is a host-side stand-in, not a device address: the address is
+// fetched once per device, with that device current, by cudaGetSymbolAddress and that pointer goes to the kernels.
+// Every call on a device shares the array: calls that overlap on the GPU (different streams) race.  Nothing in it has
+// to start at zero -- both paths (CUDA cores below 8192 tokens, tensor pipe from there on) write every element the
+// reduction reads, the bf16 split and the chunk table included -- so a call is independent of the previous one's leftovers.
+constexpr int64_t kDwgStaticFloats = B200MOE_DWG_STATIC_MAX_FLOATS;
+static __device__ __align__(256) float g_dwg_static_scratch[kDwgStaticFloats];
+
+extern "C" int b200moe_router_bwd_dwg_noalloc(const float* dlogits, const void* x, int T, int d, int E, float* dwg,
+                                              void* stream) {
+  B200MOE_REQUIRE(dlogits != nullptr && x != nullptr && dwg != nullptr, B200MOE_EINVAL, "router_bwd_dwg_noalloc: NULL argument");
+  B200MOE_REQUIRE(T >= 0 && E >= 1 && E <= 64 && d > 0 && d % 128 == 0, B200MOE_EINVAL,
+                  "router_bwd_dwg_noalloc: bad T=%d / E=%d / d=%d", T, E, d);
+  const int64_t need = b200moe_dwg_scratch_floats(T, d, E);
+  B200MOE_REQUIRE(need <= kDwgStaticFloats, B200MOE_EINVAL,
+                  "router_bwd_dwg_noalloc: T=%d d=%d E=%d needs %lld scratch floats, the built-in array holds %lld "
+                  "(B200MOE_DWG_STATIC_MAX_FLOATS); use b200moe_router_bwd_dwg with caller scratch",
+                  T, d, E, static_cast<long long>(need), static_cast<long long>(kDwgStaticFloats));
+  if (int rc = b200moe_check_device()) return rc;
+  static DeviceOnce once;
+  static float* addr_dev[64];
+  const int dev = current_device();
+  B200MOE_REQUIRE(dev >= 0 && dev < 64, B200MOE_ECUDA, "router_bwd_dwg_noalloc: no current CUDA device");
+  if (!once.done(dev)) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_dwg_static_scratch);
+    B200MOE_REQUIRE(e == cudaSuccess && p != nullptr, B200MOE_ECUDA, "router_bwd_dwg_noalloc: cudaGetSymbolAddress: %s",
+                    cudaGetErrorString(e));
+    addr_dev[dev] = p;
+    once.set(dev);
+  }
+  return b200moe_router_bwd_params(dlogits, x, T, d, E, 0, addr_dev[dev], dwg, nullptr, stream);
+}
