@@ -612,7 +612,14 @@ extern "C" int b200moe_prepare_weights(const float* w1, void* w1_bf16, int64_t n
   const int64_t total = n1 / 8 + n2 / 8 + (wg ? (static_cast<int64_t>(2) * EP * d) / 8 : 0);
   if (total == 0) return B200MOE_OK;
   int64_t blocks = (total + 255) / 256;
-  if (blocks > num_sms() * 4) blocks = num_sms() * 4;      // half of the thread slots: see the kernel
+  // Blocks per SM.  4 = half of the thread slots, so that the routing / dispatch kernels this cast runs beside find room
+  // (expert parallelism, 32 local experts of workload D: 2.34 ms per step against 2.42 with 8).  A cast longer than
+  // anything it can hide behind (>= 2.4 GB of traffic ~ 0.4 ms: all 64 experts of workload D on one GPU) takes every
+  // slot instead: the up-projection waits for it either way, and it finishes in 0.56 ms instead of 0.73 (2.70 vs 2.86 ms
+  // per step).  B200MOE_PREP_BLOCKS_PER_SM: measurement aid.
+  static const int env_per_sm = [] { const char* e = getenv("B200MOE_PREP_BLOCKS_PER_SM"); const int v = e ? atoi(e) : 0; return v >= 1 && v <= 8 ? v : 0; }();
+  const int per_sm = env_per_sm ? env_per_sm : ((n1 + n2) * 6 >= 2400000000ll ? 8 : 4);
+  if (blocks > static_cast<int64_t>(num_sms()) * per_sm) blocks = static_cast<int64_t>(num_sms()) * per_sm;
   prepare_weights_kernel<<<static_cast<int>(blocks), 256, 0, ST(stream)>>>(
       w1, BFW(w1_bf16), n1 / 8, w2, BFW(w2_bf16), n2 / 8, wg, BFW(wg_split), E, EP, d);
   return check_launch("prepare_weights");

@@ -7,6 +7,7 @@
 //   followed by the softmax Jacobian  dlogit_e = p_e (dp_e - sum_j p_j dp_j).
 // Then dWg = dlogits^T x (two-stage fixed-order reduction), dctx_bias = per-image segment sums.
 #include <math.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "router_grad.cuh"
@@ -170,7 +171,13 @@ router_dwg_reduce_kernel(const float* __restrict__ scratch, int nchunks, int n, 
 // weight-gradient mode of the grouped GEMM (gemm.cu) computes it with fake experts = chunks of rows: A = the bf16
 // (hi | lo) split of dlogits ([T,128]: hi in columns 0..E-1, lo = bf16(v - hi) in columns 64..64+E-1 -- 16 mantissa bits,
 // x is bf16 already), B = x, partial[c] [128,d] fp32, then the fixed-order reduction above adds chunks and hi + lo.
-constexpr int kDwgTensorMinT = 8192;
+constexpr int kDwgTensorMinTDefault = 8192;
+// B200MOE_DWG_TENSOR_MIN_T: measurement aid (a huge value keeps the CUDA-core path at every size)
+static int dwg_tensor_min_t() {
+  static const int v = [] { const char* e = getenv("B200MOE_DWG_TENSOR_MIN_T"); return e ? atoi(e) : kDwgTensorMinTDefault; }();
+  return v;
+}
+#define kDwgTensorMinT dwg_tensor_min_t()
 struct DwgPlan { int t64, chunk_rows, nchunks; };
 static DwgPlan dwg_tensor_plan(int T, int d) {
   DwgPlan p;
