@@ -816,6 +816,23 @@ def main():
         except Exception as ex:  # noqa: BLE001
             line["ep_parity"] = {"ok": False, "error": repr(ex)}
 
+    if dist_on and w["E"] != WORKLOADS["E"]["E"] and WORKLOADS["E"]["E"] % world == 0:
+        # BASELINE.json configs[4] beside the metric's own config: data-parallel tokens (16x920 per rank) + expert-parallel
+        # experts (E=16, d=512, ffn=2048), every rank takes part; same timing rules, fewer steps
+        we = WORKLOADS["E"]
+        try:
+            re_ = measure_layer(we, min(args.steps, 10), 3, device, ep_group, dist_on, want_e2e=False, want_roofline=False)
+            te = torch.tensor(re_["ms"], device=device)
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+            ms_e = float(te.sum()) / len(re_["ms"])
+            line["config_E"] = {"workload": we["name"], "n_gpus": world, "tokens_per_step": we["B"] * we["HW"] * world,
+                                "ms_per_step": ms_e, "value": we["B"] * we["HW"] * world / (ms_e * 1e-3),
+                                "unit": "tokens/s", "transport": re_.get("transport"), "cuda_graph": re_["graph"],
+                                "kept_assignments_rank0": re_["kept"], "dropped_assignments_rank0": re_["dropped"]}
+        except Exception as ex:  # noqa: BLE001
+            line["config_E"] = {"error": repr(ex)}
+        torch.cuda.empty_cache()
+
     # the same workload (configs[3]) on ONE GPU, measured in the same run: all experts local, one rank's tokens.  The
     # driver's N=1 line is configs[1], so efficiency has to be recomputed from these numbers.
     if rank == 0 and (dist_on or not args.no_sweep):

@@ -232,6 +232,9 @@ class _EPFunction(torch.autograd.Function):
         ctx.save_for_backward(x2, wgf, w1b, w2b, ys)
         aux = p.losses[0]
         stats = p.losses.detach()
+        # undefined upstream gradients stay None (the engine would otherwise launch a zero fill per missing one, on the
+        # critical path between forward and backward); backward handles dy / d_aux == None itself
+        ctx.set_materialize_grads(False)
         ctx.mark_non_differentiable(stats)
         mod._stash(r, p)
         return y, aux, stats

@@ -217,6 +217,9 @@ class _P2PFunction(torch.autograd.Function):
         ar.pending = need_grad
         aux = p.losses[0]
         stats = p.losses.detach()
+        # undefined upstream gradients stay None (the engine would otherwise launch a zero fill per missing one, on the
+        # critical path between forward and backward); backward handles dy / d_aux == None itself
+        ctx.set_materialize_grads(False)
         ctx.mark_non_differentiable(stats)
         mod._stash(r, p)
         return y, aux, stats

@@ -227,6 +227,9 @@ class _MoEFunction(torch.autograd.Function):
         losses = pl.view(ws, "losses")
         aux = losses[0]
         stats = losses.detach()
+        # undefined upstream gradients stay None (the engine would otherwise launch a zero fill per missing one, on the
+        # critical path between forward and backward); backward handles dy / d_aux == None itself
+        ctx.set_materialize_grads(False)
         ctx.mark_non_differentiable(stats)
         mod.__dict__["_last_ws"] = (pl, ws)
         return y, aux, stats
