@@ -465,6 +465,42 @@ def measure_layer(w, steps, warmup, device, ep_group=None, dist_on=False, want_e
                 torch.cuda.synchronize()
                 res["e2e_ms_" + name + ("_prefetch" if pipelined else "_inline")] = a.elapsed_time(b) / steps
             res["e2e_ms_" + name] = min(res["e2e_ms_" + name + "_prefetch"], res["e2e_ms_" + name + "_inline"])
+        if not dist_on and use_graph:
+            # multi-scale training (dataloader.yml:22): the token count changes per step, so one captured shape cannot
+            # serve; b200moe.MultiShapeGraphedMoE keeps a graph per shape.  Same rules: pinned host batch in, loss out.
+            import b200moe
+            ms_ = {}
+            scales = [(w["B"], hw) for hw in (225, 400, 625)]
+            batches = []
+            for B_, hw in scales:
+                xb, gb, cb = make_inputs(dict(w, B=B_, HW=hw), seed=77 + hw)
+                batches.append((xb.pin_memory(), cb.pin_memory(), gb.to(device)))
+            for name, call in (("eager", m), ("multishape_graphed", b200moe.MultiShapeGraphedMoE(m))):
+                def ms_step(i, call=call):
+                    xh, ch, g_ = batches[i % len(batches)]
+                    m.zero_grad(set_to_none=True)
+                    xd = xh.to(device, non_blocking=True).requires_grad_(True)
+                    y = call(xd, ch.to(device, non_blocking=True))
+                    loss = (y.float() * g_).sum() + call.aux_loss
+                    loss.backward()
+                    return float(loss.item())
+                for i in range(max(warmup, 2 * len(batches))):
+                    ms_step(i)
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                n_ms = len(batches) * max(steps // len(batches), 1)
+                a.record()
+                for i in range(n_ms):
+                    ms_step(i)
+                b.record()
+                torch.cuda.synchronize()
+                ms_[name] = a.elapsed_time(b) / n_ms
+            tok = sum(B_ * hw for B_, hw in scales) / len(scales)
+            res["e2e_multiscale"] = {"tokens_per_step": [B_ * hw for B_, hw in scales],
+                                     "ms_per_step": {k_: round(v, 5) for k_, v in ms_.items()},
+                                     "tokens_per_s": {k_: tok / (v * 1e-3) for k_, v in ms_.items()},
+                                     "api": "MultiShapeGraphedMoE (one CUDA graph pair per shape) vs the eager module; "
+                                            "shapes cycle 225 / 400 / 625 tokens per image"}
         res["e2e_api"] = "GraphedMoE" if "graphed" in calls else "ContextMoE"
         res["e2e_ms"] = res["e2e_ms_graphed"] if "graphed" in calls else res["e2e_ms_eager"]
         if "e2e_ms_step_inline" in res and res["e2e_ms_step_inline"] < res["e2e_ms"]:
@@ -758,6 +794,8 @@ def main():
                        "pipeline": "best of: inline = inputs copied on the compute stream just before the step; prefetch = "
                                    "batch i+1 copied on a copy stream during step i.  Loss read back every step in both.",
                        "eager_api_value": T_all / (res["e2e_ms_eager"] * 1e-3)}
+        if "e2e_multiscale" in res:
+            line["e2e"]["multiscale"] = res["e2e_multiscale"]
     if "gemm_ms" in res and res["gemm_ms"] > 0:
         # per rank: kept rows of this rank's tokens at N=1; at N>1 the rows this rank's experts received are, summed
         # over the ranks, the kept rows of all tokens -- the per-rank average is what the FLOP count uses

@@ -208,3 +208,52 @@ class GraphedStep:
                 p.grad = g
         self.moe.last_aux = self._telemetry
         return self.loss_s
+
+
+class MultiShapeGraphedMoE(nn.Module):
+    """`GraphedMoE` for training loops whose token count changes from step to step.  The vendored recipe trains
+    multi-scale (configs/rtdetrv2/include/dataloader.yml:22: a scale out of 480 .. 800 in steps of 32 per batch, i.e. about
+    a dozen distinct [B, HW, d] at the S5 level), which a single captured shape cannot serve; launched call by call the
+    layer costs ~0.5 ms of host time per step against ~0.1 ms on the device.  This wrapper keeps one `GraphedMoE` per
+    (shape, dtype, context shape), captured the first time the shape is seen, and replays it afterwards:
+
+        fast = MultiShapeGraphedMoE(moe, max_shapes=16)
+        y = fast(x, context); loss = crit(y) + fast.aux_loss; loss.backward()
+
+    Every cached shape owns its captured workspaces and gradient buffers (about the size of the layer's parameters in
+    fp32 plus the activations of that shape), hence `max_shapes`; shapes beyond it, no-grad calls and expert-parallel
+    layers run the eager module.  Results are those of the eager module bit for bit
+    (tests/test_gpu_layer.py::test_multishape_graphed_matches_eager)."""
+
+    def __init__(self, moe: ContextMoE, max_shapes: int = 16, warmup: int = 3):
+        super().__init__()
+        if not isinstance(moe, ContextMoE):
+            raise TypeError("MultiShapeGraphedMoE wraps a b200moe.ContextMoE")
+        self.moe = moe
+        self.max_shapes, self._warmup = int(max_shapes), int(warmup)
+        self.__dict__["_graphs"] = {}              # plain dict: the wrapped module must not be registered once per shape
+
+    @property
+    def aux_loss(self) -> torch.Tensor:
+        return self.moe.aux_loss
+
+    @property
+    def last_aux(self):
+        return self.moe.last_aux
+
+    @property
+    def cached_shapes(self):
+        return sorted(k_[0] for k_ in self._graphs)
+
+    def forward(self, x: torch.Tensor, context: Optional[torch.Tensor] = None) -> torch.Tensor:
+        moe = self.moe
+        if not torch.is_grad_enabled() or moe.ep_size > 1 or not x.is_cuda:
+            return moe(x, context)
+        key = (tuple(x.shape), x.dtype, None if context is None else tuple(context.shape))
+        g = self._graphs.get(key)
+        if g is None:
+            if len(self._graphs) >= self.max_shapes:
+                return moe(x, context)
+            g = GraphedMoE(moe, x.detach(), context, warmup=self._warmup)
+            self._graphs[key] = g
+        return g(x, context)

@@ -263,6 +263,41 @@ def test_graphed_matches_eager(ctx):
     assert fast(xs[0][:2], None if cs[0] is None else cs[0][:2]).shape == (2, HW, d)
 
 
+def test_multishape_graphed_matches_eager():
+    """MultiShapeGraphedMoE over a multi-scale sequence of token counts (dataloader.yml:22: HW = 225, 400, 625 per image):
+    one captured graph per shape, bit-exact with the eager module on every step, shapes beyond max_shapes run eagerly."""
+    import b200moe
+    d, F, E, k = 256, 512, 8, 2
+    _, m = _pair(d, F, E, k, 1.25, ctx=True, seed=21)
+    ref = copy.deepcopy(m)
+    fast = b200moe.MultiShapeGraphedMoE(m, max_shapes=2)
+    g = torch.Generator().manual_seed(8)
+    for step, HW in enumerate([225, 400, 225, 625, 400, 225]):
+        B = 4
+        x = torch.randn(B, HW, d, generator=g).to(torch.bfloat16).cuda()
+        c = torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1).cuda()
+        go = torch.randn(B, HW, d, generator=g).cuda()
+        outs = []
+        for mod, call in ((ref, ref), (m, fast)):
+            mod.zero_grad(set_to_none=True)
+            xg = x.clone().requires_grad_(True)
+            y = call(xg, c)
+            ((y.float() * go).sum() + call.aux_loss).backward()
+            outs.append((y.detach().clone(), xg.grad.clone(),
+                         {n: p.grad.clone() for n, p in mod.named_parameters() if p.grad is not None}))
+        (y0, dx0, g0), (y1, dx1, g1) = outs
+        assert torch.equal(y0, y1) and torch.equal(dx0, dx1), (step, HW)
+        assert g0.keys() == g1.keys()
+        for n in g0:
+            assert torch.equal(g0[n], g1[n]), (step, HW, n)
+        with torch.no_grad():
+            for p, q in zip(ref.parameters(), m.parameters()):
+                if p.grad is not None:
+                    p.add_(p.grad, alpha=-1e-3)
+                    q.add_(q.grad, alpha=-1e-3)
+    assert fast.cached_shapes == [(4, 225, d), (4, 400, d)]          # 625 came third: served by the eager module
+
+
 def test_graphed_gradient_accumulation():
     """Two micro-batches without zeroing in between: p.grad must be the sum, although every replay writes the gradients
     into the same captured buffers."""
