@@ -450,6 +450,21 @@ def measure_layer(w, steps, warmup, device, ep_group=None, dist_on=False, want_e
             torch.cuda.synchronize()
             res["e2e_ms_step_inline"] = a.elapsed_time(b) / steps
             del gstep
+            # the same with the copy of batch i+1 on a copy stream under step i (b200moe.PipelinedGraphedStep): every
+            # timed step still contains one host->device copy of a full batch and the loss read-back
+            pstep = b200moe.PipelinedGraphedStep(m, lambda y, g_: (y.float() * g_).sum(), x, ctx, go)
+            pstep.prefetch(xp_h, ctxp_h)
+            for i in range(warmup):
+                l_ = pstep(); pstep.prefetch(xp_h, ctxp_h); float(l_.item())
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for i in range(steps):
+                l_ = pstep(); pstep.prefetch(xp_h, ctxp_h); float(l_.item())
+            b.record()
+            torch.cuda.synchronize()
+            res["e2e_ms_step_prefetch"] = a.elapsed_time(b) / steps
+            del pstep
         for name, call in calls.items():
             for pipelined in (False, True):
                 torch.cuda.synchronize()
@@ -505,6 +520,8 @@ def measure_layer(w, steps, warmup, device, ep_group=None, dist_on=False, want_e
         res["e2e_ms"] = res["e2e_ms_graphed"] if "graphed" in calls else res["e2e_ms_eager"]
         if "e2e_ms_step_inline" in res and res["e2e_ms_step_inline"] < res["e2e_ms"]:
             res["e2e_api"], res["e2e_ms"] = "GraphedStep", res["e2e_ms_step_inline"]
+        if "e2e_ms_step_prefetch" in res and res["e2e_ms_step_prefetch"] < res["e2e_ms"]:
+            res["e2e_api"], res["e2e_ms"] = "PipelinedGraphedStep", res["e2e_ms_step_prefetch"]
         res["h2d"] = x_h.numel() * 2 + ctx_h.numel() * 8
         res["d2h"] = 4
     return res

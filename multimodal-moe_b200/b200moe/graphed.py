@@ -202,12 +202,76 @@ class GraphedStep:
                 self.ctx_s.copy_(context, non_blocking=True)
             for s, e in zip(self.extra_s, extra):
                 s.copy_(e, non_blocking=True)
+        return self.replay()
+
+    def replay(self) -> torch.Tensor:
+        """Replays the step on whatever the captured input buffers (`x_s`, `ctx_s`, `extra_s`) hold."""
         self.graph.replay()
         for p, g in zip(self._params, self._grads):       # optimizer.zero_grad(set_to_none=True) detaches them
             if p.grad is not g:
                 p.grad = g
         self.moe.last_aux = self._telemetry
         return self.loss_s
+
+
+class PipelinedGraphedStep:
+    """`GraphedStep` with the input copy of batch i+1 overlapped with the step on batch i: two captured steps with their
+    own input buffers, a copy stream, and events in both directions (a buffer is refilled only after the replay that read
+    it, a replay starts only after its buffer is filled).
+
+        step = PipelinedGraphedStep(moe, loss_fn, x_example, context_example, *extra_examples)
+        step.prefetch(x0, c0, *e0)
+        for batch in loader:                       # batch = the NEXT inputs (pinned host tensors)
+            loss = step()                          # launches the step on the batch prefetched last
+            step.prefetch(*batch)                  # its copies run on the copy stream under that step
+            opt.step(); print(loss.item())
+
+    Gradients land in `.grad` as with `GraphedStep` (each of the two captured steps owns a set of gradient buffers; the
+    one of the step just replayed is attached)."""
+
+    def __init__(self, moe: ContextMoE, loss_fn, x_example: torch.Tensor, context_example: Optional[torch.Tensor] = None,
+                 *extra_examples: torch.Tensor, warmup: int = 3):
+        self._steps = [GraphedStep(moe, loss_fn, x_example, context_example, *extra_examples, warmup=warmup)
+                       for _ in range(2)]
+        dev = self._steps[0].x_s.device
+        self._copy = torch.cuda.Stream(device=dev)
+        self._ready = [torch.cuda.Event() for _ in range(2)]
+        self._done = [torch.cuda.Event() for _ in range(2)]
+        for e in self._done:
+            e.record(torch.cuda.current_stream(dev))
+        self._next, self._pending = 0, None
+        self.moe = moe
+
+    @property
+    def dx(self) -> Optional[torch.Tensor]:
+        return self._steps[1 - self._next].dx             # of the step replayed last
+
+    def prefetch(self, x: torch.Tensor, context: Optional[torch.Tensor] = None, *extra: torch.Tensor) -> None:
+        if self._pending is not None:
+            raise RuntimeError("PipelinedGraphedStep.prefetch: the batch prefetched before has not been run yet")
+        j = self._next
+        s = self._steps[j]
+        self._copy.wait_event(self._done[j])              # the last replay that read these buffers
+        with torch.cuda.stream(self._copy), torch.no_grad():
+            s.x_s.copy_(x, non_blocking=True)
+            if s.ctx_s is not None and context is not None:
+                s.ctx_s.copy_(context, non_blocking=True)
+            for b, e in zip(s.extra_s, extra):
+                b.copy_(e, non_blocking=True)
+            self._ready[j].record(self._copy)
+        self._pending = j
+
+    def __call__(self) -> torch.Tensor:
+        if self._pending is None:
+            raise RuntimeError("PipelinedGraphedStep: call prefetch(x, context, ...) before the step")
+        j, self._pending = self._pending, None
+        s = self._steps[j]
+        cur = torch.cuda.current_stream(s.x_s.device)
+        cur.wait_event(self._ready[j])
+        loss = s.replay()
+        self._done[j].record(cur)
+        self._next = 1 - j
+        return loss
 
 
 class MultiShapeGraphedMoE(nn.Module):

@@ -452,3 +452,43 @@ def test_graphed_step_matches_eager():
         assert torch.equal(m.last_aux["topk_idx"], ref.last_aux["topk_idx"])
         opt_m.step(); opt_r.step()
         opt_m.zero_grad(set_to_none=True); opt_r.zero_grad(set_to_none=True)
+
+
+def test_pipelined_graphed_step_matches_eager():
+    """PipelinedGraphedStep (two captured steps, the copy of batch i+1 on a copy stream under step i) against the eager
+    module: bit-exact loss, dx and gradients over five steps that alternate between the two captured buffers, with an
+    optimizer step in between."""
+    import b200moe
+    B, HW, d, F, E, k = 4, 200, 256, 512, 8, 2
+    _, m = _pair(d, F, E, k, 1.25, ctx=True, seed=29)
+    ref = copy.deepcopy(m)
+    g = torch.Generator().manual_seed(12)
+    n = 5
+    xs = [torch.randn(B, HW, d, generator=g).to(torch.bfloat16).pin_memory() for _ in range(n)]
+    cs = [torch.stack([torch.randint(0, v, (B,), generator=g) for v in R.CONTEXT_VOCAB_SIZES], 1).pin_memory()
+          for _ in range(n)]
+    go = torch.randn(B, HW, d, generator=g).cuda()
+
+    def loss_fn(y, w):
+        return (y.float() * w).sum()
+
+    step = b200moe.PipelinedGraphedStep(m, loss_fn, xs[0], cs[0], go)
+    with pytest.raises(RuntimeError):
+        step()                                                        # nothing prefetched yet
+    opt_m, opt_r = torch.optim.SGD(m.parameters(), lr=1e-3), torch.optim.SGD(ref.parameters(), lr=1e-3)
+    step.prefetch(xs[0], cs[0], go)
+    for i in range(n):
+        loss = step()
+        if i + 1 < n:
+            step.prefetch(xs[i + 1], cs[i + 1], go)                   # copies run under the step just launched
+        xr = xs[i].cuda().requires_grad_(True)
+        lr_ = loss_fn(ref(xr, cs[i].cuda()), go) + ref.aux_loss
+        lr_.backward()
+        assert torch.equal(loss, lr_.detach()) and torch.equal(step.dx, xr.grad), i
+        grads_m = {n_: p.grad for n_, p in m.named_parameters() if p.grad is not None}
+        grads_r = {n_: p.grad for n_, p in ref.named_parameters() if p.grad is not None}
+        assert grads_m.keys() == grads_r.keys() and len(grads_m) >= 7
+        for n_ in grads_r:
+            assert torch.equal(grads_m[n_], grads_r[n_]), (i, n_)
+        opt_m.step(); opt_r.step()
+        opt_m.zero_grad(set_to_none=True); opt_r.zero_grad(set_to_none=True)
