@@ -34,6 +34,9 @@ constexpr int BK = 64;
 // copy: 8 warps with 4 KB boxes.
 __host__ __device__ constexpr int epi_warps(int epi) { return epi == 4 /*EPI_WGRAD*/ ? 8 : 16; }
 __host__ __device__ constexpr int gemm_threads(int epi) { return 64 + 32 * epi_warps(epi); }
+// (Tried in round 2 and dropped: two staging boxes per warp for the fp32 weight-gradient copy-out, paid for with one ring
+// stage -- 64 experts x 512 rows, d=1024, F=4096: 598 -> 633 us; the kernel already writes its 2.1 GB at 3.6 TB/s next to
+// 0.7 GB of reads, i.e. it sits on the HBM read+write limit, and the shallower ring costs more than the second box gains.)
 // (Tried in round 2 and dropped: a two-stage, 8-epilogue-warp configuration with TWO CTAs per SM for the latency-bound
 // problem sizes.  At 3200 tokens every GEMM got slower -- up 11.9 -> 14.4 us, dgrad_down 12.1 -> 18.4 us: two k-blocks in
 // flight do not cover the TMA latency -- and the co-residency of independent branches did not make up for it: 104 -> 107

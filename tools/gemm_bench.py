@@ -46,3 +46,8 @@ timed("down", lambda: ops.ffn_down(h, w2, b2, meta, te, row_pad=pad), fl, R * F 
 dyp = xp
 timed("dgrad_down", lambda: ops.ffn_dgrad_down(dyp, w2, pre, meta, te, row_pad=pad, activation=ACT), fl, R * d * 2 + 2 * R * F * 2)
 timed("dgrad_up", lambda: ops.ffn_dgrad_up(h, w1, meta, te, row_pad=pad), fl, R * F * 2 + R * d * 2)
+dh = torch.randn(R, F, device="cuda", generator=g).to(torch.bfloat16)
+dw2 = torch.empty(E, d, F, device="cuda")
+dw1 = torch.empty(E, F, d, device="cuda")
+timed("wgrad2 (dw2 + dw1)", lambda: ops.ffn_wgrad2(dyp, h, dh, xp, offs, E, out0=dw2, out1=dw1), 2 * fl,
+      2 * (R * d * 2 + R * F * 2) + 2 * E * d * F * 4)
