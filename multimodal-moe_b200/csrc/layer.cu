@@ -64,7 +64,7 @@ struct PdlScope {
 // (plain event fork/join, so the pattern is captured into a CUDA graph as parallel branches).
 struct ForkState {
   bool ok = false;
-  cudaStream_t s1 = nullptr, s2 = nullptr, s3 = nullptr;
+  cudaStream_t s0 = nullptr, s1 = nullptr, s2 = nullptr, s3 = nullptr;
   cudaEvent_t ev[6] = {};
 };
 static ForkState g_fork[16];
@@ -74,8 +74,16 @@ static ForkState* fork_state() {
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
   ForkState& f = g_fork[dev];
   if (!f.ok) {
-    // (tried in round 2: the router branch at the highest stream priority -- its blocks then take the SMs the next GEMM
-    // of the dx chain is waiting for: dgrad_up started 83 us late at C/65533)
+    // s0 carries ONLY the dlogits kernel, at the highest priority.  The hardware launches the CTAs of queued grids in order
+    // within a priority level: dgrad_up, launched programmatically behind dgrad_down, sits in that queue with CTAs that
+    // cannot be placed until dgrad_down's retire, and every grid behind it waits too (round-2 timelines: dlogits ready at
+    // 58 us, started at 70 us at 3200 tokens; at C/65533 it started when dgrad_down ended and then ran 219 us beside
+    // dgrad_up).  dlogits blocks are 128 threads without shared memory and fit beside a GEMM CTA; the rest of the router
+    // branch uses shared memory and stays at normal priority (at the highest priority its blocks took the SMs the next
+    // GEMM of the dx chain was waiting for: dgrad_up started 83 us late at C/65533).
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+    if (cudaStreamCreateWithPriority(&f.s0, cudaStreamNonBlocking, prio_hi) != cudaSuccess) return nullptr;
     if (cudaStreamCreateWithFlags(&f.s1, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     if (cudaStreamCreateWithFlags(&f.s2, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
     if (cudaStreamCreateWithFlags(&f.s3, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
@@ -471,7 +479,8 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
   }
   ForkState* fk = (!g_prof_on && g_fork_mode) ? fork_state() : nullptr;
   cudaStream_t main_s = static_cast<cudaStream_t>(stream);
-  void* s1 = fk ? static_cast<void*>(fk->s1) : stream;   // router gradients (+ context-path gradients)
+  void* s0 = fk ? static_cast<void*>(fk->s0) : stream;   // dlogits alone, high priority
+  void* s1 = fk ? static_cast<void*>(fk->s1) : stream;   // router parameter gradients (+ context-path gradients)
   void* s2 = fk ? static_cast<void*>(fk->s2) : stream;   // weight gradients
   void* s3 = fk ? static_cast<void*>(fk->s3) : stream;   // bias column sums
   float* dctx = (dctx_bias && has_ctx_bias) ? dctx_bias : nullptr;
@@ -484,13 +493,11 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
                            WS(float, B200MOE_WS_GATE_OF_ROW), meta, R, d, dyp, BWS(float, B200MOE_BWS_DGATE_ROW), stream));
   if (fk) {
     cudaEventRecord(fk->ev[0], main_s);
-    cudaStreamWaitEvent(fk->s1, fk->ev[0], 0);
+    cudaStreamWaitEvent(fk->s0, fk->ev[0], 0);
     cudaStreamWaitEvent(fk->s2, fk->ev[0], 0);
   }
-  STEP("ffn_dgrad_down",
-       b200moe_ffn_dgrad_down(dyp, w2, WS(void, B200MOE_WS_PRE), meta, tile_expert, R, d, F, E, dhpre, q->activation,
-                              pad, stream));
-  if (fk) cudaEventRecord(fk->ev[1], main_s);
+  // dlogits is queued BEFORE dgrad_down: in a replayed graph a side-branch kernel queued behind a persistent GEMM started
+  // only when that GEMM drained (round-2 timeline at 3200 tokens: ready at 58 us, started at 70 us)
   {
     // (tried in round 2 and dropped: finishing dlogits inside combine_bwd by per-token arrival counters -- it removes this
     // launch and the cross-stream edge into unpermute_bwd, but the fence / atomic / dependent-load chain made combine_bwd,
@@ -499,9 +506,16 @@ extern "C" int b200moe_layer_bwd(const b200moe_layer_desc* q, const void* x, con
     STEP("router_bwd_dlogits",
          b200moe_router_bwd_dlogits(WS(float, B200MOE_WS_LOGITS), WS(int32_t, B200MOE_WS_TOPK_IDX), roa,
                                     BWS(float, B200MOE_BWS_DGATE_ROW), WS(int32_t, B200MOE_WS_TOKENS_PER_EXPERT), d_aux,
-                                    T, E, k, q->normalize_topk, q->aux_loss_weight, q->z_loss_weight, dlogits, s1));
+                                    T, E, k, q->normalize_topk, q->aux_loss_weight, q->z_loss_weight, dlogits, s0));
   }
-  if (fk) cudaEventRecord(fk->ev[2], fk->s1);
+  if (fk) {
+    cudaEventRecord(fk->ev[2], fk->s0);
+    cudaStreamWaitEvent(fk->s1, fk->ev[2], 0);     // the rest of the router branch; also joins s0 into s1
+  }
+  STEP("ffn_dgrad_down",
+       b200moe_ffn_dgrad_down(dyp, w2, WS(void, B200MOE_WS_PRE), meta, tile_expert, R, d, F, E, dhpre, q->activation,
+                              pad, stream));
+  if (fk) cudaEventRecord(fk->ev[1], main_s);
   if (dwg || dctx) {
     STEP("router_bwd_params", b200moe_router_bwd_params(dlogits, x, T, d, E, q->tokens_per_image,
                                                         BWS(float, B200MOE_BWS_DWG_SCRATCH), dwg, dctx, s1));
