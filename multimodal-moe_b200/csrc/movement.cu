@@ -229,11 +229,79 @@ struct ColsumJob {
   float* db;
   int ncols;
 };
-constexpr int kColsumPhases = 128;
+// Block = (64-column slab, expert), 256 threads: thread (phase, chunk) sums the rows phase, phase + 32, ... of its 8
+// columns (four 16-byte loads in flight), the four phases of a warp are folded by shuffles, the eight warps through
+// 512 bytes of shared memory in four rounds of 16 columns -- every sum in a fixed order.  The small footprint is the
+// point: 256 threads x 40 registers and half a KB of shared memory fit on an SM BESIDE a persistent GEMM CTA (576
+// threads x 96 registers, ~226 KB), so this bandwidth-bound kernel runs under the tensor-bound dgrad-up / weight-gradient
+// GEMMs.  The round-1 version (1024 threads, 35 KB of shared memory) could not: it ran between them, alone on the GPU
+// (round-2 timelines: a ~110 us hole in front of the weight gradients at C/65533 and at D).
+constexpr int kColsumPhases = 32;
 
 __global__ void __launch_bounds__(8 * kColsumPhases)
 colsum_kernel(const ColsumJob j0, const ColsumJob j1, const int32_t* __restrict__ expert_offsets, int accumulate) {
-  __shared__ float part[kColsumPhases][65];
+  __shared__ float part[8][16];
+  pdl_sync();
+  const int slabs0 = j0.ncols >> 6;
+  const bool second = static_cast<int>(blockIdx.x) >= slabs0;
+  const ColsumJob j = second ? j1 : j0;
+  const int slab = second ? blockIdx.x - slabs0 : blockIdx.x;
+  const int e = blockIdx.y;
+  const int r0 = expert_offsets[e], r1 = expert_offsets[e + 1];
+  const int chunk = threadIdx.x & 7, phase = threadIdx.x >> 3;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int col0 = slab * 64 + chunk * 8;
+  const __nv_bfloat16* base = j.a + col0;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int r = r0 + phase; r < r1; r += 4 * kColsumPhases) {
+    uint4 raw[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int rr = r + kColsumPhases * u;
+      raw[u] = rr < r1 ? ldg128(base + static_cast<size_t>(rr) * j.ncols) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float v[8];
+      unpack8(raw[u], v);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc[q] += v[q];
+    }
+  }
+  // the four phases of a warp (lanes l, l+8, l+16, l+24 share a chunk): lanes 0..7 end up with the warp's sums
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], 8);
+    acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], 16);
+  }
+  // the eight warps, 16 columns (two chunks) per round, in warp order
+#pragma unroll 1
+  for (int round = 0; round < 4; ++round) {
+    if (lane < 8 && (chunk >> 1) == round) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) part[warp][(chunk & 1) * 8 + q] = acc[q];
+    }
+    __syncthreads();
+    if (threadIdx.x < 16) {
+      float sum = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) sum += part[w][threadIdx.x];
+      float* o = j.db + static_cast<size_t>(e) * j.ncols + slab * 64 + round * 16 + threadIdx.x;
+      *o = accumulate ? *o + sum : sum;
+    }
+    __syncthreads();
+  }
+}
+
+// The round-1 shape of the same sum: 1024 threads per (slab, expert) and 35 KB of shared memory.  It cannot share an SM
+// with a GEMM CTA, but it has four times the loads in flight per block: used when there are too few (slab, expert) blocks
+// for 256 threads each to fill the memory system (8 experts x 20 slabs at 65600 tokens: 459 us with the small blocks,
+// 80 us with these).
+constexpr int kColsumWidePhases = 128;
+
+__global__ void __launch_bounds__(8 * kColsumWidePhases)
+colsum_wide_kernel(const ColsumJob j0, const ColsumJob j1, const int32_t* __restrict__ expert_offsets, int accumulate) {
+  __shared__ float part[kColsumWidePhases][65];
   __shared__ float part2[8][64];
   pdl_sync();
   const int slabs0 = j0.ncols >> 6;
@@ -246,11 +314,11 @@ colsum_kernel(const ColsumJob j0, const ColsumJob j1, const int32_t* __restrict_
   const int col0 = slab * 64 + chunk * 8;
   const __nv_bfloat16* base = j.a + col0;
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  for (int r = r0 + phase; r < r1; r += 4 * kColsumPhases) {
+  for (int r = r0 + phase; r < r1; r += 4 * kColsumWidePhases) {
     uint4 raw[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      const int rr = r + kColsumPhases * u;
+      const int rr = r + kColsumWidePhases * u;
       raw[u] = rr < r1 ? ldg128(base + static_cast<size_t>(rr) * j.ncols) : make_uint4(0, 0, 0, 0);
     }
 #pragma unroll
@@ -597,7 +665,11 @@ extern "C" int b200moe_colsum(const void* a0, int ncols0, float* db0, const void
   ColsumJob j0{BF(a0), db0, ncols0};
   ColsumJob j1{BF(a1), db1, a1 ? ncols1 : 0};
   dim3 grid((ncols0 >> 6) + (a1 ? (ncols1 >> 6) : 0), E);
-  launch_k(colsum_kernel, grid, 8 * kColsumPhases, 0, ST(stream), j0, j1, expert_offsets, accumulate);
+  // small co-resident blocks once there are enough of them (blocks x 256 threads >= one full wave of 1024 per SM)
+  if (static_cast<long long>(grid.x) * grid.y >= 4LL * num_sms())
+    launch_k(colsum_kernel, grid, 8 * kColsumPhases, 0, ST(stream), j0, j1, expert_offsets, accumulate);
+  else
+    launch_k(colsum_wide_kernel, grid, 8 * kColsumWidePhases, 0, ST(stream), j0, j1, expert_offsets, accumulate);
   return check_launch("colsum");
 }
 
