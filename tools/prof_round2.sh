@@ -12,7 +12,7 @@ python bench.py --steps 2 --warmup 3 --no-sweep > $O/prof_bench_plain.json 2> $O
 for cfg in "A 8 400" "C 71 923"; do
   set -- $cfg
   python tools/profile_step.py $1 $2 $3 2 > $O/prof_step_$1_plain.log 2>&1 &&
-    $NCU --set full -s 22 -c 40 -o $O/r02_ncu_all_$1 -f python tools/profile_step.py $1 $2 $3 2 > $O/prof_step_$1_ncu.log 2>&1
+    $NCU --set full -s 18 -c 40 -o $O/r02_ncu_all_$1 -f python tools/profile_step.py $1 $2 $3 2 > $O/prof_step_$1_ncu.log 2>&1
   # the reports are 25-35 MB each and gpurun_out/ travels back only below 64 MiB: summarise on the box, drop the report
   T=$(( $2 * $3 ))
   python tools/ncu_summary.py $O/r02_ncu_all_$1.ncu-rep $O/r02_ncu_all_$1$T.md \
